@@ -1,0 +1,365 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the REMMAX hot path on B200 (contract: see DESIGN.md section 6).
+
+    python bench.py --gpus N --steps K --warmup W            # CUDA engine (this repo)
+    python bench.py --impl reference --gpus N --steps K --warmup W   # reference CPU path on host cores
+
+Workload (config.workload): BASELINE.json configs[2] -- remma_epiAA EXACT test, synthetic n=2,000 x m=20,000
+(the largest exact-scan configuration that fits one GPU; configs[1] (agmat GRM n=10,000 x m=500,000) is
+reported in the same line under "extra").  One step = one pass of the hot path over one batch of first-SNPs
+(256 first-SNPs spread over the range, all j > i: ~2.56e6 pairs); under torchrun every rank takes its own
+batch (weak scaling), value = pairs of all ranks / max-over-ranks device time.
+"""
+import argparse
+import json
+import os
+import sys
+import tempfile
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+N_ID, N_SNP, SEED = 2000, 20000, 20201013 + 2
+VAR_COM = [0.35, 0.10, 0.55]            # [A, A*A, residual]; fixed (throughput does not depend on it)
+P_CUT = 1.0e-5
+BATCH = 256                             # first-SNPs per step
+METRIC = "snp_pairs_per_sec_remma_epiAA_exact"
+CONFIG = {"workload": "remma_epiAA exact test, synthetic n=%d x m=%d, GRMs [A, A*A] (BASELINE configs[2])"
+                      % (N_ID, N_SNP),
+          "step": "one batch of %d evenly spread first-SNPs, all j>i (~2.5e6 pairs) per rank" % BATCH,
+          "p_cut": P_CUT, "l2": "flushed (256 MB write) between timed iterations"}
+
+
+def f_exact(n):
+    """Algorithmic flop per pair of the reference formulation: GEMM 2n^2 + 5n."""
+    return 2.0 * n * n + 5.0 * n
+
+
+def batch_first_snps(m, rank, world, batch=BATCH):
+    """Evenly spread first-SNPs (every ceil(m/batch)-th), offset per rank so ranks take disjoint batches."""
+    stride = max(1, (m - 1) // batch)
+    lst = [(q * stride + rank * (stride // max(world, 1))) % (m - 1) for q in range(batch)]
+    return sorted(set(lst))
+
+
+def n_pairs(lst, m):
+    return int(sum(m - 1 - i for i in lst))
+
+
+class ClockSampler(threading.Thread):
+    """Samples SM clock / throttle reasons with NVML during the timed region."""
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.samples, self.reasons, self.stop_flag = index, [], set(), False
+        self.max_mhz = None
+
+    def run(self):
+        try:
+            import pynvml as nv
+            nv.nvmlInit()
+            h = nv.nvmlDeviceGetHandleByIndex(self.index)
+            self.max_mhz = nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)
+            names = {0x2: "applications_clocks_setting", 0x4: "sw_power_cap", 0x8: "hw_slowdown",
+                     0x20: "sw_thermal_slowdown", 0x40: "hw_thermal_slowdown", 0x80: "hw_power_brake_slowdown"}
+            while not self.stop_flag:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM))
+                try:
+                    r = nv.nvmlDeviceGetCurrentClocksEventReasons(h)
+                except Exception:
+                    r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+                for bit, name in names.items():
+                    if r & bit:
+                        self.reasons.add(name)
+                time.sleep(0.1)
+        except Exception as e:                      # never fail the benchmark because of NVML
+            self.reasons.add("nvml_unavailable:%s" % type(e).__name__)
+
+    def result(self):
+        self.stop_flag = True
+        self.join(timeout=2)
+        med = float(np.median(self.samples)) if self.samples else None
+        return {"sm_mhz": med, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons)}
+
+
+def make_dataset(workdir, n=N_ID, m=N_SNP):
+    from gmat_b200 import synth
+    prefix = os.path.join(workdir, "c3_n%d_m%d" % (n, m))
+    ds = synth.write_dataset(prefix, n, m, seed=SEED, n_planted=10, planted_kind="AA")
+    return prefix, ds["pheno"]
+
+
+class CpuExact(object):
+    """The reference formulation of the exact scan on the host cores: numpy restatement (oracle.py) of
+    remma_epiAA.py:72-77 -- the reference's exact path IS numpy, so this is what its users run.  The model
+    (GRM, preamble, coded genotypes) is built once, outside the timed region, exactly like on the GPU arm."""
+
+    def __init__(self, prefix, pheno, ag=None):
+        from oracle import oracle
+        from gmat_b200.uvlmm.design_matrix import design_matrix_wemai_multi_gmat
+        self.oracle = oracle
+        if ag is None:
+            ag, _ = oracle.agmat(prefix)
+        y, xmat, zmat = design_matrix_wemai_multi_gmat(pheno, prefix)
+        self.py, self.pvp = oracle.preamble(y, xmat, zmat, [ag, ag * ag], VAR_COM)
+        self.U, self.V = oracle.coded_pair("AA", oracle.read_plink(prefix))
+        self.m = self.U.shape[1]
+
+    def sample(self, n_first):
+        """Time ``n_first`` evenly spread first-SNPs (all j > i).  Returns (pairs, seconds)."""
+        lst = batch_first_snps(self.m, 0, 1, n_first)
+        t0 = time.perf_counter()
+        hits = 0
+        for i in lst:
+            js, eff, var, chi, p = self.oracle.exact_first_snp(self.U, self.V, i, self.py, self.pvp, False)
+            hits += int(np.sum(p < P_CUT))
+        return n_pairs(lst, self.m), time.perf_counter() - t0
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU formulation on the host cores, bounded sample per step."""
+    if int(os.environ.get("RANK", "0")) != 0:
+        return 0
+    n_first = 4
+    with tempfile.TemporaryDirectory() as d:
+        prefix, pheno = make_dataset(d)
+        cpu = CpuExact(prefix, pheno)
+        times, pairs = [], 0
+        for it in range(args.warmup + args.steps):
+            pairs, dt = cpu.sample(n_first)
+            if it >= args.warmup:
+                times.append(dt)
+    t = float(np.mean(times))
+    value = pairs / t
+    sample = "%d evenly spread first-SNPs, all j>i = %d pairs per step" % (n_first, pairs)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": "pairs/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": t * 1e3,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": dict(CONFIG, sample=sample),
+        "cpu_baseline": {"value": value, "unit": "pairs/s", "cores": os.cpu_count(), "kind": "port",
+                         "sample": "numpy restatement of remma_epiAA.py:72-77 (the reference's exact path is "
+                                   "numpy/BLAS, all host threads); " + sample},
+        "e2e": {"value": value, "unit": "pairs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line))
+    return 0
+
+
+def measure_fp64_peaks(engine, torch):
+    """Roofline denominators for FP64 (absent from MEASURED_PEAKS.json): the library's DMMA issue-rate
+    microbenchmark and cuBLAS DGEMM 4096^3 (torch.matmul float64), best of a few runs, CUDA events."""
+    dmma = engine.fp64_peak(0, 20000)
+    dfma = engine.fp64_peak(1, 20000)
+    a = torch.randn((4096, 4096), dtype=torch.float64, device="cuda")
+    b = torch.randn((4096, 4096), dtype=torch.float64, device="cuda")
+    best = 1e30
+    for it in range(4):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        torch.matmul(a, b)
+        e1.record()
+        torch.cuda.synchronize()
+        if it:
+            best = min(best, e0.elapsed_time(e1))
+    dgemm = 2.0 * 4096 ** 3 / (best * 1e-3) / 1e12
+    return {"dmma_tflops": dmma, "dfma_tflops": dfma, "cublas_dgemm_tflops": dgemm}
+
+
+def run_gpu(args):
+    import torch
+    import torch.distributed as dist
+    from scipy.stats import chi2
+    from gmat_b200 import engine, synth
+    from gmat_b200._ffi import lib
+    from gmat_b200.gmatrix.gmatrix import grm_device
+    from gmat_b200.remma import _core
+    from gmat_b200.remma.remma_epiAA import remma_epiAA
+    from gmat_b200.uvlmm.design_matrix import design_matrix_wemai_multi_gmat
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    dev = engine.current_device()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def reduce(v, op):
+        if world == 1:
+            return v
+        t = torch.tensor([v], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=op)
+        return float(t.item())
+
+    workdir = tempfile.mkdtemp(prefix="gmat_bench_r%d_" % rank)
+    prefix, pheno = make_dataset(workdir)            # every rank writes its own identical copy (seeded)
+    # ------------- setup, outside the timed region: GRM on the GPU, preamble on the host, upload -------------
+    store = engine.GenotypeStore(prefix)
+    ag_dev, _ = grm_device(store, engine.ADD)
+    ag = ag_dev.cpu().numpy()
+    gmat_lst = [ag, ag * ag]
+    y, xmat, zmat = design_matrix_wemai_multi_gmat(pheno, prefix)
+    pymat, pvpmat = _core.preamble(y, xmat, zmat, gmat_lst, VAR_COM, scipy_inv=True)
+    model = _core.DeviceModel(pymat, pvpmat, dev)
+    lut = store.lut(engine.ADD)
+    chi_cut = float(chi2.isf(P_CUT, 1)) * (1 - 1e-9)
+    lst = batch_first_snps(N_SNP, rank, world)
+    pairs_rank = n_pairs(lst, N_SNP)
+    il = np.asarray(lst, dtype=np.int64)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)       # > 126 MB L2
+
+    def step():
+        return engine.epi_exact_scan(store, lut, lut, model.py, model.packed, il, engine.PAIRS_UPPER, chi_cut)
+
+    for _ in range(args.warmup):
+        step()
+    sampler = ClockSampler(local)
+    sampler.start()
+    barrier()
+    launches0 = lib.gmat_b200_kernel_launches()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    hits = None
+    for k in range(args.steps):
+        flush.zero_()                                # L2 flush between timed iterations
+        ev[k][0].record()
+        hits = step()
+        ev[k][1].record()
+    barrier()
+    launches = lib.gmat_b200_kernel_launches() - launches0
+    clocks = sampler.result()
+    ms = reduce(sum(a.elapsed_time(b) for a, b in ev) / args.steps, dist.ReduceOp.MAX if world > 1 else None)
+    total_pairs = reduce(float(pairs_rank), dist.ReduceOp.SUM if world > 1 else None)
+    value = total_pairs / (ms * 1e-3)
+
+    # ------------- e2e: the public drop-in call, HOST buffers, files in / file out, copies inside -------------
+    e2e_lst = batch_first_snps(N_SNP, rank, world, 1024)
+    e2e_pairs = n_pairs(e2e_lst, N_SNP)
+    out_file = os.path.join(workdir, "epiAA_e2e")
+    e2e_t = []
+    for it in range(2):
+        barrier()
+        t0 = time.perf_counter()
+        remma_epiAA(pheno, prefix, gmat_lst, VAR_COM, snp_lst_0=e2e_lst, p_cut=P_CUT, out_file=out_file)
+        barrier()
+        if it:
+            e2e_t.append(time.perf_counter() - t0)
+    e2e_s = reduce(float(np.mean(e2e_t)), dist.ReduceOp.MAX if world > 1 else None)
+    e2e_value = reduce(float(e2e_pairs), dist.ReduceOp.SUM if world > 1 else None) / e2e_s
+    h2d = store.h2d_bytes + model.h2d_bytes + len(e2e_lst) * 8
+    d2h = 8 + 32 * (len(hits) if hits is not None else 0)
+
+    line = None
+    if rank == 0:
+        n = N_ID
+        achieved = (pairs_rank * f_exact(n)) / (ms * 1e-3) / 1e12          # per GPU, algorithmic flops
+        npad = (n + 127) // 128 * 128
+        nb = npad // 128
+        issued = pairs_rank * 2.0 * (128 * 128 * nb * (nb + 1) / 2) / (ms * 1e-3) / 1e12
+        line = {
+            "metric": METRIC, "value": value, "unit": "pairs/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": CONFIG,
+            "clocks": clocks, "gpu_launches": int(launches),
+            "e2e": {"value": e2e_value, "unit": "pairs/s", "h2d_bytes_per_step": int(h2d),
+                    "d2h_bytes_per_step": int(d2h),
+                    "what": "gmat_b200.remma.remma_epiAA(pheno_file, bed_file, gmat_lst, var_com, snp_lst_0=1024 "
+                            "first-SNPs): phenotype parse + host preamble + .bed read + H2D + scan + D2H + file"},
+            "roofline": {"bound": "tensor", "achieved": achieved, "unit": "TFLOP/s", "peak": None, "frac": None,
+                         "traffic": None, "kernel": "epi_exact_kernel<4,4,false>",
+                         "flops_per_pair_algorithmic": f_exact(n), "issued_tflops": issued},
+        }
+        if world == 1:
+            peaks = measure_fp64_peaks(engine, torch)
+            peak = max(peaks["dmma_tflops"], peaks["cublas_dgemm_tflops"])
+            line["roofline"].update({"peak": peak, "frac": achieved / peak, "frac_issued": issued / peak,
+                                     "peak_source": "measured live: max(DMMA issue-rate microbenchmark, cuBLAS DGEMM "
+                                                    "4096^3); FP64 is absent from MEASURED_PEAKS.json", **peaks})
+            if not args.no_extra:
+                line["extra"] = extras(engine, torch, synth, store, model, lut, args)
+            if not args.no_cpu:
+                cpu = CpuExact(prefix, pheno, ag)
+                cp, ct = cpu.sample(4)
+                line["cpu_baseline"] = {"value": cp / ct, "unit": "pairs/s", "cores": os.cpu_count(), "kind": "port",
+                                        "sample": "numpy restatement of remma_epiAA.py:72-77 on 4 evenly spread "
+                                                  "first-SNPs of the same data (%d pairs, %.1f s)" % (cp, ct)}
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+def extras(engine, torch, synth, store, model, lut, args):
+    """Secondary numbers of BASELINE.json's metric, same process, N=1: approximate screen pairs/s on the same
+    data, agmat TFLOP/s on configs[1] (n=10,000 x m=500,000, generated in HBM), decode GB/s."""
+    out = {}
+
+    def timed(fn, reps=3):
+        best = 1e30
+        for it in range(reps + 1):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            fn()
+            e1.record()
+            torch.cuda.synchronize()
+            if it:
+                best = min(best, e0.elapsed_time(e1))
+        return best * 1e-3
+
+    # approximate screen: full scan of the C3 data (1.9999e8 pairs), F_approx = 2n flop per pair
+    la = store.lut(engine.ADD, engine.FREQ_CLOOP)
+    full = np.arange(N_SNP - 1, dtype=np.int64)
+    t = timed(lambda: engine.epi_eff(store, la, la, model.py, full, 0, 1e30))
+    pairs = N_SNP * (N_SNP - 1) // 2
+    out["approx_screen"] = {"pairs_per_s": pairs / t, "seconds": t, "pairs": pairs,
+                            "tflops_algorithmic": pairs * 2.0 * N_ID / t / 1e12,
+                            "workload": "remma_epiAA_eff_cpu formulation, full scan n=%d x m=%d" % (N_ID, N_SNP)}
+    # decode: .bed -> float64 [m][n] (what read_plink_bed materialises), HBM-bound
+    t = timed(lambda: store.decode(None))
+    nbytes = N_SNP * ((N_ID + 3) // 4) + 8.0 * N_SNP * N_ID
+    out["decode"] = {"gb_per_s": nbytes / t / 1e9, "seconds": t, "bytes": nbytes,
+                     "workload": "gmat_b200_decode n=%d x m=%d (0.25 B in + 8 B out per genotype)" % (N_ID, N_SNP)}
+    if not args.no_grm:
+        n2, m2 = args.grm_n, args.grm_m
+        rb = engine.row_stride(n2)
+        payload = synth.device_payload(n2, m2, SEED + 1, store.device, rb)
+        st2 = engine.GenotypeStore.from_device_payload(payload, n2)
+        st2.lut(engine.ADD)
+        kin = torch.empty((n2, n2), dtype=torch.float64, device=store.device)
+        t = timed(lambda: engine.grm(st2, engine.ADD, 1.0, 0.001, out=kin), reps=2)
+        out["agmat"] = {"tflops_full_gemm_convention_2n2m": 2.0 * n2 * n2 * m2 / t / 1e12,
+                        "tflops_algorithmic_n(n+1)m": float(n2) * (n2 + 1) * m2 / t / 1e12,
+                        "seconds": t, "workload": "agmat GRM kernel, synthetic n=%d x m=%d generated in HBM "
+                                                  "(BASELINE configs[1])" % (n2, m2)}
+        del kin, st2, payload
+    return out
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="gmat_b200", choices=["gmat_b200", "reference"])
+    ap.add_argument("--no-extra", action="store_true", help="skip the approx/GRM/decode secondary numbers")
+    ap.add_argument("--no-grm", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--grm-n", type=int, default=10000)
+    ap.add_argument("--grm-m", type=int, default=500000)
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+    return run_gpu(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

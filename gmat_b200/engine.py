@@ -1,0 +1,249 @@
+"""Device-side plumbing shared by the drop-in front-ends: torch owns every device buffer, the CUDA
+engine (libgmat_b200.so, through cffi) does all the work.  Nothing here computes statistics on the
+host; if CUDA or the library is unavailable every entry point raises.
+"""
+import os
+
+import numpy as np
+import torch
+
+from ._ffi import CONST, check, ffi, lib
+
+HIT_DTYPE = np.dtype([("snp_0", "<i4"), ("snp_1", "<i4"), ("eff", "<f8"), ("var", "<f8"), ("chi", "<f8")])
+assert HIT_DTYPE.itemsize == 32
+
+ADD, DOM, RAW = CONST["GMAT_B200_CODING_ADD"], CONST["GMAT_B200_CODING_DOM"], CONST["GMAT_B200_CODING_RAW"]
+FREQ_NUMPY, FREQ_CLOOP = CONST["GMAT_B200_FREQ_NUMPY"], CONST["GMAT_B200_FREQ_CLOOP"]
+PAIRS_UPPER, PAIRS_ALL = CONST["GMAT_B200_PAIRS_UPPER"], CONST["GMAT_B200_PAIRS_ALL"]
+EFF_GE, EFF_SWAP = CONST["GMAT_B200_EFF_GE"], CONST["GMAT_B200_EFF_SWAP"]
+
+
+def require_cuda():
+    if not torch.cuda.is_available():
+        raise RuntimeError("gmat_b200 needs a CUDA device (B200, sm_100a); there is no CPU fallback")
+
+
+def current_device():
+    require_cuda()
+    dev = torch.cuda.current_device()
+    check(lib.gmat_b200_set_device(dev), "gmat_b200_set_device")
+    return torch.device("cuda", dev)
+
+
+def _p(t, ctype):
+    return ffi.cast(ctype, t.data_ptr()) if t is not None else ffi.NULL
+
+
+def _stream():
+    return ffi.cast("void *", torch.cuda.current_stream().cuda_stream)
+
+
+def count_lines(path):
+    """Row count of a .bim/.fam file (the reference counts rows with pd.read_csv(header=None),
+    gmat/remma/remma_epiAA/remma_epiAA_eff.py:55-56)."""
+    with open(path) as f:
+        return sum(1 for line in f if line.strip())
+
+
+def row_stride(n):
+    """Bytes between SNP rows of the device genotype store: ceil(n/4) padded to 32 B (=128 ids)."""
+    return ((n + 3) // 4 + 31) // 32 * 32
+
+
+class GenotypeStore(object):
+    """The PLINK .bed payload resident in HBM as 2-bit codes, plus per-SNP counts and coding LUTs.
+
+    Replaces the reference's dense float64 ``snp_mat`` (``read_plink``; gmat/process_plink/process_plink.py:7-9)
+    and its centred copies (remma_epiAA.py:59-61): a coded column is ``lut[snp][code]``.
+    """
+
+    def __init__(self, bed_file=None, n=None, m=None, payload=None, device=None):
+        self.device = device or current_device()
+        if bed_file is not None:
+            n = count_lines(bed_file + ".fam") if n is None else n
+            m = count_lines(bed_file + ".bim") if m is None else m
+        self.n, self.m = int(n), int(m)
+        self.row_bytes = row_stride(self.n)
+        host = torch.empty((self.m, self.row_bytes), dtype=torch.uint8, pin_memory=True)
+        if bed_file is not None:
+            check(lib.gmat_b200_bed_read_host(bed_file.encode("ascii"), self.n, self.m, self.row_bytes,
+                                              ffi.cast("unsigned char *", host.data_ptr())),
+                  "gmat_b200_bed_read_host")
+        else:
+            src = np.frombuffer(payload, dtype=np.uint8).reshape(self.m, (self.n + 3) // 4)
+            host.zero_()
+            host.numpy()[:, :src.shape[1]] = src
+        self.h2d_bytes = host.numel()
+        self.bed = host.to(self.device, non_blocking=True)
+        self._luts = {}
+        self._freq = {}
+        self.counts = torch.empty((self.m, 4), dtype=torch.int32, device=self.device)
+        check(lib.gmat_b200_bed_stats(_p(self.bed, "unsigned char *"), self.n, self.m, self.row_bytes,
+                                      _p(self.counts, "int *"), _stream()), "gmat_b200_bed_stats")
+
+    # -- statistics ------------------------------------------------------------------------------
+    def n_missing(self):
+        return int(self.counts[:, 1].sum().item())
+
+    def lut(self, coding, freq_mode=FREQ_NUMPY):
+        key = (coding, freq_mode)
+        if key not in self._luts:
+            lut = torch.empty((self.m, 4), dtype=torch.float64, device=self.device)
+            freq = torch.empty((self.m,), dtype=torch.float64, device=self.device)
+            check(lib.gmat_b200_build_lut(_p(self.bed, "unsigned char *"), self.n, self.m, self.row_bytes,
+                                          _p(self.counts, "int *"), coding, freq_mode,
+                                          _p(lut, "double *"), _p(freq, "double *"), _stream()),
+                  "gmat_b200_build_lut")
+            self._luts[key] = lut
+            self._freq[freq_mode] = freq
+        return self._luts[key]
+
+    def freq(self, freq_mode=FREQ_NUMPY):
+        """p = allele frequency of the counted (A2) allele, numpy form (remma_epiAA.py:59)."""
+        if freq_mode not in self._freq:
+            self.lut(ADD, freq_mode)
+        return self._freq[freq_mode]
+
+    def decode(self, coding=None, freq_mode=FREQ_NUMPY, snp_begin=0, snp_end=None):
+        """Dense float64 [snp][id] (device).  coding None = raw read_plink_bed values (code 01 -> 1/3)."""
+        snp_end = self.m if snp_end is None else snp_end
+        ms = snp_end - snp_begin
+        out = torch.empty((ms, self.n), dtype=torch.float64, device=self.device)
+        lut = None if coding is None else self.lut(coding, freq_mode)[snp_begin:snp_end]
+        check(lib.gmat_b200_decode(_p(self.bed[snp_begin:snp_end], "unsigned char *"), self.n, ms, self.row_bytes,
+                                   _p(lut, "double *"), _p(out, "double *"), _stream()), "gmat_b200_decode")
+        return out
+
+    @classmethod
+    def from_device_payload(cls, bed_dev, n):
+        """Wrap an existing device tensor uint8 [m][row_bytes] (row_bytes % 16 == 0) as a store."""
+        self = cls.__new__(cls)
+        self.device, self.n, self.m = bed_dev.device, int(n), int(bed_dev.shape[0])
+        self.row_bytes = int(bed_dev.shape[1])
+        self.h2d_bytes = 0
+        self.bed = bed_dev
+        self._luts, self._freq = {}, {}
+        self.counts = torch.empty((self.m, 4), dtype=torch.int32, device=self.device)
+        check(lib.gmat_b200_bed_stats(_p(self.bed, "unsigned char *"), self.n, self.m, self.row_bytes,
+                                      _p(self.counts, "int *"), _stream()), "gmat_b200_bed_stats")
+        return self
+
+    @classmethod
+    def from_dense(cls, geno_snp_major, device=None):
+        """Pack a dense [snp][id] matrix of 0/1/2 (NaN -> missing) into a store (used after imputation)."""
+        device = device or current_device()
+        g = torch.as_tensor(np.ascontiguousarray(geno_snp_major), dtype=torch.float64).to(device)
+        m, n = g.shape
+        self = cls.__new__(cls)
+        self.device, self.n, self.m = device, int(n), int(m)
+        self.row_bytes = row_stride(self.n)
+        self.h2d_bytes = g.numel() * 8
+        self.bed = torch.zeros((self.m, self.row_bytes), dtype=torch.uint8, device=device)
+        check(lib.gmat_b200_pack(_p(g, "double *"), self.n, self.m, self.row_bytes,
+                                 _p(self.bed, "unsigned char *"), _stream()), "gmat_b200_pack")
+        self._luts, self._freq = {}, {}
+        self.counts = torch.empty((self.m, 4), dtype=torch.int32, device=device)
+        check(lib.gmat_b200_bed_stats(_p(self.bed, "unsigned char *"), self.n, self.m, self.row_bytes,
+                                      _p(self.counts, "int *"), _stream()), "gmat_b200_bed_stats")
+        return self
+
+
+# ----------------------------------------------------------------------------------------------
+def pack_pvp(pvp_dev):
+    """Re-tile Z'PZ (device, [n][n] float64) into the exact kernel's streaming order."""
+    n = pvp_dev.shape[0]
+    elems = lib.gmat_b200_pvp_packed_elems(n)
+    packed = torch.empty((elems,), dtype=torch.float64, device=pvp_dev.device)
+    check(lib.gmat_b200_pack_pvp(_p(pvp_dev, "double *"), n, _p(packed, "double *"), _stream()),
+          "gmat_b200_pack_pvp")
+    return packed
+
+
+def hits_to_numpy(hits_dev, count):
+    raw = hits_dev[:count].cpu().numpy()
+    return raw.view(HIT_DTYPE).reshape(-1)
+
+
+def alloc_hits(cap, device):
+    return torch.empty((max(int(cap), 1), 32), dtype=torch.uint8, device=device)
+
+
+def epi_exact_scan(store, lutU, lutV, py_dev, packed, ilist, pair_space, chi_cut, cap=1 << 20):
+    """Run the exact scan for first-SNPs ``ilist`` (host int64 array); returns a HIT_DTYPE array."""
+    dev = store.device
+    il = torch.as_tensor(np.ascontiguousarray(ilist, dtype=np.int64)).to(dev)
+    count = torch.zeros((1,), dtype=torch.int64, device=dev)
+    while True:
+        hits = alloc_hits(cap, dev)
+        count.zero_()
+        check(lib.gmat_b200_epi_exact_scan(
+            _p(store.bed, "unsigned char *"), store.n, store.m, store.row_bytes,
+            _p(lutU, "double *"), _p(lutV, "double *"), _p(py_dev, "double *"), _p(packed, "double *"),
+            _p(il, "long long *"), il.numel(), pair_space, float(chi_cut),
+            ffi.cast("gmat_b200_hit *", hits.data_ptr()), cap,
+            ffi.cast("unsigned long long *", count.data_ptr()), _stream()), "gmat_b200_epi_exact_scan")
+        cnt = int(count.item())
+        if cnt <= cap:
+            return hits_to_numpy(hits, cnt)
+        cap = cnt               # the kernel counted every hit: one retry with the exact capacity
+
+
+def epi_exact_pairs(store, lutU, lutV, py_dev, packed, pairs):
+    """Exact statistics for explicit pairs (host int array [k][2]); returns HIT_DTYPE array, list order."""
+    dev = store.device
+    pr = torch.as_tensor(np.ascontiguousarray(pairs, dtype=np.int32)).to(dev)
+    k = pr.shape[0]
+    out = alloc_hits(k, dev)
+    check(lib.gmat_b200_epi_exact_pairs(
+        _p(store.bed, "unsigned char *"), store.n, store.m, store.row_bytes,
+        _p(lutU, "double *"), _p(lutV, "double *"), _p(py_dev, "double *"), _p(packed, "double *"),
+        ffi.cast("int *", pr.data_ptr()), k, ffi.cast("gmat_b200_hit *", out.data_ptr()), _stream()),
+        "gmat_b200_epi_exact_pairs")
+    return hits_to_numpy(out, k)
+
+
+def epi_eff(store, lutU, lutV, py_dev, ilist, flags, eff_cut, cut_table=None, binI=None, binJ=None,
+            cap=1 << 20):
+    """Approximate screen on device buffers; returns HIT_DTYPE array (unordered)."""
+    dev = store.device
+    il = torch.as_tensor(np.ascontiguousarray(ilist, dtype=np.int64)).to(dev)
+    count = torch.zeros((1,), dtype=torch.int64, device=dev)
+    tab = bI = bJ = None
+    if cut_table is not None:
+        tab = torch.as_tensor(np.ascontiguousarray(cut_table, dtype=np.float64)).to(dev)
+        bI = torch.as_tensor(np.ascontiguousarray(binI, dtype=np.int32)).to(dev)
+        bJ = torch.as_tensor(np.ascontiguousarray(binJ, dtype=np.int32)).to(dev)
+    while True:
+        hits = alloc_hits(cap, dev)
+        count.zero_()
+        check(lib.gmat_b200_epi_eff(
+            _p(store.bed, "unsigned char *"), store.n, store.m, store.row_bytes,
+            _p(lutU, "double *"), _p(lutV, "double *"), _p(py_dev, "double *"),
+            _p(il, "long long *"), il.numel(), flags, float(eff_cut),
+            _p(tab, "double *"), _p(bI, "int *"), _p(bJ, "int *"),
+            ffi.cast("gmat_b200_hit *", hits.data_ptr()), cap,
+            ffi.cast("unsigned long long *", count.data_ptr()), _stream()), "gmat_b200_epi_eff")
+        cnt = int(count.item())
+        if cnt <= cap:
+            return hits_to_numpy(hits, cnt)
+        cap = cnt
+
+
+def grm(store, coding, scale, small_val, snp_begin=0, snp_end=None, out=None, accumulate=False):
+    """K = X X'/scale (+ diagonal inflation) on the device; returns the [n][n] float64 device tensor."""
+    snp_end = store.m if snp_end is None else snp_end
+    lut = store.lut(coding, FREQ_NUMPY)
+    if out is None:
+        out = torch.zeros((store.n, store.n), dtype=torch.float64, device=store.device) if accumulate \
+            else torch.empty((store.n, store.n), dtype=torch.float64, device=store.device)
+    check(lib.gmat_b200_grm(_p(store.bed, "unsigned char *"), store.n, store.m, store.row_bytes,
+                            _p(lut, "double *"), snp_begin, snp_end, float(scale), float(small_val),
+                            1 if accumulate else 0, _p(out, "double *"), _stream()), "gmat_b200_grm")
+    return out
+
+
+def fp64_peak(kind=0, iters=20000):
+    require_cuda()
+    out = ffi.new("double *")
+    check(lib.gmat_b200_fp64_peak(kind, iters, out), "gmat_b200_fp64_peak")
+    return float(out[0])

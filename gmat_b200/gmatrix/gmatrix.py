@@ -1,0 +1,90 @@
+"""Drop-in for gmat/gmatrix/gmatrix.py: ``agmat`` / ``dgmat_as`` with the same signatures, return values
+and output files (``bed_file.agrm0`` / ``.dgrm_as0`` ...), the GEMM done by the CUDA GRM kernel straight from
+the 2-bit genotype store (no dense float64 genotype matrix is ever formed)."""
+import logging
+import sys
+import time
+
+import numpy as np
+import pandas as pd
+import torch
+
+from .. import engine
+from ..process_plink.process_plink import load_store
+
+
+def output_mat(mat, id, out_file, out_fmt):
+    """Same three formats as gmatrix.py:10-31."""
+    if out_fmt == 'mat':
+        np.savetxt(out_file + '0', mat)
+    elif out_fmt == 'row_col_val':
+        ind = np.tril_indices_from(mat)
+        df = pd.DataFrame({"row": ind[0] + 1, "col": ind[1] + 1, "val": mat[ind]})
+        df.to_csv(out_file + '1', sep=' ', index=False, header=False, columns=["row", "col", "val"])
+    elif out_fmt == 'id_id_val':
+        ind = np.tril_indices_from(mat)
+        df = pd.DataFrame({"id0": id[ind[0]], "id1": id[ind[1]], "val": mat[ind]})
+        df.to_csv(out_file + '2', sep=' ', index=False, header=False, columns=["id0", "id1", "val"])
+    else:
+        return 0
+    return 1
+
+
+def _read_ids(bed_file):
+    fam_info = pd.read_csv(bed_file + '.fam', sep=r'\s+', header=None)
+    return np.array(fam_info.iloc[:, 1])
+
+
+def grm_device(store, coding, small_val=0.001):
+    """(K on the device, scale).  coding ADD: gmatrix.py:53-66; coding DOM: gmatrix.py:116-130."""
+    freq = store.freq().cpu().numpy().reshape(1, -1)
+    if coding == engine.ADD:
+        scale = np.sum(2 * freq * (1 - freq))                     # gmatrix.py:55-56
+    else:
+        scale_vec = 2 * freq * (1 - freq)
+        scale = np.sum(scale_vec * (1 - scale_vec))               # gmatrix.py:118-119
+    kin = engine.grm(store, coding, float(scale), small_val)
+    return kin, float(scale)
+
+
+def _gmat(bed_file, coding, suffix, inv_suffix, inv, small_val, out_fmt, title):
+    logging.info("{:#^80}".format("Read the SNP data"))
+    store = load_store(bed_file, warn=logging.info)
+    logging.info("There are {:d} individuals and {:d} SNPs.".format(store.n, store.m))
+    logging.info("{:#^80}".format("Calculate the %s genomic relationship matrix" % title))
+    clock_t0 = time.perf_counter()
+    cpu_t0 = time.process_time()
+    kin_dev, scale = grm_device(store, coding, small_val)
+    torch.cuda.synchronize()
+    clock_t1 = time.perf_counter()
+    cpu_t1 = time.process_time()
+    logging.info('The scaled factor is: {:.3f}'.format(scale))
+    logging.info("Running time: Clock time, {:.5f} sec; CPU time, {:.5f} sec.".format(clock_t1 - clock_t0,
+                                                                                   cpu_t1 - cpu_t0))
+    kin = kin_dev.cpu().numpy()
+    logging.info("{:#^80}".format("Output"))
+    id = _read_ids(bed_file)
+    out_file = bed_file + suffix
+    logging.info("The output file is " + out_file)
+    res = output_mat(kin, id, out_file, out_fmt)
+    if res == 0:
+        logging.error('Not Recognized output format: ' + out_fmt)
+        sys.exit()
+    kin_inv = None
+    if inv:
+        logging.info("{:#^80}".format("Calculate the inversion of kinship"))
+        kin_inv = torch.linalg.inv(kin_dev).cpu().numpy()         # gmatrix.py:85 (scipy.linalg.inv)
+        out_file = bed_file + inv_suffix
+        logging.info("The output file is: " + out_file)
+        output_mat(kin_inv, id, out_file, out_fmt)
+    return kin, kin_inv
+
+
+def agmat(bed_file, inv=False, small_val=0.001, out_fmt='mat'):
+    """additive genomic relationship matrix and its inversion (reference: gmatrix.py:34-94)."""
+    return _gmat(bed_file, engine.ADD, '.agrm', '.agiv', inv, small_val, out_fmt, 'additive')
+
+
+def dgmat_as(bed_file, inv=False, small_val=0.001, out_fmt='mat'):
+    """dominance genomic relationship matrix and its inversion (reference: gmatrix.py:97-159)."""
+    return _gmat(bed_file, engine.DOM, '.dgrm_as', '.dgiv_as', inv, small_val, out_fmt, 'dominance')

@@ -1,0 +1,530 @@
+"""Generic implementation behind the remma_epiAA / remma_epiAD / remma_epiDD drop-in front-ends.
+
+The reference keeps three near-identical copies of every routine (gmat/remma/remma_epi{AA,AD,DD}/);
+here one parametrised implementation is specialised by an ``EpiKind``.  The host does what the reference
+host does around the hot loop (phenotype parsing, the V / P preamble in numpy so that Z'Py and Z'PZ are the
+same inputs both engines see, p-values with scipy for the few reported rows, file formats); every
+O(pairs) computation runs in the CUDA engine.
+"""
+import gc
+import logging
+import os
+import sys
+import time
+from functools import reduce
+
+import numpy as np
+import pandas as pd
+import torch
+from scipy import linalg
+from scipy.stats import chi2
+
+from .. import engine
+from .._ffi import check, ffi, lib
+from ..process_plink.process_plink import load_store
+from ..uvlmm.design_matrix import design_matrix_wemai_multi_gmat
+from . import parallel as par
+
+
+class EpiKind(object):
+    """What differs between the AA, AD and DD copies of the reference code."""
+
+    def __init__(self, name, coding_u, coding_v, all_pairs):
+        self.name = name
+        self.coding_u, self.coding_v = coding_u, coding_v
+        self.all_pairs = all_pairs          # AD exact: j in [0, m) incl. j == i (remma_epiAD.py:67-77)
+
+    def default_snp_lst_0(self, num_snp):
+        return range(num_snp) if self.all_pairs else range(num_snp - 1)
+
+    def check_snp_lst_0(self, snp_lst_0, num_snp):
+        # remma_epiAA.py:66 / remma_epiAD.py:70
+        bad = (max(snp_lst_0) > num_snp - 1) if self.all_pairs else (max(snp_lst_0) >= num_snp - 1)
+        if bad or min(snp_lst_0) < 0:
+            logging.error('snp_lst_0 is out of range!')
+            sys.exit()
+
+
+AA = EpiKind('AA', engine.ADD, engine.ADD, False)
+AD = EpiKind('AD', engine.ADD, engine.DOM, True)
+DD = EpiKind('DD', engine.DOM, engine.DOM, False)
+
+
+# ----------------------------------------------------------------------------------------------
+# preamble (host numpy; restated from remma_epiAA.py:31-51 / remma_epiAA_pair.py:32-52)
+# ----------------------------------------------------------------------------------------------
+def preamble(y, xmat, zmat, gmat_lst, var_com, scipy_inv=True, need_pvp=True):
+    """V = sigma_e^2 I + sum sigma_k^2 Z G_k Z';  P = V^-1 - V^-1 X (X'V^-1X)^-1 X'V^-1;
+    returns (Z'Py [n,1], Z'PZ [n,n] or None).  ``scipy_inv`` selects scipy.linalg.inv (exact scan,
+    remma_epiAA.py:40) or numpy.linalg.inv (pair / eff paths, remma_epiAA_pair.py:41)."""
+    inv = linalg.inv if scipy_inv else np.linalg.inv
+    y = np.array(y).reshape(-1, 1)
+    n = y.shape[0]
+    xmat = np.array(xmat).reshape(n, -1)
+    vmat = np.diag([var_com[-1]] * n)
+    for val in range(len(gmat_lst)):
+        vmat += zmat.dot((zmat.dot(gmat_lst[val])).T) * var_com[val]
+    vmat_inv = inv(vmat)
+    vxmat = np.dot(vmat_inv, xmat)
+    xvxmat = np.dot(xmat.T, vxmat)
+    xvxmat = inv(xvxmat)
+    pmat = reduce(np.dot, [vxmat, xvxmat, vxmat.T])
+    pmat = vmat_inv - pmat
+    pymat = zmat.T.dot(np.dot(pmat, y))
+    pvpmat = zmat.T.dot((zmat.T.dot(pmat)).T) if need_pvp else None
+    del vmat, vmat_inv, pmat
+    gc.collect()
+    return np.ascontiguousarray(pymat, dtype=np.float64), pvpmat
+
+
+class DeviceModel(object):
+    """py = Z'Py and the packed Z'PZ resident on the device."""
+
+    def __init__(self, pymat, pvpmat, device):
+        self.py = torch.as_tensor(np.ascontiguousarray(pymat.reshape(-1))).to(device)
+        pvp = torch.as_tensor(np.ascontiguousarray(pvpmat, dtype=np.float64)).to(device)
+        self.packed = engine.pack_pvp(pvp)
+        self.h2d_bytes = self.py.numel() * 8 + pvp.numel() * 8
+        del pvp
+
+
+# ----------------------------------------------------------------------------------------------
+# exact scan (remma_epiAA.py:16-86 and the AD / DD copies)
+# ----------------------------------------------------------------------------------------------
+MAX_PAIRS_PER_LAUNCH = 1 << 28      # candidate pairs per kernel launch (bounds the hit buffer retries)
+
+
+def _chunks(kind, snp_lst_0, num_snp):
+    """Split the first-SNP list into launches of at most MAX_PAIRS_PER_LAUNCH candidate pairs."""
+    out, cur, cur_pairs = [], [], 0
+    for i in snp_lst_0:
+        npair = num_snp if kind.all_pairs else (num_snp - 1 - i)
+        if cur and cur_pairs + npair > MAX_PAIRS_PER_LAUNCH:
+            out.append(cur)
+            cur, cur_pairs = [], 0
+        cur.append(i)
+        cur_pairs += npair
+    if cur:
+        out.append(cur)
+    return out
+
+
+def _write_rows(out_file, cols):
+    res = pd.DataFrame(cols)
+    res.to_csv(out_file, sep=' ', header=False, index=False, mode='a')
+
+
+def exact_scan(kind, y, xmat, zmat, gmat_lst, var_com, bed_file, snp_lst_0=None, p_cut=1.0e-5,
+               out_file='epi'):
+    logging.info("Calculate the phenotypic covariance matrix and inversion")
+    pymat, pvpmat = preamble(y, xmat, zmat, gmat_lst, var_com, scipy_inv=True)
+    logging.info("Read the SNP")
+    rank, world = par.rank_world()
+    if rank == 0:
+        np.savetxt(out_file, ['snp_0 snp_1 eff chi p_val'], fmt='%s')     # header first (remma_epiAA.py:53)
+    store = load_store(bed_file)
+    num_snp = store.m
+    logging.info('Test')
+    if snp_lst_0 is None:
+        snp_lst_0 = kind.default_snp_lst_0(num_snp)
+    else:
+        kind.check_snp_lst_0(snp_lst_0, num_snp)
+    snp_lst_0 = [int(i) for i in snp_lst_0]
+    order = {}
+    for pos, i in enumerate(snp_lst_0):
+        order.setdefault(i, pos)
+    model = DeviceModel(pymat, pvpmat, store.device)
+    del pvpmat
+    lut_u, lut_v = store.lut(kind.coding_u), store.lut(kind.coding_v)
+    # p < p_cut  <=>  chi > isf(p_cut); the device keeps a slightly larger set, the host re-applies the
+    # reference's own comparison on scipy p-values (remma_epiAA.py:77,81)
+    chi_cut = -1.0 if p_cut >= 1.0 else float(chi2.isf(p_cut, 1)) * (1.0 - 1e-9)
+    pair_space = engine.PAIRS_ALL if kind.all_pairs else engine.PAIRS_UPPER
+    my_list = par.shard_first_snps(snp_lst_0, num_snp, kind.all_pairs, rank, world)
+    clock_t0 = time.perf_counter()
+    cpu_t0 = time.process_time()
+    def emit(hits):
+        if len(hits) == 0:
+            return
+        pos = np.array([order[i] for i in hits['snp_0']], dtype=np.int64)
+        hits = hits[np.lexsort((hits['snp_1'], pos))]          # (i in list order, j ascending)
+        p_vec = chi2.sf(hits['chi'], 1)
+        keep = p_vec < p_cut                                   # the reference's comparison (remma_epiAA.py:81)
+        _write_rows(out_file, {0: hits['snp_0'][keep].astype(np.int64), 1: hits['snp_1'][keep].astype(np.int64),
+                               2: hits['eff'][keep], 3: hits['chi'][keep], 4: p_vec[keep]})
+
+    mine = []
+    for chunk in _chunks(kind, my_list, num_snp):
+        hits = engine.epi_exact_scan(store, lut_u, lut_v, model.py, model.packed,
+                                     np.asarray(chunk, dtype=np.int64), pair_space, chi_cut)
+        if world == 1:
+            emit(hits)                                         # appended launch by launch (resume granularity)
+        else:
+            mine.append(hits)
+    if world > 1:
+        # the only collective of the scan: variable-length gather of hit records to rank 0
+        local = np.concatenate(mine) if mine else np.zeros((0,), dtype=engine.HIT_DTYPE)
+        hits = par.gather_hits(local, store.device)
+        if rank == 0:
+            emit(hits)
+    torch.cuda.synchronize()
+    clock_t1 = time.perf_counter()
+    cpu_t1 = time.process_time()
+    logging.info("Running time: Clock time, {:.5f} sec; CPU time, {:.5f} sec.".format(clock_t1 - clock_t0,
+                                                                                   cpu_t1 - cpu_t0))
+    return 0
+
+
+def exact_scan_parallel(kind, y, xmat, zmat, gmat_lst, var_com, bed_file, parallel, p_cut, out_file):
+    """remma_epiAA.py:109-140: part k of P, output ``out_file.k``."""
+    logging.info("Parallel: " + str(parallel[0]) + ', ' + str(parallel[1]))
+    num_snp = engine.count_lines(bed_file + '.bim')
+    snp_list_0, pos = par.parallel_lists(num_snp, parallel, kind.all_pairs)
+    logging.info('SNP position point: ' + ','.join(str(v) for v in pos))
+    return exact_scan(kind, y, xmat, zmat, gmat_lst, var_com, bed_file, snp_lst_0=snp_list_0, p_cut=p_cut,
+                      out_file=out_file + '.' + str(parallel[1]))
+
+
+# ----------------------------------------------------------------------------------------------
+# explicit pair list (remma_epiAA_pair.py:16-92 and copies)
+# ----------------------------------------------------------------------------------------------
+def pair_test(kind, y, xmat, zmat, gmat_lst, var_com, bed_file, snp_pair_file, max_test_pair=50000,
+              p_cut=1.0e-4, out_file='epi_pair'):
+    logging.info("Calculate the phenotypic covariance matrix and inversion")
+    pymat, pvpmat = preamble(y, xmat, zmat, gmat_lst, var_com, scipy_inv=False)
+    logging.info("Read the SNP")
+    store = load_store(bed_file)
+    num_snp = store.m
+    model = DeviceModel(pymat, pvpmat, store.device)
+    del pvpmat
+    lut_u, lut_v = store.lut(kind.coding_u), store.lut(kind.coding_v)
+    logging.info('Test')
+    np.savetxt(out_file, ['snp_0 snp_1 eff var chi p'], fmt='%s')
+    clock_t0 = time.perf_counter()
+    cpu_t0 = time.process_time()
+    ipart = -1
+    while True:
+        ipart += 1
+        skiprows = 1 + ipart * max_test_pair          # first line is a header (remma_epiAA_pair.py:69)
+        try:
+            snp_pair = pd.read_csv(snp_pair_file, header=None, sep=r'\s+', skiprows=skiprows,
+                                   nrows=max_test_pair)
+        except Exception as e:
+            logging.info(e)
+            break
+        snp_pair = np.array(snp_pair.iloc[:, 0:2], dtype=int)
+        if np.max(snp_pair) > num_snp - 1 or np.min(snp_pair) < 0:
+            logging.error('snp_pair is out of range!')
+            sys.exit()
+        res = engine.epi_exact_pairs(store, lut_u, lut_v, model.py, model.packed, snp_pair)
+        p_vec = chi2.sf(res['chi'], 1)
+        keep = p_vec < p_cut
+        _write_rows(out_file, {0: snp_pair[keep, 0], 1: snp_pair[keep, 1], 2: res['eff'][keep],
+                               3: res['var'][keep], 4: res['chi'][keep], 5: p_vec[keep]})
+    torch.cuda.synchronize()
+    clock_t1 = time.perf_counter()
+    cpu_t1 = time.process_time()
+    logging.info("Running time: Clock time, {:.5f} sec; CPU time, {:.5f} sec.".format(clock_t1 - clock_t0,
+                                                                                   cpu_t1 - cpu_t0))
+    return 0
+
+
+# ----------------------------------------------------------------------------------------------
+# approximate screen through the drop-in C symbols (remma_epiAA_eff.py:20-96 and copies)
+# ----------------------------------------------------------------------------------------------
+def _screen_defaults(kind, maf, snp_lst_0, num_snp):
+    # quirk kept: AD _eff defaults to range(m) (remma_epiAD_eff.py:57), AD _maf_eff to range(m-1)
+    # (remma_epiAD_maf_eff.py:59); both are equivalent (the last first-SNP has no j > i)
+    if snp_lst_0 is None:
+        return range(num_snp) if (kind.all_pairs and not maf) else range(num_snp - 1)
+    upper_ok = (max(snp_lst_0) <= num_snp - 1) if (kind.all_pairs and not maf) else (max(snp_lst_0) < num_snp - 1)
+    if not upper_ok or min(snp_lst_0) < 0:
+        logging.error('snp_lst_0 is out of range!')
+        sys.exit()
+    return snp_lst_0
+
+
+def eff_screen(kind, y, xmat, zmat, gmat_lst, var_com, bed_file, snp_lst_0=None, var_app=1.0, p_cut=1.0e-5,
+               out_file='epi_eff'):
+    logging.info("Calculate the phenotypic covariance matrix and inversion")
+    pymat, _ = preamble(y, xmat, zmat, gmat_lst, var_com, scipy_inv=False, need_pvp=False)
+    num_snp = engine.count_lines(bed_file + '.bim')
+    num_id = engine.count_lines(bed_file + '.fam')
+    snp_lst_0 = _screen_defaults(kind, False, snp_lst_0, num_snp)
+    engine.current_device()
+    logging.info("Convert python variates to C type")
+    pbed_file = ffi.new("char[]", bed_file.encode('ascii'))
+    snp_lst_0 = np.array(list(snp_lst_0), dtype=np.longlong)
+    psnp_lst_0 = ffi.cast("long long *", snp_lst_0.ctypes.data)
+    ppymat = ffi.cast("double *", pymat.ctypes.data)
+    chi_cut = chi2.isf(p_cut, 1)
+    eff_cut = np.sqrt(chi_cut * var_app)
+    temp_file = out_file + '.temp'
+    pout_file = ffi.new("char[]", temp_file.encode('ascii'))
+    logging.info('Test')
+    clock_t0 = time.perf_counter()
+    cpu_t0 = time.process_time()
+    fn = getattr(lib, 'remma_epi%s_eff_cpu' % kind.name)
+    check(fn(pbed_file, num_id, num_snp, psnp_lst_0, len(snp_lst_0), ppymat, float(eff_cut), pout_file),
+          'remma_epi%s_eff_cpu' % kind.name)
+    clock_t1 = time.perf_counter()
+    cpu_t1 = time.process_time()
+    logging.info("Running time: Clock time, {:.5f} sec; CPU time, {:.5f} sec.".format(clock_t1 - clock_t0,
+                                                                                   cpu_t1 - cpu_t0))
+    logging.info('Add the approximate P values')
+    with open(temp_file) as fin, open(out_file, 'w') as fout:
+        head_line = fin.readline().strip() + ' chi_app p_app\n'
+        fout.write(head_line)
+        for line in fin:
+            arr = line.split()
+            chi_app = float(arr[-1]) * float(arr[-1]) / var_app      # from the %g-truncated text, like the reference
+            p_app = chi2.sf(chi_app, 1)
+            fout.write(' '.join(arr + [str(chi_app), str(p_app)]) + '\n')
+    os.remove(temp_file)
+    return 0
+
+
+def eff_screen_parallel(kind, y, xmat, zmat, gmat_lst, var_com, bed_file, parallel, var_app, p_cut, out_file):
+    logging.info("Parallel: " + str(parallel[0]) + ', ' + str(parallel[1]))
+    num_snp = engine.count_lines(bed_file + '.bim')
+    # every _eff_parallel copy uses the AA cut points (num_snp - 1), also AD (remma_epiAD_eff.py:120-153)
+    snp_list_0, pos = par.parallel_lists(num_snp, parallel, False)
+    logging.info('SNP position point: ' + ','.join(str(v) for v in pos))
+    return eff_screen(kind, y, xmat, zmat, gmat_lst, var_com, bed_file, snp_lst_0=snp_list_0, var_app=var_app,
+                      p_cut=p_cut, out_file=out_file + '.' + str(parallel[1]))
+
+
+def maf_eff_screen(kind, y, xmat, zmat, gmat_lst, var_com, bed_file, snp_lst_0=None, freq=None, freq2=None,
+                   freq_deno=None, p_cut=1.0e-5, out_file='epi_maf_eff'):
+    """remma_epiAA_maf_eff.py:20-104; ``freq2`` is the second bin vector of the AD variant (freqD)."""
+    logging.info("Calculate the phenotypic covariance matrix and inversion")
+    pymat, _ = preamble(y, xmat, zmat, gmat_lst, var_com, scipy_inv=False, need_pvp=False)
+    num_snp = engine.count_lines(bed_file + '.bim')
+    num_id = engine.count_lines(bed_file + '.fam')
+    snp_lst_0 = _screen_defaults(kind, True, snp_lst_0, num_snp)
+    if freq is None:
+        freq = np.zeros((num_snp,), dtype=np.longlong)
+    if freq2 is None:
+        freq2 = np.zeros((num_snp,), dtype=np.longlong) if kind.all_pairs else freq
+    if freq_deno is None:
+        freq_deno = np.ones(111)
+    engine.current_device()
+    freq = np.ascontiguousarray(freq, dtype=np.longlong)
+    freq2 = np.ascontiguousarray(freq2, dtype=np.longlong)
+    pbed_file = ffi.new("char[]", bed_file.encode('ascii'))
+    snp_lst_0 = np.array(list(snp_lst_0), dtype=np.longlong)
+    psnp_lst_0 = ffi.cast("long long *", snp_lst_0.ctypes.data)
+    ppymat = ffi.cast("double *", pymat.ctypes.data)
+    chi_cut = chi2.isf(p_cut, 1)
+    eff_cut = np.ascontiguousarray(np.sqrt(chi_cut * np.asarray(freq_deno, dtype=np.float64)))
+    if not kind.all_pairs:
+        np.savetxt('eff_cut', eff_cut)                              # side effect kept (remma_epiAA_maf_eff.py:79)
+    peff_cut = ffi.cast("double *", eff_cut.ctypes.data)
+    temp_file = out_file + '.temp'
+    pout_file = ffi.new("char[]", temp_file.encode('ascii'))
+    logging.info('Test')
+    fn = getattr(lib, 'remma_epi%s_maf_eff_cpu' % kind.name)
+    pf = ffi.cast("long long *", freq.ctypes.data)
+    if kind.all_pairs:
+        rc = fn(pbed_file, num_id, num_snp, psnp_lst_0, len(snp_lst_0), ppymat, pf,
+                ffi.cast("long long *", freq2.ctypes.data), peff_cut, pout_file)
+    else:
+        rc = fn(pbed_file, num_id, num_snp, psnp_lst_0, len(snp_lst_0), ppymat, pf, peff_cut, pout_file)
+    check(rc, 'remma_epi%s_maf_eff_cpu' % kind.name)
+    logging.info('Add the approximate P values')
+    with open(temp_file) as fin, open(out_file, 'w') as fout:
+        head_line = fin.readline().strip() + ' chi_app p_app\n'
+        fout.write(head_line)
+        for line in fin:
+            arr = line.split()
+            deno = freq_deno[freq[int(arr[0])] * 10 + freq2[int(arr[1])]]
+            chi_app = float(arr[-1]) * float(arr[-1]) / deno
+            p_app = chi2.sf(chi_app, 1)
+            fout.write(' '.join(arr + [str(chi_app), str(p_app)]) + '\n')
+    os.remove(temp_file)
+    return 0
+
+
+# ----------------------------------------------------------------------------------------------
+# approximate pipelines (remma_epiAA_approx.py:10-53, remma_epiAA_maf_approx.py:11-90 and copies),
+# run in memory on one resident genotype store / one preamble instead of three.
+# ----------------------------------------------------------------------------------------------
+class Prepared(object):
+    """Everything the three pipeline stages share."""
+
+    def __init__(self, kind, pheno_file, bed_file, gmat_lst, var_com):
+        from ..engine import GenotypeStore
+        self.kind = kind
+        y, xmat, zmat = design_matrix_wemai_multi_gmat(pheno_file, bed_file)
+        pymat, pvpmat = preamble(y, xmat, zmat, gmat_lst, var_com, scipy_inv=False)
+        self.raw_store = GenotypeStore(bed_file)              # what the C screen sees (no imputation)
+        self.store = self.raw_store
+        if self.raw_store.n_missing() > 0:
+            self.store = load_store(bed_file)                 # what the numpy paths see (imputed)
+        self.model = DeviceModel(pymat, pvpmat, self.store.device)
+        self.num_snp, self.num_id = self.store.m, self.store.n
+
+    def pair_stats(self, pairs):
+        k = self.kind
+        return engine.epi_exact_pairs(self.store, self.store.lut(k.coding_u), self.store.lut(k.coding_v),
+                                      self.model.py, self.model.packed, pairs)
+
+    def screen(self, snp_lst_0, eff_cut=0.0, cut_table=None, bin_i=None, bin_j=None):
+        """Hits of the C screen in single-threaded C row order; returns list of (snp_0, snp_1, eff)."""
+        k, st = self.kind, self.raw_store
+        la = st.lut(engine.ADD, engine.FREQ_CLOOP)
+        ld = st.lut(engine.DOM, engine.FREQ_CLOOP)
+        ilist = np.asarray(list(snp_lst_0), dtype=np.int64)
+        if k.name == 'AD':
+            passes = [(la, ld, engine.EFF_GE), (ld, la, engine.EFF_SWAP)]
+        elif k.name == 'AA':
+            passes = [(la, la, 0)]
+        else:
+            passes = [(ld, ld, 0)]
+        rows = []
+        for d, (lu, lv, flags) in enumerate(passes):
+            h = engine.epi_eff(st, lu, lv, self.model.py, ilist, flags, eff_cut, cut_table, bin_i, bin_j)
+            swap = bool(flags & engine.EFF_SWAP)
+            for s0, s1, e in zip(h['snp_0'].tolist(), h['snp_1'].tolist(), h['eff'].tolist()):
+                rows.append(((s1, s0, d) if swap else (s0, s1, d), s0, s1, e))
+        rows.sort(key=lambda r: r[0])
+        return [(r[1], r[2], r[3]) for r in rows]
+
+
+def random_pair(num_snp, out_file='random_pair', num_pair=100000, num_each_pair=5000, ordered=True):
+    """Restated from gmat/remma/random_pair.py:6-65 (``ordered`` False = random_pairAD): global numpy RNG,
+    string set, truncation to num_pair, written with a 'snp_0 snp_1' header and read back."""
+    limit = num_snp * (num_snp - 1) / 2 if ordered else num_snp * (num_snp - 1)
+    if num_pair > limit:
+        logging.error('num_pair must be not greater than: ' + str(limit))
+        sys.exit()
+    if num_pair < num_each_pair:
+        logging.error('num_pair must be greater than num_each_pair')
+        sys.exit()
+    res_lst = set()
+    while True:
+        arr = np.random.randint(num_snp, size=(num_each_pair, 2))
+        arr = arr[arr[:, 0] < arr[:, 1], :] if ordered else arr[arr[:, 0] != arr[:, 1], :]
+        arr = np.array(arr, dtype=str)
+        lst = map(lambda x, y: x + ' ' + y, arr[:, 0], arr[:, 1])
+        res_lst.update(set(lst))
+        if len(res_lst) >= num_pair:
+            break
+    res_lst = list(res_lst)[:num_pair]
+    np.savetxt(out_file, np.array(res_lst), fmt="%s", header='snp_0 snp_1', comments='')
+    return np.loadtxt(out_file, dtype=int, skiprows=1)
+
+
+def random_pairAD(num_snp, out_file='random_pair', num_pair=100000, num_each_pair=5000):
+    return random_pair(num_snp, out_file, num_pair, num_each_pair, ordered=False)
+
+
+def _exact_rows_text(pairs, res):
+    """The rows remma_epiXX_pair(p_cut=1) would have written for these pairs, as lists of strings."""
+    import io
+    p_vec = chi2.sf(res['chi'], 1)
+    keep = p_vec < 1
+    buf = io.StringIO()
+    pd.DataFrame({0: pairs[keep, 0], 1: pairs[keep, 1], 2: res['eff'][keep], 3: res['var'][keep],
+                  4: res['chi'][keep], 5: p_vec[keep]}).to_csv(buf, sep=' ', header=False, index=False)
+    return [line.split() for line in buf.getvalue().splitlines()], res['var'][keep]
+
+
+def _maf_bins(kind, store):
+    """Per-SNP bin vectors (allele-frequency / heterozygosity * 20, truncated) and the arrays the reference
+    saves next to the output (remma_epiAA_maf_approx.py:38-42, remma_epiAD_maf_approx.py:39-49,
+    remma_epiDD_maf_approx.py:39-44).  Formed from exact device genotype counts."""
+    counts = store.counts.cpu().numpy().astype(np.int64)
+    num_id = store.n
+    allele_sum = (counts[:, 2] + 2 * counts[:, 3]).astype(np.float64)
+    saved = {}
+    if kind.name == 'AA':
+        freq = 1 - allele_sum / (2 * num_id)
+        freq[freq > 0.5] = 1 - freq[freq > 0.5]
+        saved['.freq'] = freq.copy()
+        b = list(map(np.longlong, freq * 20))
+        return b, b, saved
+    het = counts[:, 2].astype(np.float64) / num_id
+    het[het > 0.5] = 1 - het[het > 0.5]
+    if kind.name == 'DD':
+        saved['.heter'] = het.copy()
+        b = np.array(het * 20, dtype=np.longlong)
+        return b, b, saved
+    freq_a = allele_sum / (2 * num_id)
+    freq_a[freq_a > 0.5] = 1 - freq_a[freq_a > 0.5]
+    saved['.maf'], saved['.heter'] = freq_a.copy(), het.copy()
+    return np.array(freq_a * 20, dtype=np.longlong), np.array(het * 20, dtype=np.longlong), saved
+
+
+def approx(kind, pheno_file, bed_file, gmat_lst, var_com, p_cut=1.0e-5, num_random_pair=100000,
+           out_file='epi_approx', maf=False, parallel=None):
+    sfx = '' if parallel is None else '.' + str(parallel[1])
+    logging.info("\n\n#####Randomly select {:d} pairs, and test these SNP pairs#####".format(num_random_pair))
+    num_snp = engine.count_lines(bed_file + '.bim')
+    ad = kind.name == 'AD'
+    rp_name = out_file + ('.random_pairAD' if (ad and maf) else '.random_pair') + sfx
+    pairs = (random_pairAD if ad else random_pair)(num_snp, out_file=rp_name, num_pair=num_random_pair)
+    os.remove(rp_name)
+    pairs = np.asarray(pairs, dtype=np.int64).reshape(-1, 2)
+    ctx = Prepared(kind, pheno_file, bed_file, gmat_lst, var_com)
+    rand_rows, rand_var = _exact_rows_text(pairs, ctx.pair_stats(pairs))
+    if parallel is None:
+        snp_lst_0 = range(num_snp) if (ad and not maf) else range(num_snp - 1)
+    else:
+        snp_lst_0, _ = par.parallel_lists(num_snp, parallel, False)
+    chi_cut = chi2.isf(p_cut, 1)
+    logging.info("\n\n#####Screen the epistatic effects and select top SNP pairs based on approximate test#####")
+    if not maf:
+        var_median = np.median(rand_var)                                   # remma_epiAA_approx.py:30-31
+        hits = ctx.screen(snp_lst_0, eff_cut=float(np.sqrt(chi_cut * var_median)))
+        deno = lambda s0, s1: var_median                                    # noqa: E731
+    else:
+        bin_i, bin_j, saved = _maf_bins(kind, ctx.store)
+        for ext, arr in saved.items():
+            np.savetxt(out_file + ext + sfx, arr)
+        sums, cnts = {}, {}
+        for arr in rand_rows:                     # per-bin MEAN of the variances (named median in the reference)
+            keys = [(bin_i[int(arr[0])], bin_j[int(arr[1])])]
+            if not ad:
+                keys.append((bin_i[int(arr[1])], bin_j[int(arr[0])]))
+            for kv in keys:
+                kv = ' '.join([str(kv[0]), str(kv[1])])
+                cnts[kv] = cnts.get(kv, 0) + 1
+                sums[kv] = sums.get(kv, 0.0) + float(arr[-3])
+        all_sum, all_cnt = 0, 0
+        for kv in cnts:
+            all_sum += sums[kv]
+            all_cnt += cnts[kv]
+            sums[kv] = sums[kv] / cnts[kv]
+        all_mean = all_sum / all_cnt
+        freq_deno = np.ones(111)
+        with open(out_file + '.freq_denominator' + sfx, 'w') as fout:
+            for key1 in set(bin_i):
+                for key2 in set(bin_j):
+                    kv = ' '.join([str(key1), str(key2)])
+                    if kv not in sums:
+                        sums[kv] = all_mean
+                    fout.write(kv + ' ' + str(sums[kv]) + '\n')
+                    freq_deno[key1 * 10 + key2] = sums[kv]
+        bi, bj = np.asarray(bin_i, dtype=np.int64), np.asarray(bin_j, dtype=np.int64)
+        hits = ctx.screen(snp_lst_0, cut_table=np.sqrt(chi_cut * freq_deno), bin_i=bi, bin_j=bj)
+        deno = lambda s0, s1: freq_deno[bi[s0] * 10 + bj[s1]]              # noqa: E731
+    # approximate p from the %g-truncated effect, exactly like the text round trip of the reference
+    p_dct = {}
+    surv = []
+    for s0, s1, e in hits:
+        e_txt = '%g' % e
+        chi_app = float(e_txt) * float(e_txt) / deno(s0, s1)
+        p_dct['%d %d' % (s0, s1)] = str(chi2.sf(chi_app, 1))
+        surv.append((s0, s1))
+    logging.info("\n\n#####Calculate exact p values for top SNP pairs#####")
+    with open(out_file + sfx, 'w') as fout:
+        # header of .exact_p with the token p_app spliced in (remma_epiAA_approx.py:41-50)
+        fout.write('snp_0 snp_1 eff var chi p_app p\n')
+        if surv:
+            sp = np.asarray(surv, dtype=np.int64)
+            rows, _ = _exact_rows_text(sp, ctx.pair_stats(sp))
+            for arr in rows:
+                arr.insert(-1, p_dct[' '.join(arr[:2])])
+                fout.write(' '.join(arr) + '\n')
+    return 0

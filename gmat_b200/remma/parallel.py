@@ -1,0 +1,81 @@
+"""Sharding of the pair space and the final hit gather.
+
+Two layers, as in SURVEY section 8e:
+ * ``parallel_lists``: the reference's manual ``parallel=[P, k]`` partition, arithmetic reproduced verbatim
+   (remma_epiAA.py:125-137; AD variant remma_epiAD.py:130-139) -- file-level drop-in (``out_file.k``).
+ * ``shard_first_snps`` / ``gather_hits``: one process per GPU (torch.distributed).  First-SNP blocks are dealt
+   round-robin in a boustrophedon order so the triangular work is balanced; the scan itself has no
+   collective; hit records (32 bytes each) are gathered to rank 0 once at the end (NCCL on GPUs, gloo in
+   CPU tests).
+"""
+import numpy as np
+import torch
+import torch.distributed as dist
+
+HIT_BYTES = 32
+
+
+def rank_world():
+    if dist.is_available() and dist.is_initialized():
+        return dist.get_rank(), dist.get_world_size()
+    return 0, 1
+
+
+def parallel_lists(num_snp, parallel, all_pairs=False):
+    """First-SNP list of part ``parallel[1]`` (1-based) of ``parallel[0]`` parts, and the four cut points."""
+    num_snp_part = int(num_snp / (2 * parallel[0]))
+    snp_pos_0 = (parallel[1] - 1) * num_snp_part
+    snp_pos_1 = parallel[1] * num_snp_part
+    snp_pos_2 = (2 * parallel[0] - parallel[1]) * num_snp_part
+    snp_pos_3 = (2 * parallel[0] - parallel[1] + 1) * num_snp_part
+    if parallel[1] == 1:
+        snp_pos_3 = num_snp if all_pairs else num_snp - 1
+    snp_list_0 = list(range(snp_pos_0, snp_pos_1)) + list(range(snp_pos_2, snp_pos_3))
+    return snp_list_0, [snp_pos_0, snp_pos_1, snp_pos_2, snp_pos_3]
+
+
+SHARD_BLOCK = 64        # first-SNPs per dealt block (multiple of the kernel's 8-SNP I-block)
+
+
+def shard_first_snps(snp_lst_0, num_snp, all_pairs, rank, world):
+    """This rank's share of the first-SNP list.  Blocks of SHARD_BLOCK consecutive list entries are dealt
+    0,1,..,R-1,R-1,..,1,0,0,1,.. so that for the triangular (j > i) workload every rank gets the same
+    number of pairs to within one block row."""
+    snp_lst_0 = list(snp_lst_0)
+    if world == 1:
+        return snp_lst_0
+    out = []
+    nblk = (len(snp_lst_0) + SHARD_BLOCK - 1) // SHARD_BLOCK
+    for b in range(nblk):
+        r = b % (2 * world)
+        owner = r if r < world else 2 * world - 1 - r
+        if owner == rank:
+            out.extend(snp_lst_0[b * SHARD_BLOCK:(b + 1) * SHARD_BLOCK])
+    return out
+
+
+def gather_hits(local, device):
+    """Gather variable-length hit arrays (engine.HIT_DTYPE) to rank 0.  Returns the concatenation on rank 0,
+    None elsewhere.  One all_gather of counts + one padded all_gather of records."""
+    rank, world = rank_world()
+    if world == 1:
+        return local
+    backend = dist.get_backend()
+    dev = device if backend == "nccl" else torch.device("cpu")
+    cnt = torch.tensor([len(local)], dtype=torch.int64, device=dev)
+    counts = [torch.zeros_like(cnt) for _ in range(world)]
+    dist.all_gather(counts, cnt)
+    counts = [int(c.item()) for c in counts]
+    mx = max(counts)
+    if mx == 0:
+        return local if rank == 0 else None
+    buf = torch.zeros((mx, HIT_BYTES), dtype=torch.uint8, device=dev)
+    if len(local):
+        raw = np.frombuffer(np.ascontiguousarray(local).tobytes(), dtype=np.uint8).reshape(-1, HIT_BYTES)
+        buf[:len(local)] = torch.from_numpy(raw.copy()).to(dev)
+    bufs = [torch.zeros_like(buf) for _ in range(world)]
+    dist.all_gather(bufs, buf)
+    if rank != 0:
+        return None
+    parts = [bufs[r][:counts[r]].cpu().numpy().view(local.dtype).reshape(-1) for r in range(world)]
+    return np.concatenate(parts)

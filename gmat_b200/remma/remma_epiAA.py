@@ -1,0 +1,4 @@
+"""Drop-in for the package gmat/remma/remma_epiAA/ (same function names and signatures)."""
+from . import _core, _frontends
+
+__all__ = _frontends.build(_core.AA, globals())

@@ -1,0 +1,170 @@
+/*
+ * gmat_b200.h -- C-ABI of the B200-native REMMAX pair-scan / GRM engine.
+ *
+ * Plain C, plain pointers and sizes, no torch / CUDA types in any signature.  Two groups:
+ *
+ *  (1) DROP-IN symbols: the seven functions GMAT's own cffi extension modules export
+ *      (`_cremma_epi_eff_cpu`, gmat/remma/_build.py:8-31; `_cread_plink_bed`,
+ *      gmat/process_plink/_build.py:8).  Same names, argument order, types and file side effects,
+ *      HOST pointers, so the reference Python (`lib.remma_epiAA_eff_cpu(...)`,
+ *      gmat/remma/remma_epiAA/remma_epiAA_eff.py:80) can bind this library unchanged.
+ *      Difference on purpose: on failure they return a negative status (see gmat_b200_last_error)
+ *      instead of calling exit(1) (gmat/remma/_remma_epi_eff_cpu.c:18-21,115-118).
+ *
+ *  (2) gmat_b200_* symbols: work the reference does in numpy (exact test, GRM, decode, coding),
+ *      operating on DEVICE pointers owned by the caller (torch tensors: tensor.data_ptr()) on a
+ *      caller-supplied CUDA stream (cudaStream_t passed as void*; NULL = default stream).
+ *      No callee-owned memory crosses the boundary; hit buffers are caller-allocated with an
+ *      atomic counter.  All functions return GMAT_B200_OK (1) or a negative error.
+ *
+ * Genotype store layout (device): `bed` = the PLINK1 SNP-major payload (file bytes after the 3-byte
+ * magic), one row per SNP, `row_bytes` >= ceil(n/4) bytes apart (pad rows to a multiple of 16 bytes
+ * for aligned vector loads), 4 individuals per byte, low bits first, 2-bit code c:
+ *   00 -> 0, 01 -> missing, 10 -> 1, 11 -> 2   (count of the .bim A2 allele;
+ *   gmat/process_plink/_read_plink_bed.c:36-37: value = (c*c+c)/6).
+ * A coded column (additive x = g-2p, dominance d = h-2p(1-p)) is never materialised: it is the
+ * 4-entry table lut[snp][c] (double[m][4]) applied to the 2-bit codes inside the kernels.
+ */
+#ifndef GMAT_B200_H
+#define GMAT_B200_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GMAT_B200_OK              1
+#define GMAT_B200_ERR_ARG        -1   /* bad argument */
+#define GMAT_B200_ERR_IO         -2   /* cannot open/read/write a file, bad .bed magic */
+#define GMAT_B200_ERR_CUDA       -3   /* CUDA runtime error (no device, launch failure, OOM) */
+#define GMAT_B200_ERR_OVERFLOW   -4   /* hit buffer too small: count > cap (count is still exact) */
+
+/* coding selectors for gmat_b200_build_lut */
+#define GMAT_B200_CODING_RAW      0   /* 0, 1/3(missing), 1, 2          _read_plink_bed.c:36-37 */
+#define GMAT_B200_CODING_ADD      1   /* g - 2p                          remma_epiAA.py:59-61    */
+#define GMAT_B200_CODING_DOM      2   /* h - 2p(1-p), h = g with 2 -> 0  remma_epiDD.py:59-65    */
+/* how p is formed */
+#define GMAT_B200_FREQ_NUMPY      0   /* p = (sum g) / (2n), sum exact       remma_epiAA.py:59   */
+#define GMAT_B200_FREQ_CLOOP      1   /* p += g_k/(2n) term by term in k     _remma_epi_eff_cpu.c:103-107 */
+
+/* flags for gmat_b200_epi_eff */
+#define GMAT_B200_EFF_GE          1   /* emit when |eff| >= cut (first AD direction, _remma_epi_eff_cpu.c:238) */
+#define GMAT_B200_EFF_SWAP        2   /* report (j,i) instead of (i,j)   (second AD direction, :245-247)       */
+
+/* pair-space selectors for the exact scan */
+#define GMAT_B200_PAIRS_UPPER     0   /* j in (i, m)   remma_epiAA.py:72, remma_epiDD.py:76 */
+#define GMAT_B200_PAIRS_ALL       1   /* j in [0, m)   remma_epiAD.py:77 (incl. j == i)      */
+
+typedef struct gmat_b200_hit {
+    int    snp_0;      /* first column of the reference output files  */
+    int    snp_1;
+    double eff;        /* w' Z'Py                                     */
+    double var;        /* w' Z'PZ w   (0 for the approximate screen)  */
+    double chi;        /* eff^2/var   (0 for the approximate screen)  */
+} gmat_b200_hit;       /* 32 bytes */
+
+/* ------------------------------------------------------------------ runtime / errors ------- */
+int         gmat_b200_version(void);
+const char *gmat_b200_last_error(void);            /* thread-local, valid until the next call   */
+int         gmat_b200_device_count(void);          /* >= 0, or negative error                   */
+int         gmat_b200_set_device(int device);
+int         gmat_b200_device_info(int *sm_count, int *cc_major, int *cc_minor, long long *hbm_bytes);
+long long   gmat_b200_kernel_launches(void);       /* kernels launched by this library so far   */
+
+/* FP64 issue-rate microbenchmarks (used by bench.py for the roofline denominator).
+ * kind 0: DMMA (mma.sync m8n8k4 f64) ; kind 1: DFMA.  Writes TFLOP/s.  */
+int gmat_b200_fp64_peak(int kind, int iters, double *tflops);
+
+/* ------------------------------------------------------------------ (1) drop-in symbols ---- */
+/* gmat/process_plink/_read_plink_bed.c:5 -- marker_mat is HOST double[num_snp][num_id]        */
+int read_plink_bed(char *bed_file, long long num_id, long long num_snp, double *marker_mat);
+
+/* gmat/remma/_remma_epi_eff_cpu.c:91,260,443 -- all pointers HOST; writes text file out_file   */
+int remma_epiAA_eff_cpu(char *bed_file, long long num_id, long long num_snp, long long *snp_lst_0,
+                        long long len_snp_lst_0, double *pymat, double eff_cut, char *out_file);
+int remma_epiAD_eff_cpu(char *bed_file, long long num_id, long long num_snp, long long *snp_lst_0,
+                        long long len_snp_lst_0, double *pymat, double eff_cut, char *out_file);
+int remma_epiDD_eff_cpu(char *bed_file, long long num_id, long long num_snp, long long *snp_lst_0,
+                        long long len_snp_lst_0, double *pymat, double eff_cut, char *out_file);
+/* gmat/remma/_remma_epi_eff_cpu.c:171,354,526 -- eff_cut is a 111-entry table indexed by
+ * freq[snp_lst_0[i]]*10 + freq[j] (:154)                                                       */
+int remma_epiAA_maf_eff_cpu(char *bed_file, long long num_id, long long num_snp, long long *snp_lst_0,
+                            long long len_snp_lst_0, double *pymat, long long *freq, double *eff_cut,
+                            char *out_file);
+int remma_epiAD_maf_eff_cpu(char *bed_file, long long num_id, long long num_snp, long long *snp_lst_0,
+                            long long len_snp_lst_0, double *pymat, long long *freqA, long long *freqD,
+                            double *eff_cut, char *out_file);
+int remma_epiDD_maf_eff_cpu(char *bed_file, long long num_id, long long num_snp, long long *snp_lst_0,
+                            long long len_snp_lst_0, double *pymat, long long *freq, double *eff_cut,
+                            char *out_file);
+
+/* ------------------------------------------------------------------ (2) device-pointer API -- */
+/* Read "<bed_file>.bed" (prefix without extension, like the reference), validate the magic
+ * (6c 1b 01), and return the payload size; with host_buf != NULL also copy the payload into it
+ * re-strided to row_bytes (zero padded).  Host-side I/O helper, no GPU work.                    */
+int gmat_b200_bed_read_host(const char *bed_file, long long num_id, long long num_snp,
+                            long long row_bytes, unsigned char *host_buf);
+
+/* per-SNP genotype counts: counts[snp][c] = number of individuals k < n with code c            */
+int gmat_b200_bed_stats(const unsigned char *bed_dev, long long n, long long m, long long row_bytes,
+                        int *counts_dev /* [m][4] */, void *stream);
+
+/* per-SNP value tables for a coding; freq_dev (optional, may be NULL) receives p[m]            */
+int gmat_b200_build_lut(const unsigned char *bed_dev, long long n, long long m, long long row_bytes,
+                        const int *counts_dev, int coding, int freq_mode,
+                        double *lut_dev /* [m][4] */, double *freq_dev /* [m] or NULL */, void *stream);
+
+/* materialise doubles: out[snp][k] = lut[snp][code]  (lut_dev == NULL: raw (c*c+c)/6, i.e. the
+ * exact output of read_plink_bed).  HBM-bound: 0.25 B read + 8 B written per genotype.          */
+int gmat_b200_decode(const unsigned char *bed_dev, long long n, long long m, long long row_bytes,
+                     const double *lut_dev, double *out_dev /* [m][n] */, void *stream);
+
+/* inverse of decode for imputed matrices: geno[snp][k] in {0,1,2} (NaN/other -> missing)        */
+int gmat_b200_pack(const double *geno_dev /* [m][n] */, long long n, long long m, long long row_bytes,
+                   unsigned char *bed_dev_out, void *stream);
+
+/* Approximate screen (gmat/remma/_remma_epi_eff_cpu.c:61-86): for i in ilist, j in (i, m):
+ * eff = sum_k lutU[i][c_ik] * lutV[j][c_jk] * py[k]; emit a hit when |eff| > cut (>= with
+ * GMAT_B200_EFF_GE), cut = eff_cut or, when cut_table_dev != NULL,
+ * cut_table[binI[i]*10 + binJ[j]] (111 doubles).  hits beyond cap are counted, not stored.     */
+int gmat_b200_epi_eff(const unsigned char *bed_dev, long long n, long long m, long long row_bytes,
+                      const double *lutU_dev, const double *lutV_dev, const double *py_dev,
+                      const long long *ilist_dev, long long n_i, int flags, double eff_cut,
+                      const double *cut_table_dev, const int *binI_dev, const int *binJ_dev,
+                      gmat_b200_hit *hits_dev, long long cap, unsigned long long *count_dev,
+                      void *stream);
+
+/* Z'PZ re-tiled for the exact kernel: lower block-triangle, 128-row blocks, DMMA fragment order.
+ * gmat_b200_pvp_packed_elems(n) doubles are needed.                                            */
+long long gmat_b200_pvp_packed_elems(long long n);
+int gmat_b200_pack_pvp(const double *pvp_dev /* [n][n] row-major, symmetric */, long long n,
+                       double *packed_dev, void *stream);
+
+/* Exact test over a scan (remma_epiAA.py:71-82): for i in ilist, j in (i,m) or [0,m):
+ * w = lutU[i][c_i.] o lutV[j][c_j.]; eff = w'py; var = w' Z'PZ w; chi = eff^2/var;
+ * emit when chi > chi_cut (strict) -- or every pair when chi_cut < 0.                           */
+int gmat_b200_epi_exact_scan(const unsigned char *bed_dev, long long n, long long m, long long row_bytes,
+                             const double *lutU_dev, const double *lutV_dev, const double *py_dev,
+                             const double *pvp_packed_dev, const long long *ilist_dev, long long n_i,
+                             int pair_space, double chi_cut,
+                             gmat_b200_hit *hits_dev, long long cap, unsigned long long *count_dev,
+                             void *stream);
+
+/* Exact test over an explicit pair list (remma_epiAA_pair.py:66-87): out[p] gets eff/var/chi of
+ * pair p (all pairs are written, dense, in list order).                                        */
+int gmat_b200_epi_exact_pairs(const unsigned char *bed_dev, long long n, long long m, long long row_bytes,
+                              const double *lutU_dev, const double *lutV_dev, const double *py_dev,
+                              const double *pvp_packed_dev, const int *pairs_dev /* [n_pairs][2] */,
+                              long long n_pairs, gmat_b200_hit *out_dev, void *stream);
+
+/* GRM (gmat/gmatrix/gmatrix.py:63-66,127-130): K = X X' / scale with X[k][snp] = lut[snp][c],
+ * then diag(K) += diag(K)*small_val.  K_dev is [n][n] row-major, fully (symmetrically) written.
+ * snp range [snp_begin, snp_end) lets ranks own K-slices (partial sums, scale applied by caller
+ * when accumulate != 0: K_dev += partial, no scale, no diagonal inflation).                    */
+int gmat_b200_grm(const unsigned char *bed_dev, long long n, long long m, long long row_bytes,
+                  const double *lut_dev, long long snp_begin, long long snp_end,
+                  double scale, double small_val, int accumulate, double *K_dev, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GMAT_B200_H */

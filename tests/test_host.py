@@ -1,0 +1,189 @@
+"""CPU tests of the host side: the C-ABI library loads and exports every symbol include/gmat_b200.h declares
+(no compute calls without a GPU), host logic (partitions, design matrix, formats), and the world_size-2
+gloo path of the hit gather."""
+import os
+import re
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+from conftest import GOLD, ROOT, read_rows
+
+
+def test_library_loads_and_exports_every_declared_symbol():
+    from gmat_b200 import _ffi
+    names = _ffi.exported_symbols()
+    assert len(names) >= 24
+    for required in ("read_plink_bed", "remma_epiAA_eff_cpu", "remma_epiAD_eff_cpu", "remma_epiDD_eff_cpu",
+                     "remma_epiAA_maf_eff_cpu", "remma_epiAD_maf_eff_cpu", "remma_epiDD_maf_eff_cpu",
+                     "gmat_b200_epi_exact_scan", "gmat_b200_epi_exact_pairs", "gmat_b200_epi_eff", "gmat_b200_grm",
+                     "gmat_b200_decode", "gmat_b200_bed_stats", "gmat_b200_build_lut", "gmat_b200_pack_pvp"):
+        assert required in names
+    for n in names:
+        assert hasattr(_ffi.lib, n), n
+    out = subprocess.run(["nm", "-D", "--defined-only", _ffi.LIB_PATH], capture_output=True, text=True).stdout
+    exported = set(re.findall(r" T (\w+)", out))
+    assert set(names) <= exported
+    assert _ffi.lib.gmat_b200_version() == 100
+    assert _ffi.ffi.sizeof("gmat_b200_hit") == 32
+
+
+def test_reference_signatures_match_the_reference_cdef():
+    """The seven drop-in symbols have exactly the reference's cffi cdef signatures (gmat/remma/_build.py:8-31)."""
+    from gmat_b200 import _ffi
+    from oracle.ref_harness import BED_CDEF, EPI_CDEF
+
+    def norm(sig):
+        return re.sub(r"\s+", " ", sig.replace("char* ", "char *")).strip()
+    theirs = {re.search(r"(\w+)\s*\(", s).group(1): norm(s) for s in (EPI_CDEF + BED_CDEF).split(";") if "(" in s}
+    ours = {}
+    for s in _ffi._CDEF.split(";"):
+        mm = re.search(r"\b(remma_epi\w+_cpu|read_plink_bed)\s*\(", s)
+        if mm:
+            ours[mm.group(1)] = norm(s[s.index("int "):])
+    assert set(ours) == set(theirs) and len(ours) == 7
+    for k in theirs:
+        a = re.sub(r"\b\w+(?=[,)])", "", theirs[k]).replace(" ", "")     # drop parameter names
+        b = re.sub(r"\b\w+(?=[,)])", "", ours[k]).replace(" ", "")
+        assert a == b, (k, a, b)
+
+
+def test_host_bed_reader_without_gpu(tmp_path):
+    from gmat_b200._ffi import ffi, lib
+    bed = os.path.join(GOLD, "mouse", "plink")
+    n, m = 1304, 1407
+    rb = 352
+    buf = np.zeros(m * rb, dtype=np.uint8)
+    assert lib.gmat_b200_bed_read_host(bed.encode(), n, m, rb, ffi.cast("unsigned char *", buf.ctypes.data)) == 1
+    raw = np.fromfile(bed + ".bed", dtype=np.uint8)[3:].reshape(m, 326)
+    assert np.array_equal(buf.reshape(m, rb)[:, :326], raw) and not buf.reshape(m, rb)[:, 326:].any()
+    assert lib.gmat_b200_bed_read_host(str(tmp_path / "missing").encode(), n, m, rb, ffi.NULL) == -2
+    assert b"missing.bed" in ffi.string(lib.gmat_b200_last_error())
+    (tmp_path / "bad.bed").write_bytes(b"abc")
+    assert lib.gmat_b200_bed_read_host(str(tmp_path / "bad").encode(), 4, 1, 16, ffi.NULL) == -2
+    assert lib.gmat_b200_pvp_packed_elems(1304) == 8 * 11 * 12 // 2 * 2048
+
+
+def test_no_cuda_fails_loudly():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("CUDA present")
+    from gmat_b200 import engine
+    with pytest.raises(RuntimeError):
+        engine.current_device()
+    from gmat_b200.gmatrix import agmat
+    with pytest.raises(RuntimeError):
+        agmat(os.path.join(GOLD, "mouse", "plink"))
+
+
+def test_product_never_imports_the_oracle():
+    for dirpath, _, files in os.walk(os.path.join(ROOT, "gmat_b200")):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h")):
+                src = open(os.path.join(dirpath, f)).read()
+                assert not re.search(r"^\s*(from|import)\s+oracle", src, flags=re.M), f
+                assert "oracle/" not in src and "/root/reference" not in src, f
+
+
+def test_parallel_partition_matches_reference(golden):
+    from gmat_b200.remma.parallel import parallel_lists, shard_first_snps
+    for part in golden["parallel_partitions"]:
+        lst, pos = parallel_lists(part["m"], [part["P"], part["k"]], False)
+        assert pos == part["AA"] and lst == list(range(pos[0], pos[1])) + list(range(pos[2], pos[3]))
+        assert parallel_lists(part["m"], [part["P"], part["k"]], True)[1] == part["AD"]
+    # the reference partition covers [0, m-1) exactly once
+    for m, P in ((1407, 3), (50000, 8), (101, 5)):
+        allv = sorted(sum((parallel_lists(m, [P, k])[0] for k in range(1, P + 1)), []))
+        assert allv == list(range(m - 1))
+    # GPU sharding: disjoint cover, triangular work balanced
+    m, R = 50000, 8
+    full = list(range(m - 1))
+    shards = [shard_first_snps(full, m, False, r, R) for r in range(R)]
+    assert sorted(sum(shards, [])) == full
+    work = [sum(m - 1 - i for i in s) for s in shards]
+    assert max(work) / min(work) < 1.01
+
+
+def test_design_matrix_matches_reference_shapes(golden):
+    from gmat_b200.uvlmm.design_matrix import design_matrix_wemai_multi_gmat
+    bed = os.path.join(GOLD, "mouse", "plink")
+    y, xmat, zmat = design_matrix_wemai_multi_gmat(os.path.join(GOLD, "mouse", "pheno"), bed)
+    assert list(xmat.shape) == golden["xmat_shape"] and np.allclose(y[:8, 0], golden["y_first8"])
+    assert zmat.shape == (1304, 1304) and np.array_equal(zmat.toarray(), np.eye(1304))
+    y3, x3, z3 = design_matrix_wemai_multi_gmat(os.path.join(GOLD, "mouse", "pheno_rep3"), bed)
+    assert z3.shape == (3912, 1304) and np.array_equal(np.asarray(z3.sum(axis=0)).ravel(), np.full(1304, 3.0))
+    assert np.array_equal(z3.indices[:6], [0, 0, 0, 1, 1, 1])
+
+
+def test_host_preamble_matches_reference(golden, mouse_model):
+    from gmat_b200.remma._core import preamble
+    M = mouse_model
+    pymat, pvpmat = preamble(M["y"], M["xmat"], M["zmat"], M["gl_aa"], M["vc_aa"], scipy_inv=True)
+    np.testing.assert_allclose(pymat.ravel(), golden["pymat_ag_agag"], rtol=1e-9, atol=1e-12)
+    np.testing.assert_allclose(np.diag(pvpmat)[:16], golden["pvpmat_diag_first16"], rtol=1e-9)
+
+
+def test_random_pair_restatement(tmp_path):
+    from gmat_b200.remma import random_pair, random_pairAD
+    np.random.seed(3)
+    a = random_pair(500, out_file=str(tmp_path / "rp"), num_pair=6000)
+    assert a.shape == (6000, 2) and (a[:, 0] < a[:, 1]).all() and len({tuple(r) for r in a}) == 6000
+    assert open(str(tmp_path / "rp")).readline() == "snp_0 snp_1\n"
+    b = random_pairAD(500, out_file=str(tmp_path / "rq"), num_pair=6000)
+    assert (b[:, 0] != b[:, 1]).all() and (b[:, 0] > b[:, 1]).any()
+
+
+def test_synth_bed_roundtrip(tmp_path):
+    from gmat_b200 import synth
+    from oracle import oracle
+    prefix = str(tmp_path / "s")
+    ds = synth.write_dataset(prefix, 37, 19, seed=1, missing_rate=0.1)
+    raw = oracle.read_bed_raw(prefix, 37, 19)
+    g = ds["geno"].astype(float)
+    want = np.where(g < 0, 1.0 / 3, g)
+    assert np.allclose(raw, want)
+
+
+_GLOO_WORKER = r'''
+import os, sys
+sys.path.insert(0, %r)
+import numpy as np, torch, torch.distributed as dist
+from gmat_b200.engine import HIT_DTYPE
+from gmat_b200.remma import parallel as par
+dist.init_process_group("gloo", init_method="tcp://127.0.0.1:%%s" %% sys.argv[2], rank=int(sys.argv[1]), world_size=2)
+rank = dist.get_rank()
+m = 1000
+lst = par.shard_first_snps(list(range(m - 1)), m, False, rank, 2)
+hits = np.zeros(len(lst) // (7 + rank), dtype=HIT_DTYPE)       # different counts per rank, rank-tagged payload
+hits["snp_0"] = lst[:len(hits)]
+hits["snp_1"] = rank
+hits["eff"] = np.arange(len(hits)) + 0.5 * rank
+out = par.gather_hits(hits, torch.device("cpu"))
+empty = par.gather_hits(np.zeros(0, dtype=HIT_DTYPE), torch.device("cpu"))
+if rank == 0:
+    n0 = len(par.shard_first_snps(list(range(m - 1)), m, False, 0, 2)) // 7
+    n1 = len(par.shard_first_snps(list(range(m - 1)), m, False, 1, 2)) // 8
+    assert len(out) == n0 + n1 and (out["snp_1"][:n0] == 0).all() and (out["snp_1"][n0:] == 1).all()
+    assert np.allclose(out["eff"][n0:], np.arange(n1) + 0.5) and len(empty) == 0
+    print("GLOO_OK")
+else:
+    assert out is None
+dist.destroy_process_group()
+'''
+
+
+def test_two_rank_hit_gather_gloo(tmp_path):
+    script = tmp_path / "w.py"
+    script.write_text(_GLOO_WORKER % ROOT)
+    import socket
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    procs = [subprocess.Popen([sys.executable, str(script), str(r), str(port)], stdout=subprocess.PIPE,
+                              stderr=subprocess.STDOUT, text=True) for r in range(2)]
+    outs = [p.communicate(timeout=240)[0] for p in procs]
+    assert all(p.returncode == 0 for p in procs), outs
+    assert "GLOO_OK" in outs[0]
