@@ -28,9 +28,13 @@ def random_genotypes(n, m, seed, missing_rate=0.0):
     rng = np.random.Generator(np.random.PCG64(seed))
     p = rng.uniform(0.05, 0.95, size=m)
     g = rng.binomial(2, p[:, None], size=(m, n)).astype(np.int8)
-    for s in range(m):                                  # no monomorphic columns
-        while g[s].min() == g[s].max():
+    for s in range(m if n >= 2 else 0):                 # no monomorphic columns (impossible for n == 1)
+        for _ in range(1000):
+            if g[s].min() != g[s].max():
+                break
             g[s] = rng.binomial(2, p[s], size=n)
+        else:                                           # tiny n with an extreme p: force one heterozygote
+            g[s, 0] = 1 if g[s, 0] != 1 else 0
     if missing_rate > 0:
         g[rng.uniform(size=(m, n)) < missing_rate] = -1
     return g

@@ -1,0 +1,98 @@
+#!/usr/bin/env python
+"""One launch of every hot kernel at a moderate, roofline-relevant size -- the command that is run first
+plain and then under ``ncu --set full`` (see scripts/gpu_profile.sh).  Prints CUDA-event times so the plain
+run doubles as a sanity check; numbers printed under ncu are never bench values.
+
+    python scripts/profile_kernels.py [--only exact,eff,grm,decode,stats] [--n 2000] [--m 20000]
+"""
+import argparse
+import json
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--only", default="exact,eff,grm,decode,stats")
+    ap.add_argument("--n", type=int, default=2000)
+    ap.add_argument("--m", type=int, default=20000)
+    ap.add_argument("--first", type=int, default=64, help="first-SNPs of the exact-scan launch")
+    ap.add_argument("--grm-n", type=int, default=4096)
+    ap.add_argument("--grm-m", type=int, default=65536)
+    ap.add_argument("--dec-n", type=int, default=5000)
+    ap.add_argument("--dec-m", type=int, default=50000)
+    ap.add_argument("--reps", type=int, default=1)
+    args = ap.parse_args()
+    only = set(args.only.split(","))
+    import torch
+    from gmat_b200 import engine, synth
+    dev = engine.current_device()
+    out = {}
+
+    def timed(fn):
+        best = 1e30
+        for _ in range(args.reps + 1):             # first call is the warm-up
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            fn()
+            e1.record()
+            torch.cuda.synchronize()
+            best = min(best, e0.elapsed_time(e1))
+        return best * 1e-3
+
+    n, m = args.n, args.m
+    rb = engine.row_stride(n)
+    store = engine.GenotypeStore.from_device_payload(synth.device_payload(n, m, 11, dev, rb), n)
+    if "stats" in only:
+        t = timed(lambda: engine.GenotypeStore.from_device_payload(store.bed, n))
+        out["bed_stats"] = {"seconds": t, "gb_per_s": m * rb / t / 1e9}
+    if only & {"exact", "eff"}:
+        gen = torch.Generator(device=dev)
+        gen.manual_seed(5)
+        b = torch.randn((n, n + 8), dtype=torch.float64, device=dev, generator=gen)
+        pvp = b @ b.T / n
+        pvp = pvp - pvp.mean(dim=0, keepdim=True)
+        pvp = pvp - pvp.mean(dim=1, keepdim=True)
+        py = torch.randn((n,), dtype=torch.float64, device=dev, generator=gen)
+        py = py - py.mean()
+    if "exact" in only:
+        packed = engine.pack_pvp(pvp)
+        lut = store.lut(engine.ADD)
+        il = np.linspace(0, m - 2, args.first).astype(np.int64)
+        pairs = int(np.sum(m - 1 - il))
+        t = timed(lambda: engine.epi_exact_scan(store, lut, lut, py, packed, il, engine.PAIRS_UPPER, 30.0))
+        out["exact"] = {"seconds": t, "pairs": pairs, "pairs_per_s": pairs / t,
+                        "tflops_algorithmic": pairs * (2.0 * n * n + 5 * n) / t / 1e12}
+    if "eff" in only:
+        la = store.lut(engine.ADD, engine.FREQ_CLOOP)
+        full = np.arange(m - 1, dtype=np.int64)
+        pairs = m * (m - 1) // 2
+        t = timed(lambda: engine.epi_eff(store, la, la, py, full, 0, 1e30))
+        out["eff"] = {"seconds": t, "pairs": pairs, "pairs_per_s": pairs / t,
+                      "tflops_algorithmic": pairs * 2.0 * n / t / 1e12}
+    if "decode" in only:
+        n2, m2 = args.dec_n, args.dec_m
+        st2 = engine.GenotypeStore.from_device_payload(synth.device_payload(n2, m2, 12, dev, engine.row_stride(n2)), n2)
+        nbytes = m2 * ((n2 + 3) // 4) + 8.0 * m2 * n2
+        t = timed(lambda: st2.decode(None))
+        out["decode_raw"] = {"seconds": t, "gb_per_s": nbytes / t / 1e9}
+        t = timed(lambda: st2.decode(engine.ADD))
+        out["decode_add"] = {"seconds": t, "gb_per_s": nbytes / t / 1e9}
+        del st2
+    if "grm" in only:
+        n2, m2 = args.grm_n, args.grm_m
+        st2 = engine.GenotypeStore.from_device_payload(synth.device_payload(n2, m2, 13, dev, engine.row_stride(n2)), n2)
+        st2.lut(engine.ADD)
+        kin = torch.empty((n2, n2), dtype=torch.float64, device=dev)
+        t = timed(lambda: engine.grm(st2, engine.ADD, 1.0, 0.001, out=kin))
+        out["grm"] = {"seconds": t, "tflops_algorithmic_n(n+1)m": float(n2) * (n2 + 1) * m2 / t / 1e12}
+    print(json.dumps(out))
+
+
+if __name__ == "__main__":
+    main()
