@@ -90,6 +90,13 @@ def test_pack_roundtrip(eng, tmp_path):
 
 
 # ------------------------------------------------------------------------------------------ approximate screen
+def _assert_g_text(texts, values):
+    """The file holds eff as C '%g' (6 significant digits, _remma_epi_eff_cpu.c:75): the text must be the
+    '%g' rendering of the oracle value, or of a value within 1e-9 relative of it (a rounding-boundary case)."""
+    for t, v in zip(texts, values):
+        assert t in ("%g" % v, "%g" % (v * (1 + RTOL)), "%g" % (v * (1 - RTOL))), (t, v)
+
+
 def _pymat(n, seed):
     rng = np.random.Generator(np.random.PCG64(seed))
     py = rng.normal(size=n)
@@ -116,8 +123,7 @@ def test_screen_dropin_symbols_vs_oracle(eng, tmp_path, kind, n, m):
     rows = read_rows(out)
     assert open(out).readline() == "snp_0 snp_1 eff\n"
     assert [(int(r[0]), int(r[1])) for r in rows] == [(r[0], r[1]) for r in want]     # same set, same order
-    assert [r[2] for r in rows] == ["%g" % r[2] for r in want] or \
-        np.allclose([float(r[2]) for r in rows], [r[2] for r in want], rtol=2e-6)
+    _assert_g_text([r[2] for r in rows], [r[2] for r in want])
     # full precision through the device API
     store = eng.GenotypeStore(prefix)
     import torch
@@ -166,7 +172,7 @@ def test_maf_screen_dropin_vs_oracle(eng, tmp_path, kind):
     rows = read_rows(out)
     assert len(want) > 20
     assert [(int(r[0]), int(r[1])) for r in rows] == [(r[0], r[1]) for r in want]
-    np.testing.assert_allclose([float(r[2]) for r in rows], [r[2] for r in want], rtol=2e-6)
+    _assert_g_text([r[2] for r in rows], [r[2] for r in want])
 
 
 def test_screen_error_paths(eng, tmp_path):
@@ -219,7 +225,7 @@ def test_exact_pairs_and_scan_vs_oracle_synthetic(eng, tmp_path, kind, n, m):
     assert np.array_equal(res["snp_0"], pairs[:, 0]) and np.array_equal(res["snp_1"], pairs[:, 1])
     np.testing.assert_allclose(res["eff"], eff, rtol=RTOL, atol=1e-11)
     np.testing.assert_allclose(res["var"], var, rtol=RTOL)
-    np.testing.assert_allclose(res["chi"], chi, rtol=4 * RTOL, atol=1e-18)
+    np.testing.assert_allclose(res["chi"], chi, rtol=4 * RTOL, atol=1e-13)     # eff ~ 0 -> chi ~ 0
     # scan over a ragged first-SNP list, every pair reported (chi_cut < 0)
     all_pairs = kind == "AD"
     lst = [i for i in range(0, m - (0 if all_pairs else 1)) if i % 3 != 1]
