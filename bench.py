@@ -323,11 +323,16 @@ def extras(engine, torch, synth, store, model, lut, args):
     out["approx_screen"] = {"pairs_per_s": pairs / t, "seconds": t, "pairs": pairs,
                             "tflops_algorithmic": pairs * 2.0 * N_ID / t / 1e12,
                             "workload": "remma_epiAA_eff_cpu formulation, full scan n=%d x m=%d" % (N_ID, N_SNP)}
-    # decode: .bed -> float64 [m][n] (what read_plink_bed materialises), HBM-bound
-    t = timed(lambda: store.decode(None))
-    nbytes = N_SNP * ((N_ID + 3) // 4) + 8.0 * N_SNP * N_ID
+    # decode: .bed -> float64 [m][n] (what read_plink_bed materialises), HBM-bound; C4 shape (2 GB out > L2)
+    n3, m3 = 5000, 50000
+    st3 = engine.GenotypeStore.from_device_payload(
+        synth.device_payload(n3, m3, SEED + 3, store.device, engine.row_stride(n3)), n3)
+    dec = torch.empty((m3, n3), dtype=torch.float64, device=store.device)
+    t = timed(lambda: engine.decode_into(st3, None, dec))
+    nbytes = m3 * ((n3 + 3) // 4) + 8.0 * m3 * n3
     out["decode"] = {"gb_per_s": nbytes / t / 1e9, "seconds": t, "bytes": nbytes,
-                     "workload": "gmat_b200_decode n=%d x m=%d (0.25 B in + 8 B out per genotype)" % (N_ID, N_SNP)}
+                     "workload": "gmat_b200_decode n=%d x m=%d (0.25 B in + 8 B out per genotype)" % (n3, m3)}
+    del dec, st3
     if not args.no_grm:
         n2, m2 = args.grm_n, args.grm_m
         rb = engine.row_stride(n2)

@@ -110,47 +110,59 @@ __global__ void __launch_bounds__(128) build_lut_kernel(const unsigned char *__r
 }
 
 // ------------------------------------------------------------------------------------------
-// decode: out[snp][k] = lut[snp][code] (or the raw (c*c+c)/6 map).  One thread per byte
-// (4 individuals -> 32 bytes out).  Writes dominate: 8 B per genotype.
+// decode: out[snp][k] = lut[snp][code] (or the raw (c*c+c)/6 map).  HBM-bound, writes dominate (8 B per
+// genotype).  One warp per 512-genotype chunk of a SNP row: lane l loads ONE 32-bit word of codes (16
+// genotypes; a coalesced 128 B per warp), then for j = 0..7 the warp writes 64 consecutive genotypes as one
+// fully coalesced 512 B streaming store (lane l: genotypes 64j+2l, 64j+2l+1, codes fetched from the owning
+// lane with a shuffle).  No integer division or FP64 arithmetic per genotype: values come from 4 registers.
 // ------------------------------------------------------------------------------------------
+__device__ __forceinline__ double sel4(int c, double t0, double t1, double t2, double t3) {
+    return (c & 2) ? ((c & 1) ? t3 : t2) : ((c & 1) ? t1 : t0);
+}
+
 template <bool HAS_LUT>
 __global__ void __launch_bounds__(256) decode_kernel(const unsigned char *__restrict__ bed,
                                                      long long n, long long m, long long row_bytes,
                                                      const double *__restrict__ lut,
                                                      double *__restrict__ out) {
-    const long long bytes_per_row = (n + 3) / 4;
-    const long long total = bytes_per_row * m;
-    const bool vec_ok = (n % 2 == 0);                 // rows start 16-byte aligned iff n even
-    for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < total;
-         e += (long long)gridDim.x * blockDim.x) {
-        const long long snp = e / bytes_per_row;
-        const long long b = e - snp * bytes_per_row;
-        const unsigned x = __ldg(bed + snp * row_bytes + b);
-        double v[4];
+    const int lane = threadIdx.x & 31;
+    const long long warp0 = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const long long nwarp = (long long)gridDim.x * (blockDim.x >> 5);
+    const long long cpr = (n + 511) / 512;                       // chunks per SNP row
+    const long long total = cpr * m;
+    for (long long chunk = warp0; chunk < total; chunk += nwarp) {
+        const long long snp = chunk / cpr;
+        const long long ch = chunk - snp * cpr;
+        const long long woff = (ch * 32 + lane) * 4;                 // byte offset of this lane's code word
+        unsigned word = 0;
+        if (woff < row_bytes) word = __ldg(reinterpret_cast<const unsigned *>(bed + snp * row_bytes + woff));
+        double t0, t1, t2, t3;
         if (HAS_LUT) {
-            const double2 t0 = __ldg(reinterpret_cast<const double2 *>(lut) + 2 * snp);
-            const double2 t1 = __ldg(reinterpret_cast<const double2 *>(lut) + 2 * snp + 1);
-            const double tt[4] = {t0.x, t0.y, t1.x, t1.y};
-#pragma unroll
-            for (int q = 0; q < 4; ++q) {
-                const int c = (x >> (2 * q)) & 3;
-                v[q] = (c == 0) ? tt[0] : (c == 1) ? tt[1] : (c == 2) ? tt[2] : tt[3];
-            }
+            const double2 a = __ldg(reinterpret_cast<const double2 *>(lut) + 2 * snp);
+            const double2 b = __ldg(reinterpret_cast<const double2 *>(lut) + 2 * snp + 1);
+            t0 = a.x; t1 = a.y; t2 = b.x; t3 = b.y;
         } else {
-#pragma unroll
-            for (int q = 0; q < 4; ++q) {
-                const int c = (x >> (2 * q)) & 3;
-                v[q] = (double)(c * c + c) / 6.0;     // _read_plink_bed.c:37
-            }
+            t0 = 0.0; t1 = 2.0 / 6.0; t2 = 1.0; t3 = 2.0;            // (c*c+c)/6.0, _read_plink_bed.c:37
         }
-        const long long k0 = b * 4;
-        double *dst = out + snp * n + k0;
-        const int valid = (int)((n - k0) < 4 ? (n - k0) : 4);
-        if (vec_ok && valid == 4) {
-            reinterpret_cast<double2 *>(dst)[0] = make_double2(v[0], v[1]);
-            reinterpret_cast<double2 *>(dst)[1] = make_double2(v[2], v[3]);
-        } else {
-            for (int q = 0; q < valid; ++q) dst[q] = v[q];
+        double *row = out + snp * n;
+        const bool vec_ok = ((snp * n) & 1) == 0;                    // 16-byte aligned double2 stores
+        const int sh = (2 * lane & 15) * 2;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const unsigned w = __shfl_sync(0xffffffffu, word, 4 * j + (lane >> 3));
+            const long long k = ch * 512 + j * 64 + 2 * lane;
+            const double v0 = sel4((w >> sh) & 3, t0, t1, t2, t3);
+            const double v1 = sel4((w >> (sh + 2)) & 3, t0, t1, t2, t3);
+            if (k + 1 < n) {
+                if (vec_ok) {
+                    __stcs(reinterpret_cast<double2 *>(row + k), make_double2(v0, v1));
+                } else {
+                    __stcs(row + k, v0);
+                    __stcs(row + k + 1, v1);
+                }
+            } else if (k < n) {
+                __stcs(row + k, v0);
+            }
         }
     }
 }
@@ -225,8 +237,8 @@ extern "C" int gmat_b200_decode(const unsigned char *bed_dev, long long n, long 
     int rc = check_store(bed_dev, n, m, row_bytes);
     if (rc != GMAT_B200_OK) return rc;
     GB_CHECK_ARG(out_dev != nullptr, "out_dev is NULL");
-    const long long total = (n + 3) / 4 * m;
-    long long blocks = (total + 255) / 256;
+    const long long total = (n + 511) / 512 * m;              // one warp per 512-genotype chunk
+    long long blocks = (total + 7) / 8;
     const long long cap = (long long)sm_count() * 32;
     if (blocks > cap) blocks = cap;
     if (lut_dev)

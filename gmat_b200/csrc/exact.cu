@@ -28,7 +28,8 @@ constexpr int EX_BI = 8;             // first-SNPs per scan tile
 constexpr int EX_BJ = 16;            // second-SNPs per scan tile
 constexpr int EX_BK = 16;            // K-slab (columns of A / individuals)
 constexpr int EX_LD = EX_T + 4;      // padded leading dimension of the W slab
-constexpr int EX_STAGES = 4;         // TMA stages of A slabs
+constexpr int EX_STAGES = 5;         // ring of {A slab, W slab} stages
+constexpr int EX_AHEAD = 2;          // slabs produced ahead of the one being consumed
 constexpr int EX_SLAB_ELEMS = BLOCK_ROWS * EX_BK;          // 2048 doubles = 16 KB
 constexpr int EX_SLABS_PER_BLOCK = BLOCK_ROWS / EX_BK;     // 8
 
@@ -104,19 +105,21 @@ struct ExactParams {
     gmat_b200_hit *out;
 };
 
+// Shared memory of one CTA (~205 KB): a ring of EX_STAGES x {A slab (TMA destination), W slab}, the per-tile pair
+// metadata, and the mbarriers that let the 16 warps run the K loop without any CTA-wide barrier.
 template <int WARPS_M>
 struct ExactSmem {
-    double A[EX_STAGES][EX_SLAB_ELEMS];           // 4 x 16 KB, TMA destination (16-byte aligned)
-    double W[2][EX_BK][EX_LD];
-    double lutU[4][EX_T];
-    double lutV[4][EX_T];
+    double A[EX_STAGES][EX_SLAB_ELEMS];           // 16 KB each, TMA destination (16-byte aligned)
+    double W[EX_STAGES][EX_BK][EX_LD];            // 16.5 KB each: w = u_i o v_j, 16 individuals x 128 pairs
+    double prod[16][EX_T];                        // per pair: lutU[i][a] * lutV[j][b] at [a*4+b]
     double red_var[WARPS_M][EX_T];
     double red_eff[WARPS_M][EX_T];
     long long uoff[EX_T];                         // byte offset of the pair's U / V genotype rows
     long long voff[EX_T];
     int pi[EX_T];                                 // SNP indices (-1: masked pair)
     int pj[EX_T];
-    uint64_t full[EX_STAGES];                     // mbarriers
+    uint64_t full[EX_STAGES];                     // A landed (TMA tx bytes) + W written (one arrival per warp)
+    uint64_t empty[EX_STAGES];                    // slab consumed (one arrival per warp)
     long long tile_ib;
 };
 
@@ -124,15 +127,23 @@ struct ExactSmem {
 
 namespace gb {
 
+// Persistent kernel, 16 warps (4 x 4, warp tile 32 rows x 32 pairs).  Every warp is both consumer (DMMA on
+// slab s) and a 1/16 producer of the W slab EX_AHEAD slabs ahead (table lookups on 2-bit codes: LDS + STS, no
+// FP64 work); thread 0 also issues the TMA bulk copy of that slab of packed A.  Hand-off is by mbarriers only
+// (full: tx bytes + 16 warp arrivals, empty: 16 warp arrivals), so inside a pair tile there is no CTA-wide
+// barrier and warps may drift min(EX_AHEAD, EX_STAGES-EX_AHEAD-1) slabs apart: when one warp waits, the DMMA
+// pipe of its SM sub-partition issues from the other three.
 template <int WARPS_M, int WARPS_N, bool PAIR_MODE>
 __global__ void __launch_bounds__(WARPS_M *WARPS_N * 32, 1) epi_exact_kernel(const ExactParams p) {
-    constexpr int NT = WARPS_M * WARPS_N * 32;
+    constexpr int NW = WARPS_M * WARPS_N;
+    constexpr int NT = NW * 32;
     constexpr int WM = BLOCK_ROWS / WARPS_M, WN = EX_T / WARPS_N;
     constexpr int MT = WM / 8, NTL = WN / 8;
     constexpr int PARTS = NT / EX_T;                 // producer threads per pair
     constexpr int KPER = EX_BK / PARTS;              // individuals per producer thread per slab
     static_assert(MT % 2 == 0, "A fragments are loaded as pairs of m-tiles (LDS.128)");
-    static_assert(KPER == 4 || KPER == 8, "producer split");
+    static_assert(KPER == 4, "a producer thread expands one code byte per operand per slab");
+    static_assert(EX_AHEAD >= 1 && EX_AHEAD < EX_STAGES - 1, "ring must leave room for warp skew");
     constexpr unsigned SLAB_BYTES = EX_SLAB_ELEMS * sizeof(double);
     extern __shared__ __align__(128) unsigned char smem_raw[];
     ExactSmem<WARPS_M> &S = *reinterpret_cast<ExactSmem<WARPS_M> *>(smem_raw);
@@ -146,25 +157,21 @@ __global__ void __launch_bounds__(WARPS_M *WARPS_N * 32, 1) epi_exact_kernel(con
     const long long my_tiles =
         ((long long)blockIdx.x < ntiles) ? (ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
     const long long s_total = ex_total_slabs(p.nb);
-    const long long total_c = my_tiles * s_total;
 
     if (tid == 0) {
-        for (int s = 0; s < EX_STAGES; ++s) mbar_init(&S.full[s], 1);
+        for (int s = 0; s < EX_STAGES; ++s) {
+            mbar_init(&S.full[s], NW + 1);           // 16 warp arrivals + the expect_tx arrival of thread 0
+            mbar_init(&S.empty[s], NW);
+        }
         mbar_fence_init();
     }
-    __syncthreads();
-    if (tid == 0) {
-        for (long long c0 = 0; c0 < EX_STAGES && c0 < total_c; ++c0) {
-            mbar_expect_tx(&S.full[c0], SLAB_BYTES);
-            tma_bulk_g2s(S.A[c0], p.packed + (c0 % s_total) * EX_SLAB_ELEMS, SLAB_BYTES, &S.full[c0]);
-        }
-    }
-    long long c = 0;                                 // running slab counter of this CTA (all tiles)
+    long long c = 0;                                 // slabs consumed so far by this CTA (all tiles)
+    long long cp = 0;                                // slabs produced so far
 
     for (long long tl = 0; tl < my_tiles; ++tl) {
         const long long tile = blockIdx.x + tl * gridDim.x;
-        __syncthreads();                             // previous tile's results consumed
-        // ---------------- tile setup: which 128 pairs -------------------------------------------
+        __syncthreads();                             // previous tile's results consumed (also orders mbar_init)
+        // ---------------- tile setup: which 128 pairs, their rows and product tables -----------------
         if (!PAIR_MODE) {
             if (tid == 0) {
                 long long lo = 0, hi = p.n_iblk;     // largest ib with prefix[ib] <= tile
@@ -194,45 +201,61 @@ __global__ void __launch_bounds__(WARPS_M *WARPS_N * 32, 1) epi_exact_kernel(con
             S.pj[tid] = valid ? (int)sj : -1;
             S.uoff[tid] = valid ? si * p.row_bytes : 0;
             S.voff[tid] = valid ? sj * p.row_bytes : 0;
+            double lu[4], lv[4];
 #pragma unroll
-            for (int q = 0; q < 4; ++q) {
-                S.lutU[q][tid] = valid ? __ldg(p.lutU + si * 4 + q) : 0.0;   // masked pair: w == 0
-                S.lutV[q][tid] = valid ? __ldg(p.lutV + sj * 4 + q) : 0.0;
+            for (int a = 0; a < 4; ++a) {
+                lu[a] = valid ? __ldg(p.lutU + si * 4 + a) : 0.0;       // masked pair: w == 0
+                lv[a] = valid ? __ldg(p.lutV + sj * 4 + a) : 0.0;
             }
+#pragma unroll
+            for (int a = 0; a < 4; ++a)
+#pragma unroll
+                for (int b = 0; b < 4; ++b) S.prod[a * 4 + b][tid] = lu[a] * lv[b];
 #pragma unroll
             for (int q = 0; q < WARPS_M; ++q) { S.red_var[q][tid] = 0.0; S.red_eff[q][tid] = 0.0; }
         }
         __syncthreads();
 
-        const unsigned char *urow = p.bed + S.uoff[ppair];
-        const unsigned char *vrow = p.bed + S.voff[ppair];
-        auto load_codes = [&](long long ks, unsigned &cu, unsigned &cv) {
-            const long long off = ks * (EX_BK / 4) + ppart * (KPER / 4);
-            cu = 0; cv = 0;
-            if (off < p.row_bytes) {
-                if (KPER == 8) {
-                    cu = __ldg(reinterpret_cast<const unsigned short *>(urow + off));
-                    cv = __ldg(reinterpret_cast<const unsigned short *>(vrow + off));
-                } else {
-                    cu = __ldg(urow + off);
-                    cv = __ldg(vrow + off);
-                }
-            }
+        // ---------------- producer side: this thread's pair, 4 individuals per slab ---------------------
+        const unsigned char *urow = p.bed + S.uoff[ppair] + ppart;
+        const unsigned char *vrow = p.bed + S.voff[ppair] + ppart;
+        long long mbp = 0, ksp = 0;                  // (row block, K slab) of the next slab to produce
+        long long sp = 0;                            // its index inside the tile, 0 .. s_total-1
+        unsigned cu, cv;                             // its code bytes (already loaded)
+        auto load_codes = [&](long long ks) {
+            const long long off = ks * (EX_BK / 4);
+            const bool ok = off + ppart < p.row_bytes;
+            cu = ok ? __ldg(urow + off) : 0u;
+            cv = ok ? __ldg(vrow + off) : 0u;
         };
-        auto store_w = [&](int buf, unsigned cu, unsigned cv) {
+        auto produce = [&]() {                       // slab sp of this tile -> ring stage cp % EX_STAGES
+            const int stage = (int)(cp % EX_STAGES);
+            const long long use = cp / EX_STAGES;
+            if (use >= 1) mbar_wait(&S.empty[stage], (unsigned)((use - 1) & 1));
+            if (tid == 0) {
+                fence_proxy_async();                 // the consumers' LDS of this stage precede the async refill
+                mbar_expect_tx(&S.full[stage], SLAB_BYTES);
+                tma_bulk_g2s(S.A[stage], p.packed + sp * EX_SLAB_ELEMS, SLAB_BYTES, &S.full[stage]);
+            }
+            const long long k0 = ksp * EX_BK + ppart * KPER;
 #pragma unroll
             for (int q = 0; q < KPER; ++q) {
-                const int c_u = (cu >> (2 * q)) & 3, c_v = (cv >> (2 * q)) & 3;
-                S.W[buf][ppart * KPER + q][ppair] = S.lutU[c_u][ppair] * S.lutV[c_v][ppair];
+                const unsigned idx = (((cu >> (2 * q)) & 3u) << 2) | ((cv >> (2 * q)) & 3u);
+                // individuals past n (row padding, stray tail bits of the .bed row) must contribute exactly 0
+                S.W[stage][ppart * KPER + q][ppair] = (k0 + q < p.n) ? S.prod[idx][ppair] : 0.0;
             }
+            ++cp; ++sp;
+            if (++ksp == (mbp + 1) * EX_SLABS_PER_BLOCK) { ksp = 0; ++mbp; }
+            if (sp < s_total) load_codes(ksp);       // next slab's codes travel under this slab's MMAs
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&S.full[stage]);     // release: the warp's W stores are visible
         };
+        load_codes(0);
+#pragma unroll 1
+        for (int d = 0; d < EX_AHEAD; ++d)
+            if (sp < s_total) produce();
 
-        unsigned cu, cv;
-        load_codes(0, cu, cv);
-        store_w(0, cu, cv);
-        __syncthreads();
-        int wbuf = 0;
-
+        // ---------------- K loop over the lower block-triangle of A -------------------------------------
         for (long long mb = 0; mb < p.nb; ++mb) {
             double acc[MT][NTL][2];
 #pragma unroll
@@ -242,9 +265,7 @@ __global__ void __launch_bounds__(WARPS_M *WARPS_N * 32, 1) epi_exact_kernel(con
             const long long nks = (mb + 1) * EX_SLABS_PER_BLOCK;
             const long long diag0 = mb * EX_SLABS_PER_BLOCK;
             for (long long ks = 0; ks < nks; ++ks, ++c) {
-                const bool has_next = !(mb == p.nb - 1 && ks == nks - 1);
-                const long long next_ks = (ks + 1 < nks) ? ks + 1 : 0;
-                if (has_next) load_codes(next_ks, cu, cv);
+                if (sp < s_total) produce();
                 if (ks == diag0 && mb > 0) {         // off-diagonal blocks count twice (symmetry)
 #pragma unroll
                     for (int a = 0; a < MT; ++a)
@@ -263,21 +284,14 @@ __global__ void __launch_bounds__(WARPS_M *WARPS_N * 32, 1) epi_exact_kernel(con
                         af[2 * a2] = v.x; af[2 * a2 + 1] = v.y;
                     }
 #pragma unroll
-                    for (int b = 0; b < NTL; ++b) bf[b] = S.W[wbuf][k4 * 4 + t][wn * WN + b * 8 + g];
+                    for (int b = 0; b < NTL; ++b) bf[b] = S.W[stage][k4 * 4 + t][wn * WN + b * 8 + g];
 #pragma unroll
                     for (int a = 0; a < MT; ++a)
 #pragma unroll
                         for (int b = 0; b < NTL; ++b) dmma884(acc[a][b][0], acc[a][b][1], af[a], bf[b]);
                 }
-                if (has_next) store_w(wbuf ^ 1, cu, cv);
-                __syncthreads();
-                if (tid == 0 && c + EX_STAGES < total_c) {
-                    fence_proxy_async();
-                    mbar_expect_tx(&S.full[stage], SLAB_BYTES);
-                    tma_bulk_g2s(S.A[stage], p.packed + ((c + EX_STAGES) % s_total) * EX_SLAB_ELEMS,
-                                 SLAB_BYTES, &S.full[stage]);
-                }
-                wbuf ^= 1;
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&S.empty[stage]);
             }
             // ---------- epilogue of row block mb: var += sum_r w_r * y_r ; eff += sum_r w_r * py_r ----
 #pragma unroll
@@ -292,8 +306,8 @@ __global__ void __launch_bounds__(WARPS_M *WARPS_N * 32, 1) epi_exact_kernel(con
                     for (int a = 0; a < MT; ++a) {
                         const long long r = mb * BLOCK_ROWS + wm * WM + a * 8 + g;
                         if (r < p.n) {
-                            const int c_u = code_at(ur, (int)r), c_v = code_at(vr, (int)r);
-                            const double w = S.lutU[c_u][pair] * S.lutV[c_v][pair];
+                            const int idx = (code_at(ur, (int)r) << 2) | code_at(vr, (int)r);
+                            const double w = S.prod[idx][pair];
                             v += w * acc[a][b][cc];
                             e += w * __ldg(p.py + r);
                         }

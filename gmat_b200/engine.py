@@ -242,6 +242,14 @@ def grm(store, coding, scale, small_val, snp_begin=0, snp_end=None, out=None, ac
     return out
 
 
+def decode_into(store, coding, out, freq_mode=FREQ_NUMPY):
+    """decode the whole store into a caller-owned [m][n] float64 device tensor (no allocation: timing)."""
+    lut = None if coding is None else store.lut(coding, freq_mode)
+    check(lib.gmat_b200_decode(_p(store.bed, "unsigned char *"), store.n, store.m, store.row_bytes,
+                               _p(lut, "double *"), _p(out, "double *"), _stream()), "gmat_b200_decode")
+    return out
+
+
 def fp64_peak(kind=0, iters=20000):
     require_cuda()
     out = ffi.new("double *")

@@ -79,11 +79,12 @@ def main():
         n2, m2 = args.dec_n, args.dec_m
         st2 = engine.GenotypeStore.from_device_payload(synth.device_payload(n2, m2, 12, dev, engine.row_stride(n2)), n2)
         nbytes = m2 * ((n2 + 3) // 4) + 8.0 * m2 * n2
-        t = timed(lambda: st2.decode(None))
+        dec = torch.empty((m2, n2), dtype=torch.float64, device=dev)
+        t = timed(lambda: engine.decode_into(st2, None, dec))
         out["decode_raw"] = {"seconds": t, "gb_per_s": nbytes / t / 1e9}
-        t = timed(lambda: st2.decode(engine.ADD))
+        t = timed(lambda: engine.decode_into(st2, engine.ADD, dec))
         out["decode_add"] = {"seconds": t, "gb_per_s": nbytes / t / 1e9}
-        del st2
+        del st2, dec
     if "grm" in only:
         n2, m2 = args.grm_n, args.grm_m
         st2 = engine.GenotypeStore.from_device_payload(synth.device_payload(n2, m2, 13, dev, engine.row_stride(n2)), n2)
