@@ -64,9 +64,154 @@ __global__ void __launch_bounds__(512) peak_dfma_kernel(double *out, int iters) 
     if (s == 12345.678) out[0] = s;
 }
 
+// DMMA issue model probe: one CTA per SM, `warps` warps, ILP independent accumulator tiles per warp arranged
+// as an (IA x IB) register tile with distinct A / B fragments (like the real kernels), no memory traffic.
+template <int IA, int IB, int MAXT>
+__global__ void __launch_bounds__(MAXT) probe_dmma_kernel(double *out, int iters) {
+    double c[IA][IB][2], a[IA], b[IB];
+#pragma unroll
+    for (int x = 0; x < IA; ++x) {
+        a[x] = 1.0 + (threadIdx.x + x) * 1e-9;
+#pragma unroll
+        for (int y = 0; y < IB; ++y) { c[x][y][0] = 0.0; c[x][y][1] = 0.0; }
+    }
+#pragma unroll
+    for (int y = 0; y < IB; ++y) b[y] = 1.0 - (threadIdx.x + y) * 1e-9;
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+        for (int x = 0; x < IA; ++x)
+#pragma unroll
+            for (int y = 0; y < IB; ++y) dmma884(c[x][y][0], c[x][y][1], a[x], b[y]);
+    }
+    double s = 0.0;
+#pragma unroll
+    for (int x = 0; x < IA; ++x)
+#pragma unroll
+        for (int y = 0; y < IB; ++y) s += c[x][y][0] + c[x][y][1];
+    if (s == 12345.678) out[0] = s;
+}
+
+// Same register tile, but the fragments of every k-step are (re)loaded from shared memory the way the
+// GEMM-shaped kernels do it: A as LDS.128 (two m-tiles per load), B as LDS.64 (BWIDE = 0) or LDS.128
+// (BWIDE = 1, two n-tiles per load).  No barriers, no producers: isolates the LDS + DMMA issue mix.
+template <int IA, int IB, int BWIDE, int MAXT>
+__global__ void __launch_bounds__(MAXT) probe_dmma_lds_kernel(double *out, int iters) {
+    extern __shared__ __align__(16) double sm[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int x = threadIdx.x; x < 4096; x += blockDim.x) sm[x] = 1.0 + x * 1e-9;     // 32 KB
+    __syncthreads();
+    double c[IA][IB][2];
+#pragma unroll
+    for (int x = 0; x < IA; ++x)
+#pragma unroll
+        for (int y = 0; y < IB; ++y) { c[x][y][0] = 0.0; c[x][y][1] = 0.0; }
+    const double2 *A2 = reinterpret_cast<const double2 *>(sm);
+    for (int it = 0; it < iters; ++it) {
+        const int base = ((it + warp) & 7) * 256;                 // moves every iteration: loads cannot be hoisted
+        double a[IA], b[IB];
+#pragma unroll
+        for (int x = 0; x < IA / 2; ++x) {
+            const double2 v = A2[(base + x * 32 + lane) & 2047];
+            a[2 * x] = v.x; a[2 * x + 1] = v.y;
+        }
+        if (BWIDE) {
+#pragma unroll
+            for (int y = 0; y < IB / 2; ++y) {
+                const double2 v = A2[(base + 1024 + y * 32 + lane) & 2047];
+                b[2 * y] = v.x; b[2 * y + 1] = v.y;
+            }
+        } else {
+#pragma unroll
+            for (int y = 0; y < IB; ++y) b[y] = sm[(2 * base + 2048 + y * 32 + lane) & 4095];
+        }
+#pragma unroll
+        for (int x = 0; x < IA; ++x)
+#pragma unroll
+            for (int y = 0; y < IB; ++y) dmma884(c[x][y][0], c[x][y][1], a[x], b[y]);
+    }
+    double s = 0.0;
+#pragma unroll
+    for (int x = 0; x < IA; ++x)
+#pragma unroll
+        for (int y = 0; y < IB; ++y) s += c[x][y][0] + c[x][y][1];
+    if (s == 12345.678) out[0] = s;
+}
+
 }  // namespace gb
 
 using namespace gb;
+
+extern "C" int gmat_b200_dmma_lds_probe(int warps, int shape, int ctas_per_sm, int iters, double *tflops) {
+    GB_CHECK_ARG(tflops != nullptr && iters > 0 && warps >= 1 && warps <= 16 && ctas_per_sm >= 1, "args");
+    void (*kern)(double *, int) = nullptr;
+    int ia = 4, ib = 4;
+    if (shape == 0) kern = probe_dmma_lds_kernel<4, 4, 0, 512>;
+    else if (shape == 1) kern = probe_dmma_lds_kernel<4, 4, 1, 512>;
+    else if (shape == 2) { kern = probe_dmma_lds_kernel<8, 4, 0, 256>; ia = 8; GB_CHECK_ARG(warps <= 8, "warps"); }
+    else if (shape == 3) { kern = probe_dmma_lds_kernel<8, 4, 1, 256>; ia = 8; GB_CHECK_ARG(warps <= 8, "warps"); }
+    else if (shape == 4) { kern = probe_dmma_lds_kernel<4, 2, 1, 512>; ib = 2; }
+    GB_CHECK_ARG(kern != nullptr, "shape");
+    double *d = nullptr;
+    GB_CUDA(cudaMalloc(&d, sizeof(double)));
+    cudaEvent_t e0, e1;
+    GB_CUDA(cudaEventCreate(&e0));
+    GB_CUDA(cudaEventCreate(&e1));
+    const int grid = sm_count() * ctas_per_sm, block = warps * 32;
+    float best = 1e30f;
+    for (int rep = 0; rep < 3; ++rep) {
+        GB_CUDA(cudaEventRecord(e0));
+        kern<<<grid, block, 32768>>>(d, iters);
+        GB_LAUNCH_CHECK();
+        GB_CUDA(cudaEventRecord(e1));
+        GB_CUDA(cudaEventSynchronize(e1));
+        float ms = 0.f;
+        GB_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+        if (rep > 0 && ms < best) best = ms;
+    }
+    const double flop = (double)grid * warps * (double)iters * ia * ib * 512.0;
+    *tflops = flop / (best * 1e-3) / 1e12;
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    cudaFree(d);
+    return GMAT_B200_OK;
+}
+
+extern "C" int gmat_b200_dmma_probe(int warps, int ia, int ib, int ctas_per_sm, int iters, double *tflops) {
+    GB_CHECK_ARG(tflops != nullptr && iters > 0 && warps >= 1 && warps <= 32 && ctas_per_sm >= 1, "args");
+    void (*kern)(double *, int) = nullptr;
+    int maxt = 1024;
+    if (ia == 1 && ib == 1) kern = probe_dmma_kernel<1, 1, 1024>;
+    else if (ia == 2 && ib == 1) kern = probe_dmma_kernel<2, 1, 1024>;
+    else if (ia == 2 && ib == 2) kern = probe_dmma_kernel<2, 2, 1024>;
+    else if (ia == 4 && ib == 2) kern = probe_dmma_kernel<4, 2, 1024>;
+    else if (ia == 4 && ib == 4) { kern = probe_dmma_kernel<4, 4, 512>; maxt = 512; }
+    else if (ia == 8 && ib == 4) { kern = probe_dmma_kernel<8, 4, 256>; maxt = 256; }
+    GB_CHECK_ARG(kern != nullptr, "unsupported (ia, ib)");
+    GB_CHECK_ARG(warps * 32 <= maxt, "too many warps for this register tile");
+    double *d = nullptr;
+    GB_CUDA(cudaMalloc(&d, sizeof(double)));
+    cudaEvent_t e0, e1;
+    GB_CUDA(cudaEventCreate(&e0));
+    GB_CUDA(cudaEventCreate(&e1));
+    const int grid = sm_count() * ctas_per_sm, block = warps * 32;
+    float best = 1e30f;
+    for (int rep = 0; rep < 3; ++rep) {
+        GB_CUDA(cudaEventRecord(e0));
+        kern<<<grid, block>>>(d, iters);
+        GB_LAUNCH_CHECK();
+        GB_CUDA(cudaEventRecord(e1));
+        GB_CUDA(cudaEventSynchronize(e1));
+        float ms = 0.f;
+        GB_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+        if (rep > 0 && ms < best) best = ms;
+    }
+    const double flop = (double)grid * warps * (double)iters * ia * ib * 512.0;
+    *tflops = flop / (best * 1e-3) / 1e12;
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    cudaFree(d);
+    return GMAT_B200_OK;
+}
 
 extern "C" int gmat_b200_version(void) { return 100; }
 extern "C" const char *gmat_b200_last_error(void) { return g_err; }

@@ -105,6 +105,16 @@ __device__ __forceinline__ void mbar_wait(uint64_t *bar, unsigned parity) {
     while (!mbar_try_wait(bar, parity)) {
     }
 }
+// warp-collective wait: lane 0 polls, the rest of the warp joins at __syncwarp (which orders memory among the
+// lanes, so the acquire of lane 0 covers the warp).  32 lanes polling the same barrier word would cost 32
+// serialized shared-memory transactions per poll.
+__device__ __forceinline__ void mbar_wait_warp(uint64_t *bar, unsigned parity) {
+    if ((threadIdx.x & 31) == 0) {
+        while (!mbar_try_wait(bar, parity)) {
+        }
+    }
+    __syncwarp();
+}
 // plain arrive (release semantics at CTA scope): one pending count of the current phase
 __device__ __forceinline__ void mbar_arrive(uint64_t *bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];\n" ::"r"(smem_u32(bar)) : "memory");

@@ -73,6 +73,12 @@ long long   gmat_b200_kernel_launches(void);       /* kernels launched by this l
 /* FP64 issue-rate microbenchmarks (used by bench.py for the roofline denominator).
  * kind 0: DMMA (mma.sync m8n8k4 f64) ; kind 1: DFMA.  Writes TFLOP/s.  */
 int gmat_b200_fp64_peak(int kind, int iters, double *tflops);
+/* DMMA issue-model probe: `ctas_per_sm` CTAs of `warps` warps per SM, each warp an (ia x ib) register tile of
+ * independent m8n8k4 accumulators with distinct A/B fragments, no memory traffic.  Writes TFLOP/s.           */
+int gmat_b200_dmma_probe(int warps, int ia, int ib, int ctas_per_sm, int iters, double *tflops);
+/* same, with every k-step's fragments re-loaded from shared memory (shape 0: 4x4 tile, B as LDS.64; 1: 4x4, B as
+ * LDS.128; 2: 8x4, LDS.64; 3: 8x4, LDS.128; 4: 4x2, LDS.128): the LDS + DMMA issue mix without any barrier.   */
+int gmat_b200_dmma_lds_probe(int warps, int shape, int ctas_per_sm, int iters, double *tflops);
 
 /* ------------------------------------------------------------------ (1) drop-in symbols ---- */
 /* gmat/process_plink/_read_plink_bed.c:5 -- marker_mat is HOST double[num_snp][num_id]        */
@@ -136,6 +142,8 @@ int gmat_b200_epi_eff(const unsigned char *bed_dev, long long n, long long m, lo
 /* Z'PZ re-tiled for the exact kernel: lower block-triangle, 128-row blocks, DMMA fragment order.
  * gmat_b200_pvp_packed_elems(n) doubles are needed.                                            */
 long long gmat_b200_pvp_packed_elems(long long n);
+/* tile shape of the exact kernel (rows of A per block, pairs per tile, resident CTAs per SM); informational */
+int gmat_b200_exact_config(int *bm, int *bn, int *ctas_per_sm);
 int gmat_b200_pack_pvp(const double *pvp_dev /* [n][n] row-major, symmetric */, long long n,
                        double *packed_dev, void *stream);
 
