@@ -28,9 +28,12 @@ VAR_COM = [0.35, 0.10, 0.55]            # [A, A*A, residual]; fixed (throughput 
 P_CUT = 1.0e-5
 BATCH = 256                             # first-SNPs per step
 METRIC = "snp_pairs_per_sec_remma_epiAA_exact"
+# dram__bytes_read.sum + dram__bytes_write.sum of one exact-kernel launch of this step, from the committed
+# ncu --set full capture (profiles/); None until a capture of the current kernel exists
+EXACT_TRAFFIC_BYTES = None
 CONFIG = {"workload": "remma_epiAA exact test, synthetic n=%d x m=%d, GRMs [A, A*A] (BASELINE configs[2])"
                       % (N_ID, N_SNP),
-          "step": "one batch of %d evenly spread first-SNPs, all j>i (~2.5e6 pairs) per rank" % BATCH,
+          "step": "one batch of %d first-SNPs (32 evenly spread blocks of 8), all j>i (~2.5e6 pairs) per rank" % BATCH,
           "p_cut": P_CUT, "l2": "flushed (256 MB write) between timed iterations"}
 
 
@@ -40,9 +43,16 @@ def f_exact(n):
 
 
 def batch_first_snps(m, rank, world, batch=BATCH):
-    """Evenly spread first-SNPs (every ceil(m/batch)-th), offset per rank so ranks take disjoint batches."""
-    stride = max(1, (m - 1) // batch)
-    lst = [(q * stride + rank * (stride // max(world, 1))) % (m - 1) for q in range(batch)]
+    """``batch`` first-SNPs as contiguous blocks of 8 (one I-block of the scan tiling -- what a full scan
+    hands the kernel), the blocks spread evenly over [0, m-1) and offset per rank so ranks take disjoint batches."""
+    blk = 8 if batch >= 8 else 1
+    nblk = max(1, batch // blk)
+    stride = max(blk, (m - 1 - blk) // nblk)
+    off = (rank * (stride // max(world, 1))) // blk * blk
+    lst = []
+    for q in range(nblk):
+        s0 = (q * stride + off) % (m - 1 - blk)
+        lst.extend(range(s0, s0 + blk))
     return sorted(set(lst))
 
 
@@ -262,9 +272,13 @@ def run_gpu(args):
     if rank == 0:
         n = N_ID
         achieved = (pairs_rank * f_exact(n)) / (ms * 1e-3) / 1e12          # per GPU, algorithmic flops
-        npad = (n + 127) // 128 * 128
-        nb = npad // 128
-        issued = pairs_rank * 2.0 * (128 * 128 * nb * (nb + 1) / 2) / (ms * 1e-3) / 1e12
+        from gmat_b200._ffi import ffi
+        cfg = ffi.new("int[3]")
+        lib.gmat_b200_exact_config(cfg, cfg + 1, cfg + 2)
+        bm, bn = int(cfg[0]), int(cfg[1])
+        nb = (n + bm - 1) // bm
+        # DMMA flop the kernel issues per pair: lower block-triangle of bm x bm blocks (diagonal blocks in full)
+        issued = pairs_rank * 2.0 * (bm * bm * nb * (nb + 1) / 2) / (ms * 1e-3) / 1e12
         line = {
             "metric": METRIC, "value": value, "unit": "pairs/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
@@ -275,7 +289,7 @@ def run_gpu(args):
                     "what": "gmat_b200.remma.remma_epiAA(pheno_file, bed_file, gmat_lst, var_com, snp_lst_0=1024 "
                             "first-SNPs): phenotype parse + host preamble + .bed read + H2D + scan + D2H + file"},
             "roofline": {"bound": "tensor", "achieved": achieved, "unit": "TFLOP/s", "peak": None, "frac": None,
-                         "traffic": None, "kernel": "epi_exact_kernel<4,4,false>",
+                         "traffic": EXACT_TRAFFIC_BYTES, "kernel": "epi_exact_rb_kernel<%d,..,scan>" % bn,
                          "flops_per_pair_algorithmic": f_exact(n), "issued_tflops": issued},
         }
         if world == 1:

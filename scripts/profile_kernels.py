@@ -63,7 +63,11 @@ def main():
     if "exact" in only:
         packed = engine.pack_pvp(pvp)
         lut = store.lut(engine.ADD)
-        il = np.linspace(0, m - 2, args.first).astype(np.int64)
+        # contiguous blocks of 8 first-SNPs (one I-block of the scan tiling), blocks spread over the range --
+        # what a full scan looks like to the kernel; isolated first-SNPs would leave 7/8 of a tile's rows masked
+        nblk = max(1, args.first // 8)
+        starts = np.linspace(0, m - 10, nblk).astype(np.int64)
+        il = np.unique((starts[:, None] + np.arange(8)[None, :]).ravel())
         pairs = int(np.sum(m - 1 - il))
         t = timed(lambda: engine.epi_exact_scan(store, lut, lut, py, packed, il, engine.PAIRS_UPPER, 30.0))
         out["exact"] = {"seconds": t, "pairs": pairs, "pairs_per_s": pairs / t,
