@@ -29,8 +29,9 @@ P_CUT = 1.0e-5
 BATCH = 256                             # first-SNPs per step
 METRIC = "snp_pairs_per_sec_remma_epiAA_exact"
 # dram__bytes_read.sum + dram__bytes_write.sum of one exact-kernel launch of this step, from the committed
-# ncu --set full capture (profiles/); None until a capture of the current kernel exists
-EXACT_TRAFFIC_BYTES = None
+# ncu --set full capture (profiles/r01_kernels_v3.md: 28.87 MB read + ~0 written = packed Z'PZ 17.8 MB + .bed
+# 10 MB + LUTs, read once; the capture ran 128 first-SNPs of the same data shape, the compulsory bytes are the same)
+EXACT_TRAFFIC_BYTES = 28.9e6
 CONFIG = {"workload": "remma_epiAA exact test, synthetic n=%d x m=%d, GRMs [A, A*A] (BASELINE configs[2])"
                       % (N_ID, N_SNP),
           "step": "one batch of %d first-SNPs (32 evenly spread blocks of 8), all j>i (~2.5e6 pairs) per rank" % BATCH,

@@ -6,16 +6,26 @@
 //   agmat:    centring, kin = dot/scale, diag inflation ... gmat/gmatrix/gmatrix.py:53-66
 //   dgmat_as: dominance coding and scale .................. gmat/gmatrix/gmatrix.py:116-130
 //
-// K dimension = SNPs, in slabs of 16: for a tile (mi, ni) a slab needs 16 x 32 B of codes per operand
-// (SNP-major rows, 128 individuals = 32 bytes), decoded into shared memory [snp][ind] (+4 padding =>
-// conflict-free fragment loads for both operands), double buffered under the MMAs.
+// B200 design (same recipe as the exact-test kernel, exact.cu):
+//  * FP64 tensor path = warp-level DMMA.8x8x4; 8 consumer warps (2 x 4, warp tile 64 x 32 individuals = 8 x 4
+//    accumulator tiles) + 4 producer warps whose registers go to the consumers (setmaxnreg).
+//  * K dimension = SNPs, in stages of 64.  A stage is 6 KB of shared memory: the 2-bit codes of the tile's 128
+//    row individuals and 128 column individuals for 64 SNPs (64 x 32 B each, straight from the SNP-major .bed
+//    rows by cp.async.bulk -- no decode pass, no doubles in shared memory) and the 64 SNPs' 4-entry value
+//    tables (2 KB, one bulk copy).  full[s] completes on the TMA byte count, empty[s] on one arrival per
+//    consumer warp; 4-deep ring, no CTA-wide barrier anywhere in the K loop.
+//  * Operand fragments are built in registers: lane (g, t) owns SNP 4*k4 + t of the step, reads its 16 B + 8 B
+//    of codes (broadcast LDS.128 / LDS.64) and fetches each of its 8 + 4 fragment elements with one LDS.64
+//    from that SNP's value table (the 4 SNPs of a step share one 128 B line: conflict-free).
 #include "common.cuh"
 
 namespace gb {
 
-constexpr int GR_T = 128;
-constexpr int GR_BK = 16;
-constexpr int GR_LD = GR_T + 4;
+constexpr int GR_T = 128;           // output tile edge (individuals)
+constexpr int GR_GS = 64;           // SNPs per ring stage
+constexpr int GR_NS = 4;            // ring depth
+constexpr int GR_CW = 8;            // consumer warps (2 x 4)
+constexpr int GR_PW = 4;            // producer warps (one per SM sub-partition; only the first one works)
 
 struct GrmParams {
     const unsigned char *bed;
@@ -29,116 +39,133 @@ struct GrmParams {
 };
 
 struct GrmSmem {
-    double X[2][2][GR_BK][GR_LD];      // [buffer][operand: rows(mi) / cols(ni)][snp][individual]
-    double lut[3][GR_BK][4];           // LUT slabs, written two slabs ahead
+    unsigned char cA[GR_NS][GR_GS][32];            // codes of the tile's row individuals, one 32 B piece per SNP
+    unsigned char cB[GR_NS][GR_GS][32];            // codes of the tile's column individuals
+    double lut[GR_NS][GR_GS][4];                   // value table of each SNP of the stage
+    uint64_t full[GR_NS], empty[GR_NS];
 };
 
-template <int WARPS_M, int WARPS_N>
-__global__ void __launch_bounds__(WARPS_M *WARPS_N * 32, 1) grm_kernel(const GrmParams p) {
-    constexpr int NT = WARPS_M * WARPS_N * 32;
-    static_assert(NT == 512, "producer mapping assumes 16 warps");
-    constexpr int WM = GR_T / WARPS_M, WN = GR_T / WARPS_N;
-    constexpr int MT = WM / 8, NTL = WN / 8;
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    GrmSmem &S = *reinterpret_cast<GrmSmem *>(smem_raw);
+__device__ __forceinline__ void grm_tile_of(long long tile, long long &mi, long long &ni) {
+    mi = (long long)((sqrt(8.0 * (double)tile + 1.0) - 1.0) * 0.5);      // tile -> (mi, ni), ni <= mi
+    while (mi * (mi + 1) / 2 > tile) --mi;
+    while ((mi + 1) * (mi + 2) / 2 <= tile) ++mi;
+    ni = tile - mi * (mi + 1) / 2;
+}
 
+__global__ void __launch_bounds__((GR_CW + GR_PW) * 32, 1) grm_kernel(const GrmParams p) {
+    constexpr int MT = 8, NTL = 4;                   // warp tile 64 x 32
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    GrmSmem &S = *reinterpret_cast<GrmSmem *>(smem_raw);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int g = lane >> 2, t = lane & 3;
-    const int wm = warp / WARPS_N, wn = warp % WARPS_N;
-    // producer role: operand = warp/8, two SNPs of the slab per warp, lane -> individuals lane + 32q
-    const int pop = warp >> 3;
-    const int ps0 = (warp & 7) * 2;
-    const long long nslab = (p.snp_end - p.snp_begin + GR_BK - 1) / GR_BK;
+    const long long nstage = (p.snp_end - p.snp_begin + GR_GS - 1) / GR_GS;
     const long long ntiles = p.nblk * (p.nblk + 1) / 2;
 
+    if (tid == 0) {
+        for (int s = 0; s < GR_NS; ++s) {
+            mbar_init(&S.full[s], 1);                // the expect_tx arrival of producer lane 0
+            mbar_init(&S.empty[s], GR_CW);
+        }
+        mbar_fence_init();
+    }
+    __syncthreads();
+
+    if (warp >= GR_CW) {
+        // =============================== producer ========================================================
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 40;\n");
+        if (warp != GR_CW) return;
+        int stage = 0;
+        unsigned use_odd = 0;
+        bool first_pass = true;
+        for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+            long long mi, ni;
+            grm_tile_of(tile, mi, ni);
+            // bytes of a row piece: 32, or what is left of the (16 B padded) row for the last block
+            const long long offA = mi * (GR_T / 4), offB = ni * (GR_T / 4);
+            const unsigned bytesA = (unsigned)((p.row_bytes - offA) < 32 ? (p.row_bytes - offA) : 32);
+            const unsigned bytesB = (unsigned)((p.row_bytes - offB) < 32 ? (p.row_bytes - offB) : 32);
+            for (long long st = 0; st < nstage; ++st) {
+                if (!first_pass) mbar_wait(&S.empty[stage], use_odd ^ 1u);
+                fence_proxy_async();                 // consumers' LDS of this stage precede the async refill
+                const long long s0 = p.snp_begin + st * GR_GS;
+                const long long left = p.snp_end - s0;
+                const int nvalid = left < GR_GS ? (int)left : GR_GS;
+                if (lane == 0) {
+                    // table rows of SNPs past the end are zero (plain stores, released by the arrive below)
+                    for (int r = nvalid; r < GR_GS; ++r)
+#pragma unroll
+                        for (int c = 0; c < 4; ++c) S.lut[stage][r][c] = 0.0;
+                    mbar_expect_tx(&S.full[stage], (unsigned)GR_GS * (bytesA + bytesB) + (unsigned)nvalid * 32u);
+                    tma_bulk_g2s(S.lut[stage], p.lut + s0 * 4, (unsigned)nvalid * 32u, &S.full[stage]);
+                }
+                __syncwarp();
+#pragma unroll
+                for (int h = 0; h < GR_GS / 32; ++h) {
+                    const int r = h * 32 + lane;
+                    // SNPs past the end re-read the last valid row; their value table is zero
+                    const long long snp = s0 + (r < nvalid ? r : nvalid - 1);
+                    const unsigned char *row = p.bed + snp * p.row_bytes;
+                    tma_bulk_g2s(S.cA[stage][r], row + offA, bytesA, &S.full[stage]);
+                    tma_bulk_g2s(S.cB[stage][r], row + offB, bytesB, &S.full[stage]);
+                }
+                if (++stage == GR_NS) { stage = 0; use_odd ^= 1u; first_pass = false; }
+            }
+        }
+        return;
+    }
+
+    // =================================== consumer warps =================================================
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 232;\n");
+    const int g = lane >> 2, t = lane & 3;
+    const int wm = warp >> 2, wn = warp & 3;
+    const int sh0 = 2 * g, sh1 = 16 + 2 * g;
+    int stage = 0;
+    unsigned fphase = 0;
     for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-        // tile -> (mi, ni), ni <= mi
-        long long mi = (long long)((sqrt(8.0 * (double)tile + 1.0) - 1.0) * 0.5);
-        while (mi * (mi + 1) / 2 > tile) --mi;
-        while ((mi + 1) * (mi + 2) / 2 <= tile) ++mi;
-        const long long ni = tile - mi * (mi + 1) / 2;
-        const long long blk = pop == 0 ? mi : ni;
-        __syncthreads();
-
-        uint32_t words[2][4];
-        auto load_codes = [&](long long slab) {
-#pragma unroll
-            for (int s2 = 0; s2 < 2; ++s2) {
-                const long long snp = p.snp_begin + slab * GR_BK + ps0 + s2;
-#pragma unroll
-                for (int q = 0; q < 4; ++q) {
-                    const long long off = blk * (GR_T / 4) + (long long)((lane >> 4) + 2 * q) * 4;
-                    uint32_t w = 0;
-                    if (snp < p.snp_end && off < p.row_bytes)
-                        w = __ldg(reinterpret_cast<const uint32_t *>(p.bed + snp * p.row_bytes + off));
-                    words[s2][q] = w;
-                }
-            }
-        };
-        auto load_lut = [&](long long slab) -> double {     // threads 0..63: one LUT entry each
-            const long long snp = p.snp_begin + slab * GR_BK + (tid >> 2);
-            return (tid < 64 && snp < p.snp_end) ? __ldg(p.lut + snp * 4 + (tid & 3)) : 0.0;
-        };
-        auto store_lut = [&](long long slab, double v) {
-            if (tid < 64) S.lut[slab % 3][tid >> 2][tid & 3] = v;
-        };
-        auto store_slab = [&](int buf, long long slab) {
-            const int sh = 2 * (lane & 15);
-#pragma unroll
-            for (int s2 = 0; s2 < 2; ++s2) {
-#pragma unroll
-                for (int q = 0; q < 4; ++q) {
-                    const int c = (words[s2][q] >> sh) & 3;
-                    S.X[buf][pop][ps0 + s2][lane + 32 * q] = S.lut[slab % 3][ps0 + s2][c];
-                }
-            }
-        };
-
+        long long mi, ni;
+        grm_tile_of(tile, mi, ni);
         double acc[MT][NTL][2];
 #pragma unroll
         for (int a = 0; a < MT; ++a)
 #pragma unroll
             for (int b = 0; b < NTL; ++b) acc[a][b][0] = acc[a][b][1] = 0.0;
 
-        // prologue: LUT slabs 0 and 1, operand slab 0
-        store_lut(0, load_lut(0));
-        if (nslab > 1) store_lut(1, load_lut(1));
-        load_codes(0);
-        __syncthreads();
-        store_slab(0, 0);
-        __syncthreads();
-        for (long long s = 0; s < nslab; ++s) {
-            const int buf = (int)(s & 1);
-            const bool more = s + 1 < nslab;
-            double lutv = 0.0;
-            if (more) load_codes(s + 1);
-            if (s + 2 < nslab) lutv = load_lut(s + 2);
-#pragma unroll
-            for (int ks = 0; ks < GR_BK / 4; ++ks) {
+        for (long long st = 0; st < nstage; ++st) {
+            mbar_wait(&S.full[stage], fphase);
+#pragma unroll 4
+            for (int k4 = 0; k4 < GR_GS / 4; ++k4) {
+                const int r = k4 * 4 + t;            // this lane's SNP of the step
+                const uint4 wa = *reinterpret_cast<const uint4 *>(&S.cA[stage][r][wm * 16]);
+                const uint2 wb = *reinterpret_cast<const uint2 *>(&S.cB[stage][r][wn * 8]);
+                const char *lb = reinterpret_cast<const char *>(&S.lut[stage][r][0]);
+                const unsigned wav[4] = {wa.x, wa.y, wa.z, wa.w};
+                const unsigned wbv[2] = {wb.x, wb.y};
                 double af[MT], bf[NTL];
+                // individual 8a + g of the warp's rows: code bits 16*(a&1) + 2g of word a >> 1
 #pragma unroll
-                for (int a = 0; a < MT; ++a) af[a] = S.X[buf][0][ks * 4 + t][wm * WM + a * 8 + g];
+                for (int a = 0; a < MT; ++a)
+                    af[a] = *reinterpret_cast<const double *>(lb + (((wav[a >> 1] >> ((a & 1) ? sh1 : sh0)) & 3u) << 3));
 #pragma unroll
-                for (int b = 0; b < NTL; ++b) bf[b] = S.X[buf][1][ks * 4 + t][wn * WN + b * 8 + g];
+                for (int b = 0; b < NTL; ++b)
+                    bf[b] = *reinterpret_cast<const double *>(lb + (((wbv[b >> 1] >> ((b & 1) ? sh1 : sh0)) & 3u) << 3));
 #pragma unroll
                 for (int a = 0; a < MT; ++a)
 #pragma unroll
                     for (int b = 0; b < NTL; ++b) dmma884(acc[a][b][0], acc[a][b][1], af[a], bf[b]);
             }
-            if (more) store_slab(buf ^ 1, s + 1);       // reads lut slab s+1 (stored one iteration ago)
-            if (s + 2 < nslab) store_lut(s + 2, lutv);
-            __syncthreads();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&S.empty[stage]);
+            if (++stage == GR_NS) { stage = 0; fphase ^= 1u; }
         }
 
         // ---- epilogue ---------------------------------------------------------------------------
 #pragma unroll
         for (int a = 0; a < MT; ++a) {
-            const long long r = mi * GR_T + wm * WM + a * 8 + g;
+            const long long r = mi * GR_T + wm * 64 + a * 8 + g;
 #pragma unroll
             for (int b = 0; b < NTL; ++b) {
 #pragma unroll
                 for (int c = 0; c < 2; ++c) {
-                    const long long col = ni * GR_T + wn * WN + b * 8 + 2 * t + c;
+                    const long long col = ni * GR_T + wn * 32 + b * 8 + 2 * t + c;
                     if (r < p.n && col < p.n && (mi != ni || col <= r)) {
                         if (p.accumulate) {
                             p.K[r * p.n + col] += acc[a][b][c];
@@ -174,12 +201,13 @@ extern "C" int gmat_b200_grm(const unsigned char *bed_dev, long long n, long lon
     p.snp_begin = snp_begin; p.snp_end = snp_end; p.scale = scale; p.small_val = small_val;
     p.accumulate = accumulate; p.K = K_dev;
     p.nblk = (n + GR_T - 1) / GR_T;
-    auto kern = grm_kernel<4, 4>;
+    if (snp_begin == snp_end && accumulate) return GMAT_B200_OK;
+    auto kern = grm_kernel;
     const size_t smem = sizeof(GrmSmem);
     GB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     long long grid = p.nblk * (p.nblk + 1) / 2;
     if (grid > sm_count()) grid = sm_count();
-    kern<<<(unsigned)grid, 512, smem, (cudaStream_t)stream>>>(p);
+    kern<<<(unsigned)grid, (GR_CW + GR_PW) * 32, smem, (cudaStream_t)stream>>>(p);
     GB_LAUNCH_CHECK();
     return GMAT_B200_OK;
 }
