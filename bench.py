@@ -248,12 +248,17 @@ def run_gpu(args):
     barrier()
     launches = lib.gmat_b200_kernel_launches() - launches0
     clocks = sampler.result()
-    ms = reduce(sum(a.elapsed_time(b) for a, b in ev) / args.steps, dist.ReduceOp.MAX if world > 1 else None)
+    ms_local = sum(a.elapsed_time(b) for a, b in ev) / args.steps
+    print("[bench] rank %d: %.1f ms/step, per-step %s" % (rank, ms_local, [round(a.elapsed_time(b), 1) for a, b in ev]),
+          file=sys.stderr)
+    ms = reduce(ms_local, dist.ReduceOp.MAX if world > 1 else None)
     total_pairs = reduce(float(pairs_rank), dist.ReduceOp.SUM if world > 1 else None)
     value = total_pairs / (ms * 1e-3)
 
     # ------------- e2e: the public drop-in call, HOST buffers, files in / file out, copies inside -------------
-    e2e_lst = batch_first_snps(N_SNP, rank, world, 1024)
+    # every rank makes the SAME call (1024 first-SNPs per GPU); the front-end shards the list over the ranks
+    # and gathers the hits to rank 0 (gmat_b200/remma/parallel.py), which writes the file
+    e2e_lst = batch_first_snps(N_SNP, 0, 1, 1024 * world)
     e2e_pairs = n_pairs(e2e_lst, N_SNP)
     out_file = os.path.join(workdir, "epiAA_e2e")
     e2e_t = []
@@ -265,8 +270,8 @@ def run_gpu(args):
         if it:
             e2e_t.append(time.perf_counter() - t0)
     e2e_s = reduce(float(np.mean(e2e_t)), dist.ReduceOp.MAX if world > 1 else None)
-    e2e_value = reduce(float(e2e_pairs), dist.ReduceOp.SUM if world > 1 else None) / e2e_s
-    h2d = store.h2d_bytes + model.h2d_bytes + len(e2e_lst) * 8
+    e2e_value = float(e2e_pairs) / e2e_s
+    h2d = world * (store.h2d_bytes + model.h2d_bytes) + len(e2e_lst) * 8      # every rank uploads its own copy
     d2h = 8 + 32 * (len(hits) if hits is not None else 0)
 
     line = None
@@ -288,7 +293,7 @@ def run_gpu(args):
             "e2e": {"value": e2e_value, "unit": "pairs/s", "h2d_bytes_per_step": int(h2d),
                     "d2h_bytes_per_step": int(d2h),
                     "what": "gmat_b200.remma.remma_epiAA(pheno_file, bed_file, gmat_lst, var_com, snp_lst_0=1024 "
-                            "first-SNPs): phenotype parse + host preamble + .bed read + H2D + scan + D2H + file"},
+                            "first-SNPs per GPU): phenotype parse + host preamble + .bed read + H2D + scan + D2H + file"},
             "roofline": {"bound": "tensor", "achieved": achieved, "unit": "TFLOP/s", "peak": None, "frac": None,
                          "traffic": EXACT_TRAFFIC_BYTES, "kernel": "epi_exact_rb_kernel<%d,..,scan>" % bn,
                          "flops_per_pair_algorithmic": f_exact(n), "issued_tflops": issued},

@@ -137,9 +137,81 @@ __global__ void __launch_bounds__(MAXT) probe_dmma_lds_kernel(double *out, int i
     if (s == 12345.678) out[0] = s;
 }
 
+// DMMA + DMUL mix probe: an 8 x 4 accumulator tile (32 DMMAs per step) plus NMUL independent DMULs per step,
+// MODE 0: the DMULs grouped before the DMMAs and independent of them; MODE 1: spread between the DMMAs, independent;
+// MODE 2: grouped, and the B fragments of the step ARE the DMUL results (dependent, like py folding in eff.cu).
+template <int NMUL, int MODE>
+__global__ void __launch_bounds__(256) probe_dmma_dmul_kernel(double *out, int iters) {
+    double c[8][4][2], a[8], b[4], m[4];
+#pragma unroll
+    for (int x = 0; x < 8; ++x) {
+        a[x] = 1.0 + (threadIdx.x + x) * 1e-9;
+#pragma unroll
+        for (int y = 0; y < 4; ++y) { c[x][y][0] = 0.0; c[x][y][1] = 0.0; }
+    }
+#pragma unroll
+    for (int y = 0; y < 4; ++y) { b[y] = 1.0 - (threadIdx.x + y) * 1e-9; m[y] = 1.0 + y * 1e-12; }
+    const double f = 1.0 + 1e-15 * (threadIdx.x & 1);
+    for (int it = 0; it < iters; ++it) {
+        if (MODE == 0 || MODE == 2) {
+#pragma unroll
+            for (int q = 0; q < NMUL; ++q) asm volatile("mul.f64 %0, %0, %1;" : "+d"(m[q & 3]) : "d"(f));
+        }
+#pragma unroll
+        for (int x = 0; x < 8; ++x)
+#pragma unroll
+            for (int y = 0; y < 4; ++y) {
+                if (MODE == 1 && y == 0 && x < NMUL) asm volatile("mul.f64 %0, %0, %1;" : "+d"(m[x & 3]) : "d"(f));
+                dmma884(c[x][y][0], c[x][y][1], a[x], MODE == 2 ? m[y] : b[y]);
+            }
+    }
+    double s = m[0] + m[1] + m[2] + m[3];
+#pragma unroll
+    for (int x = 0; x < 8; ++x)
+#pragma unroll
+        for (int y = 0; y < 4; ++y) s += c[x][y][0] + c[x][y][1];
+    if (s == 12345.678) out[0] = s;
+}
+
 }  // namespace gb
 
 using namespace gb;
+
+extern "C" int gmat_b200_dmma_dmul_probe(int warps, int nmul, int mode, int iters, double *tflops) {
+    GB_CHECK_ARG(tflops != nullptr && iters > 0 && warps >= 1 && warps <= 8, "args");
+    void (*kern)(double *, int) = nullptr;
+    if (nmul == 0) kern = probe_dmma_dmul_kernel<0, 0>;
+    else if (nmul == 4 && mode == 0) kern = probe_dmma_dmul_kernel<4, 0>;
+    else if (nmul == 4 && mode == 1) kern = probe_dmma_dmul_kernel<4, 1>;
+    else if (nmul == 4 && mode == 2) kern = probe_dmma_dmul_kernel<4, 2>;
+    else if (nmul == 8 && mode == 0) kern = probe_dmma_dmul_kernel<8, 0>;
+    else if (nmul == 8 && mode == 1) kern = probe_dmma_dmul_kernel<8, 1>;
+    else if (nmul == 1 && mode == 0) kern = probe_dmma_dmul_kernel<1, 0>;
+    GB_CHECK_ARG(kern != nullptr, "unsupported (nmul, mode)");
+    double *d = nullptr;
+    GB_CUDA(cudaMalloc(&d, sizeof(double)));
+    cudaEvent_t e0, e1;
+    GB_CUDA(cudaEventCreate(&e0));
+    GB_CUDA(cudaEventCreate(&e1));
+    const int grid = sm_count(), block = warps * 32;
+    float best = 1e30f;
+    for (int rep = 0; rep < 3; ++rep) {
+        GB_CUDA(cudaEventRecord(e0));
+        kern<<<grid, block>>>(d, iters);
+        GB_LAUNCH_CHECK();
+        GB_CUDA(cudaEventRecord(e1));
+        GB_CUDA(cudaEventSynchronize(e1));
+        float ms = 0.f;
+        GB_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+        if (rep > 0 && ms < best) best = ms;
+    }
+    *tflops = (double)grid * warps * (double)iters * 32 * 512.0 / (best * 1e-3) / 1e12;      // DMMA flop only
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    cudaFree(d);
+    return GMAT_B200_OK;
+}
+
 
 extern "C" int gmat_b200_dmma_lds_probe(int warps, int shape, int ctas_per_sm, int iters, double *tflops) {
     GB_CHECK_ARG(tflops != nullptr && iters > 0 && warps >= 1 && warps <= 16 && ctas_per_sm >= 1, "args");

@@ -79,6 +79,9 @@ int gmat_b200_dmma_probe(int warps, int ia, int ib, int ctas_per_sm, int iters, 
 /* same, with every k-step's fragments re-loaded from shared memory (shape 0: 4x4 tile, B as LDS.64; 1: 4x4, B as
  * LDS.128; 2: 8x4, LDS.64; 3: 8x4, LDS.128; 4: 4x2, LDS.128): the LDS + DMMA issue mix without any barrier.   */
 int gmat_b200_dmma_lds_probe(int warps, int shape, int ctas_per_sm, int iters, double *tflops);
+/* 8x4 tile (32 DMMAs per step) + nmul DMULs per step; mode 0 grouped/independent, 1 spread/independent,
+ * 2 grouped and feeding the step's B fragments.  Writes the DMMA-only TFLOP/s.                               */
+int gmat_b200_dmma_dmul_probe(int warps, int nmul, int mode, int iters, double *tflops);
 
 /* ------------------------------------------------------------------ (1) drop-in symbols ---- */
 /* gmat/process_plink/_read_plink_bed.c:5 -- marker_mat is HOST double[num_snp][num_id]        */
