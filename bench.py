@@ -27,6 +27,7 @@ N_ID, N_SNP, SEED = 2000, 20000, 20201013 + 2
 VAR_COM = [0.35, 0.10, 0.55]            # [A, A*A, residual]; fixed (throughput does not depend on it)
 P_CUT = 1.0e-5
 BATCH = 256                             # first-SNPs per step
+E2E_FIRST = 4096                        # first-SNPs per GPU of the end-to-end call (~3.6e7 pairs)
 METRIC = "snp_pairs_per_sec_remma_epiAA_exact"
 # dram__bytes_read.sum + dram__bytes_write.sum of one exact-kernel launch of this step, from the committed
 # ncu --set full capture (profiles/r01_kernels_v3.md: 28.87 MB read + ~0 written = packed Z'PZ 17.8 MB + .bed
@@ -256,9 +257,9 @@ def run_gpu(args):
     value = total_pairs / (ms * 1e-3)
 
     # ------------- e2e: the public drop-in call, HOST buffers, files in / file out, copies inside -------------
-    # every rank makes the SAME call (1024 first-SNPs per GPU); the front-end shards the list over the ranks
+    # every rank makes the SAME call (E2E_FIRST first-SNPs per GPU); the front-end shards the list over the ranks
     # and gathers the hits to rank 0 (gmat_b200/remma/parallel.py), which writes the file
-    e2e_lst = batch_first_snps(N_SNP, 0, 1, 1024 * world)
+    e2e_lst = batch_first_snps(N_SNP, 0, 1, E2E_FIRST * world)
     e2e_pairs = n_pairs(e2e_lst, N_SNP)
     out_file = os.path.join(workdir, "epiAA_e2e")
     e2e_t = []
@@ -292,20 +293,21 @@ def run_gpu(args):
             "clocks": clocks, "gpu_launches": int(launches),
             "e2e": {"value": e2e_value, "unit": "pairs/s", "h2d_bytes_per_step": int(h2d),
                     "d2h_bytes_per_step": int(d2h),
-                    "what": "gmat_b200.remma.remma_epiAA(pheno_file, bed_file, gmat_lst, var_com, snp_lst_0=1024 "
-                            "first-SNPs per GPU): phenotype parse + host preamble + .bed read + H2D + scan + D2H + file"},
+                    "what": "gmat_b200.remma.remma_epiAA(pheno_file, bed_file, gmat_lst, var_com, snp_lst_0=%d "
+                            "first-SNPs per GPU): phenotype parse + host preamble + .bed read + H2D + scan + D2H + file" % E2E_FIRST},
             "roofline": {"bound": "tensor", "achieved": achieved, "unit": "TFLOP/s", "peak": None, "frac": None,
                          "traffic": EXACT_TRAFFIC_BYTES, "kernel": "epi_exact_rb_kernel<%d,..,scan>" % bn,
                          "flops_per_pair_algorithmic": f_exact(n), "issued_tflops": issued},
         }
+        peaks = measure_fp64_peaks(engine, torch)
+        peak = max(peaks["dmma_tflops"], peaks["cublas_dgemm_tflops"])
+        line["roofline"].update({"peak": peak, "frac": achieved / peak, "frac_issued": issued / peak,
+                                 "peak_source": "measured live on rank 0: max(DMMA issue-rate microbenchmark, cuBLAS "
+                                                "DGEMM 4096^3); FP64 is absent from MEASURED_PEAKS.json; achieved "
+                                                "and issued are per GPU", **peaks})
         if world == 1:
-            peaks = measure_fp64_peaks(engine, torch)
-            peak = max(peaks["dmma_tflops"], peaks["cublas_dgemm_tflops"])
-            line["roofline"].update({"peak": peak, "frac": achieved / peak, "frac_issued": issued / peak,
-                                     "peak_source": "measured live: max(DMMA issue-rate microbenchmark, cuBLAS DGEMM "
-                                                    "4096^3); FP64 is absent from MEASURED_PEAKS.json", **peaks})
             if not args.no_extra:
-                line["extra"] = extras(engine, torch, synth, store, model, lut, args)
+                line["extra"] = extras(engine, torch, synth, store, model, lut, args, prefix, pymat)
             if not args.no_cpu:
                 cpu = CpuExact(prefix, pheno, ag)
                 cp, ct = cpu.sample(4)
@@ -318,7 +320,7 @@ def run_gpu(args):
     return 0
 
 
-def extras(engine, torch, synth, store, model, lut, args):
+def extras(engine, torch, synth, store, model, lut, args, prefix, pymat):
     """Secondary numbers of BASELINE.json's metric, same process, N=1: approximate screen pairs/s on the same
     data, agmat TFLOP/s on configs[1] (n=10,000 x m=500,000, generated in HBM), decode GB/s."""
     out = {}
@@ -343,6 +345,19 @@ def extras(engine, torch, synth, store, model, lut, args):
     out["approx_screen"] = {"pairs_per_s": pairs / t, "seconds": t, "pairs": pairs,
                             "tflops_algorithmic": pairs * 2.0 * N_ID / t / 1e12,
                             "workload": "remma_epiAA_eff_cpu formulation, full scan n=%d x m=%d" % (N_ID, N_SNP)}
+    if not args.no_cpu:
+        # the reference's own C screen (oracle/_ref, compiled from gmat/remma/_remma_epi_eff_cpu.c) on the same
+        # files with all host threads; bounded sample of first-SNPs.  It re-reads and re-codes the whole .bed into
+        # double[m*n] on every call, which is part of what its users pay (remma_epiAA_eff.py:78-83 times it too).
+        from oracle import oracle
+        sub = batch_first_snps(N_SNP, 0, 1, 2048)
+        t0 = time.perf_counter()
+        oracle.ref_screen_file(prefix, "AA", sub, pymat, 1e30, prefix + ".ref_screen.tmp")
+        dt = time.perf_counter() - t0
+        out["approx_screen"]["cpu_reference"] = {
+            "pairs_per_s": n_pairs(sub, N_SNP) / dt, "seconds": dt, "cores": os.cpu_count(), "kind": "reference",
+            "sample": "oracle/_ref remma_epiAA_eff_cpu (OpenMP, all threads) on 2048 first-SNPs in blocks of 8 "
+                      "spread over the range = %d pairs, incl. its .bed read" % n_pairs(sub, N_SNP)}
     # decode: .bed -> float64 [m][n] (what read_plink_bed materialises), HBM-bound; C4 shape (2 GB out > L2)
     n3, m3 = 5000, 50000
     st3 = engine.GenotypeStore.from_device_payload(
