@@ -33,6 +33,21 @@ int sm_count() {
     return cached[dev];
 }
 
+// Stream-ordered scratch (cudaMallocAsync) comes from the device's default memory pool, whose default is to hand
+// freed memory back to the driver at the next synchronisation: the screen's 0.3 - 1 GiB operand scratch would then
+// be re-mapped on every call (measured: 4.5 ms of a 28 ms scan).  Keep it cached in the pool instead.
+void keep_scratch_pool() {
+    static bool done[64];
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64 || done[dev]) return;
+    cudaMemPool_t pool;
+    if (cudaDeviceGetDefaultMemPool(&pool, dev) == cudaSuccess) {
+        unsigned long long keep = ~0ull;
+        cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+    }
+    done[dev] = true;
+}
+
 // ---- FP64 issue-rate microbenchmarks ---------------------------------------------------------
 __global__ void __launch_bounds__(512) peak_dmma_kernel(double *out, int iters) {
     double c[8][2];

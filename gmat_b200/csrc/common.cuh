@@ -48,6 +48,7 @@ inline void count_launch(int n = 1) { g_launches.fetch_add(n, std::memory_order_
     } while (0)
 
 int sm_count();   // cached multiprocessor count of the current device
+void keep_scratch_pool();   // make the default stream-ordered pool of the current device retain freed scratch
 
 // ---------------------------------------------------------------- device helpers
 constexpr int BLOCK_ROWS = 128;   // row-block of Z'PZ in the packed layout / exact kernel M tile

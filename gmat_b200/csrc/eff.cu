@@ -7,14 +7,20 @@
 //   MAF-binned threshold eff_cut[freq[i]*10+freq[j]] ...... gmat/remma/_remma_epi_eff_cpu.c:154
 //   AD: two directions, '>=' then '>' ..................... gmat/remma/_remma_epi_eff_cpu.c:233-247
 //
-// B200 design (the recipe of exact.cu, simpler because nothing is shared between warps in the K loop):
-//  * tile = 128 first-SNPs (list entries) x 128 second-SNPs per persistent CTA; 8 warps (2 x 4), warp tile
-//    64 x 32 SNPs = 8 x 4 DMMA.8x8x4 accumulator tiles (128 registers), K = individuals in slabs of 16.
-//  * operands are built in registers: lane (g, t) keeps the 16-individual code word of each of its 8 + 4 SNP
-//    rows (one LDG.32 per row per slab through L1, prefetched a slab ahead) and fetches every fragment element
-//    with one LDS.64 from the per-tile value tables lutU[row][code], lutV[col][code] (32 B per SNP: the four rows
-//    of a half warp cover one 128 B line, conflict-free); py[k] is folded into the 4 B-side values (4 DMUL per
-//    32 DMMA).  No decoded slab in shared memory, no barrier of any kind inside the K loop.
+// B200 design (the recipe of exact.cu):
+//  * tile = 128 first-SNPs (list entries) x 128 second-SNPs per persistent CTA; 8 consumer warps (2 x 4), warp
+//    tile 64 x 32 SNPs = 8 x 4 DMMA.8x8x4 accumulator tiles, K = individuals in slabs of 16; 4 producer warps
+//    whose registers go to the consumers (setmaxnreg).
+//  * A operand (first SNPs, py folded in): eff_pack_kernel writes  U_I[row][k] * py[k]  for a chunk of I-blocks
+//    ONCE, as doubles in DMMA A-fragment order (128 x 16 slab = one contiguous 16 KB piece).  This is the only
+//    place decoded doubles exist outside registers: a bounded scratch (<= 1 GiB per chunk), written once and
+//    re-read from L2 by every J-tile of the I-block.  One producer lane streams the slabs through an 8-deep TMA
+//    ring (cp.async.bulk + mbarrier expect_tx); fragment loads are conflict-free LDS.128.
+//  * B operand (second SNPs) is built in registers: lane (g, t) keeps the 16-individual code word of its 4 SNP
+//    rows (LDG.32 through L1, prefetched a slab ahead) and fetches each element with one LDS.64 from the per-tile
+//    value table lutV[col][code].  No DMUL and no cross-warp hand-over in the K loop.
+//    (v2 built both operands in registers with py multiplied in by DMUL: 82 % of the DMMA peak; the probe in
+//    profiles/r01_dmma_probe.md shows what DMULs inside a DMMA stream cost.)
 //  * epilogue thresholds the 64 effects of a lane and compacts hits with a warp ballot + one atomic per warp.
 #include "common.cuh"
 
@@ -22,6 +28,10 @@ namespace gb {
 
 constexpr int EFF_T = 128;          // tile edge (SNPs)
 constexpr int EFF_BK = 16;          // individuals per slab (= 4 bytes of codes per SNP)
+constexpr int EFF_NS = 8;           // ring depth (16 KB slabs of packed A)
+constexpr int EFF_CW = 8;           // consumer warps (2 x 4)
+constexpr int EFF_PW = 4;           // producer warps (one per SM sub-partition; only one lane works)
+constexpr int EFF_SLAB = EFF_T * EFF_BK;      // doubles per slab
 
 struct EffParams {
     const unsigned char *bed;
@@ -39,23 +49,23 @@ struct EffParams {
     long long n_iblk, n_jblk;
     const long long *prefix;        // [n_iblk + 1] first work-list position of each I-block
     const long long *jb0;           // [n_iblk] first J-block holding a j > min(i of the block)
-    unsigned long long *next_tile;  // dynamic tile counter (zeroed before the launch)
+    const double *packedU;          // [chunk I-blocks][nslab][EFF_SLAB] A operand, fragment order
+    long long ib_begin, ib_end;     // I-blocks of this launch (the chunk packedU holds)
+    long long nslab;
 };
 
 struct EffSmem {
-    double lutU[EFF_T][4];          // value table of each tile row (first SNP), zero for masked rows
-    double lutV[EFF_T][4];          // value table of each tile column (second SNP)
+    double A[EFF_NS][EFF_SLAB];     // TMA destination
+    double lutV[EFF_T][4];          // value table of each tile column (second SNP), zero past m
     double cut[112];
     long long isnp[EFF_T];          // SNP index of each tile row (-1: past the end of ilist)
     int binI[EFF_T];
     int binJ[EFF_T];
-    long long tile_next;
+    uint64_t full[EFF_NS], empty[EFF_NS];
 };
 
 // Work list of the screen: I-blocks of 128 list entries; block ib only needs the J-blocks from jb0[ib] =
-// (min first-SNP of the block + 1) / 128 on (j > i).  prefix[] turns a position of the compacted list into
-// (ib, jb); the tiles are then handed out dynamically (atomic counter), because a static round-robin over the
-// triangular tile set leaves the CTAs up to ~10 % apart.
+// (min first-SNP of the block + 1) / 128 on (j > i).  prefix[] turns a position of the compacted list into (ib, jb).
 __global__ void eff_tiles_kernel(const long long *__restrict__ ilist, long long n_i, long long n_iblk,
                                  long long n_jblk, long long *__restrict__ prefix, long long *__restrict__ jb0) {
     for (long long ib = threadIdx.x; ib < n_iblk; ib += blockDim.x) {
@@ -76,98 +86,127 @@ __global__ void eff_tiles_kernel(const long long *__restrict__ ilist, long long 
     }
 }
 
-__global__ void __launch_bounds__(256, 1) epi_eff_kernel(const EffParams p) {
-    constexpr int NT = 256;
+// packedU[blk][slab][k4][mtp][lane][h] = lutU[i][code(i, k)] * py[k],  i = ilist[(ib_begin + blk)*128 + (2*mtp+h)*8
+// + (lane>>2)],  k = slab*16 + k4*4 + (lane&3);  zero for list positions past n_i and individuals past n.
+__global__ void __launch_bounds__(256) eff_pack_kernel(const EffParams p, double *__restrict__ out) {
+    // one CTA per (slab = blockIdx.x, I-block = blockIdx.y): 2048 doubles, 8 per thread, no 64-bit divisions
+    const long long slab = blockIdx.x, blk = blockIdx.y;
+    double *dst = out + (blk * p.nslab + slab) * EFF_SLAB;
+#pragma unroll
+    for (int x = 0; x < EFF_SLAB / 256; ++x) {
+        const int q = x * 256 + threadIdx.x;
+        const int h = q & 1, lane = (q >> 1) & 31, mtp = (q >> 6) & 7, k4 = q >> 9;
+        const long long li = (p.ib_begin + blk) * EFF_T + (2 * mtp + h) * 8 + (lane >> 2);
+        const long long k = slab * EFF_BK + k4 * 4 + (lane & 3);
+        double v = 0.0;
+        if (li < p.n_i && k < p.n) {
+            const long long si = p.ilist[li];
+            if (si >= 0) {
+                const int c = (p.bed[si * p.row_bytes + (k >> 2)] >> ((k & 3) * 2)) & 3;
+                v = __ldg(p.lutU + si * 4 + c) * __ldg(p.py + k);
+            }
+        }
+        dst[q] = v;
+    }
+}
+
+__global__ void __launch_bounds__((EFF_CW + EFF_PW) * 32, 1) epi_eff_kernel(const EffParams p) {
+    constexpr int NCT = EFF_CW * 32;
     constexpr int MT = 8, NTL = 4;                // warp tile 64 x 32
+    constexpr unsigned SLAB_BYTES = EFF_SLAB * sizeof(double);
     extern __shared__ __align__(128) unsigned char smem_raw[];
     EffSmem &S = *reinterpret_cast<EffSmem *>(smem_raw);
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int g = lane >> 2, t = lane & 3;
-    const int wm = warp >> 2, wn = warp & 3;
-    const long long nslab = (p.n + EFF_BK - 1) / EFF_BK;
     const bool use_table = p.cut_table != nullptr;
+    // tiles of this launch = positions [prefix[ib_begin], prefix[ib_end]) of the compacted work list
+    const long long t_begin = p.prefix[p.ib_begin], t_end = p.prefix[p.ib_end];
 
+    if (tid == 0) {
+        for (int s = 0; s < EFF_NS; ++s) {
+            mbar_init(&S.full[s], 1);
+            mbar_init(&S.empty[s], EFF_CW);
+        }
+        mbar_fence_init();
+    }
     if (use_table) {
-        for (int x = tid; x < 111; x += NT) S.cut[x] = p.cut_table[x];
+        for (int x = tid; x < 111; x += blockDim.x) S.cut[x] = p.cut_table[x];
+    }
+    __syncthreads();
+
+    auto tile_iblock = [&](long long tile) {
+        long long lo = p.ib_begin, hi = p.ib_end;     // largest ib with prefix[ib] <= tile (uniform)
+        while (hi - lo > 1) {
+            const long long mid = (lo + hi) >> 1;
+            if (p.prefix[mid] <= tile) lo = mid; else hi = mid;
+        }
+        return lo;
+    };
+
+    if (warp >= EFF_CW) {
+        // =============================== A-stream producer ==============================================
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 40;\n");
+        if (warp == EFF_CW && lane == 0) {
+            int stage = 0;
+            unsigned use_odd = 0;
+            bool first_pass = true;
+            for (long long tile = t_begin + blockIdx.x; tile < t_end; tile += gridDim.x) {
+                const long long ib = tile_iblock(tile);
+                const double *src = p.packedU + (ib - p.ib_begin) * p.nslab * EFF_SLAB;
+                for (long long s = 0; s < p.nslab; ++s) {
+                    if (!first_pass) mbar_wait(&S.empty[stage], use_odd ^ 1u);
+                    fence_proxy_async();             // consumers' LDS of this stage precede the async refill
+                    mbar_expect_tx(&S.full[stage], SLAB_BYTES);
+                    tma_bulk_g2s(S.A[stage], src + s * EFF_SLAB, SLAB_BYTES, &S.full[stage]);
+                    if (++stage == EFF_NS) { stage = 0; use_odd ^= 1u; first_pass = false; }
+                }
+            }
+        }
+        return;
     }
 
-    const long long ntiles = p.prefix[p.n_iblk];
-    if (tid == 0) S.tile_next = (long long)atomicAdd(p.next_tile, 1ull);
-    __syncthreads();
-    while (true) {
-        const long long tile = S.tile_next;
-        __syncthreads();                          // everyone holds `tile`; previous tile fully consumed
-        if (tile >= ntiles) break;
-        if (tid == 0) S.tile_next = (long long)atomicAdd(p.next_tile, 1ull);   // read after the next barrier pair
-        long long ib;
-        {
-            long long lo = 0, hi = p.n_iblk;      // largest ib with prefix[ib] <= tile (uniform)
-            while (hi - lo > 1) {
-                const long long mid = (lo + hi) >> 1;
-                if (p.prefix[mid] <= tile) lo = mid; else hi = mid;
-            }
-            ib = lo;
-        }
+    // =================================== consumer warps =================================================
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 232;\n");
+    const int g = lane >> 2, t = lane & 3;
+    const int wm = warp >> 2, wn = warp & 3;
+    int stage = 0;
+    unsigned fphase = 0;
+    for (long long tile = t_begin + blockIdx.x; tile < t_end; tile += gridDim.x) {
+        const long long ib = tile_iblock(tile);
         const long long jb = p.jb0[ib] + (tile - p.prefix[ib]);
         const long long jbase = jb * EFF_T;
-        // ---- tile setup: row SNP indices, value tables, bins ---------------------------------
+        named_bar_sync(1, NCT);                   // previous tile fully consumed
+        // ---- tile setup: row SNP indices, column value tables, bins -----------------------------
         if (tid < EFF_T) {
             const long long li = ib * EFF_T + tid;
             const long long si = (li < p.n_i) ? p.ilist[li] : -1;
             S.isnp[tid] = si;
             const long long sj = jbase + tid;
 #pragma unroll
-            for (int c = 0; c < 4; ++c) {
-                S.lutU[tid][c] = (si >= 0) ? __ldg(p.lutU + si * 4 + c) : 0.0;
-                S.lutV[tid][c] = (sj < p.m) ? __ldg(p.lutV + sj * 4 + c) : 0.0;
-            }
+            for (int c = 0; c < 4; ++c) S.lutV[tid][c] = (sj < p.m) ? __ldg(p.lutV + sj * 4 + c) : 0.0;
             if (use_table) {
                 S.binI[tid] = (si >= 0) ? p.binI[si] : 0;
                 S.binJ[tid] = (sj < p.m) ? p.binJ[sj] : 0;
             }
         }
-        __syncthreads();
+        named_bar_sync(1, NCT);
 
-        // ---- this lane's operand sources -------------------------------------------------------
-        // A rows: wm*64 + 8a + g (list entries, arbitrary SNPs);  B columns: wn*32 + 8b + g (consecutive SNPs).
-        // Row offsets are 32-bit (the host checks m * row_bytes < 2^32): registers are the scarce resource here.
-        unsigned ua[MT], vb[NTL];
-        unsigned ta[MT];
-#pragma unroll
-        for (int a = 0; a < MT; ++a) {
-            const int r = wm * 64 + a * 8 + g;
-            const long long si = S.isnp[r];
-            ua[a] = (unsigned)((si >= 0 ? si : 0) * p.row_bytes);
-            ta[a] = smem_u32(&S.lutU[r][0]);
-        }
+        // ---- this lane's B sources: columns wn*32 + 8b + g (consecutive SNPs) ---------------------
+        const unsigned char *vb[NTL];
 #pragma unroll
         for (int b = 0; b < NTL; ++b) {
             const long long sj = jbase + wn * 32 + 8 * b + g;      // columns past m re-read a valid row (table zero)
-            vb[b] = (unsigned)((sj < p.m ? sj : p.m - 1) * p.row_bytes);
+            vb[b] = p.bed + (sj < p.m ? sj : p.m - 1) * p.row_bytes;
         }
-        const unsigned tb = smem_u32(&S.lutV[wn * 32 + g][0]);
-
-        unsigned nwa[MT], nwb[NTL];                  // code words of the next slab (prefetched through L1)
-        double npy[EFF_BK / 4];
-        auto load_slab = [&](long long slab) {
+        const char *tb = reinterpret_cast<const char *>(&S.lutV[wn * 32 + g][0]);
+        unsigned nwb[NTL];                        // code words of the next slab (prefetched through L1)
+        auto load_codes = [&](long long slab) {
             const long long off = slab * (EFF_BK / 4);
             const bool ok = off + 4 <= p.row_bytes;
 #pragma unroll
-            for (int a = 0; a < MT; ++a) nwa[a] = ok ? __ldg(reinterpret_cast<const unsigned *>(p.bed + ua[a] + off)) : 0u;
-#pragma unroll
-            for (int b = 0; b < NTL; ++b) nwb[b] = ok ? __ldg(reinterpret_cast<const unsigned *>(p.bed + vb[b] + off)) : 0u;
-#pragma unroll
-            for (int k4 = 0; k4 < EFF_BK / 4; ++k4) {
-                const long long k = slab * EFF_BK + k4 * 4 + t;
-                npy[k4] = (k < p.n) ? __ldg(p.py + k) : 0.0;      // padded individuals contribute exactly 0
-            }
+            for (int b = 0; b < NTL; ++b) nwb[b] = ok ? __ldg(reinterpret_cast<const unsigned *>(vb[b] + off)) : 0u;
         };
-        auto lds64 = [](unsigned addr) -> double {
-            double v;
-            asm volatile("ld.shared.f64 %0, [%1];\n" : "=d"(v) : "r"(addr));
-            return v;
-        };
+        load_codes(0);
 
         double acc[MT][NTL][2];
 #pragma unroll
@@ -175,32 +214,33 @@ __global__ void __launch_bounds__(256, 1) epi_eff_kernel(const EffParams p) {
 #pragma unroll
             for (int b = 0; b < NTL; ++b) acc[a][b][0] = acc[a][b][1] = 0.0;
 
-        load_slab(0);
-        for (long long s = 0; s < nslab; ++s) {
-            // byte k4 of xa / xb = 8 * code of individual 16 s + 4 k4 + t: a byte offset into the SNP's value table
-            unsigned xa[MT], xb[NTL];
-            double pyv[EFF_BK / 4];
-#pragma unroll
-            for (int a = 0; a < MT; ++a) xa[a] = ((nwa[a] >> (2 * t)) & 0x03030303u) << 3;
+        for (long long s = 0; s < p.nslab; ++s) {
+            // byte k4 of xb = 8 * code of individual 16 s + 4 k4 + t: a byte offset into the column's value table
+            unsigned xb[NTL];
 #pragma unroll
             for (int b = 0; b < NTL; ++b) xb[b] = ((nwb[b] >> (2 * t)) & 0x03030303u) << 3;
-#pragma unroll
-            for (int k4 = 0; k4 < EFF_BK / 4; ++k4) pyv[k4] = npy[k4];
-            if (s + 1 < nslab) load_slab(s + 1);
-            // (hand-pipelining the fragments a step ahead, or pinning the four DMULs together, was measured slower
-            // than leaving the schedule to ptxas: 28.4 vs 30.3 TFLOP/s at n=2000)
+            load_codes(s + 1 < p.nslab ? s + 1 : 0);
+            mbar_wait(&S.full[stage], fphase);
+            const double2 *Af = reinterpret_cast<const double2 *>(S.A[stage]);
 #pragma unroll
             for (int k4 = 0; k4 < EFF_BK / 4; ++k4) {
                 double af[MT], bf[NTL];
 #pragma unroll
-                for (int a = 0; a < MT; ++a) af[a] = lds64(ta[a] + ((xa[a] >> (8 * k4)) & 0xffu));
+                for (int a2 = 0; a2 < MT / 2; ++a2) {
+                    const double2 v = Af[(k4 * 8 + wm * (MT / 2) + a2) * 32 + lane];
+                    af[2 * a2] = v.x; af[2 * a2 + 1] = v.y;
+                }
 #pragma unroll
-                for (int b = 0; b < NTL; ++b) bf[b] = lds64(tb + b * (8 * 32) + ((xb[b] >> (8 * k4)) & 0xffu)) * pyv[k4];
+                for (int b = 0; b < NTL; ++b)
+                    bf[b] = *reinterpret_cast<const double *>(tb + b * (8 * 32) + ((xb[b] >> (8 * k4)) & 0xffu));
 #pragma unroll
                 for (int a = 0; a < MT; ++a)
 #pragma unroll
                     for (int b = 0; b < NTL; ++b) dmma884(acc[a][b][0], acc[a][b][1], af[a], bf[b]);
             }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&S.empty[stage]);
+            if (++stage == EFF_NS) { stage = 0; fphase ^= 1u; }
         }
 
         // ---- epilogue: threshold + warp-ballot compaction ------------------------------------------
@@ -257,7 +297,6 @@ extern "C" int gmat_b200_epi_eff(const unsigned char *bed_dev, long long n, long
     GB_CHECK_ARG(n > 0 && m > 0 && n_i >= 0, "sizes");
     GB_CHECK_ARG(row_bytes >= (n + 3) / 4 && row_bytes % 16 == 0, "row_bytes");
     GB_CHECK_ARG(row_bytes * 4 >= round_up(n, EFF_BK), "row_bytes must cover n rounded up to 16 individuals");
-    GB_CHECK_ARG(m * row_bytes < (1LL << 32), "genotype store larger than 4 GiB");
     GB_CHECK_ARG(cap == 0 || hits_dev != nullptr, "hits_dev is NULL");
     GB_CHECK_ARG(cut_table_dev == nullptr || (binI_dev && binJ_dev), "bins required with cut table");
     if (n_i == 0) return GMAT_B200_OK;
@@ -270,23 +309,38 @@ extern "C" int gmat_b200_epi_eff(const unsigned char *bed_dev, long long n, long
     p.n_iblk = (n_i + EFF_T - 1) / EFF_T;
     p.n_jblk = (m + EFF_T - 1) / EFF_T;
     cudaStream_t st = (cudaStream_t)stream;
-    long long *scratch = nullptr;                 // prefix[n_iblk + 1], jb0[n_iblk], tile counter
+    keep_scratch_pool();
+    p.nslab = (n + EFF_BK - 1) / EFF_BK;
+    long long *scratch = nullptr;                 // prefix[n_iblk + 1], jb0[n_iblk]
     const size_t sbytes = sizeof(long long) * (2 * p.n_iblk + 2);
     GB_CUDA(cudaMallocAsync(reinterpret_cast<void **>(&scratch), sbytes, st));
-    GB_CUDA(cudaMemsetAsync(scratch, 0, sbytes, st));
     p.prefix = scratch;
     p.jb0 = scratch + p.n_iblk + 1;
-    p.next_tile = reinterpret_cast<unsigned long long *>(scratch + 2 * p.n_iblk + 1);
     eff_tiles_kernel<<<1, 1024, 0, st>>>(ilist_dev, n_i, p.n_iblk, p.n_jblk, scratch, scratch + p.n_iblk + 1);
     GB_LAUNCH_CHECK();
+    // packed A operand for a chunk of I-blocks at a time: bounded scratch (<= 1 GiB), written once per chunk
+    const long long blk_bytes = p.nslab * EFF_SLAB * (long long)sizeof(double);
+    long long chunk = (1LL << 30) / blk_bytes;
+    if (chunk < 1) chunk = 1;
+    if (chunk > p.n_iblk) chunk = p.n_iblk;
+    double *packed = nullptr;
+    GB_CUDA(cudaMallocAsync(reinterpret_cast<void **>(&packed), (size_t)(chunk * blk_bytes), st));
+    p.packedU = packed;
     auto kern = epi_eff_kernel;
     const size_t smem = sizeof(EffSmem);
     GB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    long long grid = p.n_iblk * p.n_jblk;         // upper bound of the tile count (exact count is on the device)
-    const long long maxgrid = (long long)sm_count();
-    if (grid > maxgrid) grid = maxgrid;
-    kern<<<(unsigned)grid, 256, smem, st>>>(p);
-    GB_LAUNCH_CHECK();
+    for (long long ib0 = 0; ib0 < p.n_iblk; ib0 += chunk) {
+        p.ib_begin = ib0;
+        p.ib_end = (ib0 + chunk < p.n_iblk) ? ib0 + chunk : p.n_iblk;
+        const dim3 pgrid((unsigned)p.nslab, (unsigned)(p.ib_end - p.ib_begin));
+        eff_pack_kernel<<<pgrid, 256, 0, st>>>(p, packed);
+        GB_LAUNCH_CHECK();
+        long long grid = (p.ib_end - p.ib_begin) * p.n_jblk;      // upper bound of the chunk's tile count
+        if (grid > sm_count()) grid = sm_count();
+        kern<<<(unsigned)grid, (EFF_CW + EFF_PW) * 32, smem, st>>>(p);
+        GB_LAUNCH_CHECK();
+    }
+    GB_CUDA(cudaFreeAsync(packed, st));
     GB_CUDA(cudaFreeAsync(scratch, st));
     return GMAT_B200_OK;
 }
