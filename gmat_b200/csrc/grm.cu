@@ -17,6 +17,11 @@
 //  * Operand fragments are built in registers: lane (g, t) owns SNP 4*k4 + t of the step, reads its 16 B + 8 B
 //    of codes (broadcast LDS.128 / LDS.64) and fetches each of its 8 + 4 fragment elements with one LDS.64
 //    from that SNP's value table (the 4 SNPs of a step share one 128 B line: conflict-free).
+//  * stream-K work split: the (tile, stage) iteration space is cut into gridDim.x equal contiguous ranges, so
+//    every SM works to the end whatever the tile count (n = 10,000: 3160 tiles = 21.35 waves of 148).  A tile cut
+//    by a range boundary is finished by two CTAs, each adding its partial sum with red.global.add.f64 into the
+//    zero-initialised output; the launch keeps every tile in at most two parts, so the sum order cannot vary and
+//    the result is run-to-run reproducible.
 #include "common.cuh"
 
 namespace gb {
@@ -36,6 +41,7 @@ struct GrmParams {
     int accumulate;
     double *K;
     long long nblk;
+    int split2;
 };
 
 struct GrmSmem {
@@ -59,6 +65,17 @@ __global__ void __launch_bounds__((GR_CW + GR_PW) * 32, 1) grm_kernel(const GrmP
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const long long nstage = (p.snp_end - p.snp_begin + GR_GS - 1) / GR_GS;
     const long long ntiles = p.nblk * (p.nblk + 1) / 2;
+    // stream-K: this CTA's contiguous share of the ntiles x nstage units (split2: two CTAs per tile, half each)
+    long long u_begin, u_end;
+    if (p.split2) {
+        const long long tile = blockIdx.x >> 1, half = (nstage + 1) / 2;
+        u_begin = tile * nstage + ((blockIdx.x & 1) ? half : 0);
+        u_end = tile * nstage + ((blockIdx.x & 1) ? nstage : half);
+    } else {
+        const long long units = ntiles * nstage, q = units / gridDim.x, rem = units % gridDim.x;
+        u_begin = q * blockIdx.x + (rem < blockIdx.x ? rem : blockIdx.x);
+        u_end = u_begin + q + (blockIdx.x < rem ? 1 : 0);
+    }
 
     if (tid == 0) {
         for (int s = 0; s < GR_NS; ++s) {
@@ -76,14 +93,17 @@ __global__ void __launch_bounds__((GR_CW + GR_PW) * 32, 1) grm_kernel(const GrmP
         int stage = 0;
         unsigned use_odd = 0;
         bool first_pass = true;
-        for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        for (long long u = u_begin; u < u_end;) {
+            const long long tile = u / nstage, st_begin = u - tile * nstage;
+            const long long st_end = (u_end - u) < (nstage - st_begin) ? st_begin + (u_end - u) : nstage;
+            u += st_end - st_begin;
             long long mi, ni;
             grm_tile_of(tile, mi, ni);
             // bytes of a row piece: 32, or what is left of the (16 B padded) row for the last block
             const long long offA = mi * (GR_T / 4), offB = ni * (GR_T / 4);
             const unsigned bytesA = (unsigned)((p.row_bytes - offA) < 32 ? (p.row_bytes - offA) : 32);
             const unsigned bytesB = (unsigned)((p.row_bytes - offB) < 32 ? (p.row_bytes - offB) : 32);
-            for (long long st = 0; st < nstage; ++st) {
+            for (long long st = st_begin; st < st_end; ++st) {
                 if (!first_pass) mbar_wait(&S.empty[stage], use_odd ^ 1u);
                 fence_proxy_async();                 // consumers' LDS of this stage precede the async refill
                 const long long s0 = p.snp_begin + st * GR_GS;
@@ -120,7 +140,11 @@ __global__ void __launch_bounds__((GR_CW + GR_PW) * 32, 1) grm_kernel(const GrmP
     const int sh0 = 2 * g, sh1 = 16 + 2 * g;
     int stage = 0;
     unsigned fphase = 0;
-    for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    for (long long u = u_begin; u < u_end;) {
+        const long long tile = u / nstage, st_begin = u - tile * nstage;
+        const long long st_end = (u_end - u) < (nstage - st_begin) ? st_begin + (u_end - u) : nstage;
+        u += st_end - st_begin;
+        const bool partial = (st_end - st_begin) != nstage;
         long long mi, ni;
         grm_tile_of(tile, mi, ni);
         double acc[MT][NTL][2];
@@ -129,7 +153,7 @@ __global__ void __launch_bounds__((GR_CW + GR_PW) * 32, 1) grm_kernel(const GrmP
 #pragma unroll
             for (int b = 0; b < NTL; ++b) acc[a][b][0] = acc[a][b][1] = 0.0;
 
-        for (long long st = 0; st < nstage; ++st) {
+        for (long long st = st_begin; st < st_end; ++st) {
             mbar_wait(&S.full[stage], fphase);
 #pragma unroll 4
             for (int k4 = 0; k4 < GR_GS / 4; ++k4) {
@@ -167,12 +191,15 @@ __global__ void __launch_bounds__((GR_CW + GR_PW) * 32, 1) grm_kernel(const GrmP
                 for (int c = 0; c < 2; ++c) {
                     const long long col = ni * GR_T + wn * 32 + b * 8 + 2 * t + c;
                     if (r < p.n && col < p.n && (mi != ni || col <= r)) {
-                        if (p.accumulate) {
-                            p.K[r * p.n + col] += acc[a][b][c];
-                            if (col != r) p.K[col * p.n + r] += acc[a][b][c];
-                        } else {
-                            double v = acc[a][b][c] / p.scale;
+                        double v = acc[a][b][c];
+                        if (!p.accumulate) {
+                            v = v / p.scale;
                             if (col == r) v = v + v * p.small_val;       // gmatrix.py:64-66
+                        }
+                        if (partial || p.accumulate) {                    // output is zero-initialised / accumulated into
+                            atomicAdd(&p.K[r * p.n + col], v);
+                            if (col != r) atomicAdd(&p.K[col * p.n + r], v);
+                        } else {
                             p.K[r * p.n + col] = v;
                             if (col != r) p.K[col * p.n + r] = v;
                         }
@@ -201,12 +228,26 @@ extern "C" int gmat_b200_grm(const unsigned char *bed_dev, long long n, long lon
     p.snp_begin = snp_begin; p.snp_end = snp_end; p.scale = scale; p.small_val = small_val;
     p.accumulate = accumulate; p.K = K_dev;
     p.nblk = (n + GR_T - 1) / GR_T;
-    if (snp_begin == snp_end && accumulate) return GMAT_B200_OK;
     auto kern = grm_kernel;
     const size_t smem = sizeof(GrmSmem);
     GB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    long long grid = p.nblk * (p.nblk + 1) / 2;
-    if (grid > sm_count()) grid = sm_count();
+    const long long ntiles = p.nblk * (p.nblk + 1) / 2;
+    const long long nstage = (snp_end - snp_begin + GR_GS - 1) / GR_GS;
+    if (nstage == 0) {                               // empty SNP range: K = 0 (or unchanged when accumulating)
+        if (!accumulate) GB_CUDA(cudaMemsetAsync(K_dev, 0, sizeof(double) * (size_t)n * (size_t)n, (cudaStream_t)stream));
+        return GMAT_B200_OK;
+    }
+    // stream-K grid.  ntiles >= SMs: one CTA per SM, equal contiguous unit ranges (a range is at least one tile
+    // long, so a tile has at most two parts and the two partial sums commute: reproducible).  2*ntiles <= SMs: two
+    // CTAs per tile, half the stages each.  In between: one CTA per tile (a third part would make the atomic sum
+    // order-dependent).
+    long long grid = sm_count();
+    p.split2 = 0;
+    if (ntiles < grid) {
+        if (2 * ntiles <= grid && nstage >= 2) { grid = 2 * ntiles; p.split2 = 1; }
+        else grid = ntiles;
+    }
+    if (!accumulate) GB_CUDA(cudaMemsetAsync(K_dev, 0, sizeof(double) * (size_t)n * (size_t)n, (cudaStream_t)stream));
     kern<<<(unsigned)grid, (GR_CW + GR_PW) * 32, smem, (cudaStream_t)stream>>>(p);
     GB_LAUNCH_CHECK();
     return GMAT_B200_OK;
