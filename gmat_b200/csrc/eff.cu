@@ -23,6 +23,7 @@
 //    profiles/r01_dmma_probe.md shows what DMULs inside a DMMA stream cost.)
 //  * epilogue thresholds the 64 effects of a lane and compacts hits with a warp ballot + one atomic per warp.
 #include "common.cuh"
+#include <cstdlib>
 
 namespace gb {
 
@@ -320,7 +321,12 @@ extern "C" int gmat_b200_epi_eff(const unsigned char *bed_dev, long long n, long
     GB_LAUNCH_CHECK();
     // packed A operand for a chunk of I-blocks at a time: bounded scratch (<= 1 GiB), written once per chunk
     const long long blk_bytes = p.nslab * EFF_SLAB * (long long)sizeof(double);
-    long long chunk = (1LL << 30) / blk_bytes;
+    long long budget = 1LL << 30;
+    if (const char *e = getenv("GMAT_B200_EFF_SCRATCH_BYTES")) {        // tests force several chunks with this
+        const long long v = atoll(e);
+        if (v > 0) budget = v;
+    }
+    long long chunk = budget / blk_bytes;
     if (chunk < 1) chunk = 1;
     if (chunk > p.n_iblk) chunk = p.n_iblk;
     double *packed = nullptr;

@@ -279,3 +279,44 @@ def test_grm_vs_oracle_synthetic(eng, tmp_path, n, m):
         eng.grm(store, eng.ADD, 1.0, 0.0, snp_begin=a, snp_end=b, out=acc, accumulate=True)
     want, scale = oracle.agmat(prefix, small_val=0.0)
     assert np.abs(acc.cpu().numpy() / scale - want).max() <= RTOL * np.abs(want).max()
+
+
+def test_grm_streamk_many_tiles_reproducible(eng, tmp_path):
+    """n large enough for more tiles than SMs (the equal-range stream-K split with atomically added partial tiles):
+    parity with the oracle and bit-identical results run to run (a tile never has more than two parts)."""
+    from gmat_b200.gmatrix.gmatrix import grm_device
+    n, m = 2300, 200                      # 18 blocks -> 171 tiles > 148 SMs; 4 stages of 64 SNPs (last one ragged)
+    prefix, _ = _dataset(tmp_path, n, m, seed=99)
+    store = eng.GenotypeStore(prefix)
+    want, scale = oracle.agmat(prefix)
+    kin, s = grm_device(store, eng.ADD)
+    got = kin.cpu().numpy()
+    assert s == scale
+    assert np.abs(got - want).max() <= RTOL * np.abs(want).max()
+    assert np.array_equal(got, got.T)
+    for _ in range(3):
+        again, _ = grm_device(store, eng.ADD)
+        assert np.array_equal(again.cpu().numpy(), got)
+
+
+def test_screen_chunked_operand_scratch(eng, tmp_path, monkeypatch):
+    """The screen packs its A operand for a chunk of I-blocks at a time; force 1-block chunks (8 launches) and
+    compare with the single-chunk result and the oracle."""
+    n, m = 150, 1000
+    prefix, _ = _dataset(tmp_path, n, m, seed=17)
+    store = eng.GenotypeStore(prefix)
+    rng = np.random.Generator(np.random.PCG64(2))
+    pymat = rng.normal(size=(n, 1))
+    import torch
+    pyd = torch.as_tensor(pymat.ravel().copy()).cuda()
+    la = store.lut(eng.ADD, eng.FREQ_CLOOP)
+    lst = np.array([i for i in range(m - 1) if i % 5 != 2], dtype=np.int64)
+    cut = 6.0
+    one = eng.epi_eff(store, la, la, pyd, lst, 0, cut)
+    monkeypatch.setenv("GMAT_B200_EFF_SCRATCH_BYTES", str(10 * 16 * 128 * 8))       # one I-block (10 slabs)
+    many = eng.epi_eff(store, la, la, pyd, lst, 0, cut)
+    key = lambda h: sorted(zip(h["snp_0"].tolist(), h["snp_1"].tolist(), h["eff"].tolist()))
+    assert key(one) == key(many) and len(one) > 0
+    ref = oracle.screen(prefix, "AA", lst, pymat, eff_cut=cut)
+    assert [(a, b) for a, b, _ in key(one)] == [(a, b) for a, b, _ in ref]
+    np.testing.assert_allclose([e for _, _, e in key(one)], [e for _, _, e in ref], rtol=RTOL, atol=1e-12)
