@@ -16,7 +16,8 @@
 //    block-triangle of 128-row blocks, each 128 x 16 slab stored in DMMA A-fragment order, so a slab is ONE
 //    contiguous 16 KB TMA bulk copy (cp.async.bulk + mbarrier complete_tx) and every fragment load is a
 //    conflict-free LDS.128.  Symmetry: w'Aw = sum_mb w_mb'( A[mb,mb] w_mb + 2 sum_{kb<mb} A[mb,kb] w_kb )
-//    -- only the lower block-triangle is streamed and multiplied (~half the flops of a full GEMM);
+//    -- only the lower block-triangle is streamed and multiplied (~half the flops of a full GEMM; inside a
+//    diagonal block the same identity is applied once more at the 64-row granularity of a warp);
 //    the packed entries are (A_kl + A_lk)/2 so the doubled term equals the reference's full sum.
 //  * W never exists as a matrix, not even in shared memory: every consumer warp builds its DMMA B fragments
 //    in registers from the 2-bit codes and a per-pair 4 x 4 product table (see epi_exact_rb_kernel).  The
@@ -327,8 +328,13 @@ epi_exact_rb_kernel(const ExactParams p) {
                 for (int b = 0; b < NTL; ++b) acc[a][b][0] = acc[a][b][1] = 0.0;
             const long long nks = (mb + 1) * SPB;
             const long long diag0 = mb * SPB;
+            // Symmetry, at the granularity of this warp's 64 rows: everything left of the warp's own 64 x 64
+            // diagonal sub-block counts twice, the sub-block itself once, and what lies right of it (the upper
+            // right quarter of the 128 x 128 diagonal block, warp row 0 only) is not multiplied at all.
+            const long long dbl_at = diag0 + (wm ? SPB / 2 : 0);
+            const long long mma_end = wm ? nks : diag0 + SPB / 2;
             for (long long ks = 0; ks < nks; ++ks) {
-                if (ks == diag0 && mb > 0) {         // off-diagonal blocks count twice (symmetry)
+                if (ks == dbl_at && ks > 0) {
 #pragma unroll
                     for (int a = 0; a < MT; ++a)
 #pragma unroll
@@ -349,6 +355,7 @@ epi_exact_rb_kernel(const ExactParams p) {
                 load_codes((ks + 1 < nks) ? ks + 1 : 0);                 // next slab's codes travel under the MMAs
                 mbar_wait(&S.full[stage], fphase);
                 const double2 *Af = reinterpret_cast<const double2 *>(S.A[stage]);
+                if (ks < mma_end)
 #pragma unroll
                 for (int k4 = 0; k4 < EX_BK / 4; ++k4) {
                     double af[MT], bf[NTL];
