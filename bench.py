@@ -18,6 +18,13 @@ import tempfile
 import threading
 import time
 
+# torchrun exports OMP_NUM_THREADS=1 for every rank when it is unset; the host-side parts of the end-to-end call
+# (numpy/BLAS in the design-matrix and file stages) then crawl.  Give each rank its share of the host cores.
+if int(os.environ.get("LOCAL_WORLD_SIZE", "1")) > 1 and os.environ.get("OMP_NUM_THREADS", "1") == "1":
+    _thr = str(max(1, (os.cpu_count() or 1) // int(os.environ["LOCAL_WORLD_SIZE"])))
+    for _k in ("OMP_NUM_THREADS", "OPENBLAS_NUM_THREADS", "MKL_NUM_THREADS"):
+        os.environ[_k] = _thr
+
 import numpy as np
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
@@ -272,7 +279,8 @@ def run_gpu(args):
             e2e_t.append(time.perf_counter() - t0)
     e2e_s = reduce(float(np.mean(e2e_t)), dist.ReduceOp.MAX if world > 1 else None)
     e2e_value = float(e2e_pairs) / e2e_s
-    h2d = world * (store.h2d_bytes + model.h2d_bytes) + len(e2e_lst) * 8      # every rank uploads its own copy
+    # every rank uploads its own copy of the .bed payload, the GRMs (GPU preamble), y and X
+    h2d = world * (store.h2d_bytes + sum(g.nbytes for g in gmat_lst) + y.nbytes + xmat.nbytes) + len(e2e_lst) * 8
     d2h = 8 + 32 * (len(hits) if hits is not None else 0)
 
     line = None
@@ -295,7 +303,7 @@ def run_gpu(args):
             "e2e": {"value": e2e_value, "unit": "pairs/s", "h2d_bytes_per_step": int(h2d),
                     "d2h_bytes_per_step": int(d2h),
                     "what": "gmat_b200.remma.remma_epiAA(pheno_file, bed_file, gmat_lst, var_com, snp_lst_0=%d "
-                            "first-SNPs per GPU): phenotype parse + host preamble + .bed read + H2D + scan + D2H + file" % E2E_FIRST},
+                            "first-SNPs per GPU): phenotype parse + GRM upload + GPU preamble + .bed read + H2D + scan + D2H + file" % E2E_FIRST},
             "roofline": {"bound": "tensor", "achieved": achieved, "unit": "TFLOP/s", "peak": None, "frac": None,
                          "traffic": EXACT_TRAFFIC_BYTES, "kernel": "epi_exact_rb_kernel<%d,..,scan>" % bn,
                          "flops_per_pair_algorithmic": f_exact(n), "issued_tflops": issued},

@@ -77,6 +77,48 @@ def preamble(y, xmat, zmat, gmat_lst, var_com, scipy_inv=True, need_pvp=True):
     return np.ascontiguousarray(pymat, dtype=np.float64), pvpmat
 
 
+def preamble_device(y, xmat, zmat, gmat_lst, var_com, device, need_pvp=True):
+    """The same preamble in float64 on the GPU: identical expressions, torch.linalg (cuSOLVER)
+    for the two inverses and cuSPARSE for the products with the incidence matrix Z.  At N = 15,000 records the
+    host version costs minutes (and under torchrun every rank repeats it on OMP_NUM_THREADS=1); this one takes
+    a fraction of a second, and Z'Py / Z'PZ never visit the host.  Returns device tensors
+    (Z'Py [n], Z'PZ [n,n] or None, bytes uploaded).  Agreement with the host version: ~1e-12 relative
+    (tests/test_gpu_dropin.py::test_device_preamble_matches_host)."""
+    f64 = torch.float64
+    yv = torch.as_tensor(np.ascontiguousarray(np.array(y, dtype=np.float64).reshape(-1, 1))).to(device)
+    n_rec = yv.shape[0]
+    xm = torch.as_tensor(np.ascontiguousarray(np.array(xmat, dtype=np.float64).reshape(n_rec, -1))).to(device)
+    zc = zmat.tocoo()
+    idx = torch.as_tensor(np.vstack([zc.row, zc.col]).astype(np.int64)).to(device)
+    val = torch.as_tensor(np.asarray(zc.data, dtype=np.float64)).to(device)
+    zs = torch.sparse_coo_tensor(idx, val, size=tuple(zc.shape), dtype=f64, device=device).coalesce()
+    zt = zs.t().coalesce()
+    h2d = yv.numel() * 8 + xm.numel() * 8 + idx.numel() * 8 + val.numel() * 8
+    vmat = torch.eye(n_rec, dtype=f64, device=device) * float(var_com[-1])
+    for k in range(len(gmat_lst)):
+        g = torch.as_tensor(np.ascontiguousarray(gmat_lst[k], dtype=np.float64)).to(device)
+        h2d += g.numel() * 8
+        vmat += torch.sparse.mm(zs, torch.sparse.mm(zs, g).t().contiguous()) * float(var_com[k])   # Z (Z G)'
+        del g
+    vinv = torch.linalg.inv(vmat)
+    del vmat
+    vx = vinv @ xm
+    xvx = torch.linalg.inv(xm.t() @ vx)
+    pmat = vinv - vx @ xvx @ vx.t()
+    del vinv
+    py = torch.sparse.mm(zt, pmat @ yv).reshape(-1).contiguous()
+    pvp = None
+    if need_pvp:
+        pvp = torch.sparse.mm(zt, torch.sparse.mm(zt, pmat).t().contiguous()).contiguous()     # Z' (Z' P)'
+    return py, pvp, h2d
+
+
+def device_preamble_enabled():
+    """GMAT_B200_PREAMBLE=host keeps the numpy preamble (bit-identical inputs for both engines: what the parity
+    tests against the golden files use); default is the GPU preamble."""
+    return os.environ.get("GMAT_B200_PREAMBLE", "device").lower() != "host"
+
+
 class DeviceModel(object):
     """py = Z'Py and the packed Z'PZ resident on the device."""
 
@@ -86,6 +128,18 @@ class DeviceModel(object):
         self.packed = engine.pack_pvp(pvp)
         self.h2d_bytes = self.py.numel() * 8 + pvp.numel() * 8
         del pvp
+
+    @classmethod
+    def build(cls, y, xmat, zmat, gmat_lst, var_com, device, scipy_inv=True):
+        """Preamble + upload: on the GPU by default, on the host with GMAT_B200_PREAMBLE=host."""
+        if not device_preamble_enabled():
+            pymat, pvpmat = preamble(y, xmat, zmat, gmat_lst, var_com, scipy_inv=scipy_inv)
+            return cls(pymat, pvpmat, device)
+        self = cls.__new__(cls)
+        self.py, pvp, self.h2d_bytes = preamble_device(y, xmat, zmat, gmat_lst, var_com, device)
+        self.packed = engine.pack_pvp(pvp)
+        del pvp
+        return self
 
 
 # ----------------------------------------------------------------------------------------------
@@ -117,7 +171,8 @@ def _write_rows(out_file, cols):
 def exact_scan(kind, y, xmat, zmat, gmat_lst, var_com, bed_file, snp_lst_0=None, p_cut=1.0e-5,
                out_file='epi'):
     logging.info("Calculate the phenotypic covariance matrix and inversion")
-    pymat, pvpmat = preamble(y, xmat, zmat, gmat_lst, var_com, scipy_inv=True)
+    device = engine.current_device()
+    model = DeviceModel.build(y, xmat, zmat, gmat_lst, var_com, device, scipy_inv=True)
     logging.info("Read the SNP")
     rank, world = par.rank_world()
     if rank == 0:
@@ -133,8 +188,6 @@ def exact_scan(kind, y, xmat, zmat, gmat_lst, var_com, bed_file, snp_lst_0=None,
     order = {}
     for pos, i in enumerate(snp_lst_0):
         order.setdefault(i, pos)
-    model = DeviceModel(pymat, pvpmat, store.device)
-    del pvpmat
     lut_u, lut_v = store.lut(kind.coding_u), store.lut(kind.coding_v)
     # p < p_cut  <=>  chi > isf(p_cut); the device keeps a slightly larger set, the host re-applies the
     # reference's own comparison on scipy p-values (remma_epiAA.py:77,81)
@@ -191,12 +244,10 @@ def exact_scan_parallel(kind, y, xmat, zmat, gmat_lst, var_com, bed_file, parall
 def pair_test(kind, y, xmat, zmat, gmat_lst, var_com, bed_file, snp_pair_file, max_test_pair=50000,
               p_cut=1.0e-4, out_file='epi_pair'):
     logging.info("Calculate the phenotypic covariance matrix and inversion")
-    pymat, pvpmat = preamble(y, xmat, zmat, gmat_lst, var_com, scipy_inv=False)
+    model = DeviceModel.build(y, xmat, zmat, gmat_lst, var_com, engine.current_device(), scipy_inv=False)
     logging.info("Read the SNP")
     store = load_store(bed_file)
     num_snp = store.m
-    model = DeviceModel(pymat, pvpmat, store.device)
-    del pvpmat
     lut_u, lut_v = store.lut(kind.coding_u), store.lut(kind.coding_v)
     logging.info('Test')
     np.savetxt(out_file, ['snp_0 snp_1 eff var chi p'], fmt='%s')
@@ -232,6 +283,14 @@ def pair_test(kind, y, xmat, zmat, gmat_lst, var_com, bed_file, snp_pair_file, m
 # ----------------------------------------------------------------------------------------------
 # approximate screen through the drop-in C symbols (remma_epiAA_eff.py:20-96 and copies)
 # ----------------------------------------------------------------------------------------------
+def _pymat_host(y, xmat, zmat, gmat_lst, var_com):
+    """Z'Py as a host [n,1] array for the drop-in C symbols (host pointers), computed on the GPU by default."""
+    if not device_preamble_enabled():
+        return preamble(y, xmat, zmat, gmat_lst, var_com, scipy_inv=False, need_pvp=False)[0]
+    py, _, _ = preamble_device(y, xmat, zmat, gmat_lst, var_com, engine.current_device(), need_pvp=False)
+    return np.ascontiguousarray(py.cpu().numpy().reshape(-1, 1))
+
+
 def _screen_defaults(kind, maf, snp_lst_0, num_snp):
     # quirk kept: AD _eff defaults to range(m) (remma_epiAD_eff.py:57), AD _maf_eff to range(m-1)
     # (remma_epiAD_maf_eff.py:59); both are equivalent (the last first-SNP has no j > i)
@@ -247,7 +306,7 @@ def _screen_defaults(kind, maf, snp_lst_0, num_snp):
 def eff_screen(kind, y, xmat, zmat, gmat_lst, var_com, bed_file, snp_lst_0=None, var_app=1.0, p_cut=1.0e-5,
                out_file='epi_eff'):
     logging.info("Calculate the phenotypic covariance matrix and inversion")
-    pymat, _ = preamble(y, xmat, zmat, gmat_lst, var_com, scipy_inv=False, need_pvp=False)
+    pymat = _pymat_host(y, xmat, zmat, gmat_lst, var_com)
     num_snp = engine.count_lines(bed_file + '.bim')
     num_id = engine.count_lines(bed_file + '.fam')
     snp_lst_0 = _screen_defaults(kind, False, snp_lst_0, num_snp)
@@ -298,7 +357,7 @@ def maf_eff_screen(kind, y, xmat, zmat, gmat_lst, var_com, bed_file, snp_lst_0=N
                    freq_deno=None, p_cut=1.0e-5, out_file='epi_maf_eff'):
     """remma_epiAA_maf_eff.py:20-104; ``freq2`` is the second bin vector of the AD variant (freqD)."""
     logging.info("Calculate the phenotypic covariance matrix and inversion")
-    pymat, _ = preamble(y, xmat, zmat, gmat_lst, var_com, scipy_inv=False, need_pvp=False)
+    pymat = _pymat_host(y, xmat, zmat, gmat_lst, var_com)
     num_snp = engine.count_lines(bed_file + '.bim')
     num_id = engine.count_lines(bed_file + '.fam')
     snp_lst_0 = _screen_defaults(kind, True, snp_lst_0, num_snp)
@@ -356,12 +415,11 @@ class Prepared(object):
         from ..engine import GenotypeStore
         self.kind = kind
         y, xmat, zmat = design_matrix_wemai_multi_gmat(pheno_file, bed_file)
-        pymat, pvpmat = preamble(y, xmat, zmat, gmat_lst, var_com, scipy_inv=False)
         self.raw_store = GenotypeStore(bed_file)              # what the C screen sees (no imputation)
         self.store = self.raw_store
         if self.raw_store.n_missing() > 0:
             self.store = load_store(bed_file)                 # what the numpy paths see (imputed)
-        self.model = DeviceModel(pymat, pvpmat, self.store.device)
+        self.model = DeviceModel.build(y, xmat, zmat, gmat_lst, var_com, self.store.device, scipy_inv=False)
         self.num_snp, self.num_id = self.store.m, self.store.n
 
     def pair_stats(self, pairs):

@@ -204,3 +204,20 @@ def test_approx_pipelines(grms, golden, kind, maf, tmp_path, monkeypatch):
         assert set(got) == set(want)
         for k in want:
             assert abs(got[k] - want[k]) <= RTOL * abs(want[k])
+
+
+def test_device_preamble_matches_host(grms, golden):
+    """The GPU preamble (default of the front-ends) against the host numpy restatement of
+    remma_epiAA.py:31-51 on the mouse model, without and with repeated records (3 per individual, extra I GRM)."""
+    import torch
+    from gmat_b200.remma import _core
+    from gmat_b200.uvlmm.design_matrix import design_matrix_wemai_multi_gmat
+    ag = grms["ag"]
+    cases = [(grms["pheno"], [ag, ag * ag], golden["var_com_ag_agag"]),
+             (grms["pheno_rep3"], [ag, ag * ag, np.eye(ag.shape[0])], golden["var_com_rep3"])]
+    for pheno, gl, vc in cases:
+        y, xmat, zmat = design_matrix_wemai_multi_gmat(pheno, grms["bed"])
+        py_h, pvp_h = _core.preamble(y, xmat, zmat, gl, vc, scipy_inv=True)
+        py_d, pvp_d, _ = _core.preamble_device(y, xmat, zmat, gl, vc, torch.device("cuda"))
+        np.testing.assert_allclose(py_d.cpu().numpy(), py_h.ravel(), rtol=1e-10, atol=1e-12 * np.abs(py_h).max())
+        np.testing.assert_allclose(pvp_d.cpu().numpy(), pvp_h, rtol=0, atol=1e-11 * np.abs(pvp_h).max())
