@@ -389,6 +389,27 @@ def extras(engine, torch, synth, store, model, lut, args, prefix, pymat):
                         "tflops_algorithmic_n(n+1)m": float(n2) * (n2 + 1) * m2 / t / 1e12,
                         "seconds": t, "workload": "agmat GRM kernel, synthetic n=%d x m=%d generated in HBM "
                                                   "(BASELINE configs[1])" % (n2, m2)}
+        if args.agmat_e2e:
+            # the public call on files: agmat(bed_file) = .bed/.bim/.fam read + H2D + counts + GRM kernel + D2H +
+            # the 2.5 GB '%.18e' text file the reference format demands (written by all host threads)
+            from gmat_b200.gmatrix import agmat
+            d = tempfile.mkdtemp(prefix="gmat_agmat_e2e_")
+            pre = os.path.join(d, "c2")
+            with open(pre + ".bed", "wb") as f:
+                f.write(bytes([0x6c, 0x1b, 0x01]))
+                f.write(payload[:, :(n2 + 3) // 4].contiguous().cpu().numpy().tobytes())
+            with open(pre + ".bim", "w") as f:
+                f.write("".join("1 snp%d 0 %d A T\n" % (j, j + 1) for j in range(m2)))
+            with open(pre + ".fam", "w") as f:
+                f.write("".join("fam%d id%d 0 0 0 -9\n" % (k, k) for k in range(n2)))
+            t0 = time.perf_counter()
+            agmat(pre)
+            dt = time.perf_counter() - t0
+            out["agmat"]["e2e"] = {"seconds": dt, "tflops_algorithmic_n(n+1)m": float(n2) * (n2 + 1) * m2 / dt / 1e12,
+                                   "text_bytes": os.path.getsize(pre + ".agrm0"),
+                                   "what": "gmat_b200.gmatrix.agmat(bed_file): file read + H2D + GRM + D2H + .agrm0 text"}
+            for ext in (".bed", ".bim", ".fam", ".agrm0"):
+                os.remove(pre + ext)
         del kin, st2, payload
     return out
 
@@ -402,6 +423,7 @@ def main():
     ap.add_argument("--no-extra", action="store_true", help="skip the approx/GRM/decode secondary numbers")
     ap.add_argument("--no-grm", action="store_true")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--agmat-e2e", action="store_true", help="also time agmat(bed_file) on files (writes ~4 GB)")
     ap.add_argument("--grm-n", type=int, default=10000)
     ap.add_argument("--grm-m", type=int, default=500000)
     args = ap.parse_args()

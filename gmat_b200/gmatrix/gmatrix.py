@@ -10,13 +10,17 @@ import pandas as pd
 import torch
 
 from .. import engine
+from .._ffi import check, ffi, lib
 from ..process_plink.process_plink import load_store
 
 
 def output_mat(mat, id, out_file, out_fmt):
     """Same three formats as gmatrix.py:10-31."""
     if out_fmt == 'mat':
-        np.savetxt(out_file + '0', mat)
+        # same bytes as np.savetxt(out_file + '0', mat), formatted by all host threads (include/gmat_b200.h)
+        mat = np.ascontiguousarray(mat, dtype=np.float64)
+        check(lib.gmat_b200_savetxt_host((out_file + '0').encode(), ffi.cast("double *", mat.ctypes.data),
+                                         mat.shape[0], mat.shape[1], 0), "gmat_b200_savetxt_host")
     elif out_fmt == 'row_col_val':
         ind = np.tril_indices_from(mat)
         df = pd.DataFrame({"row": ind[0] + 1, "col": ind[1] + 1, "val": mat[ind]})

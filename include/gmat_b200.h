@@ -175,6 +175,11 @@ int gmat_b200_grm(const unsigned char *bed_dev, long long n, long long m, long l
                   const double *lut_dev, long long snp_begin, long long snp_end,
                   double scale, double small_val, int accumulate, double *K_dev, void *stream);
 
+/* Host text writer, byte-identical to np.savetxt(path, mat) as used by output_mat (gmat/gmatrix/gmatrix.py:10-14:
+ * '%.18e', ' ' delimiter, '\n'): rows formatted in parallel by `threads` host threads (<= 0: all).  No GPU work. */
+int gmat_b200_savetxt_host(const char *path, const double *mat /* HOST [rows][cols] */, long long rows,
+                           long long cols, int threads);
+
 #ifdef __cplusplus
 }
 #endif

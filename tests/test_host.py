@@ -187,3 +187,21 @@ def test_two_rank_hit_gather_gloo(tmp_path):
     outs = [p.communicate(timeout=240)[0] for p in procs]
     assert all(p.returncode == 0 for p in procs), outs
     assert "GLOO_OK" in outs[0]
+
+
+def test_savetxt_host_is_byte_identical_to_numpy(tmp_path):
+    """gmat_b200_savetxt_host == np.savetxt(path, mat) (the 'mat' output of agmat, gmatrix.py:10-14), no GPU."""
+    from gmat_b200._ffi import ffi, lib
+    rng = np.random.Generator(np.random.PCG64(4))
+    mats = [rng.normal(size=(37, 53)) * 10.0 ** rng.integers(-30, 30, size=(37, 53)),
+            np.array([[0.0, -0.0, 1.0, -1.0, 1e-310, 1.7976931348623157e308, 5e-324, 0.1, 1 / 3]]),
+            rng.normal(size=(1300, 7)), np.zeros((0, 4)), rng.normal(size=(5, 1))]
+    for k, mat in enumerate(mats):
+        mat = np.ascontiguousarray(mat)
+        a, b = str(tmp_path / ("np%d.txt" % k)), str(tmp_path / ("c%d.txt" % k))
+        np.savetxt(a, mat)
+        for threads in (1, 0):
+            assert lib.gmat_b200_savetxt_host(b.encode(), ffi.cast("double *", mat.ctypes.data), mat.shape[0],
+                                              mat.shape[1], threads) == 1
+            assert open(a, "rb").read() == open(b, "rb").read()
+    assert lib.gmat_b200_savetxt_host(str(tmp_path / "no" / "dir.txt").encode(), ffi.NULL, 0, 0, 1) == -2
