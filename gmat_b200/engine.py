@@ -38,6 +38,20 @@ def _stream():
     return ffi.cast("void *", torch.cuda.current_stream().cuda_stream)
 
 
+def sparse_incidence(zmat, device):
+    """scipy CSR/COO incidence matrix Z (records x individuals) -> coalesced torch sparse COO float64 on the
+    device, and the bytes uploaded."""
+    import warnings
+    zc = zmat.tocoo()
+    idx = torch.as_tensor(np.vstack([zc.row, zc.col]).astype(np.int64)).to(device)
+    val = torch.as_tensor(np.asarray(zc.data, dtype=np.float64)).to(device)
+    with warnings.catch_warnings():
+        warnings.filterwarnings("ignore", message="Sparse invariant checks")
+        zs = torch.sparse_coo_tensor(idx, val, size=tuple(zc.shape), dtype=torch.float64, device=device,
+                                     check_invariants=False).coalesce()
+    return zs, idx.numel() * 8 + val.numel() * 8
+
+
 def count_lines(path):
     """Row count of a .bim/.fam file (the reference counts rows with pd.read_csv(header=None),
     gmat/remma/remma_epiAA/remma_epiAA_eff.py:55-56)."""

@@ -88,12 +88,9 @@ def preamble_device(y, xmat, zmat, gmat_lst, var_com, device, need_pvp=True):
     yv = torch.as_tensor(np.ascontiguousarray(np.array(y, dtype=np.float64).reshape(-1, 1))).to(device)
     n_rec = yv.shape[0]
     xm = torch.as_tensor(np.ascontiguousarray(np.array(xmat, dtype=np.float64).reshape(n_rec, -1))).to(device)
-    zc = zmat.tocoo()
-    idx = torch.as_tensor(np.vstack([zc.row, zc.col]).astype(np.int64)).to(device)
-    val = torch.as_tensor(np.asarray(zc.data, dtype=np.float64)).to(device)
-    zs = torch.sparse_coo_tensor(idx, val, size=tuple(zc.shape), dtype=f64, device=device).coalesce()
+    zs, zbytes = engine.sparse_incidence(zmat, device)
     zt = zs.t().coalesce()
-    h2d = yv.numel() * 8 + xm.numel() * 8 + idx.numel() * 8 + val.numel() * 8
+    h2d = yv.numel() * 8 + xm.numel() * 8 + zbytes
     vmat = torch.eye(n_rec, dtype=f64, device=device) * float(var_com[-1])
     for k in range(len(gmat_lst)):
         g = torch.as_tensor(np.ascontiguousarray(gmat_lst[k], dtype=np.float64)).to(device)

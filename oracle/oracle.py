@@ -284,3 +284,44 @@ def parallel_lists(num_snp, parallel, all_pairs=False):
     if parallel[1] == 1:
         p3 = num_snp if all_pairs else num_snp - 1
     return list(range(p0, p1)) + list(range(p2, p3)), [p0, p1, p2, p3]
+
+
+# ---------------------------------------------------------------- REML (row f3), numpy restatement
+def wemai_multi_gmat(y, xmat, zmat, gmat_lst, init=None, maxiter=200, cc_par=1.0e-8, cc_gra=1.0e-6):
+    """gmat/uvlmm/uvlmm_varcom.py:8-104 restated: weighted EM + AI REML.  Pinned by tests/test_oracle.py against
+    the reference's own golden vector (examples/remma/remma_cpu.py:178) and the fixtures of make_golden.py."""
+    var_com = np.array([1.0] * (len(gmat_lst) + 1) if init is None else init[:], dtype=np.float64)
+    y = np.array(y).reshape(-1, 1)
+    n = y.shape[0]
+    xmat = np.array(xmat).reshape(n, -1)
+    zg = [zmat.dot((zmat.dot(g)).T) for g in gmat_lst]
+    for _ in range(maxiter):
+        vmat = np.diag([var_com[-1]] * n)
+        for k in range(len(zg)):
+            vmat += zg[k] * var_com[k]
+        vmat = np.linalg.inv(vmat)
+        vx = np.dot(vmat, xmat)
+        xvx = np.linalg.inv(np.dot(xmat.T, vx))
+        pmat = vmat - reduce(np.dot, [vx, xvx, vx.T])
+        py = np.dot(pmat, y)
+        fd, wv = [], []
+        for k in range(len(zg)):
+            fd.append(0.5 * np.sum(-np.trace(np.dot(pmat, zg[k])) + reduce(np.dot, [py.T, zg[k], py])))
+            wv.append(np.dot(zg[k], py))
+        fd.append(0.5 * np.sum(-np.trace(pmat) + np.dot(py.T, py)))
+        fd = np.array(fd)
+        wv.append(py)
+        wv = np.concatenate(wv, axis=1)
+        ai = 0.5 * reduce(np.dot, [wv.T, pmat, wv])
+        em = np.diag([n / (v * v) for v in var_com])
+        for j in range(0, 101):
+            w = j * 0.01
+            delta = np.dot(np.linalg.inv((1 - w) * ai + w * em), fd)
+            new = var_com + delta
+            if min(new) > 0:
+                break
+        cc_par_val = np.sqrt(np.sum(delta * delta) / np.sum(new * new))
+        var_com = new[:]
+        if np.sqrt(np.sum(fd * fd)) < cc_gra and cc_par_val < cc_par:
+            break
+    return var_com

@@ -221,3 +221,17 @@ def test_device_preamble_matches_host(grms, golden):
         py_d, pvp_d, _ = _core.preamble_device(y, xmat, zmat, gl, vc, torch.device("cuda"))
         np.testing.assert_allclose(py_d.cpu().numpy(), py_h.ravel(), rtol=1e-10, atol=1e-12 * np.abs(py_h).max())
         np.testing.assert_allclose(pvp_d.cpu().numpy(), pvp_h, rtol=0, atol=1e-11 * np.abs(pvp_h).max())
+
+
+def test_reml_wemai_multi_gmat_matches_reference(grms, golden, tmp_path):
+    """gmat_b200.uvlmm.wemai_multi_gmat (GPU REML) against the reference's variance components
+    on mouse for both model lists; the first equals the reference's own golden vector remma_cpu.py:178."""
+    from gmat_b200.uvlmm import wemai_multi_gmat
+    ag, dg = grms["ag"], grms["dg"]
+    out = str(tmp_path / "var.txt")
+    vc = wemai_multi_gmat(grms["pheno"], grms["bed"], [ag, ag * ag], out_file=out)
+    np.testing.assert_allclose(vc, golden["var_com_ag_agag"], rtol=1e-6)
+    assert [round(float(v), 8) for v in vc] == [0.06289206, 0.07641075, 0.08121168]
+    np.testing.assert_allclose(np.loadtxt(out), vc, rtol=0, atol=0)
+    vc2 = wemai_multi_gmat(grms["pheno"], grms["bed"], [ag, dg, ag * ag], out_file=out)
+    np.testing.assert_allclose(vc2, golden["var_com_ag_dg_agag"], rtol=1e-5)

@@ -110,3 +110,12 @@ def test_parallel_partition_matches_reference(golden):
 def test_reference_golden_vector(golden):
     """The reference's only own known answer: examples/remma/remma_cpu.py:178."""
     np.testing.assert_allclose(golden["var_com_ag_agag"], [0.06289206, 0.07641075, 0.08121168], atol=5e-9)
+
+
+def test_reml_restatement_matches_reference(golden, mouse_model):
+    """oracle.wemai_multi_gmat against the variance components the unmodified reference produced on mouse
+    (== the reference's own golden vector, examples/remma/remma_cpu.py:178, to its 8 printed digits)."""
+    M = mouse_model
+    vc = oracle.wemai_multi_gmat(M["y"], M["xmat"], M["zmat"], M["gl_aa"])
+    np.testing.assert_allclose(vc, golden["var_com_ag_agag"], rtol=1e-7)
+    assert [round(float(v), 8) for v in vc] == [0.06289206, 0.07641075, 0.08121168]
