@@ -20,6 +20,8 @@ What is produced, and the reference entry point each file pins:
   out/epiXX_maf_approx.txt (+ aux)         MAF-binned pipeline (remma_epiAA_maf_approx.py:11)
   out/epiAA_rep3.txt                       repeated-measures exact scan on a first-SNP subset
   out/epiAA_parallel.{1,2}                 _parallel parts (remma_epiAA.py:143)
+  out/epiAD.anno_* epiAD.ld_table          annotation_snp_pos on out/epiAD.txt (annotation.py:22); made by the
+                                           snippet in this file's annotation_golden()
 """
 import json
 import logging
@@ -42,6 +44,29 @@ SRC = os.path.join(ref_harness.REF_ROOT, "examples", "data", "mouse")
 
 def flt(a):
     return [float(x) for x in np.asarray(a).ravel()]
+
+
+def annotation_golden():
+    """annotation_snp_pos fixtures from the unmodified reference (run after main(); needs out/epiAD.txt)."""
+    ref_harness.install()
+    from gmat.remma.annotation import annotation_snp_pos as ref_anno
+    work = tempfile.mkdtemp()
+    shutil.copyfile(os.path.join(GOLD, "mouse", "plink.bim"), os.path.join(work, "plink.bim"))
+    res = os.path.join(work, "epiAD.txt")
+    shutil.copyfile(os.path.join(GOLD, "out", "epiAD.txt"), res)
+    rows = [line.split() for line in open(res).read().splitlines()[1:]]
+    bim = [line.split() for line in open(os.path.join(work, "plink.bim"))]
+    with open(os.path.join(work, "ld.txt"), "w") as f:       # plink --r2 style table: 5 linked, 5 weak pairs
+        f.write(" CHR_A BP_A SNP_A CHR_B BP_B SNP_B R2\n")
+        for k, r in enumerate(rows[:10]):
+            a, b = bim[int(r[0])], bim[int(r[1])]
+            f.write(" %s %s %s %s %s %s %s\n" % (a[0], a[3], a[1], b[0], b[3], b[1], "0.9" if k < 5 else "0.1"))
+    ref_anno(res, os.path.join(work, "plink"), p_cut=1.0e-5, dis=0)
+    shutil.copyfile(res + ".anno", os.path.join(GOLD, "out", "epiAD.anno_p1e-5"))
+    ref_anno(res, os.path.join(work, "plink"), p_cut=1, dis=5.0e7, ld_file=os.path.join(work, "ld.txt"), r2=0.2)
+    shutil.copyfile(res + ".anno", os.path.join(GOLD, "out", "epiAD.anno_dis5e7"))
+    shutil.copyfile(res + ".anno.ld", os.path.join(GOLD, "out", "epiAD.anno_dis5e7.ld"))
+    shutil.copyfile(os.path.join(work, "ld.txt"), os.path.join(GOLD, "out", "epiAD.ld_table"))
 
 
 def main():
@@ -241,3 +266,4 @@ def main():
 
 if __name__ == "__main__":
     main()
+    annotation_golden()

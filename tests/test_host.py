@@ -205,3 +205,19 @@ def test_savetxt_host_is_byte_identical_to_numpy(tmp_path):
                                               mat.shape[1], threads) == 1
             assert open(a, "rb").read() == open(b, "rb").read()
     assert lib.gmat_b200_savetxt_host(str(tmp_path / "no" / "dir.txt").encode(), ffi.NULL, 0, 0, 1) == -2
+
+
+def test_annotation_snp_pos_matches_reference(tmp_path):
+    """annotation_snp_pos (README step 4, gmat/remma/annotation.py:22-74) against files written by the unmodified
+    reference (fixtures made in the build container: p_cut filter, distance filter, LD filter)."""
+    import shutil
+    from gmat_b200.remma.annotation import annotation_snp_pos
+    out = os.path.join(GOLD, "out")
+    res = str(tmp_path / "epiAD.txt")
+    shutil.copyfile(os.path.join(out, "epiAD.txt"), res)
+    bed = os.path.join(GOLD, "mouse", "plink")
+    assert annotation_snp_pos(res, bed, p_cut=1.0e-5, dis=0) == 0
+    assert open(res + ".anno").read() == open(os.path.join(out, "epiAD.anno_p1e-5")).read()
+    assert annotation_snp_pos(res, bed, p_cut=1, dis=5.0e7, ld_file=os.path.join(out, "epiAD.ld_table"), r2=0.2) == 0
+    assert open(res + ".anno").read() == open(os.path.join(out, "epiAD.anno_dis5e7")).read()
+    assert open(res + ".anno.ld").read() == open(os.path.join(out, "epiAD.anno_dis5e7.ld")).read()
