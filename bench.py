@@ -51,6 +51,23 @@ def f_exact(n):
     return 2.0 * n * n + 5.0 * n
 
 
+def exact_issued_flop_per_pair(n, bm=128):
+    """DMMA flop the exact kernel issues per pair (gmat_b200/csrc/exact.cu): per 128-row block and per warp row
+    (64 rows) the slabs left of / inside the warp's diagonal sub-block, the upper-right quarter of the diagonal
+    block skipped, slabs past n skipped, and in the last block only the m-tile pairs that hold a row below n."""
+    nb = (n + bm - 1) // bm
+    kslabs = (n + 15) // 16
+    flop = 0.0
+    for mb in range(nb):
+        diag0, nks = mb * (bm // 16), (mb + 1) * (bm // 16)
+        for wm in (0, 1):
+            rows_left = n - (mb * bm + wm * 64)
+            mtv = 8 if rows_left >= 64 else (0 if rows_left <= 0 else (rows_left + 15) // 16 * 2)
+            mma_end = min(nks if wm else diag0 + bm // 32, kslabs)
+            flop += 2.0 * (mtv * 8) * 16 * mma_end
+    return flop
+
+
 def batch_first_snps(m, rank, world, batch=BATCH):
     """``batch`` first-SNPs as contiguous blocks of 8 (one I-block of the scan tiling -- what a full scan
     hands the kernel), the blocks spread evenly over [0, m-1) and offset per rank so ranks take disjoint batches."""
@@ -292,9 +309,7 @@ def run_gpu(args):
         lib.gmat_b200_exact_config(cfg, cfg + 1, cfg + 2)
         bm, bn = int(cfg[0]), int(cfg[1])
         nb = (n + bm - 1) // bm
-        # DMMA flop the kernel issues per pair: the strictly lower bm x bm blocks plus 3 of the 4 (bm/2)^2 quarters
-        # of every diagonal block (exact.cu: the upper-right quarter is never multiplied)
-        issued = pairs_rank * 2.0 * bm * bm * (nb * (nb - 1) / 2 + 0.75 * nb) / (ms * 1e-3) / 1e12
+        issued = pairs_rank * exact_issued_flop_per_pair(n, bm) / (ms * 1e-3) / 1e12
         line = {
             "metric": METRIC, "value": value, "unit": "pairs/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",

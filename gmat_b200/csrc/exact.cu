@@ -193,6 +193,31 @@ __device__ __forceinline__ void exact_row_epilogue_prod(const double (&acc)[MT][
     }
 }
 
+// One K slab (16 individuals) of DMMAs for the first MTV of the warp's 8 m-tiles.  MTV < 8 is used in the last row
+// block, where the rows past n are padding: with n = 5000 only 8 of its 128 rows exist, and that block has the
+// longest K loop of all (it is 5 % of the kernel).
+template <int MTV, int NTL>
+__device__ __forceinline__ void exact_slab_mma(double (&acc)[8][NTL][2], const double2 *Af, int frag0, int lane,
+                                               const char *const (&pb)[NTL], const unsigned (&z)[NTL]) {
+    constexpr int SPB = RB_BM / EX_BK;
+#pragma unroll
+    for (int k4 = 0; k4 < EX_BK / 4; ++k4) {
+        double af[MTV], bf[NTL];
+#pragma unroll
+        for (int a2 = 0; a2 < MTV / 2; ++a2) {
+            const double2 v = Af[(k4 * SPB + frag0 + a2) * 32 + lane];
+            af[2 * a2] = v.x; af[2 * a2 + 1] = v.y;
+        }
+#pragma unroll
+        for (int b = 0; b < NTL; ++b)
+            bf[b] = *reinterpret_cast<const double *>(pb[b] + ((z[b] >> (8 * k4)) & 0xffu));
+#pragma unroll
+        for (int a = 0; a < MTV; ++a)
+#pragma unroll
+            for (int b = 0; b < NTL; ++b) dmma884(acc[a][b][0], acc[a][b][1], af[a], bf[b]);
+    }
+}
+
 template <int BN, int NS, int CTAS_PER_SM, bool PAIR_MODE>
 // Register budget: the file is 16 K registers per SM sub-partition, so what matters is warps per sub-partition.
 // Four producer warps (one per sub-partition, three of them idle) keep the CTA symmetric: the kernel starts at
@@ -332,7 +357,13 @@ epi_exact_rb_kernel(const ExactParams p) {
             // diagonal sub-block counts twice, the sub-block itself once, and what lies right of it (the upper
             // right quarter of the 128 x 128 diagonal block, warp row 0 only) is not multiplied at all.
             const long long dbl_at = diag0 + (wm ? SPB / 2 : 0);
-            const long long mma_end = wm ? nks : diag0 + SPB / 2;
+            long long mma_end = wm ? nks : diag0 + SPB / 2;
+            // padding: columns past n are zero in packed A (skip their slabs), and of this warp's 8 m-tiles only
+            // those with a row below n need multiplying (pairs of m-tiles: fragments are loaded two at a time)
+            const long long kslabs = (p.n + EX_BK - 1) / EX_BK;
+            if (mma_end > kslabs) mma_end = kslabs;
+            const long long rows_left = p.n - (mb * BM + wm * 64);
+            const int mtv = rows_left >= 64 ? 8 : (rows_left <= 0 ? 0 : (int)((rows_left + 15) / 16) * 2);
             for (long long ks = 0; ks < nks; ++ks) {
                 if (ks == dbl_at && ks > 0) {
 #pragma unroll
@@ -355,22 +386,12 @@ epi_exact_rb_kernel(const ExactParams p) {
                 load_codes((ks + 1 < nks) ? ks + 1 : 0);                 // next slab's codes travel under the MMAs
                 mbar_wait(&S.full[stage], fphase);
                 const double2 *Af = reinterpret_cast<const double2 *>(S.A[stage]);
-                if (ks < mma_end)
-#pragma unroll
-                for (int k4 = 0; k4 < EX_BK / 4; ++k4) {
-                    double af[MT], bf[NTL];
-#pragma unroll
-                    for (int a2 = 0; a2 < MT / 2; ++a2) {
-                        const double2 v = Af[(k4 * SPB + wm * (MT / 2) + a2) * 32 + lane];
-                        af[2 * a2] = v.x; af[2 * a2 + 1] = v.y;
-                    }
-#pragma unroll
-                    for (int b = 0; b < NTL; ++b)
-                        bf[b] = *reinterpret_cast<const double *>(pb[b] + ((z[b] >> (8 * k4)) & 0xffu));
-#pragma unroll
-                    for (int a = 0; a < MT; ++a)
-#pragma unroll
-                        for (int b = 0; b < NTL; ++b) dmma884(acc[a][b][0], acc[a][b][1], af[a], bf[b]);
+                if (ks < mma_end) {
+                    const int frag0 = wm * (MT / 2);
+                    if (mtv == 8) exact_slab_mma<8, NTL>(acc, Af, frag0, lane, pb, z);
+                    else if (mtv == 6) exact_slab_mma<6, NTL>(acc, Af, frag0, lane, pb, z);
+                    else if (mtv == 4) exact_slab_mma<4, NTL>(acc, Af, frag0, lane, pb, z);
+                    else if (mtv == 2) exact_slab_mma<2, NTL>(acc, Af, frag0, lane, pb, z);
                 }
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&S.empty[stage]);
