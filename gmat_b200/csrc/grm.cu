@@ -30,7 +30,7 @@ constexpr int GR_T = 128;           // output tile edge (individuals)
 constexpr int GR_GS = 64;           // SNPs per ring stage
 constexpr int GR_NS = 4;            // ring depth
 constexpr int GR_CW = 8;            // consumer warps (2 x 4)
-constexpr int GR_PW = 4;            // producer warps (one per SM sub-partition; only the first one works)
+constexpr int GR_PW = 4;            // producer warps (one per SM sub-partition): 128 lanes, one row piece each per stage
 
 struct GrmParams {
     const unsigned char *bed;
@@ -41,7 +41,7 @@ struct GrmParams {
     int accumulate;
     double *K;
     long long nblk;
-    int split2;
+    int split2;                     // 0: cost-balanced stream-K ranges, 1: two CTAs per tile, 2: one tile per CTA
 };
 
 struct GrmSmem {
@@ -58,6 +58,41 @@ __device__ __forceinline__ void grm_tile_of(long long tile, long long &mi, long 
     ni = tile - mi * (mi + 1) / 2;
 }
 
+// One ring stage (64 SNPs) of DMMAs for the first MTV of the warp's 8 row m-tiles.  MTV < 8 only in the last block
+// row, whose rows past n are padding (n = 10,000: 16 of its 128 rows exist).
+template <int MTV, int NTL>
+__device__ __forceinline__ void grm_stage_mma(double (&acc)[8][NTL][2], const unsigned char (*cA)[32],
+                                              const unsigned char (*cB)[32], const double (*lut)[4], int wm, int wn,
+                                              int t, int sh0, int sh1) {
+#pragma unroll 4
+    for (int k4 = 0; k4 < GR_GS / 4; ++k4) {
+        const int r = k4 * 4 + t;                    // this lane's SNP of the step
+        const uint4 wa = *reinterpret_cast<const uint4 *>(&cA[r][wm * 16]);
+        const uint2 wb = *reinterpret_cast<const uint2 *>(&cB[r][wn * 8]);
+        const char *lb = reinterpret_cast<const char *>(&lut[r][0]);
+        const unsigned wav[4] = {wa.x, wa.y, wa.z, wa.w};
+        const unsigned wbv[2] = {wb.x, wb.y};
+        double af[MTV], bf[NTL];
+        // individual 8a + g of the warp's rows: code bits 16*(a&1) + 2g of word a >> 1
+#pragma unroll
+        for (int a = 0; a < MTV; ++a)
+            af[a] = *reinterpret_cast<const double *>(lb + (((wav[a >> 1] >> ((a & 1) ? sh1 : sh0)) & 3u) << 3));
+#pragma unroll
+        for (int b = 0; b < NTL; ++b)
+            bf[b] = *reinterpret_cast<const double *>(lb + (((wbv[b >> 1] >> ((b & 1) ? sh1 : sh0)) & 3u) << 3));
+#pragma unroll
+        for (int a = 0; a < MTV; ++a)
+#pragma unroll
+            for (int b = 0; b < NTL; ++b) dmma884(acc[a][b][0], acc[a][b][1], af[a], bf[b]);
+    }
+}
+
+// m-tiles (in pairs) of warp row wm of block row mi that hold an individual below n
+__device__ __forceinline__ int grm_mtv(long long n, long long mi, int wm) {
+    const long long left = n - (mi * GR_T + wm * 64);
+    return left >= 64 ? 8 : (left <= 0 ? 0 : (int)((left + 15) / 16) * 2);
+}
+
 __global__ void __launch_bounds__((GR_CW + GR_PW) * 32, 1) grm_kernel(const GrmParams p) {
     constexpr int MT = 8, NTL = 4;                   // warp tile 64 x 32
     extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -67,14 +102,29 @@ __global__ void __launch_bounds__((GR_CW + GR_PW) * 32, 1) grm_kernel(const GrmP
     const long long ntiles = p.nblk * (p.nblk + 1) / 2;
     // stream-K: this CTA's contiguous share of the ntiles x nstage units (split2: two CTAs per tile, half each)
     long long u_begin, u_end;
-    if (p.split2) {
+    if (p.split2 == 2) {                             // one whole tile per CTA
+        u_begin = (long long)blockIdx.x * nstage;
+        u_end = u_begin + nstage;
+    } else if (p.split2 == 1) {
         const long long tile = blockIdx.x >> 1, half = (nstage + 1) / 2;
         u_begin = tile * nstage + ((blockIdx.x & 1) ? half : 0);
         u_end = tile * nstage + ((blockIdx.x & 1) ? nstage : half);
     } else {
-        const long long units = ntiles * nstage, q = units / gridDim.x, rem = units % gridDim.x;
-        u_begin = q * blockIdx.x + (rem < blockIdx.x ? rem : blockIdx.x);
-        u_end = u_begin + q + (blockIdx.x < rem ? 1 : 0);
+        // equal COST per CTA: a stage of a full tile costs 16 (m-tile pairs x 2 warp rows), a stage of the last
+        // block row only what its non-padding m-tiles cost; tiles are numbered row-major, the last row last
+        const long long nfull = ntiles - p.nblk, ufull = nfull * nstage;
+        // (floor of 4: a stage costs its barrier round trip and 129 bulk copies however few DMMAs it has)
+        long long w_last = grm_mtv(p.n, p.nblk - 1, 0) + grm_mtv(p.n, p.nblk - 1, 1);            // 2 .. 16
+        if (w_last < 4) w_last = 4;
+        const long long total = 16 * ufull + w_last * p.nblk * nstage;
+        auto unit_at = [&](long long c) {            // first unit whose cost prefix reaches c
+            if (c <= 16 * ufull) return (c + 15) / 16;
+            return ufull + (c - 16 * ufull + w_last - 1) / w_last;
+        };
+        u_begin = unit_at(total / gridDim.x * blockIdx.x + total % gridDim.x * blockIdx.x / gridDim.x);
+        u_end = (blockIdx.x + 1 == gridDim.x)
+                    ? ntiles * nstage
+                    : unit_at(total / gridDim.x * (blockIdx.x + 1) + total % gridDim.x * (blockIdx.x + 1) / gridDim.x);
     }
 
     if (tid == 0) {
@@ -89,7 +139,11 @@ __global__ void __launch_bounds__((GR_CW + GR_PW) * 32, 1) grm_kernel(const GrmP
     if (warp >= GR_CW) {
         // =============================== producer ========================================================
         asm volatile("setmaxnreg.dec.sync.aligned.u32 40;\n");
-        if (warp != GR_CW) return;
+        // all four producer warps work: 128 lanes, one 32 B row piece each per stage (64 SNPs x 2 operands); a single
+        // warp issuing all 129 copies took ~2300 clocks per stage, which is more than a stage of a padded
+        // last-row tile needs for its DMMAs
+        const int pl = (warp - GR_CW) * 32 + lane;   // 0..127
+        const int prow = pl & (GR_GS - 1), pop = pl >> 6;           // SNP of the stage, operand (0: rows, 1: columns)
         int stage = 0;
         unsigned use_odd = 0;
         bool first_pass = true;
@@ -109,23 +163,22 @@ __global__ void __launch_bounds__((GR_CW + GR_PW) * 32, 1) grm_kernel(const GrmP
                 const long long s0 = p.snp_begin + st * GR_GS;
                 const long long left = p.snp_end - s0;
                 const int nvalid = left < GR_GS ? (int)left : GR_GS;
-                if (lane == 0) {
-                    // table rows of SNPs past the end are zero (plain stores, released by the arrive below)
+                if (pl == 0) {
+                    // table rows of SNPs past the end are zero (plain stores, released by the arrive below).  The
+                    // other lanes' copies may complete before this expect_tx: the phase cannot, it still waits for
+                    // this arrival, and the transaction count is allowed to run negative in between.
                     for (int r = nvalid; r < GR_GS; ++r)
 #pragma unroll
                         for (int c = 0; c < 4; ++c) S.lut[stage][r][c] = 0.0;
                     mbar_expect_tx(&S.full[stage], (unsigned)GR_GS * (bytesA + bytesB) + (unsigned)nvalid * 32u);
                     tma_bulk_g2s(S.lut[stage], p.lut + s0 * 4, (unsigned)nvalid * 32u, &S.full[stage]);
                 }
-                __syncwarp();
-#pragma unroll
-                for (int h = 0; h < GR_GS / 32; ++h) {
-                    const int r = h * 32 + lane;
+                {
                     // SNPs past the end re-read the last valid row; their value table is zero
-                    const long long snp = s0 + (r < nvalid ? r : nvalid - 1);
+                    const long long snp = s0 + (prow < nvalid ? prow : nvalid - 1);
                     const unsigned char *row = p.bed + snp * p.row_bytes;
-                    tma_bulk_g2s(S.cA[stage][r], row + offA, bytesA, &S.full[stage]);
-                    tma_bulk_g2s(S.cB[stage][r], row + offB, bytesB, &S.full[stage]);
+                    if (pop == 0) tma_bulk_g2s(S.cA[stage][prow], row + offA, bytesA, &S.full[stage]);
+                    else tma_bulk_g2s(S.cB[stage][prow], row + offB, bytesB, &S.full[stage]);
                 }
                 if (++stage == GR_NS) { stage = 0; use_odd ^= 1u; first_pass = false; }
             }
@@ -147,6 +200,7 @@ __global__ void __launch_bounds__((GR_CW + GR_PW) * 32, 1) grm_kernel(const GrmP
         const bool partial = (st_end - st_begin) != nstage;
         long long mi, ni;
         grm_tile_of(tile, mi, ni);
+        const int mtv = grm_mtv(p.n, mi, wm);
         double acc[MT][NTL][2];
 #pragma unroll
         for (int a = 0; a < MT; ++a)
@@ -155,27 +209,10 @@ __global__ void __launch_bounds__((GR_CW + GR_PW) * 32, 1) grm_kernel(const GrmP
 
         for (long long st = st_begin; st < st_end; ++st) {
             mbar_wait(&S.full[stage], fphase);
-#pragma unroll 4
-            for (int k4 = 0; k4 < GR_GS / 4; ++k4) {
-                const int r = k4 * 4 + t;            // this lane's SNP of the step
-                const uint4 wa = *reinterpret_cast<const uint4 *>(&S.cA[stage][r][wm * 16]);
-                const uint2 wb = *reinterpret_cast<const uint2 *>(&S.cB[stage][r][wn * 8]);
-                const char *lb = reinterpret_cast<const char *>(&S.lut[stage][r][0]);
-                const unsigned wav[4] = {wa.x, wa.y, wa.z, wa.w};
-                const unsigned wbv[2] = {wb.x, wb.y};
-                double af[MT], bf[NTL];
-                // individual 8a + g of the warp's rows: code bits 16*(a&1) + 2g of word a >> 1
-#pragma unroll
-                for (int a = 0; a < MT; ++a)
-                    af[a] = *reinterpret_cast<const double *>(lb + (((wav[a >> 1] >> ((a & 1) ? sh1 : sh0)) & 3u) << 3));
-#pragma unroll
-                for (int b = 0; b < NTL; ++b)
-                    bf[b] = *reinterpret_cast<const double *>(lb + (((wbv[b >> 1] >> ((b & 1) ? sh1 : sh0)) & 3u) << 3));
-#pragma unroll
-                for (int a = 0; a < MT; ++a)
-#pragma unroll
-                    for (int b = 0; b < NTL; ++b) dmma884(acc[a][b][0], acc[a][b][1], af[a], bf[b]);
-            }
+            if (mtv == 8) grm_stage_mma<8, NTL>(acc, S.cA[stage], S.cB[stage], S.lut[stage], wm, wn, t, sh0, sh1);
+            else if (mtv == 6) grm_stage_mma<6, NTL>(acc, S.cA[stage], S.cB[stage], S.lut[stage], wm, wn, t, sh0, sh1);
+            else if (mtv == 4) grm_stage_mma<4, NTL>(acc, S.cA[stage], S.cB[stage], S.lut[stage], wm, wn, t, sh0, sh1);
+            else if (mtv == 2) grm_stage_mma<2, NTL>(acc, S.cA[stage], S.cB[stage], S.lut[stage], wm, wn, t, sh0, sh1);
             __syncwarp();
             if (lane == 0) mbar_arrive(&S.empty[stage]);
             if (++stage == GR_NS) { stage = 0; fphase ^= 1u; }
@@ -245,7 +282,7 @@ extern "C" int gmat_b200_grm(const unsigned char *bed_dev, long long n, long lon
     p.split2 = 0;
     if (ntiles < grid) {
         if (2 * ntiles <= grid && nstage >= 2) { grid = 2 * ntiles; p.split2 = 1; }
-        else grid = ntiles;
+        else { grid = ntiles; p.split2 = 2; }
     }
     if (!accumulate) GB_CUDA(cudaMemsetAsync(K_dev, 0, sizeof(double) * (size_t)n * (size_t)n, (cudaStream_t)stream));
     kern<<<(unsigned)grid, (GR_CW + GR_PW) * 32, smem, (cudaStream_t)stream>>>(p);
