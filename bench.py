@@ -21,7 +21,9 @@ import time
 # torchrun exports OMP_NUM_THREADS=1 for every rank when it is unset; the host-side parts of the end-to-end call
 # (numpy/BLAS in the design-matrix and file stages) then crawl.  Give each rank its share of the host cores.
 if int(os.environ.get("LOCAL_WORLD_SIZE", "1")) > 1 and os.environ.get("OMP_NUM_THREADS", "1") == "1":
-    _thr = str(max(1, (os.cpu_count() or 1) // int(os.environ["LOCAL_WORLD_SIZE"])))
+    # (the reference arm runs on rank 0 alone and may use every core)
+    _share = 1 if "reference" in sys.argv else int(os.environ["LOCAL_WORLD_SIZE"])
+    _thr = str(max(1, (os.cpu_count() or 1) // _share))
     for _k in ("OMP_NUM_THREADS", "OPENBLAS_NUM_THREADS", "MKL_NUM_THREADS"):
         os.environ[_k] = _thr
 
