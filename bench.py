@@ -323,7 +323,10 @@ def run_gpu(args):
                             "first-SNPs per GPU): phenotype parse + GRM upload + GPU preamble + .bed read + H2D + scan + D2H + file" % E2E_FIRST},
             "roofline": {"bound": "tensor", "achieved": achieved, "unit": "TFLOP/s", "peak": None, "frac": None,
                          "traffic": EXACT_TRAFFIC_BYTES, "kernel": "epi_exact_rb_kernel<%d,..,scan>" % bn,
-                         "flops_per_pair_algorithmic": f_exact(n), "issued_tflops": issued},
+                         "flops_per_pair_algorithmic": f_exact(n), "issued_tflops": issued,
+                         "note": "achieved = pairs/s x (2n^2+5n), the reference formulation's flop; the kernel exploits the "
+                                 "symmetry of Z'PZ and issues ~51.5 % of them, so frac > 1 is expected: read "
+                                 "frac_issued (DMMA flop actually issued / measured DMMA peak) as pipe utilisation"},
         }
         peaks = measure_fp64_peaks(engine, torch)
         peak = max(peaks["dmma_tflops"], peaks["cublas_dgemm_tflops"])
