@@ -1,0 +1,483 @@
+// INT8 tensor-core engine of the exact epistasis test (sm_100a: tcgen05.mma kind::i8, TMEM, TMA).
+//
+// The exact test of the reference (gmat/remma/remma_epiAA.py:72-77) needs, per SNP pair, var = w' A w with
+// A = Z'PZ (n x n, FP64) and w = u_i o v_j.  With v_j = a_j - o_j (a_j the integer dosage / heterozygote
+// indicator, o_j = 2p_j or 2p_j q_j) and B_i = diag(u_i) A diag(u_i):
+//
+//     var_ij = a_j' B_i a_j  -  2 o_j a_j.r_i  +  o_j^2 s_i,      r_i = u_i o (A u_i),  s_i = sum(r_i)
+//     eff_ij = a_j.(u_i o Z'Py) - o_j (u_i . Z'Py)
+//
+// Only a_j' B_i a_j costs n^2 per pair, and a_j is an exact small-integer vector.  B_i is split error-free into
+// S signed base-128 digit planes (int8); "plane x genotype" products are exact int8 x int8 -> int32 tensor-core
+// GEMMs, recombined in FP64 (S = 8 carries 56 bits: the split is finer than the FP64 rounding of B_i itself).
+// The FP64 DMMA kernel (exact.cu) issues 2 n^2 FP64 flop per pair at 37 TFLOP/s; this path issues S n^2 / 2
+// int8 MACs per pair (block-lower-triangle of the symmetric B_i, diagonal blocks halved, result doubled) on a
+// pipe that is two orders of magnitude faster.
+//
+// Kernel roles (one CTA per SM, 192 threads): warp 0 = TMA producer, warp 1 = tcgen05.mma issuer (one lane),
+// warps 2..5 = epilogue (TMEM -> registers -> a_jk-weighted row sums, kept per thread: the TMEM lane IS the
+// pair, so no cross-lane reduction exists anywhere).  MMA shape M=128 (second SNPs j) x N=256 (rows k of a
+// plane) x K=32 ids; accumulators double-buffered in TMEM (2 x 256 columns).
+#include "common.cuh"
+#include <cuda.h>
+
+namespace gb {
+
+constexpr int I8_TJ = 128;        // second SNPs per tile  (UMMA M, TMEM lanes)
+constexpr int I8_TK = 256;        // plane rows per tile   (UMMA N, TMEM columns)
+constexpr int I8_SLAB = 128;      // ids per pipeline stage = one 128-byte swizzle atom of int8
+constexpr int I8_NS = 4;          // smem ring stages
+constexpr int I8_A_BYTES = I8_TJ * I8_SLAB;            // 16 KB genotype tile
+constexpr int I8_B_BYTES = I8_TK * I8_SLAB;            // 32 KB plane tile
+constexpr int I8_STAGE_BYTES = I8_A_BYTES + I8_B_BYTES;
+constexpr int I8_THREADS = 192;
+constexpr int I8_MAX_PLANES = 8;
+
+struct I8Params {
+    int n, m, ld, np, n_planes, n_kt, n_slab;
+    int n_i, total_items, pair_space;
+    const long long *ilist;
+    const int *item_prefix;      // [n_i+1] first work item of every first SNP
+    const int *jt0;              // [n_i]   first j tile of every first SNP
+    const signed char *g8;       // [m][ld] integer coded second SNPs
+    const double *scale, *s_i, *upy;      // [n_i]
+    const double *t1, *e;        // [n_i][m]  a_j.r_i  and  a_j.(u_i o py)
+    const double *offs;          // [m]   o_j
+    double chi_cut;
+    gmat_b200_hit *hits;
+    long long cap;
+    unsigned long long *count;
+    double *q_debug;             // optional [n_i][m]: a_j' B_i a_j
+};
+
+// ------------------------------------------------------------------------------------------ PTX wrappers
+__device__ __forceinline__ void tma_load_2d(void *smem_dst, const CUtensorMap *map, int c0, int c1, uint64_t *bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];\n"
+        ::"r"(smem_u32(smem_dst)), "l"(map), "r"(c0), "r"(c1), "r"(smem_u32(bar))
+        : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;\n" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;\n" ::: "memory"); }
+__device__ __forceinline__ void tc_commit(uint64_t *bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n" ::"r"(smem_u32(bar))
+                 : "memory");
+}
+// D[tmem] (+)= A[smem] * B[smem], int8 x int8 -> int32, issued by ONE thread for the CTA
+__device__ __forceinline__ void umma_i8(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
+                                        uint32_t accumulate) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "setp.ne.b32 p, %4, 0;\n"
+        "tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n"
+        "}\n" ::"r"(tmem_d),
+        "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+// K-major operand tile, rows of 128 bytes, 128-byte swizzle (what TMA SWIZZLE_128B writes): 8-row groups
+// are 1024 bytes apart (SBO); LBO is unused for swizzled K-major tiles; descriptor version 1 = sm_100.
+__device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t saddr) {
+    uint64_t d = 0;
+    d |= (uint64_t)((saddr & 0x3FFFFu) >> 4);
+    d |= (uint64_t)(1024u >> 4) << 32;
+    d |= (uint64_t)1 << 46;
+    d |= (uint64_t)2 << 61;
+    return d;
+}
+// instruction descriptor: D = S32 (2) at [4,6), A = INT8 (1) at [7,10), B = INT8 (1) at [10,13), both K-major,
+// N>>3 at [17,23), M>>4 at [24,29)
+constexpr uint32_t I8_IDESC = (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(I8_TK >> 3) << 17) |
+                              ((uint32_t)(I8_TJ >> 4) << 24);
+
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, int (&v)[32]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];\n"
+        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+          "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
+          "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
+          "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+        : "r"(taddr)
+        : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;\n" ::: "memory"); }
+
+struct I8Bars {
+    uint64_t full[I8_NS], empty[I8_NS], tfull[2], tempty[2];
+    uint32_t tmem_base;
+};
+
+__device__ __forceinline__ int i8_slabs_of(int kt, int n_slab) {
+    const int want = 2 * kt + 2;              // block-lower-triangle: id slabs 0 .. (last 128-row block of the tile)
+    return want < n_slab ? want : n_slab;
+}
+__device__ __forceinline__ int i8_find_first(const int *prefix, int n_i, int item) {
+    int lo = 0, hi = n_i - 1;                 // largest ii with prefix[ii] <= item
+    while (lo < hi) {
+        const int mid = (lo + hi + 1) >> 1;
+        if (prefix[mid] <= item) lo = mid; else hi = mid - 1;
+    }
+    return lo;
+}
+
+__global__ void __launch_bounds__(I8_THREADS, 1)
+i8_scan_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_constant__ CUtensorMap map_p,
+               const I8Params p) {
+    extern __shared__ unsigned char smem_raw[];
+    unsigned char *smem = reinterpret_cast<unsigned char *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                                           ~static_cast<uintptr_t>(1023));
+    I8Bars *bars = reinterpret_cast<I8Bars *>(smem + I8_NS * I8_STAGE_BYTES);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < I8_NS; ++s) { mbar_init(&bars->full[s], 1); mbar_init(&bars->empty[s], 1); }
+        for (int b = 0; b < 2; ++b) { mbar_init(&bars->tfull[b], 1); mbar_init(&bars->tempty[b], 4); }
+        mbar_fence_init();
+    }
+    if (warp == 1) {                          // TMEM: all 512 columns (two 256-column accumulators)
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;\n" ::"r"(
+                         smem_u32(&bars->tmem_base)), "r"(512)
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;\n" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = bars->tmem_base;
+
+    if (warp == 0) {
+        // ================================ TMA producer ==========================================
+        if (lane == 0) {
+            int stage = 0; unsigned phase = 0;
+            for (int item = blockIdx.x; item < p.total_items; item += gridDim.x) {
+                const int ii = i8_find_first(p.item_prefix, p.n_i, item);
+                const int jt = p.jt0[ii] + (item - p.item_prefix[ii]);
+                for (int s = 0; s < p.n_planes; ++s) {
+                    const int prow = (ii * p.n_planes + s) * p.np;
+                    for (int kt = 0; kt < p.n_kt; ++kt) {
+                        const int nl = i8_slabs_of(kt, p.n_slab);
+                        for (int l = 0; l < nl; ++l) {
+                            mbar_wait(&bars->empty[stage], phase ^ 1u);
+                            mbar_expect_tx(&bars->full[stage], I8_STAGE_BYTES);
+                            unsigned char *sa = smem + stage * I8_STAGE_BYTES;
+                            tma_load_2d(sa, &map_g, l * I8_SLAB, jt * I8_TJ, &bars->full[stage]);
+                            tma_load_2d(sa + I8_A_BYTES, &map_p, l * I8_SLAB, prow + kt * I8_TK, &bars->full[stage]);
+                            if (++stage == I8_NS) { stage = 0; phase ^= 1u; }
+                        }
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ================================ MMA issuer (one thread) ================================
+        if (lane == 0) {
+            int stage = 0; unsigned phase = 0;
+            int abuf = 0; unsigned aphase = 0;
+            for (int item = blockIdx.x; item < p.total_items; item += gridDim.x) {
+                for (int s = 0; s < p.n_planes; ++s) {
+                    for (int kt = 0; kt < p.n_kt; ++kt) {
+                        const int nl = i8_slabs_of(kt, p.n_slab);
+                        mbar_wait(&bars->tempty[abuf], aphase ^ 1u);       // epilogue drained this accumulator
+                        tc_fence_after();
+                        const uint32_t tmem_d = tmem_base + (uint32_t)(abuf * I8_TK);
+                        for (int l = 0; l < nl; ++l) {
+                            mbar_wait(&bars->full[stage], phase);           // TMA bytes have landed
+                            tc_fence_after();
+                            const uint32_t sa = smem_u32(smem + stage * I8_STAGE_BYTES);
+                            const uint64_t da = umma_desc_sw128(sa), db = umma_desc_sw128(sa + I8_A_BYTES);
+#pragma unroll
+                            for (int k = 0; k < I8_SLAB / 32; ++k)          // K = 32 ids per MMA: +32 B in the atom
+                                umma_i8(tmem_d, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), I8_IDESC,
+                                        (uint32_t)((l | k) != 0));
+                            tc_commit(&bars->empty[stage]);                 // frees the smem slot when the MMAs retire
+                            if (++stage == I8_NS) { stage = 0; phase ^= 1u; }
+                        }
+                        tc_commit(&bars->tfull[abuf]);                      // accumulator complete
+                        if (++abuf == 2) { abuf = 0; aphase ^= 1u; }
+                    }
+                }
+            }
+        }
+    } else {
+        // ================================ epilogue warps =========================================
+        const int q = warp & 3;                                             // TMEM lane quarter of this warp
+        int abuf = 0; unsigned aphase = 0;
+        for (int item = blockIdx.x; item < p.total_items; item += gridDim.x) {
+            const int ii = i8_find_first(p.item_prefix, p.n_i, item);
+            const int jt = p.jt0[ii] + (item - p.item_prefix[ii]);
+            const int j = jt * I8_TJ + q * 32 + lane;
+            const signed char *arow = p.g8 + (size_t)(j < p.m ? j : p.m - 1) * p.ld;
+            double qacc = 0.0, wgt = 1.0;
+            for (int s = 0; s < p.n_planes; ++s) {
+                wgt *= 0.0078125;                                           // 128^-(s+1)
+                double plane_sum = 0.0;                                     // integer valued, exact in FP64
+                for (int kt = 0; kt < p.n_kt; ++kt) {
+                    const int4 *ap = reinterpret_cast<const int4 *>(arow + kt * I8_TK);
+                    int4 a0 = __ldg(ap), a1 = __ldg(ap + 1);
+                    mbar_wait_warp(&bars->tfull[abuf], aphase);
+                    tc_fence_after();
+                    const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(abuf * I8_TK);
+#pragma unroll 1
+                    for (int ch = 0; ch < I8_TK / 32; ++ch) {
+                        int v[32];
+                        tmem_ld32(taddr + ch * 32, v);
+                        int4 n0 = a0, n1 = a1;
+                        if (ch + 1 < I8_TK / 32) { n0 = __ldg(ap + 2 * ch + 2); n1 = __ldg(ap + 2 * ch + 3); }
+                        tmem_ld_wait();
+                        const int aw[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+                        int csum = 0;
+#pragma unroll
+                        for (int c = 0; c < 32; ++c) csum += ((aw[c >> 2] >> ((c & 3) * 8)) & 0xff) * v[c];
+                        plane_sum += (double)csum;
+                        a0 = n0; a1 = n1;
+                    }
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(&bars->tempty[abuf]);
+                    if (++abuf == 2) { abuf = 0; aphase ^= 1u; }
+                }
+                qacc += plane_sum * wgt;
+            }
+            // ---- finish the pair: FP64 terms, test, emit (remma_epiAA.py:75-82) ----
+            const int i = (int)p.ilist[ii];
+            const bool valid = j < p.m && (p.pair_space == GMAT_B200_PAIRS_ALL || j > i);
+            const int jc = j < p.m ? j : p.m - 1;
+            const double quad = 2.0 * p.scale[ii] * qacc;                   // a_j' B_i a_j
+            const double o = p.offs[jc];
+            const size_t at = (size_t)ii * p.m + jc;
+            const double var = quad - 2.0 * o * p.t1[at] + o * o * p.s_i[ii];
+            const double eff = p.e[at] - o * p.upy[ii];
+            const double chi = eff * eff / var;
+            if (p.q_debug != nullptr && j < p.m) p.q_debug[at] = quad;
+            gmat_b200_hit h;
+            h.snp_0 = i; h.snp_1 = j; h.eff = eff; h.var = var; h.chi = chi;
+            const bool hit = valid && (p.chi_cut < 0.0 || chi > p.chi_cut);
+            const unsigned ballot = __ballot_sync(0xffffffffu, hit);
+            if (ballot) {
+                unsigned long long base = 0;
+                if (lane == 0) base = atomicAdd(p.count, (unsigned long long)__popc(ballot));
+                base = __shfl_sync(0xffffffffu, base, 0);
+                if (hit) {
+                    const unsigned long long pos = base + __popc(ballot & ((1u << lane) - 1u));
+                    if ((long long)pos < p.cap) p.hits[pos] = h;
+                }
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;\n" ::"r"(tmem_base), "r"(512) : "memory");
+    }
+}
+
+// ------------------------------------------------------------------------------------------ operand builders
+// integer code of the second SNP: additive dosage {0,miss->0,1,2}; dominance indicator {0,miss->0,1,0}
+__global__ void i8_dosage_kernel(const unsigned char *__restrict__ bed, int n, long long m, long long row_bytes,
+                                 int coding, signed char *__restrict__ g8, int ld) {
+    const long long groups = ld / 16;
+    const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= m * groups) return;
+    const long long snp = t / groups;
+    const int k0 = (int)(t % groups) * 16;
+    const unsigned tab = coding == GMAT_B200_CODING_DOM ? 0x00010000u : 0x02010000u;   // byte[code]
+    unsigned w = 0;
+    if (k0 / 4 + 3 < row_bytes) w = *reinterpret_cast<const unsigned *>(bed + snp * row_bytes + k0 / 4);
+    unsigned out[4];
+#pragma unroll
+    for (int g = 0; g < 4; ++g) {
+        unsigned o = 0;
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            const int k = k0 + g * 4 + c;
+            const unsigned code = (w >> (2 * (g * 4 + c))) & 3u;
+            const unsigned val = k < n ? ((tab >> (8 * code)) & 0xffu) : 0u;
+            o |= val << (8 * c);
+        }
+        out[g] = o;
+    }
+    *reinterpret_cast<uint4 *>(g8 + snp * ld + k0) = make_uint4(out[0], out[1], out[2], out[3]);
+}
+
+// B_i = diag(u_i) A diag(u_i) / scale_i -> S signed base-128 digits.  Lower block-triangle of 128 x 128 blocks,
+// diagonal blocks halved (the kernel doubles the sum); everything else in the plane buffer stays zero.
+template <int S>
+__global__ void __launch_bounds__(256)
+i8_split_kernel(const double *__restrict__ A, int n, const double *__restrict__ U, int n_i, int i_per_block,
+                const double *__restrict__ scale, int np, int ld, signed char *__restrict__ planes) {
+    int pk = 0, rem = blockIdx.x;                       // blockIdx.x -> (pk, pl), pl <= pk
+    while (rem > pk) { rem -= pk + 1; ++pk; }
+    const int pl = rem;
+    const int cg = threadIdx.x & 7, r0 = threadIdx.x >> 3;
+    const int l0 = pl * 128 + cg * 16;
+    const double half = pk == pl ? 0.5 : 1.0;
+    const double big = 72057594037927936.0;             // 128^8 = 2^56
+    double top = 1.0;
+    for (int s = S; s < 8; ++s) top *= 128.0;
+    const double mul = half * (big / top);              // 128^S (x 1/2 on the diagonal blocks)
+    const int i_begin = blockIdx.y * i_per_block;
+    const int i_end = min(n_i, i_begin + i_per_block);
+    for (int pass = 0; pass < 4; ++pass) {
+        const int k = pk * 128 + pass * 32 + r0;
+        double a[16];
+#pragma unroll
+        for (int c = 0; c < 16; ++c) a[c] = (k < n && l0 + c < n) ? A[(size_t)k * n + l0 + c] : 0.0;
+        for (int ii = i_begin; ii < i_end; ++ii) {
+            const double *u = U + (size_t)ii * n;
+            const double uk = k < n ? u[k] * (mul / scale[ii]) : 0.0;
+            unsigned dg[S][4];
+#pragma unroll
+            for (int s = 0; s < S; ++s) dg[s][0] = dg[s][1] = dg[s][2] = dg[s][3] = 0u;
+#pragma unroll
+            for (int c = 0; c < 16; ++c) {
+                const double ul = l0 + c < n ? u[l0 + c] : 0.0;
+                long long t = __double2ll_rn(uk * a[c] * ul);
+#pragma unroll
+                for (int s = S - 1; s >= 1; --s) {
+                    const long long d = ((t + 64) & 127) - 64;          // balanced digit in [-64, 63]
+                    t = (t - d) >> 7;
+                    dg[s][c >> 2] |= ((unsigned)d & 0xffu) << (8 * (c & 3));
+                }
+                dg[0][c >> 2] |= ((unsigned)t & 0xffu) << (8 * (c & 3));  // |t| <= 127 by the choice of scale
+            }
+#pragma unroll
+            for (int s = 0; s < S; ++s) {
+                signed char *dst = planes + ((size_t)(ii * S + s) * np + k) * ld + l0;
+                *reinterpret_cast<uint4 *>(dst) = make_uint4(dg[s][0], dg[s][1], dg[s][2], dg[s][3]);
+            }
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------ host side
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                  const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn encode_tiled_fn() {
+    static EncodeTiledFn fn = nullptr;
+    if (fn == nullptr) {
+        void *ptr = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &qres) == cudaSuccess &&
+            qres == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn>(ptr);
+    }
+    return fn;
+}
+
+// int8 matrix [rows][ld bytes], box = 128 bytes x box_rows, 128-byte swizzle, out-of-range rows read as zero
+static int make_map(CUtensorMap *map, const void *base, long long inner, long long rows, long long ld, int box_rows) {
+    EncodeTiledFn enc = encode_tiled_fn();
+    if (enc == nullptr) { set_error("cuTensorMapEncodeTiled is not available from this driver"); return GMAT_B200_ERR_CUDA; }
+    cuuint64_t dims[2] = {(cuuint64_t)inner, (cuuint64_t)rows};
+    cuuint64_t strides[1] = {(cuuint64_t)ld};
+    cuuint32_t box[2] = {(cuuint32_t)I8_SLAB, (cuuint32_t)box_rows};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, const_cast<void *>(base), dims, strides, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled failed with CUresult %d", (int)r); return GMAT_B200_ERR_CUDA; }
+    return GMAT_B200_OK;
+}
+
+}  // namespace gb
+
+using namespace gb;
+
+extern "C" long long gmat_b200_i8_ld(long long n) { return round_up(n, I8_TK); }
+
+extern "C" int gmat_b200_i8_dosage(const unsigned char *bed_dev, long long n, long long m, long long row_bytes,
+                                   int coding, signed char *g8_dev, long long ld, void *stream) {
+    GB_CHECK_ARG(bed_dev && g8_dev && n > 0 && m > 0, "null buffer or empty shape");
+    GB_CHECK_ARG(ld == round_up(n, I8_TK) && row_bytes % 4 == 0, "ld must be gmat_b200_i8_ld(n)");
+    GB_CHECK_ARG(coding == GMAT_B200_CODING_ADD || coding == GMAT_B200_CODING_DOM, "coding");
+    const long long work = m * (ld / 16);
+    i8_dosage_kernel<<<(unsigned)((work + 255) / 256), 256, 0, (cudaStream_t)stream>>>(bed_dev, (int)n, m, row_bytes,
+                                                                                      coding, g8_dev, (int)ld);
+    GB_LAUNCH_CHECK();
+    return GMAT_B200_OK;
+}
+
+extern "C" int gmat_b200_i8_split(const double *pvp_dev, long long n, const double *u_dev, long long n_i,
+                                  const double *scale_dev, int n_planes, signed char *planes_dev, void *stream) {
+    GB_CHECK_ARG(pvp_dev && u_dev && scale_dev && planes_dev && n > 0 && n_i > 0, "null buffer or empty shape");
+    GB_CHECK_ARG(n_planes >= 2 && n_planes <= I8_MAX_PLANES, "n_planes must be in [2, 8]");
+    const int ld = (int)round_up(n, I8_TK), np = ld;
+    const int nb = (int)((n + 127) / 128);
+    const int blocks = nb * (nb + 1) / 2;
+    // enough CTAs for the chip; each keeps its 16 A values per thread across its share of the first SNPs
+    int ysplit = (int)((2LL * sm_count() + blocks - 1) / blocks);
+    if (ysplit > n_i) ysplit = (int)n_i;
+    if (ysplit < 1) ysplit = 1;
+    const int per = (int)((n_i + ysplit - 1) / ysplit);
+    dim3 grid(blocks, (unsigned)((n_i + per - 1) / per));
+    cudaStream_t st = (cudaStream_t)stream;
+#define GB_SPLIT(SV) i8_split_kernel<SV><<<grid, 256, 0, st>>>(pvp_dev, (int)n, u_dev, (int)n_i, per, scale_dev, np, ld, planes_dev)
+    switch (n_planes) {
+        case 2: GB_SPLIT(2); break; case 3: GB_SPLIT(3); break; case 4: GB_SPLIT(4); break; case 5: GB_SPLIT(5); break;
+        case 6: GB_SPLIT(6); break; case 7: GB_SPLIT(7); break; default: GB_SPLIT(8); break;
+    }
+#undef GB_SPLIT
+    GB_LAUNCH_CHECK();
+    return GMAT_B200_OK;
+}
+
+extern "C" int gmat_b200_i8_scan(const signed char *g8_dev, long long n, long long m, const signed char *planes_dev,
+                                 int n_planes, const long long *ilist_dev, const long long *ilist_host, long long n_i,
+                                 const double *scale_dev, const double *s_dev, const double *upy_dev,
+                                 const double *t1_dev, const double *e_dev, const double *offs_dev,
+                                 int pair_space, double chi_cut, gmat_b200_hit *hits_dev, long long cap,
+                                 unsigned long long *count_dev, double *q_debug_dev, void *stream) {
+    GB_CHECK_ARG(g8_dev && planes_dev && ilist_dev && ilist_host && scale_dev && s_dev && upy_dev && t1_dev && e_dev &&
+                 offs_dev && count_dev, "null buffer");
+    GB_CHECK_ARG(n > 0 && m > 0 && n_i > 0 && n_i <= 4096, "shape");
+    GB_CHECK_ARG(n_planes >= 2 && n_planes <= I8_MAX_PLANES, "n_planes must be in [2, 8]");
+    GB_CHECK_ARG(pair_space == GMAT_B200_PAIRS_UPPER || pair_space == GMAT_B200_PAIRS_ALL, "pair_space");
+    GB_CHECK_ARG(cap == 0 || hits_dev, "hits buffer");
+    cudaStream_t st = (cudaStream_t)stream;
+    I8Params p;
+    p.n = (int)n; p.m = (int)m; p.ld = (int)round_up(n, I8_TK); p.np = p.ld;
+    p.n_planes = n_planes; p.n_kt = p.ld / I8_TK; p.n_slab = (int)((n + I8_SLAB - 1) / I8_SLAB);
+    p.n_i = (int)n_i; p.pair_space = pair_space;
+    GB_CHECK_ARG((long long)n_i * n_planes * p.np < (1LL << 31), "plane buffer has too many rows for one tensor map");
+    // work items: (first SNP, tile of 128 second SNPs)
+    const int n_jt = (int)((m + I8_TJ - 1) / I8_TJ);
+    int *host_tab = (int *)malloc(sizeof(int) * (2 * n_i + 1));
+    if (!host_tab) { set_error("out of host memory"); return GMAT_B200_ERR_ARG; }
+    int *prefix = host_tab, *jt0 = host_tab + n_i + 1;
+    long long total = 0;
+    for (long long ii = 0; ii < n_i; ++ii) {
+        const long long i = ilist_host[ii];
+        if (i < 0 || i >= m) { free(host_tab); set_error("bad argument: first SNP out of range"); return GMAT_B200_ERR_ARG; }
+        const int first = pair_space == GMAT_B200_PAIRS_ALL ? 0 : (int)((i + 1) / I8_TJ);
+        prefix[ii] = (int)total; jt0[ii] = first;
+        total += (first < n_jt && (pair_space == GMAT_B200_PAIRS_ALL || i + 1 < m)) ? n_jt - first : 0;
+    }
+    prefix[n_i] = (int)total;
+    if (total == 0) { free(host_tab); return GMAT_B200_OK; }
+    int *tab_dev = nullptr;
+    cudaError_t e = cudaMallocAsync((void **)&tab_dev, sizeof(int) * (2 * n_i + 1), st);
+    if (e != cudaSuccess) { free(host_tab); set_error("cudaMallocAsync failed: %s", cudaGetErrorString(e)); return GMAT_B200_ERR_CUDA; }
+    e = cudaMemcpyAsync(tab_dev, host_tab, sizeof(int) * (2 * n_i + 1), cudaMemcpyHostToDevice, st);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(st);       // host_tab is pageable: finish before freeing it
+    free(host_tab);
+    if (e != cudaSuccess) { cudaFreeAsync(tab_dev, st); set_error("table upload failed: %s", cudaGetErrorString(e)); return GMAT_B200_ERR_CUDA; }
+    p.total_items = (int)total; p.item_prefix = tab_dev; p.jt0 = tab_dev + n_i + 1;
+    p.ilist = ilist_dev; p.g8 = g8_dev; p.scale = scale_dev; p.s_i = s_dev; p.upy = upy_dev; p.t1 = t1_dev; p.e = e_dev;
+    p.offs = offs_dev; p.chi_cut = chi_cut; p.hits = hits_dev; p.cap = cap; p.count = count_dev; p.q_debug = q_debug_dev;
+
+    CUtensorMap map_g, map_p;
+    int rc = make_map(&map_g, g8_dev, p.ld, m, p.ld, I8_TJ);
+    if (rc == GMAT_B200_OK) rc = make_map(&map_p, planes_dev, p.ld, (long long)n_i * n_planes * p.np, p.ld, I8_TK);
+    if (rc != GMAT_B200_OK) { cudaFreeAsync(tab_dev, st); return rc; }
+    const int smem_bytes = I8_NS * I8_STAGE_BYTES + 1024 + (int)sizeof(I8Bars);
+    GB_CUDA(cudaFuncSetAttribute(i8_scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
+    const int grid = (int)(total < sm_count() ? total : sm_count());
+    i8_scan_kernel<<<grid, I8_THREADS, smem_bytes, st>>>(map_g, map_p, p);
+    GB_LAUNCH_CHECK();
+    GB_CUDA(cudaFreeAsync(tab_dev, st));
+    return GMAT_B200_OK;
+}

@@ -202,6 +202,84 @@ def epi_exact_scan(store, lutU, lutV, py_dev, packed, ilist, pair_space, chi_cut
         cap = cnt               # the kernel counted every hit: one retry with the exact capacity
 
 
+class I8Exact(object):
+    """INT8 tensor-core engine of the exact scan (gmat_b200/csrc/ozaki.cu): same statistics as
+    ``epi_exact_scan`` (remma_epiAA.py:72-82), the n^2-per-pair quadratic form evaluated with tcgen05 int8 MMAs on
+    an error-free digit-plane split of diag(u_i) Z'PZ diag(u_i).  Built once per scan (operands of the second SNPs
+    stay resident: integer codes [m][ld] int8, their FP64 copy for the two O(n)-per-pair GEMM terms)."""
+
+    PLANE_BYTES = 2 << 30          # budget of the digit-plane buffer (first SNPs per launch follow from it)
+
+    def __init__(self, store, lutU, lutV, coding_v, py_dev, pvp_dev, n_planes=8):
+        if store.n_missing() != 0:
+            raise ValueError("the int8 engine needs second SNPs without missing genotypes")
+        self.store, self.lutU, self.py = store, lutU, py_dev.reshape(-1)
+        self.A = pvp_dev
+        self.n_planes = int(n_planes)
+        n, m, dev = store.n, store.m, store.device
+        self.ld = int(lib.gmat_b200_i8_ld(n))
+        self.g8 = torch.empty((m, self.ld), dtype=torch.int8, device=dev)
+        check(lib.gmat_b200_i8_dosage(_p(store.bed, "unsigned char *"), n, m, store.row_bytes, coding_v,
+                                      _p(self.g8, "signed char *"), self.ld, _stream()), "gmat_b200_i8_dosage")
+        self.gd = self.g8[:, :n].to(torch.float64)                 # [m][n] integer codes as FP64
+        self.offs = (-lutV[:, 0]).contiguous()                     # lut[j][code 0] = 0 - o_j
+        self.amax = float(pvp_dev.abs().max())
+        per_first = self.n_planes * self.ld * self.ld
+        self.batch = int(max(1, min(64, self.PLANE_BYTES // per_first)))
+        self.planes = torch.zeros((self.batch * per_first,), dtype=torch.int8, device=dev)
+        self._shifts = torch.tensor([0, 2, 4, 6], dtype=torch.uint8, device=dev)
+
+    def _coded_first(self, il):
+        """[len(il)][n] FP64 coded first SNPs: lutU[i][code] (missing calls of a FIRST SNP are fine: they code 0)."""
+        rows = self.store.bed[il]
+        codes = ((rows[:, :, None] >> self._shifts) & 3).reshape(len(il), -1)[:, :self.store.n]
+        return torch.gather(self.lutU[il], 1, codes.long())
+
+    def scan(self, ilist, pair_space, chi_cut, cap=1 << 20, q_debug=False):
+        store, dev = self.store, self.store.device
+        n, m = store.n, store.m
+        ilist = np.ascontiguousarray(ilist, dtype=np.int64)
+        out, dbg = [], []
+        count = torch.zeros((1,), dtype=torch.int64, device=dev)
+        for b0 in range(0, len(ilist), self.batch):
+            ih = np.ascontiguousarray(ilist[b0:b0 + self.batch])
+            il = torch.as_tensor(ih).to(dev)
+            ni = len(ih)
+            u = self._coded_first(il)                                   # [ni][n]
+            r = u * (u @ self.A)                                        # u o (A u)   (A symmetric)
+            upy_vec = u * self.py
+            s_i = r.sum(dim=1).contiguous()
+            upy = upy_vec.sum(dim=1).contiguous()
+            te = torch.cat([r, upy_vec]) @ self.gd.T                    # [2 ni][m]: a_j.r_i and a_j.(u_i o py)
+            t1, e = te[:ni].contiguous(), te[ni:].contiguous()
+            scale = (u.abs().amax(dim=1) ** 2 * (self.amax / 0.99)).clamp_min(1e-300).contiguous()
+            check(lib.gmat_b200_i8_split(_p(self.A, "double *"), n, _p(u, "double *"), ni, _p(scale, "double *"),
+                                         self.n_planes, _p(self.planes, "signed char *"), _stream()),
+                  "gmat_b200_i8_split")
+            qd = torch.zeros((ni, m), dtype=torch.float64, device=dev) if q_debug else None
+            this_cap = cap
+            while True:
+                hits = alloc_hits(this_cap, dev)
+                count.zero_()
+                check(lib.gmat_b200_i8_scan(
+                    _p(self.g8, "signed char *"), n, m, _p(self.planes, "signed char *"), self.n_planes,
+                    _p(il, "long long *"), ffi.cast("long long *", ih.ctypes.data), ni,
+                    _p(scale, "double *"), _p(s_i, "double *"), _p(upy, "double *"), _p(t1, "double *"),
+                    _p(e, "double *"), _p(self.offs, "double *"), pair_space, float(chi_cut),
+                    ffi.cast("gmat_b200_hit *", hits.data_ptr()), this_cap,
+                    ffi.cast("unsigned long long *", count.data_ptr()), _p(qd, "double *"), _stream()),
+                    "gmat_b200_i8_scan")
+                cnt = int(count.item())
+                if cnt <= this_cap:
+                    out.append(hits_to_numpy(hits, cnt))
+                    break
+                this_cap = cnt
+            if q_debug:
+                dbg.append(qd)
+        res = np.concatenate(out) if out else np.zeros((0,), dtype=HIT_DTYPE)
+        return (res, torch.cat(dbg)) if q_debug else res
+
+
 def epi_exact_pairs(store, lutU, lutV, py_dev, packed, pairs):
     """Exact statistics for explicit pairs (host int array [k][2]); returns HIT_DTYPE array, list order."""
     dev = store.device

@@ -175,6 +175,30 @@ int gmat_b200_grm(const unsigned char *bed_dev, long long n, long long m, long l
                   const double *lut_dev, long long snp_begin, long long snp_end,
                   double scale, double small_val, int accumulate, double *K_dev, void *stream);
 
+/* ---- INT8 tensor-core engine of the exact test (tcgen05.mma kind::i8; see gmat_b200/csrc/ozaki.cu) --------
+ * Same statistics as gmat_b200_epi_exact_scan (remma_epiAA.py:72-82).  With v_j = a_j - o_j (a_j the integer
+ * dosage or heterozygote indicator of the second SNP) and B_i = diag(u_i) Z'PZ diag(u_i):
+ *   var_ij = a_j' B_i a_j - 2 o_j (a_j . r_i) + o_j^2 s_i ,  r_i = u_i o (Z'PZ u_i), s_i = sum r_i
+ *   eff_ij = a_j . (u_i o Z'Py) - o_j (u_i . Z'Py)
+ * a_j' B_i a_j is evaluated on the INT8 tensor cores from an error-free split of B_i/scale_i into n_planes signed
+ * base-128 digit planes (exact int8 x int8 -> int32 products, recombined in FP64; 8 planes = 56 bits).  Second
+ * SNPs must have no missing genotype (callers route data sets with missing calls to the FP64 kernel).         */
+long long gmat_b200_i8_ld(long long n);      /* bytes per row (and rows per plane) of the int8 operands       */
+int gmat_b200_i8_dosage(const unsigned char *bed_dev, long long n, long long m, long long row_bytes, int coding,
+                        signed char *g8_dev /* [m][ld] */, long long ld, void *stream);
+/* planes_dev: [n_i][n_planes][ld][ld] int8, ZERO-initialised by the caller once (blocks above the block diagonal
+ * are never written); u_dev [n_i][n] coded first SNPs; scale_dev[i] >= max|B_i| / 0.99                          */
+int gmat_b200_i8_split(const double *pvp_dev /* [n][n] */, long long n, const double *u_dev, long long n_i,
+                       const double *scale_dev, int n_planes, signed char *planes_dev, void *stream);
+/* t1_dev/e_dev: [n_i][m] FP64 (a_j . r_i and a_j . (u_i o Z'Py)); offs_dev[m] = o_j; ilist_host mirrors ilist_dev;
+ * q_debug_dev (optional, [n_i][m]) receives a_j' B_i a_j.  Hits as in gmat_b200_epi_exact_scan.                */
+int gmat_b200_i8_scan(const signed char *g8_dev, long long n, long long m, const signed char *planes_dev,
+                      int n_planes, const long long *ilist_dev, const long long *ilist_host, long long n_i,
+                      const double *scale_dev, const double *s_dev, const double *upy_dev,
+                      const double *t1_dev, const double *e_dev, const double *offs_dev,
+                      int pair_space, double chi_cut, gmat_b200_hit *hits_dev, long long cap,
+                      unsigned long long *count_dev, double *q_debug_dev, void *stream);
+
 /* Host text writer, byte-identical to np.savetxt(path, mat) as used by output_mat (gmat/gmatrix/gmatrix.py:10-14:
  * '%.18e', ' ' delimiter, '\n'): rows formatted in parallel by `threads` host threads (<= 0: all).  No GPU work. */
 int gmat_b200_savetxt_host(const char *path, const double *mat /* HOST [rows][cols] */, long long rows,
