@@ -247,8 +247,9 @@ i8_scan_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_constant_
             const double quad = 2.0 * p.scale[ii] * qacc;                   // a_j' B_i a_j
             const double o = p.offs[jc];
             const size_t at = (size_t)ii * p.m + jc;
-            const double var = quad - 2.0 * o * p.t1[at] + o * o * p.s_i[ii];
-            const double eff = p.e[at] - o * p.upy[ii];
+            double var = quad - 2.0 * o * p.t1[at] + o * o * p.s_i[ii];
+            double eff = p.e[at] - o * p.upy[ii];
+            if (o != o) { var = 0.0; eff = 0.0; }                          // monomorphic second SNP: w == 0 exactly
             const double chi = eff * eff / var;
             if (p.q_debug != nullptr && j < p.m) p.q_debug[at] = quad;
             gmat_b200_hit h;

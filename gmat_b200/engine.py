@@ -202,6 +202,21 @@ def epi_exact_scan(store, lutU, lutV, py_dev, packed, ilist, pair_space, chi_cut
         cap = cnt               # the kernel counted every hit: one retry with the exact capacity
 
 
+def exact_engine(store):
+    """Which kernel runs the exact scan: "i8" (tcgen05 int8 digit planes) or "f64" (DMMA)."""
+    want = os.environ.get("GMAT_B200_EXACT_ENGINE", "auto").lower()
+    if want not in ("auto", "i8", "f64"):
+        raise ValueError("GMAT_B200_EXACT_ENGINE must be auto, i8 or f64")
+    if want == "auto":
+        return "i8" if store.n_missing() == 0 else "f64"
+    return want
+
+
+def i8_planes():
+    """Digit planes of the int8 engine (GMAT_B200_I8_PLANES, 2..8; 8 = 56 bits, finer than FP64 itself)."""
+    return int(os.environ.get("GMAT_B200_I8_PLANES", "8"))
+
+
 class I8Exact(object):
     """INT8 tensor-core engine of the exact scan (gmat_b200/csrc/ozaki.cu): same statistics as
     ``epi_exact_scan`` (remma_epiAA.py:72-82), the n^2-per-pair quadratic form evaluated with tcgen05 int8 MMAs on
@@ -210,12 +225,12 @@ class I8Exact(object):
 
     PLANE_BYTES = 2 << 30          # budget of the digit-plane buffer (first SNPs per launch follow from it)
 
-    def __init__(self, store, lutU, lutV, coding_v, py_dev, pvp_dev, n_planes=8):
+    def __init__(self, store, lutU, lutV, coding_v, py_dev, pvp_dev, n_planes=None):
         if store.n_missing() != 0:
             raise ValueError("the int8 engine needs second SNPs without missing genotypes")
         self.store, self.lutU, self.py = store, lutU, py_dev.reshape(-1)
         self.A = pvp_dev
-        self.n_planes = int(n_planes)
+        self.n_planes = int(i8_planes() if n_planes is None else n_planes)
         n, m, dev = store.n, store.m, store.device
         self.ld = int(lib.gmat_b200_i8_ld(n))
         self.g8 = torch.empty((m, self.ld), dtype=torch.int8, device=dev)
@@ -223,6 +238,13 @@ class I8Exact(object):
                                       _p(self.g8, "signed char *"), self.ld, _stream()), "gmat_b200_i8_dosage")
         self.gd = self.g8[:, :n].to(torch.float64)                 # [m][n] integer codes as FP64
         self.offs = (-lutV[:, 0]).contiguous()                     # lut[j][code 0] = 0 - o_j
+        # second SNPs whose integer code is the same for everybody have w == 0 exactly (eff = var = 0, chi = NaN in
+        # the reference); the expanded form would return rounding noise instead, so they are flagged (o_j = NaN)
+        tabv = torch.tensor([0, 0, 1, 2] if coding_v == ADD else [0, 0, 1, 0], dtype=torch.int32, device=dev)
+        present = store.counts > 0
+        hi = torch.where(present, tabv, torch.full_like(tabv, -1)).amax(dim=1)
+        lo = torch.where(present, tabv, torch.full_like(tabv, 9)).amin(dim=1)
+        self.offs[hi <= lo] = float("nan")
         self.amax = float(pvp_dev.abs().max())
         per_first = self.n_planes * self.ld * self.ld
         self.batch = int(max(1, min(64, self.PLANE_BYTES // per_first)))
@@ -252,7 +274,7 @@ class I8Exact(object):
             upy = upy_vec.sum(dim=1).contiguous()
             te = torch.cat([r, upy_vec]) @ self.gd.T                    # [2 ni][m]: a_j.r_i and a_j.(u_i o py)
             t1, e = te[:ni].contiguous(), te[ni:].contiguous()
-            scale = (u.abs().amax(dim=1) ** 2 * (self.amax / 0.99)).clamp_min(1e-300).contiguous()
+            scale = (u.abs().amax(dim=1) ** 2 * (self.amax / 0.99)).clamp_min(1e-200).contiguous()
             check(lib.gmat_b200_i8_split(_p(self.A, "double *"), n, _p(u, "double *"), ni, _p(scale, "double *"),
                                          self.n_planes, _p(self.planes, "signed char *"), _stream()),
                   "gmat_b200_i8_split")

@@ -121,10 +121,9 @@ class DeviceModel(object):
 
     def __init__(self, pymat, pvpmat, device):
         self.py = torch.as_tensor(np.ascontiguousarray(pymat.reshape(-1))).to(device)
-        pvp = torch.as_tensor(np.ascontiguousarray(pvpmat, dtype=np.float64)).to(device)
-        self.packed = engine.pack_pvp(pvp)
-        self.h2d_bytes = self.py.numel() * 8 + pvp.numel() * 8
-        del pvp
+        self.pvp = torch.as_tensor(np.ascontiguousarray(pvpmat, dtype=np.float64)).to(device)
+        self.packed = engine.pack_pvp(self.pvp)
+        self.h2d_bytes = self.py.numel() * 8 + self.pvp.numel() * 8
 
     @classmethod
     def build(cls, y, xmat, zmat, gmat_lst, var_com, device, scipy_inv=True):
@@ -133,10 +132,20 @@ class DeviceModel(object):
             pymat, pvpmat = preamble(y, xmat, zmat, gmat_lst, var_com, scipy_inv=scipy_inv)
             return cls(pymat, pvpmat, device)
         self = cls.__new__(cls)
-        self.py, pvp, self.h2d_bytes = preamble_device(y, xmat, zmat, gmat_lst, var_com, device)
-        self.packed = engine.pack_pvp(pvp)
-        del pvp
+        self.py, self.pvp, self.h2d_bytes = preamble_device(y, xmat, zmat, gmat_lst, var_com, device)
+        self.packed = engine.pack_pvp(self.pvp)
         return self
+
+    def scanner(self, store, lut_u, lut_v, coding_v):
+        """The exact-scan engine for this model and genotype store: ``scan(ilist, pair_space, chi_cut)``.
+        GMAT_B200_EXACT_ENGINE = auto (default: the INT8 tensor-core engine when no genotype is missing, else the
+        FP64 DMMA kernel) | i8 | f64."""
+        which = engine.exact_engine(store)
+        if which == "i8":
+            eng = engine.I8Exact(store, lut_u, lut_v, coding_v, self.py, self.pvp)
+            return eng.scan
+        return lambda ilist, pair_space, chi_cut: engine.epi_exact_scan(store, lut_u, lut_v, self.py, self.packed,
+                                                                        ilist, pair_space, chi_cut)
 
 
 # ----------------------------------------------------------------------------------------------
@@ -204,9 +213,9 @@ def exact_scan(kind, y, xmat, zmat, gmat_lst, var_com, bed_file, snp_lst_0=None,
                                2: hits['eff'][keep], 3: hits['chi'][keep], 4: p_vec[keep]})
 
     mine = []
+    scan = model.scanner(store, lut_u, lut_v, kind.coding_v)
     for chunk in _chunks(kind, my_list, num_snp):
-        hits = engine.epi_exact_scan(store, lut_u, lut_v, model.py, model.packed,
-                                     np.asarray(chunk, dtype=np.int64), pair_space, chi_cut)
+        hits = scan(np.asarray(chunk, dtype=np.int64), pair_space, chi_cut)
         if world == 1:
             emit(hits)                                         # appended launch by launch (resume granularity)
         else:

@@ -1,0 +1,193 @@
+"""GPU parity tests of the INT8 tensor-core engine of the exact scan (gmat_b200/csrc/ozaki.cu, tcgen05 kind::i8):
+the same oracle and the same 1e-9 relative tolerance as the FP64 DMMA kernel, plus the properties the digit-plane
+split itself must have (integer operands bit-exact, the planes reconstruct diag(u) Z'PZ diag(u) to the last bit of
+the split, results do not depend on which engine ran)."""
+import numpy as np
+import pytest
+
+from oracle import oracle
+
+pytestmark = pytest.mark.gpu
+RTOL = 1e-9
+
+
+@pytest.fixture(scope="module")
+def eng():
+    import torch
+    assert torch.cuda.is_available(), "gpu tests need a CUDA device"
+    from gmat_b200 import engine
+    return engine
+
+
+def _dataset(tmp_path, n, m, seed, missing=0.0, geno=None):
+    from gmat_b200 import synth
+    prefix = str(tmp_path / ("syn_%d_%d" % (n, m)))
+    return prefix, synth.write_dataset(prefix, n, m, seed=seed, missing_rate=missing, geno=geno)
+
+
+def _random_model(n, seed):
+    rng = np.random.Generator(np.random.PCG64(seed))
+    b = rng.normal(size=(n, n + 3))
+    a = b @ b.T / n
+    c = np.eye(n) - np.ones((n, n)) / n
+    a = c @ a @ c
+    py = c @ rng.normal(size=n)
+    return py.reshape(-1, 1), 0.5 * (a + a.T)
+
+
+def _codings(eng, kind):
+    return {"AA": (eng.ADD, eng.ADD), "AD": (eng.ADD, eng.DOM), "DD": (eng.DOM, eng.DOM)}[kind]
+
+
+@pytest.mark.parametrize("kind", ["AA", "AD", "DD"])
+@pytest.mark.parametrize("n,m", [(128, 40), (131, 77), (300, 150), (17, 9), (257, 129), (520, 260)])
+def test_i8_scan_vs_oracle(eng, tmp_path, kind, n, m):
+    """Every pair of a ragged first-SNP list (chi_cut < 0): eff, var within 1e-9 of the numpy oracle; n and m off
+    every tile boundary (128 second SNPs, 256 plane rows, 128 ids per slab)."""
+    import torch
+    prefix, _ = _dataset(tmp_path, n, m, seed=n * 7 + m)
+    pymat, pvp = _random_model(n, n + m)
+    store = eng.GenotypeStore(prefix)
+    cu, cv = _codings(eng, kind)
+    lu, lv = store.lut(cu), store.lut(cv)
+    pyd = torch.as_tensor(pymat.ravel().copy()).cuda()
+    pvd = torch.as_tensor(pvp).cuda().contiguous()
+    U, V = oracle.coded_pair(kind, oracle.read_plink(prefix))
+    all_pairs = kind == "AD"
+    lst = [i for i in range(0, m - (0 if all_pairs else 1)) if i % 3 != 1]
+    scanner = eng.I8Exact(store, lu, lv, cv, pyd, pvd)
+    hits = scanner.scan(np.array(lst), eng.PAIRS_ALL if all_pairs else eng.PAIRS_UPPER, -1.0)
+    want = {}
+    for i in lst:
+        js, e, v, c, _ = oracle.exact_first_snp(U, V, i, pymat, pvp, all_pairs)
+        for q in range(len(js)):
+            want[(i, int(js[q]))] = (e[q], v[q])
+    got = {(int(a), int(b)): (e, v) for a, b, e, v in zip(hits["snp_0"], hits["snp_1"], hits["eff"], hits["var"])}
+    assert set(got) == set(want) and len(hits) == len(want)
+    ge = np.array([got[k] for k in want])
+    we = np.array([want[k] for k in want])
+    np.testing.assert_allclose(ge[:, 0], we[:, 0], rtol=RTOL, atol=1e-11)
+    np.testing.assert_allclose(ge[:, 1], we[:, 1], rtol=RTOL, atol=1e-13 * np.abs(we[:, 1]).max())
+
+
+def test_i8_operands_exact(eng, tmp_path):
+    """Integer codes are the reference's dosage / heterozygote indicator bit for bit; the digit planes rebuild
+    diag(u) A diag(u) (lower block-triangle, diagonal blocks halved) to 128^-S of its largest entry."""
+    import torch
+    from gmat_b200.engine import lib, _p, _stream, check
+    n, m = 300, 90
+    prefix, _ = _dataset(tmp_path, n, m, seed=3)
+    pymat, pvp = _random_model(n, 8)
+    store = eng.GenotypeStore(prefix)
+    raw = oracle.read_bed_raw(prefix)                                     # [m][n] 0/1/2
+    pyd = torch.as_tensor(pymat.ravel().copy()).cuda()
+    pvd = torch.as_tensor(pvp).cuda().contiguous()
+    for coding, want in ((eng.ADD, raw), (eng.DOM, np.where(raw > 1.5, 0.0, raw))):
+        sc = eng.I8Exact(store, store.lut(coding), store.lut(coding), coding, pyd, pvd)
+        g8 = sc.g8.cpu().numpy()
+        assert np.array_equal(g8[:, :n].astype(np.float64), want) and not g8[:, n:].any()
+    for planes in (3, 6, 8):
+        sc = eng.I8Exact(store, store.lut(eng.ADD), store.lut(eng.ADD), eng.ADD, pyd, pvd, n_planes=planes)
+        il = torch.as_tensor(np.array([1, m - 2], dtype=np.int64)).cuda()
+        u = sc._coded_first(il)
+        scale = (u.abs().amax(dim=1) ** 2 * (sc.amax / 0.99)).contiguous()
+        check(lib.gmat_b200_i8_split(_p(pvd, "double *"), n, _p(u, "double *"), 2, _p(scale, "double *"), planes,
+                                     _p(sc.planes, "signed char *"), _stream()), "gmat_b200_i8_split")
+        pl = sc.planes[: 2 * planes * sc.ld * sc.ld].view(2, planes, sc.ld, sc.ld).cpu().numpy().astype(np.float64)
+        rec = sum(pl[:, s] * 128.0 ** -(s + 1) for s in reversed(range(planes))) * scale.cpu().numpy()[:, None, None]
+        B = np.zeros((2, sc.ld, sc.ld))
+        uh = u.cpu().numpy()
+        B[:, :n, :n] = uh[:, :, None] * pvp[None] * uh[:, None, :]
+        blk = np.arange(sc.ld) // 128
+        lower = (blk[:, None] > blk[None, :]) + 0.5 * (blk[:, None] == blk[None, :])
+        err = np.abs(rec - B * lower).max() / scale.cpu().numpy().max()
+        assert err <= 0.51 * 128.0 ** -planes + 1e-15
+        assert np.abs(pl).max() <= 127
+
+
+def test_i8_and_f64_engines_report_the_same_hits(eng, tmp_path):
+    """Thresholded scan (what the drop-in runs): identical pair set, statistics within 1e-9 of the DMMA kernel."""
+    import torch
+    n, m = 700, 1500
+    prefix, _ = _dataset(tmp_path, n, m, seed=21)
+    pymat, pvp = _random_model(n, 4)
+    store = eng.GenotypeStore(prefix)
+    lu = store.lut(eng.ADD)
+    pyd = torch.as_tensor(pymat.ravel().copy()).cuda()
+    pvd = torch.as_tensor(pvp).cuda().contiguous()
+    packed = eng.pack_pvp(pvd)
+    first = np.arange(0, m - 1, 7)
+    ref = eng.epi_exact_scan(store, lu, lu, pyd, packed, first, eng.PAIRS_UPPER, 6.0)
+    got = eng.I8Exact(store, lu, lu, eng.ADD, pyd, pvd).scan(first, eng.PAIRS_UPPER, 6.0)
+    key = lambda h: h["snp_0"].astype(np.int64) * m + h["snp_1"]
+    ref, got = ref[np.argsort(key(ref))], got[np.argsort(key(got))]
+    border = np.abs(ref["chi"] / 6.0 - 1) < 1e-7
+    assert len(ref) > 1000
+    assert set(key(ref)[~border]) <= set(key(got)) and len(got) <= len(ref) + border.sum()
+    if len(ref) == len(got):
+        assert np.array_equal(key(ref), key(got))
+        np.testing.assert_allclose(got["eff"], ref["eff"], rtol=RTOL, atol=1e-12)
+        np.testing.assert_allclose(got["var"], ref["var"], rtol=RTOL)
+        np.testing.assert_allclose(got["chi"], ref["chi"], rtol=4 * RTOL)
+
+
+def test_i8_monomorphic_snps_and_small_batches(eng, tmp_path, monkeypatch):
+    """A second SNP whose code is the same for everybody has w == 0: eff = var = 0 and chi = NaN, as in the
+    reference (0/0), never a hit; a first SNP of that kind too.  Also: plane buffer budget of one first SNP per
+    launch gives the same result as one launch."""
+    import torch
+    from gmat_b200 import synth
+    n, m = 140, 60
+    g = synth.random_genotypes(n, m, 77, 0.0)
+    g[5, :] = 0
+    g[17, :] = 2
+    g[30, :] = 1
+    prefix, _ = _dataset(tmp_path, n, m, seed=1, geno=g)
+    pymat, pvp = _random_model(n, 2)
+    store = eng.GenotypeStore(prefix)
+    lu = store.lut(eng.ADD)
+    pyd = torch.as_tensor(pymat.ravel().copy()).cuda()
+    pvd = torch.as_tensor(pvp).cuda().contiguous()
+    packed = eng.pack_pvp(pvd)
+    first = np.arange(m - 1)
+    ref = eng.epi_exact_scan(store, lu, lu, pyd, packed, first, eng.PAIRS_UPPER, -1.0)
+    sc = eng.I8Exact(store, lu, lu, eng.ADD, pyd, pvd)
+    got = sc.scan(first, eng.PAIRS_UPPER, -1.0)
+    monkeypatch.setattr(sc, "batch", 1)
+    got1 = sc.scan(first, eng.PAIRS_UPPER, -1.0)
+    key = lambda h: h["snp_0"].astype(np.int64) * m + h["snp_1"]
+    ref, got, got1 = ref[np.argsort(key(ref))], got[np.argsort(key(got))], got1[np.argsort(key(got1))]
+    assert np.array_equal(key(ref), key(got)) and np.array_equal(key(ref), key(got1))
+    # (the two O(n) terms come from library DGEMMs whose summation order depends on the batch shape)
+    np.testing.assert_allclose(got1["var"], got["var"], rtol=1e-12)
+    np.testing.assert_allclose(got1["eff"], got["eff"], rtol=1e-12, atol=1e-13)
+    dead = np.isin(ref["snp_0"], [5, 17, 30]) | np.isin(ref["snp_1"], [5, 17, 30])
+    assert dead.sum() > 0
+    assert np.all(got["eff"][dead] == 0) and np.all(got["var"][dead] == 0) and np.all(np.isnan(got["chi"][dead]))
+    assert np.all(ref["var"][dead] == 0) and np.all(np.isnan(ref["chi"][dead]))
+    np.testing.assert_allclose(got["eff"][~dead], ref["eff"][~dead], rtol=RTOL, atol=1e-12)
+    np.testing.assert_allclose(got["var"][~dead], ref["var"][~dead], rtol=RTOL)
+    assert len(sc.scan(first, eng.PAIRS_UPPER, 1e-3)) == int(np.sum(ref["chi"] > 1e-3))
+
+
+def test_engine_selection(eng, tmp_path, monkeypatch):
+    """auto = int8 engine without missing genotypes, FP64 DMMA kernel otherwise; the int8 engine refuses a store
+    with missing genotypes instead of computing something else."""
+    import torch
+    p0, _ = _dataset(tmp_path, 40, 12, seed=5)
+    s0 = eng.GenotypeStore(p0)
+    p1 = str(tmp_path / "miss")
+    from gmat_b200 import synth
+    synth.write_dataset(p1, 40, 12, seed=5, missing_rate=0.1)
+    s1 = eng.GenotypeStore(p1)
+    monkeypatch.delenv("GMAT_B200_EXACT_ENGINE", raising=False)
+    assert eng.exact_engine(s0) == "i8" and eng.exact_engine(s1) == "f64"
+    monkeypatch.setenv("GMAT_B200_EXACT_ENGINE", "f64")
+    assert eng.exact_engine(s0) == "f64"
+    monkeypatch.setenv("GMAT_B200_EXACT_ENGINE", "bogus")
+    with pytest.raises(ValueError):
+        eng.exact_engine(s0)
+    pymat, pvp = _random_model(40, 2)
+    with pytest.raises(ValueError):
+        eng.I8Exact(s1, s1.lut(eng.ADD), s1.lut(eng.ADD), eng.ADD, torch.as_tensor(pymat.ravel().copy()).cuda(),
+                    torch.as_tensor(pvp).cuda())
