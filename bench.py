@@ -33,19 +33,37 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 N_ID, N_SNP, SEED = 2000, 20000, 20201013 + 2
-VAR_COM = [0.35, 0.10, 0.55]            # [A, A*A, residual]; fixed (throughput does not depend on it)
+VAR_PROP = [0.35, 0.10, 0.55]           # [A, A*A, residual] proportions of the phenotypic variance; fixed
 P_CUT = 1.0e-5
-BATCH = 256                             # first-SNPs per step
-E2E_FIRST = 4096                        # first-SNPs per GPU of the end-to-end call (~3.6e7 pairs)
+BATCH = 1024                            # first-SNPs per step
+E2E_FIRST = 4096                        # first-SNPs per GPU of the end-to-end call (~4.1e7 pairs)
 METRIC = "snp_pairs_per_sec_remma_epiAA_exact"
 # dram__bytes_read.sum + dram__bytes_write.sum of one exact-kernel launch of this step, from the committed
 # ncu --set full capture (profiles/r01_kernels_v3.md: 28.87 MB read + ~0 written = packed Z'PZ 17.8 MB + .bed
 # 10 MB + LUTs, read once; the capture ran 128 first-SNPs of the same data shape, the compulsory bytes are the same)
 EXACT_TRAFFIC_BYTES = 28.9e6
+I8_TRAFFIC_BYTES = None                 # dram bytes of one i8_scan_kernel launch (ncu --set full), set after the capture
 CONFIG = {"workload": "remma_epiAA exact test, synthetic n=%d x m=%d, GRMs [A, A*A] (BASELINE configs[2])"
                       % (N_ID, N_SNP),
-          "step": "one batch of %d first-SNPs (32 evenly spread blocks of 8), all j>i (~2.5e6 pairs) per rank" % BATCH,
+          "step": "one batch of %d first-SNPs (evenly spread blocks of 8), all j>i (~1.0e7 pairs) per rank" % BATCH,
           "p_cut": P_CUT, "l2": "flushed (256 MB write) between timed iterations"}
+
+
+def var_com_for(pheno):
+    """Fixed variance components (REML is not on the timed path): VAR_PROP scaled to the phenotypic variance of the
+    data set, so that the test statistics are calibrated and the output file holds the handful of rows a real scan
+    yields (unscaled components made every chi-square anti-conservative: ~0.3 % of all pairs were written)."""
+    yv = np.array([float(line.split()[-1]) for line in open(pheno)])
+    return [float(v * np.var(yv)) for v in VAR_PROP]
+
+
+def i8_ops_per_pair(n, planes):
+    """int8 tensor-core ops (2 per MAC) per pair: (algorithmic, issued).  Algorithmic = the lower triangle of the
+    symmetric B_i once per digit plane, planes * n(n+1); issued = what the kernel's tiling launches: per plane and per
+    256-row tile kt the id slabs 0..min(2kt+2, ceil(n/128))-1, each 256 x 128 MACs per pair."""
+    n_kt, n_slab = (n + 255) // 256, (n + 127) // 128
+    slabs = sum(min(2 * kt + 2, n_slab) for kt in range(n_kt))
+    return planes * float(n) * (n + 1), planes * slabs * 256.0 * 128.0 * 2.0
 
 
 def f_exact(n):
@@ -143,7 +161,7 @@ class CpuExact(object):
         if ag is None:
             ag, _ = oracle.agmat(prefix)
         y, xmat, zmat = design_matrix_wemai_multi_gmat(pheno, prefix)
-        self.py, self.pvp = oracle.preamble(y, xmat, zmat, [ag, ag * ag], VAR_COM)
+        self.py, self.pvp = oracle.preamble(y, xmat, zmat, [ag, ag * ag], var_com_for(pheno))
         self.U, self.V = oracle.coded_pair("AA", oracle.read_plink(prefix))
         self.m = self.U.shape[1]
 
@@ -247,7 +265,8 @@ def run_gpu(args):
     ag = ag_dev.cpu().numpy()
     gmat_lst = [ag, ag * ag]
     y, xmat, zmat = design_matrix_wemai_multi_gmat(pheno, prefix)
-    pymat, pvpmat = _core.preamble(y, xmat, zmat, gmat_lst, VAR_COM, scipy_inv=True)
+    var_com = var_com_for(pheno)
+    pymat, pvpmat = _core.preamble(y, xmat, zmat, gmat_lst, var_com, scipy_inv=True)
     model = _core.DeviceModel(pymat, pvpmat, dev)
     lut = store.lut(engine.ADD)
     chi_cut = float(chi2.isf(P_CUT, 1)) * (1 - 1e-9)
@@ -255,8 +274,13 @@ def run_gpu(args):
     pairs_rank = n_pairs(lst, N_SNP)
     il = np.asarray(lst, dtype=np.int64)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)       # > 126 MB L2
+    # the engine the drop-in runs for this data (GMAT_B200_EXACT_ENGINE, default auto -> int8 tensor cores)
+    which = engine.exact_engine(store)
+    i8 = engine.I8Exact(store, lut, lut, engine.ADD, model.py, model.pvp) if which == "i8" else None
 
     def step():
+        if i8 is not None:
+            return i8.scan(il, engine.PAIRS_UPPER, chi_cut)
         return engine.epi_exact_scan(store, lut, lut, model.py, model.packed, il, engine.PAIRS_UPPER, chi_cut)
 
     for _ in range(args.warmup):
@@ -266,6 +290,8 @@ def run_gpu(args):
     barrier()
     launches0 = lib.gmat_b200_kernel_launches()
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    if i8 is not None:
+        i8.kernel_events = []
     hits = None
     for k in range(args.steps):
         flush.zero_()                                # L2 flush between timed iterations
@@ -276,6 +302,11 @@ def run_gpu(args):
     launches = lib.gmat_b200_kernel_launches() - launches0
     clocks = sampler.result()
     ms_local = sum(a.elapsed_time(b) for a, b in ev) / args.steps
+    kern_ms = kern_n = None
+    if i8 is not None:
+        kern_n = len(i8.kernel_events)
+        kern_ms = sum(a.elapsed_time(b) for a, b in i8.kernel_events) / max(kern_n, 1)   # per i8_scan launch
+        i8.kernel_events = None
     print("[bench] rank %d: %.1f ms/step, per-step %s" % (rank, ms_local, [round(a.elapsed_time(b), 1) for a, b in ev]),
           file=sys.stderr)
     ms = reduce(ms_local, dist.ReduceOp.MAX if world > 1 else None)
@@ -285,55 +316,88 @@ def run_gpu(args):
     # ------------- e2e: the public drop-in call, HOST buffers, files in / file out, copies inside -------------
     # every rank makes the SAME call (E2E_FIRST first-SNPs per GPU); the front-end shards the list over the ranks
     # and gathers the hits to rank 0 (gmat_b200/remma/parallel.py), which writes the file
-    e2e_lst = batch_first_snps(N_SNP, 0, 1, E2E_FIRST * world)
+    e2e_lst = batch_first_snps(N_SNP, 0, 1, min(E2E_FIRST * world, (N_SNP - 1) // 8 * 8))
     e2e_pairs = n_pairs(e2e_lst, N_SNP)
     out_file = os.path.join(workdir, "epiAA_e2e")
     e2e_t = []
-    for it in range(2):
+    for it in range(3):
         barrier()
         t0 = time.perf_counter()
-        remma_epiAA(pheno, prefix, gmat_lst, VAR_COM, snp_lst_0=e2e_lst, p_cut=P_CUT, out_file=out_file)
+        remma_epiAA(pheno, prefix, gmat_lst, var_com, snp_lst_0=e2e_lst, p_cut=P_CUT, out_file=out_file)
         barrier()
         if it:
             e2e_t.append(time.perf_counter() - t0)
     e2e_s = reduce(float(np.mean(e2e_t)), dist.ReduceOp.MAX if world > 1 else None)
     e2e_value = float(e2e_pairs) / e2e_s
+    e2e_rows = sum(1 for _ in open(out_file)) - 1 if rank == 0 else 0
     # every rank uploads its own copy of the .bed payload, the GRMs (GPU preamble), y and X
     h2d = world * (store.h2d_bytes + sum(g.nbytes for g in gmat_lst) + y.nbytes + xmat.nbytes) + len(e2e_lst) * 8
-    d2h = 8 + 32 * (len(hits) if hits is not None else 0)
+    d2h = 8 + 32 * e2e_rows
 
     line = None
     if rank == 0:
         n = N_ID
-        achieved = (pairs_rank * f_exact(n)) / (ms * 1e-3) / 1e12          # per GPU, algorithmic flops
-        from gmat_b200._ffi import ffi
-        cfg = ffi.new("int[3]")
-        lib.gmat_b200_exact_config(cfg, cfg + 1, cfg + 2)
-        bm, bn = int(cfg[0]), int(cfg[1])
-        nb = (n + bm - 1) // bm
-        issued = pairs_rank * exact_issued_flop_per_pair(n, bm) / (ms * 1e-3) / 1e12
         line = {
             "metric": METRIC, "value": value, "unit": "pairs/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": CONFIG,
             "clocks": clocks, "gpu_launches": int(launches),
             "e2e": {"value": e2e_value, "unit": "pairs/s", "h2d_bytes_per_step": int(h2d),
-                    "d2h_bytes_per_step": int(d2h),
+                    "d2h_bytes_per_step": int(d2h), "seconds": e2e_s, "pairs": e2e_pairs, "rows_in_file": e2e_rows,
                     "what": "gmat_b200.remma.remma_epiAA(pheno_file, bed_file, gmat_lst, var_com, snp_lst_0=%d "
-                            "first-SNPs per GPU): phenotype parse + GRM upload + GPU preamble + .bed read + H2D + scan + D2H + file" % E2E_FIRST},
-            "roofline": {"bound": "tensor", "achieved": achieved, "unit": "TFLOP/s", "peak": None, "frac": None,
-                         "traffic": EXACT_TRAFFIC_BYTES, "kernel": "epi_exact_rb_kernel<%d,..,scan>" % bn,
-                         "flops_per_pair_algorithmic": f_exact(n), "issued_tflops": issued,
-                         "note": "achieved = pairs/s x (2n^2+5n), the reference formulation's flop; the kernel exploits the "
-                                 "symmetry of Z'PZ and issues ~51.5 % of them, so frac > 1 is expected: read "
-                                 "frac_issued (DMMA flop actually issued / measured DMMA peak) as pipe utilisation"},
+                            "first-SNPs): phenotype parse + GRM upload + GPU preamble + .bed read + H2D + scan + D2H "
+                            "+ file" % len(e2e_lst)},
         }
-        peaks = measure_fp64_peaks(engine, torch)
-        peak = max(peaks["dmma_tflops"], peaks["cublas_dgemm_tflops"])
-        line["roofline"].update({"peak": peak, "frac": achieved / peak, "frac_issued": issued / peak,
-                                 "peak_source": "measured live on rank 0: max(DMMA issue-rate microbenchmark, cuBLAS "
-                                                "DGEMM 4096^3); FP64 is absent from MEASURED_PEAKS.json; achieved "
-                                                "and issued are per GPU", **peaks})
+        if i8 is not None:
+            planes = i8.n_planes
+            alg, iss = i8_ops_per_pair(n, planes)
+            launches_per_step = kern_n / float(args.steps)
+            pairs_per_launch = pairs_rank / launches_per_step
+            achieved = pairs_per_launch * alg / (kern_ms * 1e-3) / 1e12
+            issued = pairs_per_launch * iss / (kern_ms * 1e-3) / 1e12
+            peaks = {"i8_mma_issue_tops": engine.i8_peak(20000)}
+            mp = {}
+            try:
+                mp = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "MEASURED_PEAKS.json")))
+            except Exception:
+                pass
+            peaks["int8_from_measured_bf16_sustained_x2"] = 2.0 * mp["bf16_tflops_sustained"] if mp else None
+            peaks["int8_from_measured_bf16_burst_x2"] = 2.0 * mp["bf16_tflops"] if mp else None
+            peak = peaks["i8_mma_issue_tops"]
+            line["dtype"] = "f64 (n^2 term: error-free int8 digit planes, %d x 7 bit, int32 accumulate; rest f64)" % planes
+            line["roofline"] = {
+                "bound": "tensor", "achieved": achieved, "unit": "TOP/s", "peak": peak, "frac": achieved / peak,
+                "traffic": I8_TRAFFIC_BYTES, "kernel": "i8_scan_kernel (tcgen05.mma kind::i8, 128x256x32)",
+                "kernel_ms_per_launch": kern_ms, "kernel_launches_per_step": launches_per_step,
+                "kernel_share_of_step": kern_ms * launches_per_step / ms_local,
+                "ops_per_pair_algorithmic": alg, "ops_per_pair_issued": iss, "issued_tops": issued,
+                "frac_issued": issued / peak,
+                "fp64_equivalent_tflops": pairs_rank * f_exact(n) / (ms * 1e-3) / 1e12,
+                "peak_source": "measured live on rank 0: issue rate of back-to-back tcgen05.mma kind::i8 128x256x32 on "
+                               "resident tiles, all SMs (gmat_b200_i8_peak); MEASURED_PEAKS.json has no int8 figure, "
+                               "2 x its dense bf16 numbers are listed beside it", **peaks,
+                "note": "achieved = planes x n(n+1) int8 ops per pair (lower triangle of the symmetric quadratic form, "
+                        "once per digit plane) / the kernel's own launch time; issued adds the tiling's padding and "
+                        "the zero half of the diagonal 256x256 blocks"}
+        else:
+            achieved = (pairs_rank * f_exact(n)) / (ms * 1e-3) / 1e12          # per GPU, algorithmic flops
+            from gmat_b200._ffi import ffi
+            cfg = ffi.new("int[3]")
+            lib.gmat_b200_exact_config(cfg, cfg + 1, cfg + 2)
+            bm, bn = int(cfg[0]), int(cfg[1])
+            issued = pairs_rank * exact_issued_flop_per_pair(n, bm) / (ms * 1e-3) / 1e12
+            line["roofline"] = {"bound": "tensor", "achieved": achieved, "unit": "TFLOP/s", "peak": None, "frac": None,
+                                "traffic": EXACT_TRAFFIC_BYTES, "kernel": "epi_exact_rb_kernel<%d,..,scan>" % bn,
+                                "flops_per_pair_algorithmic": f_exact(n), "issued_tflops": issued,
+                                "note": "achieved = pairs/s x (2n^2+5n), the reference formulation's flop; the kernel exploits the "
+                                        "symmetry of Z'PZ and issues ~51.5 % of them, so frac > 1 is expected: read "
+                                        "frac_issued (DMMA flop actually issued / measured DMMA peak) as pipe utilisation"}
+            peaks = measure_fp64_peaks(engine, torch)
+            peak = max(peaks["dmma_tflops"], peaks["cublas_dgemm_tflops"])
+            line["roofline"].update({"peak": peak, "frac": achieved / peak, "frac_issued": issued / peak,
+                                     "peak_source": "measured live on rank 0: max(DMMA issue-rate microbenchmark, cuBLAS "
+                                                    "DGEMM 4096^3); FP64 is absent from MEASURED_PEAKS.json; achieved "
+                                                    "and issued are per GPU", **peaks})
         if world == 1:
             if not args.no_extra:
                 line["extra"] = extras(engine, torch, synth, store, model, lut, args, prefix, pymat)
@@ -366,6 +430,14 @@ def extras(engine, torch, synth, store, model, lut, args, prefix, pymat):
                 best = min(best, e0.elapsed_time(e1))
         return best * 1e-3
 
+    # the FP64 DMMA kernel on a 256-first-SNP batch of the same data: what the exact scan runs when genotypes are
+    # missing (GMAT_B200_EXACT_ENGINE=f64), and the yardstick for the int8 engine
+    sub = np.asarray(batch_first_snps(N_SNP, 0, 1, 256), dtype=np.int64)
+    t = timed(lambda: engine.epi_exact_scan(store, lut, lut, model.py, model.packed, sub, engine.PAIRS_UPPER, 19.5),
+              reps=2)
+    out["exact_f64_engine"] = {"pairs_per_s": n_pairs(sub, N_SNP) / t, "seconds": t,
+                               "tflops_algorithmic": n_pairs(sub, N_SNP) * f_exact(N_ID) / t / 1e12,
+                               "workload": "epi_exact_rb_kernel (DMMA), 256 first-SNPs, all j>i"}
     # approximate screen: full scan of the C3 data (1.9999e8 pairs), F_approx = 2n flop per pair
     la = store.lut(engine.ADD, engine.FREQ_CLOOP)
     full = np.arange(N_SNP - 1, dtype=np.int64)

@@ -274,6 +274,46 @@ i8_scan_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_constant_
     }
 }
 
+// Issue-rate microbenchmark of the int8 MMA (the roofline denominator of the engine): one thread per CTA issues
+// back-to-back 128x256x32 MMAs on a resident (pseudo-random) smem tile pair, alternating two TMEM accumulators.
+__global__ void __launch_bounds__(128, 1) i8_peak_kernel(int iters) {
+    extern __shared__ unsigned char smem_raw[];
+    unsigned char *smem = reinterpret_cast<unsigned char *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                                           ~static_cast<uintptr_t>(1023));
+    __shared__ uint64_t bar;
+    __shared__ uint32_t tbase_slot;
+    for (int k = threadIdx.x; k < I8_STAGE_BYTES / 4; k += blockDim.x)
+        reinterpret_cast<unsigned *>(smem)[k] = (unsigned)(k * 2654435761u) ^ (blockIdx.x * 40503u);
+    if (threadIdx.x == 0) { mbar_init(&bar, 1); mbar_fence_init(); }
+    if (threadIdx.x < 32) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;\n" ::"r"(smem_u32(&tbase_slot)),
+                     "r"(512)
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;\n" ::: "memory");
+    }
+    fence_proxy_async();
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tbase = tbase_slot;
+    if (threadIdx.x == 0) {
+        const uint32_t sa = smem_u32(smem);
+        const uint64_t da = umma_desc_sw128(sa), db = umma_desc_sw128(sa + I8_A_BYTES);
+        for (int it = 0; it < iters; ++it) {
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+                umma_i8(tbase + (uint32_t)((it & 1) * I8_TK), da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), I8_IDESC,
+                        (uint32_t)(it > 1));
+        }
+        tc_commit(&bar);
+        mbar_wait(&bar, 0);
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (threadIdx.x < 32)
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;\n" ::"r"(tbase), "r"(512) : "memory");
+}
+
 // ------------------------------------------------------------------------------------------ operand builders
 // integer code of the second SNP: additive dosage {0,miss->0,1,2}; dominance indicator {0,miss->0,1,0}
 __global__ void i8_dosage_kernel(const unsigned char *__restrict__ bed, int n, long long m, long long row_bytes,
@@ -427,58 +467,59 @@ extern "C" int gmat_b200_i8_split(const double *pvp_dev, long long n, const doub
 }
 
 extern "C" int gmat_b200_i8_scan(const signed char *g8_dev, long long n, long long m, const signed char *planes_dev,
-                                 int n_planes, const long long *ilist_dev, const long long *ilist_host, long long n_i,
+                                 int n_planes, const long long *ilist_dev, long long n_i,
+                                 const int *item_prefix_dev, const int *jt0_dev, long long total_items,
                                  const double *scale_dev, const double *s_dev, const double *upy_dev,
                                  const double *t1_dev, const double *e_dev, const double *offs_dev,
                                  int pair_space, double chi_cut, gmat_b200_hit *hits_dev, long long cap,
                                  unsigned long long *count_dev, double *q_debug_dev, void *stream) {
-    GB_CHECK_ARG(g8_dev && planes_dev && ilist_dev && ilist_host && scale_dev && s_dev && upy_dev && t1_dev && e_dev &&
-                 offs_dev && count_dev, "null buffer");
-    GB_CHECK_ARG(n > 0 && m > 0 && n_i > 0 && n_i <= 4096, "shape");
+    GB_CHECK_ARG(g8_dev && planes_dev && ilist_dev && item_prefix_dev && jt0_dev && scale_dev && s_dev && upy_dev &&
+                 t1_dev && e_dev && offs_dev && count_dev, "null buffer");
+    GB_CHECK_ARG(n > 0 && m > 0 && n_i > 0 && total_items >= 0 && total_items < (1LL << 31), "shape");
     GB_CHECK_ARG(n_planes >= 2 && n_planes <= I8_MAX_PLANES, "n_planes must be in [2, 8]");
     GB_CHECK_ARG(pair_space == GMAT_B200_PAIRS_UPPER || pair_space == GMAT_B200_PAIRS_ALL, "pair_space");
     GB_CHECK_ARG(cap == 0 || hits_dev, "hits buffer");
+    if (total_items == 0) return GMAT_B200_OK;
     cudaStream_t st = (cudaStream_t)stream;
     I8Params p;
     p.n = (int)n; p.m = (int)m; p.ld = (int)round_up(n, I8_TK); p.np = p.ld;
     p.n_planes = n_planes; p.n_kt = p.ld / I8_TK; p.n_slab = (int)((n + I8_SLAB - 1) / I8_SLAB);
     p.n_i = (int)n_i; p.pair_space = pair_space;
     GB_CHECK_ARG((long long)n_i * n_planes * p.np < (1LL << 31), "plane buffer has too many rows for one tensor map");
-    // work items: (first SNP, tile of 128 second SNPs)
-    const int n_jt = (int)((m + I8_TJ - 1) / I8_TJ);
-    int *host_tab = (int *)malloc(sizeof(int) * (2 * n_i + 1));
-    if (!host_tab) { set_error("out of host memory"); return GMAT_B200_ERR_ARG; }
-    int *prefix = host_tab, *jt0 = host_tab + n_i + 1;
-    long long total = 0;
-    for (long long ii = 0; ii < n_i; ++ii) {
-        const long long i = ilist_host[ii];
-        if (i < 0 || i >= m) { free(host_tab); set_error("bad argument: first SNP out of range"); return GMAT_B200_ERR_ARG; }
-        const int first = pair_space == GMAT_B200_PAIRS_ALL ? 0 : (int)((i + 1) / I8_TJ);
-        prefix[ii] = (int)total; jt0[ii] = first;
-        total += (first < n_jt && (pair_space == GMAT_B200_PAIRS_ALL || i + 1 < m)) ? n_jt - first : 0;
-    }
-    prefix[n_i] = (int)total;
-    if (total == 0) { free(host_tab); return GMAT_B200_OK; }
-    int *tab_dev = nullptr;
-    cudaError_t e = cudaMallocAsync((void **)&tab_dev, sizeof(int) * (2 * n_i + 1), st);
-    if (e != cudaSuccess) { free(host_tab); set_error("cudaMallocAsync failed: %s", cudaGetErrorString(e)); return GMAT_B200_ERR_CUDA; }
-    e = cudaMemcpyAsync(tab_dev, host_tab, sizeof(int) * (2 * n_i + 1), cudaMemcpyHostToDevice, st);
-    if (e == cudaSuccess) e = cudaStreamSynchronize(st);       // host_tab is pageable: finish before freeing it
-    free(host_tab);
-    if (e != cudaSuccess) { cudaFreeAsync(tab_dev, st); set_error("table upload failed: %s", cudaGetErrorString(e)); return GMAT_B200_ERR_CUDA; }
-    p.total_items = (int)total; p.item_prefix = tab_dev; p.jt0 = tab_dev + n_i + 1;
+    p.total_items = (int)total_items; p.item_prefix = item_prefix_dev; p.jt0 = jt0_dev;
     p.ilist = ilist_dev; p.g8 = g8_dev; p.scale = scale_dev; p.s_i = s_dev; p.upy = upy_dev; p.t1 = t1_dev; p.e = e_dev;
     p.offs = offs_dev; p.chi_cut = chi_cut; p.hits = hits_dev; p.cap = cap; p.count = count_dev; p.q_debug = q_debug_dev;
 
     CUtensorMap map_g, map_p;
     int rc = make_map(&map_g, g8_dev, p.ld, m, p.ld, I8_TJ);
     if (rc == GMAT_B200_OK) rc = make_map(&map_p, planes_dev, p.ld, (long long)n_i * n_planes * p.np, p.ld, I8_TK);
-    if (rc != GMAT_B200_OK) { cudaFreeAsync(tab_dev, st); return rc; }
+    if (rc != GMAT_B200_OK) return rc;
     const int smem_bytes = I8_NS * I8_STAGE_BYTES + 1024 + (int)sizeof(I8Bars);
     GB_CUDA(cudaFuncSetAttribute(i8_scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
-    const int grid = (int)(total < sm_count() ? total : sm_count());
+    const int grid = (int)(total_items < sm_count() ? total_items : sm_count());
     i8_scan_kernel<<<grid, I8_THREADS, smem_bytes, st>>>(map_g, map_p, p);
     GB_LAUNCH_CHECK();
-    GB_CUDA(cudaFreeAsync(tab_dev, st));
+    return GMAT_B200_OK;
+}
+
+extern "C" int gmat_b200_i8_peak(int iters, double *tops) {
+    GB_CHECK_ARG(iters > 0 && tops, "iters/tops");
+    const int smem_bytes = I8_STAGE_BYTES + 1024;
+    GB_CUDA(cudaFuncSetAttribute(i8_peak_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
+    cudaEvent_t e0, e1;
+    GB_CUDA(cudaEventCreate(&e0));
+    GB_CUDA(cudaEventCreate(&e1));
+    const int grid = sm_count();
+    i8_peak_kernel<<<grid, 128, smem_bytes>>>(iters / 8 + 1);          // warm-up
+    GB_CUDA(cudaEventRecord(e0));
+    i8_peak_kernel<<<grid, 128, smem_bytes>>>(iters);
+    GB_CUDA(cudaEventRecord(e1));
+    GB_CUDA(cudaEventSynchronize(e1));
+    GB_LAUNCH_CHECK();
+    float ms = 0.f;
+    GB_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    *tops = 2.0 * grid * (double)iters * 4.0 * I8_TJ * I8_TK * 32.0 / (ms * 1e-3) / 1e12;
     return GMAT_B200_OK;
 }

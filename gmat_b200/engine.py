@@ -250,6 +250,7 @@ class I8Exact(object):
         self.batch = int(max(1, min(64, self.PLANE_BYTES // per_first)))
         self.planes = torch.zeros((self.batch * per_first,), dtype=torch.int8, device=dev)
         self._shifts = torch.tensor([0, 2, 4, 6], dtype=torch.uint8, device=dev)
+        self.kernel_events = None      # bench.py: list of (start, end) CUDA events around every i8_scan launch
 
     def _coded_first(self, il):
         """[len(il)][n] FP64 coded first SNPs: lutU[i][code] (missing calls of a FIRST SNP are fine: they code 0)."""
@@ -257,48 +258,75 @@ class I8Exact(object):
         codes = ((rows[:, :, None] >> self._shifts) & 3).reshape(len(il), -1)[:, :self.store.n]
         return torch.gather(self.lutU[il], 1, codes.long())
 
+    def _work_items(self, ih, pair_space):
+        """(item_prefix[n_i+1], jt0[n_i]) int32 host arrays: tiles of 128 second SNPs every first SNP needs."""
+        m = self.store.m
+        n_jt = (m + 127) // 128
+        if pair_space == PAIRS_ALL:
+            jt0 = np.zeros(len(ih), dtype=np.int64)
+            cnt = np.full(len(ih), n_jt, dtype=np.int64)
+        else:
+            jt0 = (ih + 1) // 128
+            cnt = np.where(ih + 1 < m, n_jt - jt0, 0)
+        prefix = np.concatenate([[0], np.cumsum(cnt)])
+        return prefix.astype(np.int32), jt0.astype(np.int32)
+
     def scan(self, ilist, pair_space, chi_cut, cap=1 << 20, q_debug=False):
+        """All launches of the scan are queued back to back (one hit buffer, one counter, no host synchronisation
+        between first-SNP batches); the counter is read once at the end and the scan repeated with the exact
+        capacity in the rare case the buffer was too small."""
         store, dev = self.store, self.store.device
         n, m = store.n, store.m
         ilist = np.ascontiguousarray(ilist, dtype=np.int64)
-        out, dbg = [], []
+        if len(ilist) and (ilist.min() < 0 or ilist.max() >= m):
+            raise ValueError("first SNP out of range")
         count = torch.zeros((1,), dtype=torch.int64, device=dev)
-        for b0 in range(0, len(ilist), self.batch):
-            ih = np.ascontiguousarray(ilist[b0:b0 + self.batch])
-            il = torch.as_tensor(ih).to(dev)
-            ni = len(ih)
-            u = self._coded_first(il)                                   # [ni][n]
-            r = u * (u @ self.A)                                        # u o (A u)   (A symmetric)
-            upy_vec = u * self.py
-            s_i = r.sum(dim=1).contiguous()
-            upy = upy_vec.sum(dim=1).contiguous()
-            te = torch.cat([r, upy_vec]) @ self.gd.T                    # [2 ni][m]: a_j.r_i and a_j.(u_i o py)
-            t1, e = te[:ni].contiguous(), te[ni:].contiguous()
-            scale = (u.abs().amax(dim=1) ** 2 * (self.amax / 0.99)).clamp_min(1e-200).contiguous()
-            check(lib.gmat_b200_i8_split(_p(self.A, "double *"), n, _p(u, "double *"), ni, _p(scale, "double *"),
-                                         self.n_planes, _p(self.planes, "signed char *"), _stream()),
-                  "gmat_b200_i8_split")
-            qd = torch.zeros((ni, m), dtype=torch.float64, device=dev) if q_debug else None
-            this_cap = cap
-            while True:
-                hits = alloc_hits(this_cap, dev)
-                count.zero_()
+        while True:
+            hits = alloc_hits(cap, dev)
+            count.zero_()
+            dbg = []
+            for b0 in range(0, len(ilist), self.batch):
+                ih = ilist[b0:b0 + self.batch]
+                ni = len(ih)
+                prefix, jt0 = self._work_items(ih, pair_space)
+                total = int(prefix[-1])
+                if total == 0:
+                    continue
+                il = torch.as_tensor(ih).to(dev, non_blocking=True)
+                tab = torch.as_tensor(np.concatenate([prefix, jt0])).to(dev, non_blocking=True)
+                u = self._coded_first(il)                                   # [ni][n]
+                r = u * (u @ self.A)                                        # u o (A u)   (A symmetric)
+                upy_vec = u * self.py
+                s_i = r.sum(dim=1).contiguous()
+                upy = upy_vec.sum(dim=1).contiguous()
+                te = torch.cat([r, upy_vec]) @ self.gd.T                    # [2 ni][m]: a_j.r_i and a_j.(u_i o py)
+                scale = (u.abs().amax(dim=1) ** 2 * (self.amax / 0.99)).clamp_min(1e-200).contiguous()
+                check(lib.gmat_b200_i8_split(_p(self.A, "double *"), n, _p(u, "double *"), ni,
+                                             _p(scale, "double *"), self.n_planes,
+                                             _p(self.planes, "signed char *"), _stream()), "gmat_b200_i8_split")
+                qd = torch.zeros((ni, m), dtype=torch.float64, device=dev) if q_debug else None
+                if self.kernel_events is not None:
+                    ev = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+                    ev[0].record()
                 check(lib.gmat_b200_i8_scan(
                     _p(self.g8, "signed char *"), n, m, _p(self.planes, "signed char *"), self.n_planes,
-                    _p(il, "long long *"), ffi.cast("long long *", ih.ctypes.data), ni,
-                    _p(scale, "double *"), _p(s_i, "double *"), _p(upy, "double *"), _p(t1, "double *"),
-                    _p(e, "double *"), _p(self.offs, "double *"), pair_space, float(chi_cut),
-                    ffi.cast("gmat_b200_hit *", hits.data_ptr()), this_cap,
+                    _p(il, "long long *"), ni, _p(tab, "int *"), ffi.cast("int *", tab.data_ptr() + 4 * (ni + 1)),
+                    total, _p(scale, "double *"), _p(s_i, "double *"), _p(upy, "double *"),
+                    _p(te, "double *"), ffi.cast("double *", te.data_ptr() + 8 * ni * m),
+                    _p(self.offs, "double *"), pair_space, float(chi_cut),
+                    ffi.cast("gmat_b200_hit *", hits.data_ptr()), cap,
                     ffi.cast("unsigned long long *", count.data_ptr()), _p(qd, "double *"), _stream()),
                     "gmat_b200_i8_scan")
-                cnt = int(count.item())
-                if cnt <= this_cap:
-                    out.append(hits_to_numpy(hits, cnt))
-                    break
-                this_cap = cnt
-            if q_debug:
-                dbg.append(qd)
-        res = np.concatenate(out) if out else np.zeros((0,), dtype=HIT_DTYPE)
+                if self.kernel_events is not None:
+                    ev[1].record()
+                    self.kernel_events.append(ev)
+                if q_debug:
+                    dbg.append(qd)
+            cnt = int(count.item())
+            if cnt <= cap:
+                break
+            cap = cnt
+        res = hits_to_numpy(hits, cnt)
         return (res, torch.cat(dbg)) if q_debug else res
 
 
@@ -362,6 +390,14 @@ def decode_into(store, coding, out, freq_mode=FREQ_NUMPY):
     check(lib.gmat_b200_decode(_p(store.bed, "unsigned char *"), store.n, store.m, store.row_bytes,
                                _p(lut, "double *"), _p(out, "double *"), _stream()), "gmat_b200_decode")
     return out
+
+
+def i8_peak(iters=20000):
+    """Measured issue rate of the int8 tensor-core MMA on this GPU, TOPS (2 ops per MAC)."""
+    require_cuda()
+    out = ffi.new("double *")
+    check(lib.gmat_b200_i8_peak(iters, out), "gmat_b200_i8_peak")
+    return float(out[0])
 
 
 def fp64_peak(kind=0, iters=20000):

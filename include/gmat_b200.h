@@ -190,14 +190,22 @@ int gmat_b200_i8_dosage(const unsigned char *bed_dev, long long n, long long m, 
  * are never written); u_dev [n_i][n] coded first SNPs; scale_dev[i] >= max|B_i| / 0.99                          */
 int gmat_b200_i8_split(const double *pvp_dev /* [n][n] */, long long n, const double *u_dev, long long n_i,
                        const double *scale_dev, int n_planes, signed char *planes_dev, void *stream);
-/* t1_dev/e_dev: [n_i][m] FP64 (a_j . r_i and a_j . (u_i o Z'Py)); offs_dev[m] = o_j; ilist_host mirrors ilist_dev;
- * q_debug_dev (optional, [n_i][m]) receives a_j' B_i a_j.  Hits as in gmat_b200_epi_exact_scan.                */
+/* Work items of one launch are (first SNP ii, tile of 128 second SNPs): item_prefix_dev[n_i+1] = first item of
+ * every first SNP, jt0_dev[n_i] = its first tile (UPPER: (i+1)/128, ALL: 0), total_items = item_prefix[n_i]; all
+ * device arrays, so that successive launches queue without a host synchronisation.  t1_dev/e_dev: [n_i][m] FP64
+ * (a_j . r_i and a_j . (u_i o Z'Py)); offs_dev[m] = o_j (NaN = monomorphic second SNP: eff = var = 0, chi = NaN);
+ * q_debug_dev (optional, [n_i][m]) receives a_j' B_i a_j.  Hits are appended at *count_dev as in
+ * gmat_b200_epi_exact_scan (count keeps counting beyond cap).                                                  */
 int gmat_b200_i8_scan(const signed char *g8_dev, long long n, long long m, const signed char *planes_dev,
-                      int n_planes, const long long *ilist_dev, const long long *ilist_host, long long n_i,
+                      int n_planes, const long long *ilist_dev, long long n_i,
+                      const int *item_prefix_dev, const int *jt0_dev, long long total_items,
                       const double *scale_dev, const double *s_dev, const double *upy_dev,
                       const double *t1_dev, const double *e_dev, const double *offs_dev,
                       int pair_space, double chi_cut, gmat_b200_hit *hits_dev, long long cap,
                       unsigned long long *count_dev, double *q_debug_dev, void *stream);
+
+/* int8 tensor-core issue-rate microbenchmark (tcgen05.mma kind::i8 128x256x32 on resident tiles, all SMs): TOPS  */
+int gmat_b200_i8_peak(int iters, double *tops);
 
 /* Host text writer, byte-identical to np.savetxt(path, mat) as used by output_mat (gmat/gmatrix/gmatrix.py:10-14:
  * '%.18e', ' ' delimiter, '\n'): rows formatted in parallel by `threads` host threads (<= 0: all).  No GPU work. */

@@ -23,12 +23,12 @@ def main():
     gl = [ag, ag * ag]
     lst = bench.batch_first_snps(bench.N_SNP, 0, 1, bench.E2E_FIRST)
     out = os.path.join(d, "o")
-    remma_epiAA(pheno, prefix, gl, bench.VAR_COM, snp_lst_0=lst, p_cut=1e-5, out_file=out)
+    remma_epiAA(pheno, prefix, gl, bench.var_com_for(pheno), snp_lst_0=lst, p_cut=1e-5, out_file=out)
     torch.cuda.synchronize()
     pr = cProfile.Profile()
     t0 = time.perf_counter()
     pr.enable()
-    remma_epiAA(pheno, prefix, gl, bench.VAR_COM, snp_lst_0=lst, p_cut=1e-5, out_file=out)
+    remma_epiAA(pheno, prefix, gl, bench.var_com_for(pheno), snp_lst_0=lst, p_cut=1e-5, out_file=out)
     torch.cuda.synchronize()
     pr.disable()
     print("total %.3f s for %d pairs" % (time.perf_counter() - t0, bench.n_pairs(lst, bench.N_SNP)))

@@ -9,7 +9,7 @@ fi
 PK="python scripts/profile_kernels.py --reps 0 ${PROFILE_ARGS:-}"
 timeout 600 $PK > gpurun_out/prof_plain.log 2>&1 &&
 timeout 1500 ncu --set full --clock-control none --import-source on \
-    -k regex:'epi_exact|epi_eff_kernel|grm_kernel|decode_kernel' -c 12 \
+    -k regex:'i8_scan|i8_split|epi_exact|epi_eff_kernel|grm_kernel|decode_kernel' -c 14 \
     -f -o gpurun_out/prof_kernels $PK > gpurun_out/prof_ncu.log 2>&1
 echo "profile rc=$?"; tail -2 gpurun_out/prof_plain.log; tail -3 gpurun_out/prof_ncu.log
 BN="python bench.py --steps 2 --warmup 1 --no-cpu ${BENCH_ARGS:-}"

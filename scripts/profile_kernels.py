@@ -18,7 +18,7 @@ sys.path.insert(0, ROOT)
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--only", default="exact,eff,grm,decode,stats")
+    ap.add_argument("--only", default="i8,exact,eff,grm,decode,stats")
     ap.add_argument("--n", type=int, default=2000)
     ap.add_argument("--m", type=int, default=20000)
     ap.add_argument("--first", type=int, default=64, help="first-SNPs of the exact-scan launch")
@@ -51,7 +51,7 @@ def main():
     if "stats" in only:
         t = timed(lambda: engine.GenotypeStore.from_device_payload(store.bed, n))
         out["bed_stats"] = {"seconds": t, "gb_per_s": m * rb / t / 1e9}
-    if only & {"exact", "eff"}:
+    if only & {"exact", "eff", "i8"}:
         gen = torch.Generator(device=dev)
         gen.manual_seed(5)
         b = torch.randn((n, n + 8), dtype=torch.float64, device=dev, generator=gen)
@@ -72,6 +72,16 @@ def main():
         t = timed(lambda: engine.epi_exact_scan(store, lut, lut, py, packed, il, engine.PAIRS_UPPER, 30.0))
         out["exact"] = {"seconds": t, "pairs": pairs, "pairs_per_s": pairs / t,
                         "tflops_algorithmic": pairs * (2.0 * n * n + 5 * n) / t / 1e12}
+    if "i8" in only:
+        lut = store.lut(engine.ADD)
+        pvp = pvp.contiguous()
+        sc = engine.I8Exact(store, lut, lut, engine.ADD, py, pvp)
+        il = np.unique((np.linspace(0, m - 10, 8).astype(np.int64)[:, None] + np.arange(8)[None, :]).ravel())
+        pairs = int(np.sum(m - 1 - il))
+        t = timed(lambda: sc.scan(il, engine.PAIRS_UPPER, 30.0))
+        out["i8"] = {"seconds": t, "pairs": pairs, "pairs_per_s": pairs / t, "planes": sc.n_planes,
+                     "int8_tops_algorithmic": pairs * sc.n_planes * float(n) * (n + 1) / t / 1e12}
+        del sc
     if "eff" in only:
         la = store.lut(engine.ADD, engine.FREQ_CLOOP)
         full = np.arange(m - 1, dtype=np.int64)
