@@ -274,6 +274,176 @@ i8_scan_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_constant_
     }
 }
 
+// ---- wide variant: TWO tiles of 128 second SNPs per CTA share every plane tile --------------------------------
+// The first kernel is bound by L2 -> SM bandwidth (ncu: lts throughput 70 %, tensor pipe 58 %): 48 KB per 512 MMA
+// cycles.  Here a stage is {genotype tile 0, genotype tile 1, plane tile} = 64 KB per 1024 MMA cycles (-33 %
+// bytes per MAC).  Both 256-column accumulators are live at once, so TMEM cannot double-buffer any more: the
+// issuer waits, per accumulator, for that accumulator's four epilogue warps before the first MMA of the next tile.
+constexpr int I8W_NS = 3;
+constexpr int I8W_STAGE_BYTES = 2 * I8_A_BYTES + I8_B_BYTES;      // 64 KB
+constexpr int I8W_THREADS = 320;                                  // producer, issuer, 2 x 4 epilogue warps
+
+struct I8WBars {
+    uint64_t full[I8W_NS], empty[I8W_NS], tfull, tempty[2];
+    uint32_t tmem_base;
+};
+
+__global__ void __launch_bounds__(I8W_THREADS, 1)
+i8_scan_wide_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_constant__ CUtensorMap map_p,
+                    const I8Params p) {
+    extern __shared__ unsigned char smem_raw[];
+    unsigned char *smem = reinterpret_cast<unsigned char *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                                           ~static_cast<uintptr_t>(1023));
+    I8WBars *bars = reinterpret_cast<I8WBars *>(smem + I8W_NS * I8W_STAGE_BYTES);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < I8W_NS; ++s) { mbar_init(&bars->full[s], 1); mbar_init(&bars->empty[s], 1); }
+        mbar_init(&bars->tfull, 1);
+        mbar_init(&bars->tempty[0], 4);
+        mbar_init(&bars->tempty[1], 4);
+        mbar_fence_init();
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;\n" ::"r"(
+                         smem_u32(&bars->tmem_base)), "r"(512)
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;\n" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = bars->tmem_base;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            int stage = 0; unsigned phase = 0;
+            for (int item = blockIdx.x; item < p.total_items; item += gridDim.x) {
+                const int ii = i8_find_first(p.item_prefix, p.n_i, item);
+                const int jt = 2 * (p.jt0[ii] + (item - p.item_prefix[ii]));       // first of the two 128-SNP tiles
+                for (int s = 0; s < p.n_planes; ++s) {
+                    const int prow = (ii * p.n_planes + s) * p.np;
+                    for (int kt = 0; kt < p.n_kt; ++kt) {
+                        const int nl = i8_slabs_of(kt, p.n_slab);
+                        for (int l = 0; l < nl; ++l) {
+                            mbar_wait(&bars->empty[stage], phase ^ 1u);
+                            mbar_expect_tx(&bars->full[stage], I8W_STAGE_BYTES);
+                            unsigned char *sa = smem + stage * I8W_STAGE_BYTES;
+                            tma_load_2d(sa, &map_g, l * I8_SLAB, jt * I8_TJ, &bars->full[stage]);
+                            tma_load_2d(sa + I8_A_BYTES, &map_g, l * I8_SLAB, (jt + 1) * I8_TJ, &bars->full[stage]);
+                            tma_load_2d(sa + 2 * I8_A_BYTES, &map_p, l * I8_SLAB, prow + kt * I8_TK, &bars->full[stage]);
+                            if (++stage == I8W_NS) { stage = 0; phase ^= 1u; }
+                        }
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            int stage = 0; unsigned phase = 0;
+            unsigned tphase = 0;                                             // parity of the tile being issued
+            for (int item = blockIdx.x; item < p.total_items; item += gridDim.x) {
+                for (int s = 0; s < p.n_planes; ++s) {
+                    for (int kt = 0; kt < p.n_kt; ++kt) {
+                        const int nl = i8_slabs_of(kt, p.n_slab);
+                        for (int l = 0; l < nl; ++l) {
+                            mbar_wait(&bars->full[stage], phase);
+                            tc_fence_after();
+                            const uint32_t sa = smem_u32(smem + stage * I8W_STAGE_BYTES);
+                            const uint64_t da0 = umma_desc_sw128(sa), da1 = umma_desc_sw128(sa + I8_A_BYTES);
+                            const uint64_t db = umma_desc_sw128(sa + 2 * I8_A_BYTES);
+                            if (l == 0) { mbar_wait(&bars->tempty[0], tphase ^ 1u); tc_fence_after(); }
+#pragma unroll
+                            for (int k = 0; k < I8_SLAB / 32; ++k)
+                                umma_i8(tmem_base, da0 + (uint64_t)(2 * k), db + (uint64_t)(2 * k), I8_IDESC,
+                                        (uint32_t)((l | k) != 0));
+                            if (l == 0) { mbar_wait(&bars->tempty[1], tphase ^ 1u); tc_fence_after(); }
+#pragma unroll
+                            for (int k = 0; k < I8_SLAB / 32; ++k)
+                                umma_i8(tmem_base + (uint32_t)I8_TK, da1 + (uint64_t)(2 * k), db + (uint64_t)(2 * k),
+                                        I8_IDESC, (uint32_t)((l | k) != 0));
+                            tc_commit(&bars->empty[stage]);
+                            if (++stage == I8W_NS) { stage = 0; phase ^= 1u; }
+                        }
+                        tc_commit(&bars->tfull);
+                        tphase ^= 1u;
+                    }
+                }
+            }
+        }
+    } else {
+        const int q = warp & 3;                                             // TMEM lane quarter
+        const int acc = (warp - 2) >> 2;                                    // which accumulator / which 128-SNP tile
+        unsigned tphase = 0;
+        for (int item = blockIdx.x; item < p.total_items; item += gridDim.x) {
+            const int ii = i8_find_first(p.item_prefix, p.n_i, item);
+            const int jt = 2 * (p.jt0[ii] + (item - p.item_prefix[ii])) + acc;
+            const int j = jt * I8_TJ + q * 32 + lane;
+            const signed char *arow = p.g8 + (size_t)(j < p.m ? j : p.m - 1) * p.ld;
+            const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * I8_TK);
+            double qacc = 0.0, wgt = 1.0;
+            for (int s = 0; s < p.n_planes; ++s) {
+                wgt *= 0.0078125;
+                double plane_sum = 0.0;
+                for (int kt = 0; kt < p.n_kt; ++kt) {
+                    const int4 *ap = reinterpret_cast<const int4 *>(arow + kt * I8_TK);
+                    int4 a0 = __ldg(ap), a1 = __ldg(ap + 1);
+                    mbar_wait_warp(&bars->tfull, tphase);
+                    tc_fence_after();
+#pragma unroll 1
+                    for (int ch = 0; ch < I8_TK / 32; ++ch) {
+                        int v[32];
+                        tmem_ld32(taddr + ch * 32, v);
+                        int4 n0 = a0, n1 = a1;
+                        if (ch + 1 < I8_TK / 32) { n0 = __ldg(ap + 2 * ch + 2); n1 = __ldg(ap + 2 * ch + 3); }
+                        tmem_ld_wait();
+                        const int aw[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+                        int csum = 0;
+#pragma unroll
+                        for (int c = 0; c < 32; ++c) csum += ((aw[c >> 2] >> ((c & 3) * 8)) & 0xff) * v[c];
+                        plane_sum += (double)csum;
+                        a0 = n0; a1 = n1;
+                    }
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(&bars->tempty[acc]);
+                    tphase ^= 1u;
+                }
+                qacc += plane_sum * wgt;
+            }
+            const int i = (int)p.ilist[ii];
+            const bool valid = j < p.m && (p.pair_space == GMAT_B200_PAIRS_ALL || j > i);
+            const int jc = j < p.m ? j : p.m - 1;
+            const double quad = 2.0 * p.scale[ii] * qacc;
+            const double o = p.offs[jc];
+            const size_t at = (size_t)ii * p.m + jc;
+            double var = quad - 2.0 * o * p.t1[at] + o * o * p.s_i[ii];
+            double eff = p.e[at] - o * p.upy[ii];
+            if (o != o) { var = 0.0; eff = 0.0; }
+            const double chi = eff * eff / var;
+            if (p.q_debug != nullptr && j < p.m) p.q_debug[at] = quad;
+            gmat_b200_hit h;
+            h.snp_0 = i; h.snp_1 = j; h.eff = eff; h.var = var; h.chi = chi;
+            const bool hit = valid && (p.chi_cut < 0.0 || chi > p.chi_cut);
+            const unsigned ballot = __ballot_sync(0xffffffffu, hit);
+            if (ballot) {
+                unsigned long long base = 0;
+                if (lane == 0) base = atomicAdd(p.count, (unsigned long long)__popc(ballot));
+                base = __shfl_sync(0xffffffffu, base, 0);
+                if (hit) {
+                    const unsigned long long pos = base + __popc(ballot & ((1u << lane) - 1u));
+                    if ((long long)pos < p.cap) p.hits[pos] = h;
+                }
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;\n" ::"r"(tmem_base), "r"(512) : "memory");
+    }
+}
+
 // Issue-rate microbenchmark of the int8 MMA (the roofline denominator of the engine): one thread per CTA issues
 // back-to-back 128x256x32 MMAs on a resident (pseudo-random) smem tile pair, alternating two TMEM accumulators.
 __global__ void __launch_bounds__(128, 1) i8_peak_kernel(int iters) {
@@ -472,7 +642,7 @@ extern "C" int gmat_b200_i8_scan(const signed char *g8_dev, long long n, long lo
                                  const double *scale_dev, const double *s_dev, const double *upy_dev,
                                  const double *t1_dev, const double *e_dev, const double *offs_dev,
                                  int pair_space, double chi_cut, gmat_b200_hit *hits_dev, long long cap,
-                                 unsigned long long *count_dev, double *q_debug_dev, void *stream) {
+                                 unsigned long long *count_dev, double *q_debug_dev, int wide, void *stream) {
     GB_CHECK_ARG(g8_dev && planes_dev && ilist_dev && item_prefix_dev && jt0_dev && scale_dev && s_dev && upy_dev &&
                  t1_dev && e_dev && offs_dev && count_dev, "null buffer");
     GB_CHECK_ARG(n > 0 && m > 0 && n_i > 0 && total_items >= 0 && total_items < (1LL << 31), "shape");
@@ -494,10 +664,16 @@ extern "C" int gmat_b200_i8_scan(const signed char *g8_dev, long long n, long lo
     int rc = make_map(&map_g, g8_dev, p.ld, m, p.ld, I8_TJ);
     if (rc == GMAT_B200_OK) rc = make_map(&map_p, planes_dev, p.ld, (long long)n_i * n_planes * p.np, p.ld, I8_TK);
     if (rc != GMAT_B200_OK) return rc;
-    const int smem_bytes = I8_NS * I8_STAGE_BYTES + 1024 + (int)sizeof(I8Bars);
-    GB_CUDA(cudaFuncSetAttribute(i8_scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
     const int grid = (int)(total_items < sm_count() ? total_items : sm_count());
-    i8_scan_kernel<<<grid, I8_THREADS, smem_bytes, st>>>(map_g, map_p, p);
+    if (wide) {
+        const int smem_bytes = I8W_NS * I8W_STAGE_BYTES + 1024 + (int)sizeof(I8WBars);
+        GB_CUDA(cudaFuncSetAttribute(i8_scan_wide_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
+        i8_scan_wide_kernel<<<grid, I8W_THREADS, smem_bytes, st>>>(map_g, map_p, p);
+    } else {
+        const int smem_bytes = I8_NS * I8_STAGE_BYTES + 1024 + (int)sizeof(I8Bars);
+        GB_CUDA(cudaFuncSetAttribute(i8_scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
+        i8_scan_kernel<<<grid, I8_THREADS, smem_bytes, st>>>(map_g, map_p, p);
+    }
     GB_LAUNCH_CHECK();
     return GMAT_B200_OK;
 }

@@ -250,6 +250,7 @@ class I8Exact(object):
         self.batch = int(max(1, min(64, self.PLANE_BYTES // per_first)))
         self.planes = torch.zeros((self.batch * per_first,), dtype=torch.int8, device=dev)
         self._shifts = torch.tensor([0, 2, 4, 6], dtype=torch.uint8, device=dev)
+        self.wide = os.environ.get("GMAT_B200_I8_WIDE", "0") != "0"    # two 128-SNP tiles per CTA share the planes
         self.kernel_events = None      # bench.py: list of (start, end) CUDA events around every i8_scan launch
 
     def _coded_first(self, il):
@@ -261,12 +262,13 @@ class I8Exact(object):
     def _work_items(self, ih, pair_space):
         """(item_prefix[n_i+1], jt0[n_i]) int32 host arrays: tiles of 128 second SNPs every first SNP needs."""
         m = self.store.m
-        n_jt = (m + 127) // 128
+        tj = 256 if self.wide else 128                 # second SNPs per work item
+        n_jt = (m + tj - 1) // tj
         if pair_space == PAIRS_ALL:
             jt0 = np.zeros(len(ih), dtype=np.int64)
             cnt = np.full(len(ih), n_jt, dtype=np.int64)
         else:
-            jt0 = (ih + 1) // 128
+            jt0 = (ih + 1) // tj
             cnt = np.where(ih + 1 < m, n_jt - jt0, 0)
         prefix = np.concatenate([[0], np.cumsum(cnt)])
         return prefix.astype(np.int32), jt0.astype(np.int32)
@@ -315,8 +317,8 @@ class I8Exact(object):
                     _p(te, "double *"), ffi.cast("double *", te.data_ptr() + 8 * ni * m),
                     _p(self.offs, "double *"), pair_space, float(chi_cut),
                     ffi.cast("gmat_b200_hit *", hits.data_ptr()), cap,
-                    ffi.cast("unsigned long long *", count.data_ptr()), _p(qd, "double *"), _stream()),
-                    "gmat_b200_i8_scan")
+                    ffi.cast("unsigned long long *", count.data_ptr()), _p(qd, "double *"), int(self.wide),
+                    _stream()), "gmat_b200_i8_scan")
                 if self.kernel_events is not None:
                     ev[1].record()
                     self.kernel_events.append(ev)
