@@ -444,6 +444,213 @@ i8_scan_wide_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_cons
     }
 }
 
+// ---- CTA-pair variant: tcgen05.mma.cta_group::2 ---------------------------------------------------------------
+// Two CTAs of a cluster (one TPC) own the two 128-SNP tiles of a work item and HALF of every plane tile each
+// (128 of its 256 rows); one MMA of the leader CTA computes M = 256 SNPs x N = 256 plane rows across both SMs,
+// each tensor core reading its own genotype tile and the two plane halves.  Per SM and per 512 MMA cycles the
+// shared memory sees 32 KB of TMA writes and 32 KB of operand reads instead of 48 + 48, which is what holds the
+// single-CTA kernel at ~60 % of the issue rate.  Accumulators stay double-buffered (2 x 256 TMEM columns per CTA).
+constexpr int I8P_NS = 6;
+constexpr int I8P_HALF = I8_TK / 2;                               // plane rows each CTA loads
+constexpr int I8P_STAGE_BYTES = I8_A_BYTES + I8P_HALF * I8_SLAB;  // 32 KB per CTA
+constexpr uint32_t I8P_IDESC = (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(I8_TK >> 3) << 17) |
+                               ((uint32_t)((2 * I8_TJ) >> 4) << 24);
+constexpr uint32_t I8P_PEER_MASK = 0xFEFFFFFFu;                   // shared::cluster address of the same offset in CTA 0
+
+struct I8PBars {
+    uint64_t full[I8P_NS], empty[I8P_NS], tfull[2], tempty[2];
+    uint32_t tmem_base;
+};
+
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;\n" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\nbarrier.cluster.wait.acquire.aligned;\n" ::: "memory");
+}
+// TMA load whose completion bytes are signalled on the LEADER CTA's barrier (executed by both CTAs)
+__device__ __forceinline__ void tma_load_2d_pair(void *smem_dst, const CUtensorMap *map, int c0, int c1, uint64_t *bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];\n"
+        ::"r"(smem_u32(smem_dst)), "l"(map), "r"(c0), "r"(c1), "r"(smem_u32(bar) & I8P_PEER_MASK)
+        : "memory");
+}
+__device__ __forceinline__ void umma_i8_pair(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
+                                             uint32_t accumulate) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "setp.ne.b32 p, %4, 0;\n"
+        "tcgen05.mma.cta_group::2.kind::i8 [%0], %1, %2, %3, p;\n"
+        "}\n" ::"r"(tmem_d),
+        "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+// arrives on the barrier at this offset in BOTH CTAs once the MMAs issued so far have retired
+__device__ __forceinline__ void tc_commit_pair(uint64_t *bar) {
+    asm volatile(
+        "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;\n" ::"r"(
+            smem_u32(bar)), "h"((unsigned short)3)
+        : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_leader(uint64_t *bar) {
+    asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];\n" ::"r"(smem_u32(bar) & I8P_PEER_MASK) : "memory");
+}
+
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(I8_THREADS, 1)
+i8_scan_pair_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_constant__ CUtensorMap map_ph,
+                    const I8Params p) {
+    extern __shared__ unsigned char smem_raw[];
+    unsigned char *smem = reinterpret_cast<unsigned char *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                                           ~static_cast<uintptr_t>(1023));
+    I8PBars *bars = reinterpret_cast<I8PBars *>(smem + I8P_NS * I8P_STAGE_BYTES);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int rank = (int)cluster_ctarank();
+    const int cluster_id = blockIdx.x >> 1, n_clusters = gridDim.x >> 1;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < I8P_NS; ++s) { mbar_init(&bars->full[s], 1); mbar_init(&bars->empty[s], 1); }
+        for (int b = 0; b < 2; ++b) { mbar_init(&bars->tfull[b], 1); mbar_init(&bars->tempty[b], 8); }
+        mbar_fence_init();
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;\n" ::"r"(
+                         smem_u32(&bars->tmem_base)), "r"(512)
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;\n" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync_all();                       // both CTAs: barriers initialised, TMEM allocated
+    tc_fence_after();
+    const uint32_t tmem_base = bars->tmem_base;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            int stage = 0; unsigned phase = 0;
+            for (int item = cluster_id; item < p.total_items; item += n_clusters) {
+                const int ii = i8_find_first(p.item_prefix, p.n_i, item);
+                const int jt = 2 * (p.jt0[ii] + (item - p.item_prefix[ii])) + rank;
+                for (int s = 0; s < p.n_planes; ++s) {
+                    const int prow = (ii * p.n_planes + s) * p.np + rank * I8P_HALF;
+                    for (int kt = 0; kt < p.n_kt; ++kt) {
+                        const int nl = i8_slabs_of(kt, p.n_slab);
+                        for (int l = 0; l < nl; ++l) {
+                            mbar_wait(&bars->empty[stage], phase ^ 1u);
+                            if (rank == 0) mbar_expect_tx(&bars->full[stage], 2 * I8P_STAGE_BYTES);
+                            unsigned char *sa = smem + stage * I8P_STAGE_BYTES;
+                            tma_load_2d_pair(sa, &map_g, l * I8_SLAB, jt * I8_TJ, &bars->full[stage]);
+                            tma_load_2d_pair(sa + I8_A_BYTES, &map_ph, l * I8_SLAB, prow + kt * I8_TK, &bars->full[stage]);
+                            if (++stage == I8P_NS) { stage = 0; phase ^= 1u; }
+                        }
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0 && rank == 0) {
+            int stage = 0; unsigned phase = 0;
+            int abuf = 0; unsigned aphase = 0;
+            for (int item = cluster_id; item < p.total_items; item += n_clusters) {
+                for (int s = 0; s < p.n_planes; ++s) {
+                    for (int kt = 0; kt < p.n_kt; ++kt) {
+                        const int nl = i8_slabs_of(kt, p.n_slab);
+                        mbar_wait(&bars->tempty[abuf], aphase ^ 1u);       // 8 epilogue warps of the pair drained it
+                        tc_fence_after();
+                        const uint32_t tmem_d = tmem_base + (uint32_t)(abuf * I8_TK);
+                        for (int l = 0; l < nl; ++l) {
+                            mbar_wait(&bars->full[stage], phase);
+                            tc_fence_after();
+                            const uint32_t sa = smem_u32(smem + stage * I8P_STAGE_BYTES);
+                            const uint64_t da = umma_desc_sw128(sa), db = umma_desc_sw128(sa + I8_A_BYTES);
+#pragma unroll
+                            for (int k = 0; k < I8_SLAB / 32; ++k)
+                                umma_i8_pair(tmem_d, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), I8P_IDESC,
+                                             (uint32_t)((l | k) != 0));
+                            tc_commit_pair(&bars->empty[stage]);
+                            if (++stage == I8P_NS) { stage = 0; phase ^= 1u; }
+                        }
+                        tc_commit_pair(&bars->tfull[abuf]);
+                        if (++abuf == 2) { abuf = 0; aphase ^= 1u; }
+                    }
+                }
+            }
+        }
+    } else {
+        const int q = warp & 3;
+        int abuf = 0; unsigned aphase = 0;
+        for (int item = cluster_id; item < p.total_items; item += n_clusters) {
+            const int ii = i8_find_first(p.item_prefix, p.n_i, item);
+            const int jt = 2 * (p.jt0[ii] + (item - p.item_prefix[ii])) + rank;
+            const int j = jt * I8_TJ + q * 32 + lane;
+            const signed char *arow = p.g8 + (size_t)(j < p.m ? j : p.m - 1) * p.ld;
+            double qacc = 0.0, wgt = 1.0;
+            for (int s = 0; s < p.n_planes; ++s) {
+                wgt *= 0.0078125;
+                double plane_sum = 0.0;
+                for (int kt = 0; kt < p.n_kt; ++kt) {
+                    const int4 *ap = reinterpret_cast<const int4 *>(arow + kt * I8_TK);
+                    int4 a0 = __ldg(ap), a1 = __ldg(ap + 1);
+                    mbar_wait_warp(&bars->tfull[abuf], aphase);
+                    tc_fence_after();
+                    const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(abuf * I8_TK);
+#pragma unroll 1
+                    for (int ch = 0; ch < I8_TK / 32; ++ch) {
+                        int v[32];
+                        tmem_ld32(taddr + ch * 32, v);
+                        int4 n0 = a0, n1 = a1;
+                        if (ch + 1 < I8_TK / 32) { n0 = __ldg(ap + 2 * ch + 2); n1 = __ldg(ap + 2 * ch + 3); }
+                        tmem_ld_wait();
+                        const int aw[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+                        int csum = 0;
+#pragma unroll
+                        for (int c = 0; c < 32; ++c) csum += ((aw[c >> 2] >> ((c & 3) * 8)) & 0xff) * v[c];
+                        plane_sum += (double)csum;
+                        a0 = n0; a1 = n1;
+                    }
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive_leader(&bars->tempty[abuf]);
+                    if (++abuf == 2) { abuf = 0; aphase ^= 1u; }
+                }
+                qacc += plane_sum * wgt;
+            }
+            const int i = (int)p.ilist[ii];
+            const bool valid = j < p.m && (p.pair_space == GMAT_B200_PAIRS_ALL || j > i);
+            const int jc = j < p.m ? j : p.m - 1;
+            const double quad = 2.0 * p.scale[ii] * qacc;
+            const double o = p.offs[jc];
+            const size_t at = (size_t)ii * p.m + jc;
+            double var = quad - 2.0 * o * p.t1[at] + o * o * p.s_i[ii];
+            double eff = p.e[at] - o * p.upy[ii];
+            if (o != o) { var = 0.0; eff = 0.0; }
+            const double chi = eff * eff / var;
+            if (p.q_debug != nullptr && j < p.m) p.q_debug[at] = quad;
+            gmat_b200_hit h;
+            h.snp_0 = i; h.snp_1 = j; h.eff = eff; h.var = var; h.chi = chi;
+            const bool hit = valid && (p.chi_cut < 0.0 || chi > p.chi_cut);
+            const unsigned ballot = __ballot_sync(0xffffffffu, hit);
+            if (ballot) {
+                unsigned long long base = 0;
+                if (lane == 0) base = atomicAdd(p.count, (unsigned long long)__popc(ballot));
+                base = __shfl_sync(0xffffffffu, base, 0);
+                if (hit) {
+                    const unsigned long long pos = base + __popc(ballot & ((1u << lane) - 1u));
+                    if ((long long)pos < p.cap) p.hits[pos] = h;
+                }
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync_all();                       // nobody frees TMEM / exits while the peer may still touch this CTA
+    if (warp == 1) {
+        asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;\n" ::"r"(tmem_base), "r"(512) : "memory");
+    }
+}
+
 // Issue-rate microbenchmark of the int8 MMA (the roofline denominator of the engine): one thread per CTA issues
 // back-to-back 128x256x32 MMAs on a resident (pseudo-random) smem tile pair, alternating two TMEM accumulators.
 __global__ void __launch_bounds__(128, 1) i8_peak_kernel(int iters) {
@@ -665,7 +872,16 @@ extern "C" int gmat_b200_i8_scan(const signed char *g8_dev, long long n, long lo
     if (rc == GMAT_B200_OK) rc = make_map(&map_p, planes_dev, p.ld, (long long)n_i * n_planes * p.np, p.ld, I8_TK);
     if (rc != GMAT_B200_OK) return rc;
     const int grid = (int)(total_items < sm_count() ? total_items : sm_count());
-    if (wide) {
+    if (wide == 2) {
+        CUtensorMap map_ph;                                       // plane map with 128-row boxes (one half per CTA)
+        rc = make_map(&map_ph, planes_dev, p.ld, (long long)n_i * n_planes * p.np, p.ld, I8P_HALF);
+        if (rc != GMAT_B200_OK) return rc;
+        const int smem_bytes = I8P_NS * I8P_STAGE_BYTES + 1024 + (int)sizeof(I8PBars);
+        GB_CUDA(cudaFuncSetAttribute(i8_scan_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
+        const int pairs_of_sms = sm_count() / 2;
+        const int grid2 = 2 * (int)(total_items < pairs_of_sms ? total_items : pairs_of_sms);
+        i8_scan_pair_kernel<<<grid2, I8_THREADS, smem_bytes, st>>>(map_g, map_ph, p);
+    } else if (wide) {
         const int smem_bytes = I8W_NS * I8W_STAGE_BYTES + 1024 + (int)sizeof(I8WBars);
         GB_CUDA(cudaFuncSetAttribute(i8_scan_wide_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
         i8_scan_wide_kernel<<<grid, I8W_THREADS, smem_bytes, st>>>(map_g, map_p, p);

@@ -196,7 +196,8 @@ int gmat_b200_i8_split(const double *pvp_dev /* [n][n] */, long long n, const do
  * (a_j . r_i and a_j . (u_i o Z'Py)); offs_dev[m] = o_j (NaN = monomorphic second SNP: eff = var = 0, chi = NaN);
  * q_debug_dev (optional, [n_i][m]) receives a_j' B_i a_j.  Hits are appended at *count_dev as in
  * gmat_b200_epi_exact_scan (count keeps counting beyond cap).  wide != 0: a work item is a PAIR of 128-SNP tiles
- * (jt0 and the item counts are then in units of 256 second SNPs) that share every plane tile in shared memory.    */
+ * (jt0 and the item counts are then in units of 256 second SNPs): wide == 1 one CTA computes both tiles and shares
+ * every plane tile in shared memory; wide == 2 a CTA PAIR (cluster of 2, tcgen05 cta_group::2) computes them.      */
 int gmat_b200_i8_scan(const signed char *g8_dev, long long n, long long m, const signed char *planes_dev,
                       int n_planes, const long long *ilist_dev, long long n_i,
                       const int *item_prefix_dev, const int *jt0_dev, long long total_items,
