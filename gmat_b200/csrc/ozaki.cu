@@ -104,6 +104,34 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, int (&v)[32]) {
 }
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;\n" ::: "memory"); }
 
+// Epilogue of one accumulator tile for one TMEM lane (= one second SNP): sum_k a_jk * Y[j][k] over the 256 plane
+// rows of the tile, all in INTEGER registers.  No FP64 instruction may sit in this loop: DADD / I2F.F64 issue into
+// the pipe the tensor MMAs occupy (ncu: 37 % of all stall samples sat on the one DADD of the first version and the
+// tensor pipe idled 37 % of the time).  |Y| <= 2*127*n, so a 32-column partial fits int32 for n < 1.3e5.
+__device__ __forceinline__ long long i8_drain_tile(uint32_t taddr, const int4 *ap, int4 a0, int4 a1) {
+    long long total = 0;
+#pragma unroll 1
+    for (int ch = 0; ch < I8_TK / 32; ++ch) {
+        int v[32];
+        tmem_ld32(taddr + ch * 32, v);
+        int4 n0 = a0, n1 = a1;
+        if (ch + 1 < I8_TK / 32) { n0 = __ldg(ap + 2 * ch + 2); n1 = __ldg(ap + 2 * ch + 3); }
+        tmem_ld_wait();
+        const int aw[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+        int c0 = 0, c1 = 0, c2 = 0, c3 = 0;                       // four independent chains
+#pragma unroll
+        for (int w = 0; w < 8; ++w) {
+            c0 += (aw[w] & 0xff) * v[4 * w];
+            c1 += ((aw[w] >> 8) & 0xff) * v[4 * w + 1];
+            c2 += ((aw[w] >> 16) & 0xff) * v[4 * w + 2];
+            c3 += ((aw[w] >> 24) & 0xff) * v[4 * w + 3];
+        }
+        total += (long long)(c0 + c1) + (long long)(c2 + c3);
+        a0 = n0; a1 = n1;
+    }
+    return total;
+}
+
 struct I8Bars {
     uint64_t full[I8_NS], empty[I8_NS], tfull[2], tempty[2];
     uint32_t tmem_base;
@@ -212,33 +240,20 @@ i8_scan_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_constant_
             double qacc = 0.0, wgt = 1.0;
             for (int s = 0; s < p.n_planes; ++s) {
                 wgt *= 0.0078125;                                           // 128^-(s+1)
-                double plane_sum = 0.0;                                     // integer valued, exact in FP64
+                long long plane_sum = 0;                                    // exact
                 for (int kt = 0; kt < p.n_kt; ++kt) {
                     const int4 *ap = reinterpret_cast<const int4 *>(arow + kt * I8_TK);
                     int4 a0 = __ldg(ap), a1 = __ldg(ap + 1);
                     mbar_wait_warp(&bars->tfull[abuf], aphase);
                     tc_fence_after();
                     const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(abuf * I8_TK);
-#pragma unroll 1
-                    for (int ch = 0; ch < I8_TK / 32; ++ch) {
-                        int v[32];
-                        tmem_ld32(taddr + ch * 32, v);
-                        int4 n0 = a0, n1 = a1;
-                        if (ch + 1 < I8_TK / 32) { n0 = __ldg(ap + 2 * ch + 2); n1 = __ldg(ap + 2 * ch + 3); }
-                        tmem_ld_wait();
-                        const int aw[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
-                        int csum = 0;
-#pragma unroll
-                        for (int c = 0; c < 32; ++c) csum += ((aw[c >> 2] >> ((c & 3) * 8)) & 0xff) * v[c];
-                        plane_sum += (double)csum;
-                        a0 = n0; a1 = n1;
-                    }
+                    plane_sum += i8_drain_tile(taddr, ap, a0, a1);
                     tc_fence_before();
                     __syncwarp();
                     if (lane == 0) mbar_arrive(&bars->tempty[abuf]);
                     if (++abuf == 2) { abuf = 0; aphase ^= 1u; }
                 }
-                qacc += plane_sum * wgt;
+                qacc += (double)plane_sum * wgt;                         // the only FP64 work per plane
             }
             // ---- finish the pair: FP64 terms, test, emit (remma_epiAA.py:75-82) ----
             const int i = (int)p.ilist[ii];
@@ -384,32 +399,19 @@ i8_scan_wide_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_cons
             double qacc = 0.0, wgt = 1.0;
             for (int s = 0; s < p.n_planes; ++s) {
                 wgt *= 0.0078125;
-                double plane_sum = 0.0;
+                long long plane_sum = 0;                                    // exact
                 for (int kt = 0; kt < p.n_kt; ++kt) {
                     const int4 *ap = reinterpret_cast<const int4 *>(arow + kt * I8_TK);
                     int4 a0 = __ldg(ap), a1 = __ldg(ap + 1);
                     mbar_wait_warp(&bars->tfull, tphase);
                     tc_fence_after();
-#pragma unroll 1
-                    for (int ch = 0; ch < I8_TK / 32; ++ch) {
-                        int v[32];
-                        tmem_ld32(taddr + ch * 32, v);
-                        int4 n0 = a0, n1 = a1;
-                        if (ch + 1 < I8_TK / 32) { n0 = __ldg(ap + 2 * ch + 2); n1 = __ldg(ap + 2 * ch + 3); }
-                        tmem_ld_wait();
-                        const int aw[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
-                        int csum = 0;
-#pragma unroll
-                        for (int c = 0; c < 32; ++c) csum += ((aw[c >> 2] >> ((c & 3) * 8)) & 0xff) * v[c];
-                        plane_sum += (double)csum;
-                        a0 = n0; a1 = n1;
-                    }
+                    plane_sum += i8_drain_tile(taddr, ap, a0, a1);
                     tc_fence_before();
                     __syncwarp();
                     if (lane == 0) mbar_arrive(&bars->tempty[acc]);
                     tphase ^= 1u;
                 }
-                qacc += plane_sum * wgt;
+                qacc += (double)plane_sum * wgt;                         // the only FP64 work per plane
             }
             const int i = (int)p.ilist[ii];
             const bool valid = j < p.m && (p.pair_space == GMAT_B200_PAIRS_ALL || j > i);
@@ -589,33 +591,20 @@ i8_scan_pair_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_cons
             double qacc = 0.0, wgt = 1.0;
             for (int s = 0; s < p.n_planes; ++s) {
                 wgt *= 0.0078125;
-                double plane_sum = 0.0;
+                long long plane_sum = 0;                                    // exact
                 for (int kt = 0; kt < p.n_kt; ++kt) {
                     const int4 *ap = reinterpret_cast<const int4 *>(arow + kt * I8_TK);
                     int4 a0 = __ldg(ap), a1 = __ldg(ap + 1);
                     mbar_wait_warp(&bars->tfull[abuf], aphase);
                     tc_fence_after();
                     const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(abuf * I8_TK);
-#pragma unroll 1
-                    for (int ch = 0; ch < I8_TK / 32; ++ch) {
-                        int v[32];
-                        tmem_ld32(taddr + ch * 32, v);
-                        int4 n0 = a0, n1 = a1;
-                        if (ch + 1 < I8_TK / 32) { n0 = __ldg(ap + 2 * ch + 2); n1 = __ldg(ap + 2 * ch + 3); }
-                        tmem_ld_wait();
-                        const int aw[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
-                        int csum = 0;
-#pragma unroll
-                        for (int c = 0; c < 32; ++c) csum += ((aw[c >> 2] >> ((c & 3) * 8)) & 0xff) * v[c];
-                        plane_sum += (double)csum;
-                        a0 = n0; a1 = n1;
-                    }
+                    plane_sum += i8_drain_tile(taddr, ap, a0, a1);
                     tc_fence_before();
                     __syncwarp();
                     if (lane == 0) mbar_arrive_leader(&bars->tempty[abuf]);
                     if (++abuf == 2) { abuf = 0; aphase ^= 1u; }
                 }
-                qacc += plane_sum * wgt;
+                qacc += (double)plane_sum * wgt;                         // the only FP64 work per plane
             }
             const int i = (int)p.ilist[ii];
             const bool valid = j < p.m && (p.pair_space == GMAT_B200_PAIRS_ALL || j > i);

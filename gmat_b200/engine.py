@@ -252,7 +252,7 @@ class I8Exact(object):
         self._shifts = torch.tensor([0, 2, 4, 6], dtype=torch.uint8, device=dev)
         # kernel variant: 0 = one 128-SNP tile per CTA (double-buffered TMEM), 1 = two tiles per CTA sharing the
         # plane tiles, 2 = CTA pair (tcgen05 cta_group::2)
-        self.wide = int(os.environ.get("GMAT_B200_I8_WIDE", "0"))
+        self.wide = int(os.environ.get("GMAT_B200_I8_WIDE", "2"))
         self.kernel_events = None      # bench.py: list of (start, end) CUDA events around every i8_scan launch
 
     def _coded_first(self, il):
