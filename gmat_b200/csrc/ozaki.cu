@@ -108,16 +108,15 @@ __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.
 // rows of the tile, all in INTEGER registers.  No FP64 instruction may sit in this loop: DADD / I2F.F64 issue into
 // the pipe the tensor MMAs occupy (ncu: 37 % of all stall samples sat on the one DADD of the first version and the
 // tensor pipe idled 37 % of the time).  |Y| <= 2*127*n, so a 32-column partial fits int32 for n < 1.3e5.
-__device__ __forceinline__ long long i8_drain_tile(uint32_t taddr, const int4 *ap, int4 a0, int4 a1) {
+__device__ __forceinline__ long long i8_drain_tile(uint32_t taddr, const int4 (&a)[I8_TK / 16]) {
     long long total = 0;
-#pragma unroll 1
+#pragma unroll
     for (int ch = 0; ch < I8_TK / 32; ++ch) {
         int v[32];
         tmem_ld32(taddr + ch * 32, v);
-        int4 n0 = a0, n1 = a1;
-        if (ch + 1 < I8_TK / 32) { n0 = __ldg(ap + 2 * ch + 2); n1 = __ldg(ap + 2 * ch + 3); }
         tmem_ld_wait();
-        const int aw[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+        const int aw[8] = {a[2 * ch].x, a[2 * ch].y, a[2 * ch].z, a[2 * ch].w,
+                           a[2 * ch + 1].x, a[2 * ch + 1].y, a[2 * ch + 1].z, a[2 * ch + 1].w};
         int c0 = 0, c1 = 0, c2 = 0, c3 = 0;                       // four independent chains
 #pragma unroll
         for (int w = 0; w < 8; ++w) {
@@ -127,9 +126,15 @@ __device__ __forceinline__ long long i8_drain_tile(uint32_t taddr, const int4 *a
             c3 += ((aw[w] >> 24) & 0xff) * v[4 * w + 3];
         }
         total += (long long)(c0 + c1) + (long long)(c2 + c3);
-        a0 = n0; a1 = n1;
     }
     return total;
+}
+// the 256 dosage bytes of this lane's SNP for one row tile: issued BEFORE the wait on the accumulator, so the L2
+// latency (the first version prefetched one 32-byte chunk ahead and stalled on it: 23 % of all samples) is hidden
+__device__ __forceinline__ void i8_load_dosage(const signed char *row, int4 (&a)[I8_TK / 16]) {
+    const int4 *ap = reinterpret_cast<const int4 *>(row);
+#pragma unroll
+    for (int q = 0; q < I8_TK / 16; ++q) a[q] = __ldg(ap + q);
 }
 
 struct I8Bars {
@@ -242,12 +247,12 @@ i8_scan_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_constant_
                 wgt *= 0.0078125;                                           // 128^-(s+1)
                 long long plane_sum = 0;                                    // exact
                 for (int kt = 0; kt < p.n_kt; ++kt) {
-                    const int4 *ap = reinterpret_cast<const int4 *>(arow + kt * I8_TK);
-                    int4 a0 = __ldg(ap), a1 = __ldg(ap + 1);
+                    int4 abytes[I8_TK / 16];
+                    i8_load_dosage(arow + kt * I8_TK, abytes);
                     mbar_wait_warp(&bars->tfull[abuf], aphase);
                     tc_fence_after();
                     const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(abuf * I8_TK);
-                    plane_sum += i8_drain_tile(taddr, ap, a0, a1);
+                    plane_sum += i8_drain_tile(taddr, abytes);
                     tc_fence_before();
                     __syncwarp();
                     if (lane == 0) mbar_arrive(&bars->tempty[abuf]);
@@ -401,11 +406,11 @@ i8_scan_wide_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_cons
                 wgt *= 0.0078125;
                 long long plane_sum = 0;                                    // exact
                 for (int kt = 0; kt < p.n_kt; ++kt) {
-                    const int4 *ap = reinterpret_cast<const int4 *>(arow + kt * I8_TK);
-                    int4 a0 = __ldg(ap), a1 = __ldg(ap + 1);
+                    int4 abytes[I8_TK / 16];
+                    i8_load_dosage(arow + kt * I8_TK, abytes);
                     mbar_wait_warp(&bars->tfull, tphase);
                     tc_fence_after();
-                    plane_sum += i8_drain_tile(taddr, ap, a0, a1);
+                    plane_sum += i8_drain_tile(taddr, abytes);
                     tc_fence_before();
                     __syncwarp();
                     if (lane == 0) mbar_arrive(&bars->tempty[acc]);
@@ -593,12 +598,12 @@ i8_scan_pair_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_cons
                 wgt *= 0.0078125;
                 long long plane_sum = 0;                                    // exact
                 for (int kt = 0; kt < p.n_kt; ++kt) {
-                    const int4 *ap = reinterpret_cast<const int4 *>(arow + kt * I8_TK);
-                    int4 a0 = __ldg(ap), a1 = __ldg(ap + 1);
+                    int4 abytes[I8_TK / 16];
+                    i8_load_dosage(arow + kt * I8_TK, abytes);
                     mbar_wait_warp(&bars->tfull[abuf], aphase);
                     tc_fence_after();
                     const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(abuf * I8_TK);
-                    plane_sum += i8_drain_tile(taddr, ap, a0, a1);
+                    plane_sum += i8_drain_tile(taddr, abytes);
                     tc_fence_before();
                     __syncwarp();
                     if (lane == 0) mbar_arrive_leader(&bars->tempty[abuf]);
