@@ -248,7 +248,9 @@ class I8Exact(object):
         self.amax = float(pvp_dev.abs().max())
         per_first = self.n_planes * self.ld * self.ld
         self.batch = int(max(1, min(64, self.PLANE_BYTES // per_first)))
-        self.planes = torch.zeros((self.batch * per_first,), dtype=torch.int8, device=dev)
+        # two plane buffers: the split of batch k+1 (side stream) overlaps the scan of batch k
+        self.planes = [torch.zeros((self.batch * per_first,), dtype=torch.int8, device=dev) for _ in range(2)]
+        self._prep_stream = torch.cuda.Stream(device=dev)
         self._shifts = torch.tensor([0, 2, 4, 6], dtype=torch.uint8, device=dev)
         # kernel variant: 0 = one 128-SNP tile per CTA (double-buffered TMEM), 1 = two tiles per CTA sharing the
         # plane tiles, 2 = CTA pair (tcgen05 cta_group::2)
@@ -275,58 +277,86 @@ class I8Exact(object):
         prefix = np.concatenate([[0], np.cumsum(cnt)])
         return prefix.astype(np.int32), jt0.astype(np.int32)
 
+    SUPER = 1024       # first SNPs whose O(n)-per-pair terms are formed by one pair of library GEMMs
+
     def scan(self, ilist, pair_space, chi_cut, cap=1 << 20, q_debug=False):
         """All launches of the scan are queued back to back (one hit buffer, one counter, no host synchronisation
         between first-SNP batches); the counter is read once at the end and the scan repeated with the exact
-        capacity in the rare case the buffer was too small."""
+        capacity in the rare case the buffer was too small.  Per chunk of SUPER first SNPs the FP64 side terms come
+        from one stacked GEMM; per batch (plane-buffer budget) the digit-plane split runs on a side stream into
+        the other plane buffer while the tensor-core scan of the previous batch is still running."""
         store, dev = self.store, self.store.device
         n, m = store.n, store.m
         ilist = np.ascontiguousarray(ilist, dtype=np.int64)
         if len(ilist) and (ilist.min() < 0 or ilist.max() >= m):
             raise ValueError("first SNP out of range")
         count = torch.zeros((1,), dtype=torch.int64, device=dev)
+        main = torch.cuda.current_stream()
+        prep = self._prep_stream
         while True:
             hits = alloc_hits(cap, dev)
             count.zero_()
-            dbg = []
-            for b0 in range(0, len(ilist), self.batch):
-                ih = ilist[b0:b0 + self.batch]
-                ni = len(ih)
-                prefix, jt0 = self._work_items(ih, pair_space)
-                total = int(prefix[-1])
-                if total == 0:
-                    continue
-                il = torch.as_tensor(ih).to(dev, non_blocking=True)
-                tab = torch.as_tensor(np.concatenate([prefix, jt0])).to(dev, non_blocking=True)
-                u = self._coded_first(il)                                   # [ni][n]
-                r = u * (u @ self.A)                                        # u o (A u)   (A symmetric)
-                upy_vec = u * self.py
-                s_i = r.sum(dim=1).contiguous()
-                upy = upy_vec.sum(dim=1).contiguous()
-                te = torch.cat([r, upy_vec]) @ self.gd.T                    # [2 ni][m]: a_j.r_i and a_j.(u_i o py)
-                scale = (u.abs().amax(dim=1) ** 2 * (self.amax / 0.99)).clamp_min(1e-200).contiguous()
-                check(lib.gmat_b200_i8_split(_p(self.A, "double *"), n, _p(u, "double *"), ni,
-                                             _p(scale, "double *"), self.n_planes,
-                                             _p(self.planes, "signed char *"), _stream()), "gmat_b200_i8_split")
-                qd = torch.zeros((ni, m), dtype=torch.float64, device=dev) if q_debug else None
-                if self.kernel_events is not None:
-                    ev = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
-                    ev[0].record()
-                check(lib.gmat_b200_i8_scan(
-                    _p(self.g8, "signed char *"), n, m, _p(self.planes, "signed char *"), self.n_planes,
-                    _p(il, "long long *"), ni, _p(tab, "int *"), ffi.cast("int *", tab.data_ptr() + 4 * (ni + 1)),
-                    total, _p(scale, "double *"), _p(s_i, "double *"), _p(upy, "double *"),
-                    _p(te, "double *"), ffi.cast("double *", te.data_ptr() + 8 * ni * m),
-                    _p(self.offs, "double *"), pair_space, float(chi_cut),
-                    ffi.cast("gmat_b200_hit *", hits.data_ptr()), cap,
-                    ffi.cast("unsigned long long *", count.data_ptr()), _p(qd, "double *"), int(self.wide),
-                    _stream()), "gmat_b200_i8_scan")
-                if self.kernel_events is not None:
-                    ev[1].record()
-                    self.kernel_events.append(ev)
-                if q_debug:
-                    dbg.append(qd)
-            cnt = int(count.item())
+            dbg, keep = [], []
+            scan_done = [None, None]                                        # event per plane buffer
+            k = 0
+            for c0 in range(0, len(ilist), self.SUPER):
+                ic = ilist[c0:c0 + self.SUPER]
+                il_all = torch.as_tensor(ic).to(dev, non_blocking=True)
+                u_all = self._coded_first(il_all)                           # [nc][n]
+                r = u_all * (u_all @ self.A)                                # u o (A u)   (A symmetric)
+                upy_vec = u_all * self.py
+                s_all = r.sum(dim=1).contiguous()
+                upy_all = upy_vec.sum(dim=1).contiguous()
+                t1_all = r @ self.gd.T                                      # [nc][m]  a_j . r_i
+                e_all = upy_vec @ self.gd.T                                 # [nc][m]  a_j . (u_i o py)
+                scale_all = (u_all.abs().amax(dim=1) ** 2 * (self.amax / 0.99)).clamp_min(1e-200).contiguous()
+                del r, upy_vec
+                side_ready = main.record_event()
+                keep.append((il_all, u_all, s_all, upy_all, t1_all, e_all, scale_all))
+                for b0 in range(0, len(ic), self.batch):
+                    ih = ic[b0:b0 + self.batch]
+                    ni = len(ih)
+                    prefix, jt0 = self._work_items(ih, pair_space)
+                    total = int(prefix[-1])
+                    if total == 0:
+                        continue
+                    tab = torch.as_tensor(np.concatenate([prefix, jt0])).to(dev, non_blocking=True)
+                    planes = self.planes[k & 1]
+                    u, scale = u_all[b0:b0 + ni], scale_all[b0:b0 + ni]
+                    with torch.cuda.stream(prep):
+                        prep.wait_event(side_ready)
+                        if scan_done[k & 1] is not None:
+                            prep.wait_event(scan_done[k & 1])               # the scan that last read this buffer
+                        check(lib.gmat_b200_i8_split(_p(self.A, "double *"), n, _p(u, "double *"), ni,
+                                                     _p(scale, "double *"), self.n_planes,
+                                                     _p(planes, "signed char *"), _stream()), "gmat_b200_i8_split")
+                        split_done = prep.record_event()
+                    main.wait_event(split_done)
+                    qd = torch.zeros((ni, m), dtype=torch.float64, device=dev) if q_debug else None
+                    if self.kernel_events is not None:
+                        ev = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+                        ev[0].record()
+                    check(lib.gmat_b200_i8_scan(
+                        _p(self.g8, "signed char *"), n, m, _p(planes, "signed char *"), self.n_planes,
+                        _p(il_all[b0:b0 + ni], "long long *"), ni, _p(tab, "int *"),
+                        ffi.cast("int *", tab.data_ptr() + 4 * (ni + 1)), total,
+                        _p(scale, "double *"), _p(s_all[b0:b0 + ni], "double *"), _p(upy_all[b0:b0 + ni], "double *"),
+                        _p(t1_all[b0:b0 + ni], "double *"), _p(e_all[b0:b0 + ni], "double *"),
+                        _p(self.offs, "double *"), pair_space, float(chi_cut),
+                        ffi.cast("gmat_b200_hit *", hits.data_ptr()), cap,
+                        ffi.cast("unsigned long long *", count.data_ptr()), _p(qd, "double *"), int(self.wide),
+                        _stream()), "gmat_b200_i8_scan")
+                    if self.kernel_events is not None:
+                        ev[1].record()
+                        self.kernel_events.append(ev)
+                    scan_done[k & 1] = main.record_event()
+                    keep.append(tab)
+                    if q_debug:
+                        dbg.append(qd)
+                    k += 1
+            cnt = int(count.item())                                         # the one synchronisation of the scan
+            prep.synchronize()
+            del keep
             if cnt <= cap:
                 break
             cap = cnt

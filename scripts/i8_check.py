@@ -55,8 +55,8 @@ def main():
         u = eng._coded_first(il)
         scale = (u.abs().amax(dim=1) ** 2 * (eng.amax / 0.99)).contiguous()
         check(lib.gmat_b200_i8_split(_p(A, "double *"), n, _p(u, "double *"), 2, _p(scale, "double *"), args.planes,
-                                     _p(eng.planes, "signed char *"), _stream()), "split")
-        pl = eng.planes[: 2 * args.planes * eng.ld * eng.ld].view(2, args.planes, eng.ld, eng.ld).double()
+                                     _p(eng.planes[0], "signed char *"), _stream()), "split")
+        pl = eng.planes[0][: 2 * args.planes * eng.ld * eng.ld].view(2, args.planes, eng.ld, eng.ld).double()
         rec = torch.zeros((2, eng.ld, eng.ld), dtype=torch.float64, device=dev)
         for s in reversed(range(args.planes)):
             rec += pl[:, s] * 128.0 ** -(s + 1)

@@ -92,8 +92,8 @@ def test_i8_operands_exact(eng, tmp_path):
         u = sc._coded_first(il)
         scale = (u.abs().amax(dim=1) ** 2 * (sc.amax / 0.99)).contiguous()
         check(lib.gmat_b200_i8_split(_p(pvd, "double *"), n, _p(u, "double *"), 2, _p(scale, "double *"), planes,
-                                     _p(sc.planes, "signed char *"), _stream()), "gmat_b200_i8_split")
-        pl = sc.planes[: 2 * planes * sc.ld * sc.ld].view(2, planes, sc.ld, sc.ld).cpu().numpy().astype(np.float64)
+                                     _p(sc.planes[0], "signed char *"), _stream()), "gmat_b200_i8_split")
+        pl = sc.planes[0][: 2 * planes * sc.ld * sc.ld].view(2, planes, sc.ld, sc.ld).cpu().numpy().astype(np.float64)
         rec = sum(pl[:, s] * 128.0 ** -(s + 1) for s in reversed(range(planes))) * scale.cpu().numpy()[:, None, None]
         B = np.zeros((2, sc.ld, sc.ld))
         uh = u.cpu().numpy()
