@@ -245,6 +245,7 @@ def run_gpu(args):
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
     if world > 1:
+        os.environ["NCCL_DEBUG"] = "WARN"            # a box-level NCCL_DEBUG=VERSION would add a line to stdout
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     dev = engine.current_device()
 
