@@ -223,7 +223,7 @@ class I8Exact(object):
     an error-free digit-plane split of diag(u_i) Z'PZ diag(u_i).  Built once per scan (operands of the second SNPs
     stay resident: integer codes [m][ld] int8, their FP64 copy for the two O(n)-per-pair GEMM terms)."""
 
-    PLANE_BYTES = 2 << 30          # budget of the digit-plane buffer (first SNPs per launch follow from it)
+    PLANE_BYTES = 4 << 30          # budget of ONE digit-plane buffer (first SNPs per launch follow from it); two exist
 
     def __init__(self, store, lutU, lutV, coding_v, py_dev, pvp_dev, n_planes=None):
         if store.n_missing() != 0:
