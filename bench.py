@@ -368,7 +368,7 @@ def run_gpu(args):
             peaks["int8_from_measured_bf16_sustained_x2"] = 2.0 * mp["bf16_tflops_sustained"] if mp else None
             peaks["int8_from_measured_bf16_burst_x2"] = 2.0 * mp["bf16_tflops"] if mp else None
             peak = peaks["i8_mma_issue_tops"]
-            line["dtype"] = "f64 (n^2 term: error-free int8 digit planes, %d x 7 bit, int32 accumulate; rest f64)" % planes
+            line["dtype"] = "f64 results; n^2 term as exact int8 x int8 -> int32 tensor-core products of an error-free %d-plane split (%d bits), rest f64" % (planes, 7 * planes)
             line["roofline"] = {
                 "bound": "tensor", "achieved": achieved, "unit": "TOP/s", "peak": peak, "frac": achieved / peak,
                 "traffic": I8_TRAFFIC_BYTES, "kernel": {0: "i8_scan_kernel (tcgen05.mma cta_group::1 kind::i8, 128x256x32)", 1: "i8_scan_wide_kernel", 2: "i8_scan_pair_kernel (tcgen05.mma cta_group::2 kind::i8, 256x256x32 per CTA pair)"}[i8.wide],
@@ -404,7 +404,21 @@ def run_gpu(args):
                                                     "and issued are per GPU", **peaks})
         if world == 1:
             if not args.no_extra:
-                line["extra"] = extras(engine, torch, synth, store, model, lut, args, prefix, pymat)
+                e2e_f64 = None
+                if i8 is not None:
+                    # the same drop-in call on the FP64 DMMA engine (one timed call after one warm call)
+                    os.environ["GMAT_B200_EXACT_ENGINE"] = "f64"
+                    try:
+                        for it in range(2):
+                            torch.cuda.synchronize()
+                            t0 = time.perf_counter()
+                            remma_epiAA(pheno, prefix, gmat_lst, var_com, snp_lst_0=e2e_lst, p_cut=P_CUT,
+                                        out_file=out_file + ".f64")
+                            torch.cuda.synchronize()
+                            e2e_f64 = float(e2e_pairs) / (time.perf_counter() - t0)
+                    finally:
+                        del os.environ["GMAT_B200_EXACT_ENGINE"]
+                line["extra"] = extras(engine, torch, synth, store, model, lut, args, prefix, pymat, e2e_f64)
             if not args.no_cpu:
                 cpu = CpuExact(prefix, pheno, ag)
                 cp, ct = cpu.sample(4)
@@ -417,7 +431,7 @@ def run_gpu(args):
     return 0
 
 
-def extras(engine, torch, synth, store, model, lut, args, prefix, pymat):
+def extras(engine, torch, synth, store, model, lut, args, prefix, pymat, e2e_f64=None):
     """Secondary numbers of BASELINE.json's metric, same process, N=1: approximate screen pairs/s on the same
     data, agmat TFLOP/s on configs[1] (n=10,000 x m=500,000, generated in HBM), decode GB/s."""
     out = {}
@@ -434,14 +448,25 @@ def extras(engine, torch, synth, store, model, lut, args, prefix, pymat):
                 best = min(best, e0.elapsed_time(e1))
         return best * 1e-3
 
-    # the FP64 DMMA kernel on a 256-first-SNP batch of the same data: what the exact scan runs when genotypes are
-    # missing (GMAT_B200_EXACT_ENGINE=f64), and the yardstick for the int8 engine
+    # the FP64 DMMA engine on a 256-first-SNP batch of the same data: the mechanism north_star names for the
+    # quadratic forms (and what the exact scan runs when genotypes are missing, GMAT_B200_EXACT_ENGINE=f64), with its
+    # own roofline against the measured FP64 peak, and its own end-to-end drop-in call
     sub = np.asarray(batch_first_snps(N_SNP, 0, 1, 256), dtype=np.int64)
     t = timed(lambda: engine.epi_exact_scan(store, lut, lut, model.py, model.packed, sub, engine.PAIRS_UPPER, 19.5),
               reps=2)
+    from gmat_b200._ffi import ffi
+    cfg = ffi.new("int[3]")
+    engine.lib.gmat_b200_exact_config(cfg, cfg + 1, cfg + 2)
+    peaks = measure_fp64_peaks(engine, torch)
+    peak = max(peaks["dmma_tflops"], peaks["cublas_dgemm_tflops"])
+    issued = n_pairs(sub, N_SNP) * exact_issued_flop_per_pair(N_ID, int(cfg[0])) / t / 1e12
     out["exact_f64_engine"] = {"pairs_per_s": n_pairs(sub, N_SNP) / t, "seconds": t,
                                "tflops_algorithmic": n_pairs(sub, N_SNP) * f_exact(N_ID) / t / 1e12,
-                               "workload": "epi_exact_rb_kernel (DMMA), 256 first-SNPs, all j>i"}
+                               "tflops_issued": issued, "fp64_peak_tflops": peak, "frac_issued": issued / peak,
+                               "workload": "epi_exact_rb_kernel (FP64 DMMA, Z'PZ staged by TMA), 256 first-SNPs, all j>i",
+                               **peaks}
+    if e2e_f64 is not None:
+        out["exact_f64_engine"]["e2e_pairs_per_s"] = e2e_f64
     # approximate screen: full scan of the C3 data (1.9999e8 pairs), F_approx = 2n flop per pair
     la = store.lut(engine.ADD, engine.FREQ_CLOOP)
     full = np.arange(N_SNP - 1, dtype=np.int64)
