@@ -371,7 +371,7 @@ def run_gpu(args):
             line["dtype"] = "f64 results; n^2 term as exact int8 x int8 -> int32 tensor-core products of an error-free %d-plane split (%d bits), rest f64" % (planes, 7 * planes)
             line["roofline"] = {
                 "bound": "tensor", "achieved": achieved, "unit": "TOP/s", "peak": peak, "frac": achieved / peak,
-                "traffic": I8_TRAFFIC_BYTES, "kernel": {0: "i8_scan_kernel (tcgen05.mma cta_group::1 kind::i8, 128x256x32)", 1: "i8_scan_wide_kernel", 2: "i8_scan_pair_kernel (tcgen05.mma cta_group::2 kind::i8, 256x256x32 per CTA pair)"}[i8.wide],
+                "traffic": I8_TRAFFIC_BYTES, "kernel": {0: "i8_scan_kernel (tcgen05.mma cta_group::1 kind::i8, 128x256x32)", 2: "i8_scan_pair_kernel (tcgen05.mma cta_group::2 kind::i8, 256x256x32 per CTA pair)"}[i8.wide],
                 "kernel_ms_per_launch": kern_ms, "kernel_launches_per_step": launches_per_step,
                 "kernel_share_of_step": kern_ms * launches_per_step / ms_local,
                 "ops_per_pair_algorithmic": alg, "ops_per_pair_issued": iss, "issued_tops": issued,

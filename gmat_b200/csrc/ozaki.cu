@@ -294,163 +294,6 @@ i8_scan_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_constant_
     }
 }
 
-// ---- wide variant: TWO tiles of 128 second SNPs per CTA share every plane tile --------------------------------
-// The first kernel is bound by L2 -> SM bandwidth (ncu: lts throughput 70 %, tensor pipe 58 %): 48 KB per 512 MMA
-// cycles.  Here a stage is {genotype tile 0, genotype tile 1, plane tile} = 64 KB per 1024 MMA cycles (-33 %
-// bytes per MAC).  Both 256-column accumulators are live at once, so TMEM cannot double-buffer any more: the
-// issuer waits, per accumulator, for that accumulator's four epilogue warps before the first MMA of the next tile.
-constexpr int I8W_NS = 3;
-constexpr int I8W_STAGE_BYTES = 2 * I8_A_BYTES + I8_B_BYTES;      // 64 KB
-constexpr int I8W_THREADS = 320;                                  // producer, issuer, 2 x 4 epilogue warps
-
-struct I8WBars {
-    uint64_t full[I8W_NS], empty[I8W_NS], tfull, tempty[2];
-    uint32_t tmem_base;
-};
-
-__global__ void __launch_bounds__(I8W_THREADS, 1)
-i8_scan_wide_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_constant__ CUtensorMap map_p,
-                    const I8Params p) {
-    extern __shared__ unsigned char smem_raw[];
-    unsigned char *smem = reinterpret_cast<unsigned char *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
-                                                           ~static_cast<uintptr_t>(1023));
-    I8WBars *bars = reinterpret_cast<I8WBars *>(smem + I8W_NS * I8W_STAGE_BYTES);
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-
-    if (threadIdx.x == 0) {
-        for (int s = 0; s < I8W_NS; ++s) { mbar_init(&bars->full[s], 1); mbar_init(&bars->empty[s], 1); }
-        mbar_init(&bars->tfull, 1);
-        mbar_init(&bars->tempty[0], 4);
-        mbar_init(&bars->tempty[1], 4);
-        mbar_fence_init();
-    }
-    if (warp == 1) {
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;\n" ::"r"(
-                         smem_u32(&bars->tmem_base)), "r"(512)
-                     : "memory");
-        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;\n" ::: "memory");
-    }
-    tc_fence_before();
-    __syncthreads();
-    tc_fence_after();
-    const uint32_t tmem_base = bars->tmem_base;
-
-    if (warp == 0) {
-        if (lane == 0) {
-            int stage = 0; unsigned phase = 0;
-            for (int item = blockIdx.x; item < p.total_items; item += gridDim.x) {
-                const int ii = i8_find_first(p.item_prefix, p.n_i, item);
-                const int jt = 2 * (p.jt0[ii] + (item - p.item_prefix[ii]));       // first of the two 128-SNP tiles
-                for (int s = 0; s < p.n_planes; ++s) {
-                    const int prow = (ii * p.n_planes + s) * p.np;
-                    for (int kt = 0; kt < p.n_kt; ++kt) {
-                        const int nl = i8_slabs_of(kt, p.n_slab);
-                        for (int l = 0; l < nl; ++l) {
-                            mbar_wait(&bars->empty[stage], phase ^ 1u);
-                            mbar_expect_tx(&bars->full[stage], I8W_STAGE_BYTES);
-                            unsigned char *sa = smem + stage * I8W_STAGE_BYTES;
-                            tma_load_2d(sa, &map_g, l * I8_SLAB, jt * I8_TJ, &bars->full[stage]);
-                            tma_load_2d(sa + I8_A_BYTES, &map_g, l * I8_SLAB, (jt + 1) * I8_TJ, &bars->full[stage]);
-                            tma_load_2d(sa + 2 * I8_A_BYTES, &map_p, l * I8_SLAB, prow + kt * I8_TK, &bars->full[stage]);
-                            if (++stage == I8W_NS) { stage = 0; phase ^= 1u; }
-                        }
-                    }
-                }
-            }
-        }
-    } else if (warp == 1) {
-        if (lane == 0) {
-            int stage = 0; unsigned phase = 0;
-            unsigned tphase = 0;                                             // parity of the tile being issued
-            for (int item = blockIdx.x; item < p.total_items; item += gridDim.x) {
-                for (int s = 0; s < p.n_planes; ++s) {
-                    for (int kt = 0; kt < p.n_kt; ++kt) {
-                        const int nl = i8_slabs_of(kt, p.n_slab);
-                        for (int l = 0; l < nl; ++l) {
-                            mbar_wait(&bars->full[stage], phase);
-                            tc_fence_after();
-                            const uint32_t sa = smem_u32(smem + stage * I8W_STAGE_BYTES);
-                            const uint64_t da0 = umma_desc_sw128(sa), da1 = umma_desc_sw128(sa + I8_A_BYTES);
-                            const uint64_t db = umma_desc_sw128(sa + 2 * I8_A_BYTES);
-                            if (l == 0) { mbar_wait(&bars->tempty[0], tphase ^ 1u); tc_fence_after(); }
-#pragma unroll
-                            for (int k = 0; k < I8_SLAB / 32; ++k)
-                                umma_i8(tmem_base, da0 + (uint64_t)(2 * k), db + (uint64_t)(2 * k), I8_IDESC,
-                                        (uint32_t)((l | k) != 0));
-                            if (l == 0) { mbar_wait(&bars->tempty[1], tphase ^ 1u); tc_fence_after(); }
-#pragma unroll
-                            for (int k = 0; k < I8_SLAB / 32; ++k)
-                                umma_i8(tmem_base + (uint32_t)I8_TK, da1 + (uint64_t)(2 * k), db + (uint64_t)(2 * k),
-                                        I8_IDESC, (uint32_t)((l | k) != 0));
-                            tc_commit(&bars->empty[stage]);
-                            if (++stage == I8W_NS) { stage = 0; phase ^= 1u; }
-                        }
-                        tc_commit(&bars->tfull);
-                        tphase ^= 1u;
-                    }
-                }
-            }
-        }
-    } else {
-        const int q = warp & 3;                                             // TMEM lane quarter
-        const int acc = (warp - 2) >> 2;                                    // which accumulator / which 128-SNP tile
-        unsigned tphase = 0;
-        for (int item = blockIdx.x; item < p.total_items; item += gridDim.x) {
-            const int ii = i8_find_first(p.item_prefix, p.n_i, item);
-            const int jt = 2 * (p.jt0[ii] + (item - p.item_prefix[ii])) + acc;
-            const int j = jt * I8_TJ + q * 32 + lane;
-            const signed char *arow = p.g8 + (size_t)(j < p.m ? j : p.m - 1) * p.ld;
-            const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * I8_TK);
-            double qacc = 0.0, wgt = 1.0;
-            for (int s = 0; s < p.n_planes; ++s) {
-                wgt *= 0.0078125;
-                long long plane_sum = 0;                                    // exact
-                for (int kt = 0; kt < p.n_kt; ++kt) {
-                    int4 abytes[I8_TK / 16];
-                    i8_load_dosage(arow + kt * I8_TK, abytes);
-                    mbar_wait_warp(&bars->tfull, tphase);
-                    tc_fence_after();
-                    plane_sum += i8_drain_tile(taddr, abytes);
-                    tc_fence_before();
-                    __syncwarp();
-                    if (lane == 0) mbar_arrive(&bars->tempty[acc]);
-                    tphase ^= 1u;
-                }
-                qacc += (double)plane_sum * wgt;                         // the only FP64 work per plane
-            }
-            const int i = (int)p.ilist[ii];
-            const bool valid = j < p.m && (p.pair_space == GMAT_B200_PAIRS_ALL || j > i);
-            const int jc = j < p.m ? j : p.m - 1;
-            const double quad = 2.0 * p.scale[ii] * qacc;
-            const double o = p.offs[jc];
-            const size_t at = (size_t)ii * p.m + jc;
-            double var = quad - 2.0 * o * p.t1[at] + o * o * p.s_i[ii];
-            double eff = p.e[at] - o * p.upy[ii];
-            if (o != o) { var = 0.0; eff = 0.0; }
-            const double chi = eff * eff / var;
-            if (p.q_debug != nullptr && j < p.m) p.q_debug[at] = quad;
-            gmat_b200_hit h;
-            h.snp_0 = i; h.snp_1 = j; h.eff = eff; h.var = var; h.chi = chi;
-            const bool hit = valid && (p.chi_cut < 0.0 || chi > p.chi_cut);
-            const unsigned ballot = __ballot_sync(0xffffffffu, hit);
-            if (ballot) {
-                unsigned long long base = 0;
-                if (lane == 0) base = atomicAdd(p.count, (unsigned long long)__popc(ballot));
-                base = __shfl_sync(0xffffffffu, base, 0);
-                if (hit) {
-                    const unsigned long long pos = base + __popc(ballot & ((1u << lane) - 1u));
-                    if ((long long)pos < p.cap) p.hits[pos] = h;
-                }
-            }
-        }
-    }
-    tc_fence_before();
-    __syncthreads();
-    if (warp == 1) {
-        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;\n" ::"r"(tmem_base), "r"(512) : "memory");
-    }
-}
-
 // ---- CTA-pair variant: tcgen05.mma.cta_group::2 ---------------------------------------------------------------
 // Two CTAs of a cluster (one TPC) own the two 128-SNP tiles of a work item and HALF of every plane tile each
 // (128 of its 256 rows); one MMA of the leader CTA computes M = 256 SNPs x N = 256 plane rows across both SMs,
@@ -866,6 +709,7 @@ extern "C" int gmat_b200_i8_scan(const signed char *g8_dev, long long n, long lo
     if (rc == GMAT_B200_OK) rc = make_map(&map_p, planes_dev, p.ld, (long long)n_i * n_planes * p.np, p.ld, I8_TK);
     if (rc != GMAT_B200_OK) return rc;
     const int grid = (int)(total_items < sm_count() ? total_items : sm_count());
+    GB_CHECK_ARG(wide == 0 || wide == 2, "variant must be 0 (one CTA per 128-SNP tile) or 2 (CTA pair)");
     if (wide == 2) {
         CUtensorMap map_ph;                                       // plane map with 128-row boxes (one half per CTA)
         rc = make_map(&map_ph, planes_dev, p.ld, (long long)n_i * n_planes * p.np, p.ld, I8P_HALF);
@@ -875,10 +719,6 @@ extern "C" int gmat_b200_i8_scan(const signed char *g8_dev, long long n, long lo
         const int pairs_of_sms = sm_count() / 2;
         const int grid2 = 2 * (int)(total_items < pairs_of_sms ? total_items : pairs_of_sms);
         i8_scan_pair_kernel<<<grid2, I8_THREADS, smem_bytes, st>>>(map_g, map_ph, p);
-    } else if (wide) {
-        const int smem_bytes = I8W_NS * I8W_STAGE_BYTES + 1024 + (int)sizeof(I8WBars);
-        GB_CUDA(cudaFuncSetAttribute(i8_scan_wide_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
-        i8_scan_wide_kernel<<<grid, I8W_THREADS, smem_bytes, st>>>(map_g, map_p, p);
     } else {
         const int smem_bytes = I8_NS * I8_STAGE_BYTES + 1024 + (int)sizeof(I8Bars);
         GB_CUDA(cudaFuncSetAttribute(i8_scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));

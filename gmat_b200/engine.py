@@ -236,7 +236,6 @@ class I8Exact(object):
         self.g8 = torch.empty((m, self.ld), dtype=torch.int8, device=dev)
         check(lib.gmat_b200_i8_dosage(_p(store.bed, "unsigned char *"), n, m, store.row_bytes, coding_v,
                                       _p(self.g8, "signed char *"), self.ld, _stream()), "gmat_b200_i8_dosage")
-        self.gd = self.g8[:, :n].to(torch.float64)                 # [m][n] integer codes as FP64
         self.offs = (-lutV[:, 0]).contiguous()                     # lut[j][code 0] = 0 - o_j
         # second SNPs whose integer code is the same for everybody have w == 0 exactly (eff = var = 0, chi = NaN in
         # the reference); the expanded form would return rounding noise instead, so they are flagged (o_j = NaN)
@@ -252,9 +251,10 @@ class I8Exact(object):
         self.planes = [torch.zeros((self.batch * per_first,), dtype=torch.int8, device=dev) for _ in range(2)]
         self._prep_stream = torch.cuda.Stream(device=dev)
         self._shifts = torch.tensor([0, 2, 4, 6], dtype=torch.uint8, device=dev)
-        # kernel variant: 0 = one 128-SNP tile per CTA (double-buffered TMEM), 1 = two tiles per CTA sharing the
-        # plane tiles, 2 = CTA pair (tcgen05 cta_group::2)
-        self.wide = int(os.environ.get("GMAT_B200_I8_WIDE", "2"))
+        # kernel variant: 2 = CTA pair (tcgen05 cta_group::2, default), 0 = one CTA per 128-SNP tile (cta_group::1)
+        self.wide = int(os.environ.get("GMAT_B200_I8_VARIANT", "2"))
+        if self.wide not in (0, 2):
+            raise ValueError("GMAT_B200_I8_VARIANT must be 0 or 2")
         self.kernel_events = None      # bench.py: list of (start, end) CUDA events around every i8_scan launch
 
     def _coded_first(self, il):
@@ -262,6 +262,23 @@ class I8Exact(object):
         rows = self.store.bed[il]
         codes = ((rows[:, :, None] >> self._shifts) & 3).reshape(len(il), -1)[:, :self.store.n]
         return torch.gather(self.lutU[il], 1, codes.long())
+
+    M_CHUNK = 65536    # second SNPs whose integer codes are widened to FP64 at a time for the side-term GEMMs
+
+    def _side_terms(self, r, upy_vec):
+        """The two O(n)-per-pair FP64 terms for a chunk of first SNPs: [nc][m] each (library DGEMMs)."""
+        n, m = self.store.n, self.store.m
+        nc = r.shape[0]
+        t1 = torch.empty((nc, m), dtype=torch.float64, device=r.device)
+        e = torch.empty((nc, m), dtype=torch.float64, device=r.device)
+        lhs = torch.cat([r, upy_vec])
+        for j0 in range(0, m, self.M_CHUNK):
+            j1 = min(m, j0 + self.M_CHUNK)
+            gd = self.g8[j0:j1, :n].to(torch.float64)                      # integer codes as FP64, [chunk][n]
+            both = lhs @ gd.T
+            t1[:, j0:j1] = both[:nc]
+            e[:, j0:j1] = both[nc:]
+        return t1, e
 
     def _work_items(self, ih, pair_space):
         """(item_prefix[n_i+1], jt0[n_i]) int32 host arrays: tiles of 128 second SNPs every first SNP needs."""
@@ -307,8 +324,7 @@ class I8Exact(object):
                 upy_vec = u_all * self.py
                 s_all = r.sum(dim=1).contiguous()
                 upy_all = upy_vec.sum(dim=1).contiguous()
-                t1_all = r @ self.gd.T                                      # [nc][m]  a_j . r_i
-                e_all = upy_vec @ self.gd.T                                 # [nc][m]  a_j . (u_i o py)
+                t1_all, e_all = self._side_terms(r, upy_vec)                # [nc][m] a_j . r_i, a_j . (u_i o py)
                 scale_all = (u_all.abs().amax(dim=1) ** 2 * (self.amax / 0.99)).clamp_min(1e-200).contiguous()
                 del r, upy_vec
                 side_ready = main.record_event()

@@ -195,16 +195,16 @@ int gmat_b200_i8_split(const double *pvp_dev /* [n][n] */, long long n, const do
  * device arrays, so that successive launches queue without a host synchronisation.  t1_dev/e_dev: [n_i][m] FP64
  * (a_j . r_i and a_j . (u_i o Z'Py)); offs_dev[m] = o_j (NaN = monomorphic second SNP: eff = var = 0, chi = NaN);
  * q_debug_dev (optional, [n_i][m]) receives a_j' B_i a_j.  Hits are appended at *count_dev as in
- * gmat_b200_epi_exact_scan (count keeps counting beyond cap).  wide != 0: a work item is a PAIR of 128-SNP tiles
- * (jt0 and the item counts are then in units of 256 second SNPs): wide == 1 one CTA computes both tiles and shares
- * every plane tile in shared memory; wide == 2 a CTA PAIR (cluster of 2, tcgen05 cta_group::2) computes them.      */
+ * gmat_b200_epi_exact_scan (count keeps counting beyond cap).  variant 0: one CTA per work item of 128 second SNPs
+ * (tcgen05 cta_group::1); variant 2 (what the engine uses): a work item is 256 second SNPs computed by a CTA PAIR
+ * (cluster of 2, tcgen05 cta_group::2) -- jt0 and the item counts are then in units of 256 second SNPs.          */
 int gmat_b200_i8_scan(const signed char *g8_dev, long long n, long long m, const signed char *planes_dev,
                       int n_planes, const long long *ilist_dev, long long n_i,
                       const int *item_prefix_dev, const int *jt0_dev, long long total_items,
                       const double *scale_dev, const double *s_dev, const double *upy_dev,
                       const double *t1_dev, const double *e_dev, const double *offs_dev,
                       int pair_space, double chi_cut, gmat_b200_hit *hits_dev, long long cap,
-                      unsigned long long *count_dev, double *q_debug_dev, int wide, void *stream);
+                      unsigned long long *count_dev, double *q_debug_dev, int variant, void *stream);
 
 /* int8 tensor-core issue-rate microbenchmark (tcgen05.mma kind::i8 128x256x32 on resident tiles, all SMs): TOPS  */
 int gmat_b200_i8_peak(int iters, double *tops);

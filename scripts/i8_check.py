@@ -75,7 +75,8 @@ def main():
     # quadratic form against torch FP64
     il = torch.as_tensor(first).to(dev)
     u = eng._coded_first(il)
-    q_ref = torch.stack([((eng.gd * u[k]) @ A * (eng.gd * u[k])).sum(dim=1) for k in range(min(len(first), 3))])
+    gd = eng.g8[:, :n].double()
+    q_ref = torch.stack([((gd * u[k]) @ A * (gd * u[k])).sum(dim=1) for k in range(min(len(first), 3))])
     qq = qd[: q_ref.shape[0]]
     mask = torch.ones_like(q_ref, dtype=torch.bool)
     if space == engine.PAIRS_UPPER:      # tiles left of the first needed tile are never computed

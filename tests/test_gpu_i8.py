@@ -168,6 +168,16 @@ def test_i8_monomorphic_snps_and_small_batches(eng, tmp_path, monkeypatch):
     np.testing.assert_allclose(got["eff"][~dead], ref["eff"][~dead], rtol=RTOL, atol=1e-12)
     np.testing.assert_allclose(got["var"][~dead], ref["var"][~dead], rtol=RTOL)
     assert len(sc.scan(first, eng.PAIRS_UPPER, 1e-3)) == int(np.sum(ref["chi"] > 1e-3))
+    # hit buffer too small: the counter keeps counting, the scan is repeated once with the exact capacity
+    small = sc.scan(first, eng.PAIRS_UPPER, -1.0, cap=100)
+    assert len(small) == len(ref) and len(set(key(small).tolist())) == len(ref)
+    # the single-CTA kernel variant gives the same numbers as the CTA-pair kernel
+    sc0 = eng.I8Exact(store, lu, lu, eng.ADD, pyd, pvd)
+    sc0.wide = 0
+    got0 = sc0.scan(first, eng.PAIRS_UPPER, -1.0)
+    got0 = got0[np.argsort(key(got0))]
+    assert np.array_equal(key(got0), key(got))
+    np.testing.assert_allclose(got0["var"], got["var"], rtol=1e-12)
 
 
 def test_engine_selection(eng, tmp_path, monkeypatch):
