@@ -270,6 +270,7 @@ i8_scan_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_constant_
             double var = quad - 2.0 * o * p.t1[at] + o * o * p.s_i[ii];
             double eff = p.e[at] - o * p.upy[ii];
             if (o != o) { var = 0.0; eff = 0.0; }                          // monomorphic second SNP: w == 0 exactly
+            else if (o > 1.0e300) { var = o - o; eff = var; }             // missing genotype in the second SNP: NaN, as numpy
             const double chi = eff * eff / var;
             if (p.q_debug != nullptr && j < p.m) p.q_debug[at] = quad;
             gmat_b200_hit h;
@@ -462,7 +463,8 @@ i8_scan_pair_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_cons
             const size_t at = (size_t)ii * p.m + jc;
             double var = quad - 2.0 * o * p.t1[at] + o * o * p.s_i[ii];
             double eff = p.e[at] - o * p.upy[ii];
-            if (o != o) { var = 0.0; eff = 0.0; }
+            if (o != o) { var = 0.0; eff = 0.0; }                          // monomorphic second SNP: w == 0 exactly
+            else if (o > 1.0e300) { var = o - o; eff = var; }             // missing genotype in the second SNP: NaN, as numpy
             const double chi = eff * eff / var;
             if (p.q_debug != nullptr && j < p.m) p.q_debug[at] = quad;
             gmat_b200_hit h;

@@ -203,13 +203,12 @@ def epi_exact_scan(store, lutU, lutV, py_dev, packed, ilist, pair_space, chi_cut
 
 
 def exact_engine(store):
-    """Which kernel runs the exact scan: "i8" (tcgen05 int8 digit planes) or "f64" (DMMA)."""
+    """Which kernel runs the exact scan: "i8" (tcgen05 int8 digit planes; GMAT_B200_EXACT_ENGINE=auto or i8) or
+    "f64" (DMMA)."""
     want = os.environ.get("GMAT_B200_EXACT_ENGINE", "auto").lower()
     if want not in ("auto", "i8", "f64"):
         raise ValueError("GMAT_B200_EXACT_ENGINE must be auto, i8 or f64")
-    if want == "auto":
-        return "i8" if store.n_missing() == 0 else "f64"
-    return want
+    return "i8" if want == "auto" else want
 
 
 def i8_planes():
@@ -226,8 +225,6 @@ class I8Exact(object):
     PLANE_BYTES = 4 << 30          # budget of ONE digit-plane buffer (first SNPs per launch follow from it); two exist
 
     def __init__(self, store, lutU, lutV, coding_v, py_dev, pvp_dev, n_planes=None):
-        if store.n_missing() != 0:
-            raise ValueError("the int8 engine needs second SNPs without missing genotypes")
         self.store, self.lutU, self.py = store, lutU, py_dev.reshape(-1)
         self.A = pvp_dev
         self.n_planes = int(i8_planes() if n_planes is None else n_planes)
@@ -241,9 +238,14 @@ class I8Exact(object):
         # the reference); the expanded form would return rounding noise instead, so they are flagged (o_j = NaN)
         tabv = torch.tensor([0, 0, 1, 2] if coding_v == ADD else [0, 0, 1, 0], dtype=torch.int32, device=dev)
         present = store.counts > 0
+        present[:, 1] = False
         hi = torch.where(present, tabv, torch.full_like(tabv, -1)).amax(dim=1)
         lo = torch.where(present, tabv, torch.full_like(tabv, 9)).amin(dim=1)
         self.offs[hi <= lo] = float("nan")
+        # a missing call makes the coded column NaN in the reference's numpy path (remma_epiAA.py:59-61 on
+        # read_plink's NaN), so every statistic of such a SNP is NaN and it is never reported: second SNPs are
+        # flagged (o_j = +inf -> eff = var = chi = NaN); for a FIRST SNP the NaN of lutU[i][code 01] propagates
+        self.offs[store.counts[:, 1] > 0] = float("inf")
         self.amax = float(pvp_dev.abs().max())
         per_first = self.n_planes * self.ld * self.ld
         self.batch = int(max(1, min(64, self.PLANE_BYTES // per_first)))

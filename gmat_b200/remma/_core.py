@@ -138,8 +138,7 @@ class DeviceModel(object):
 
     def scanner(self, store, lut_u, lut_v, coding_v):
         """The exact-scan engine for this model and genotype store: ``scan(ilist, pair_space, chi_cut)``.
-        GMAT_B200_EXACT_ENGINE = auto (default: the INT8 tensor-core engine when no genotype is missing, else the
-        FP64 DMMA kernel) | i8 | f64."""
+        GMAT_B200_EXACT_ENGINE = auto (default: the INT8 tensor-core engine) | i8 | f64 (the FP64 DMMA kernel)."""
         which = engine.exact_engine(store)
         if which == "i8":
             eng = engine.I8Exact(store, lut_u, lut_v, coding_v, self.py, self.pvp)

@@ -181,8 +181,9 @@ int gmat_b200_grm(const unsigned char *bed_dev, long long n, long long m, long l
  *   var_ij = a_j' B_i a_j - 2 o_j (a_j . r_i) + o_j^2 s_i ,  r_i = u_i o (Z'PZ u_i), s_i = sum r_i
  *   eff_ij = a_j . (u_i o Z'Py) - o_j (u_i . Z'Py)
  * a_j' B_i a_j is evaluated on the INT8 tensor cores from an error-free split of B_i/scale_i into n_planes signed
- * base-128 digit planes (exact int8 x int8 -> int32 products, recombined in FP64; 8 planes = 56 bits).  Second
- * SNPs must have no missing genotype (callers route data sets with missing calls to the FP64 kernel).         */
+ * base-128 digit planes (exact int8 x int8 -> int32 products, recombined in FP64; 8 planes = 56 bits).  A SNP
+ * with a missing call has NaN statistics in the reference's numpy path; callers flag such second SNPs with
+ * offs = +inf (eff = var = chi = NaN) and monomorphic ones with offs = NaN (eff = var = 0, chi = NaN).          */
 long long gmat_b200_i8_ld(long long n);      /* bytes per row (and rows per plane) of the int8 operands       */
 int gmat_b200_i8_dosage(const unsigned char *bed_dev, long long n, long long m, long long row_bytes, int coding,
                         signed char *g8_dev /* [m][ld] */, long long ld, void *stream);
@@ -193,7 +194,7 @@ int gmat_b200_i8_split(const double *pvp_dev /* [n][n] */, long long n, const do
 /* Work items of one launch are (first SNP ii, tile of 128 second SNPs): item_prefix_dev[n_i+1] = first item of
  * every first SNP, jt0_dev[n_i] = its first tile (UPPER: (i+1)/128, ALL: 0), total_items = item_prefix[n_i]; all
  * device arrays, so that successive launches queue without a host synchronisation.  t1_dev/e_dev: [n_i][m] FP64
- * (a_j . r_i and a_j . (u_i o Z'Py)); offs_dev[m] = o_j (NaN = monomorphic second SNP: eff = var = 0, chi = NaN);
+ * (a_j . r_i and a_j . (u_i o Z'Py)); offs_dev[m] = o_j (NaN = monomorphic second SNP, +inf = SNP with a missing call);
  * q_debug_dev (optional, [n_i][m]) receives a_j' B_i a_j.  Hits are appended at *count_dev as in
  * gmat_b200_epi_exact_scan (count keeps counting beyond cap).  variant 0: one CTA per work item of 128 second SNPs
  * (tcgen05 cta_group::1); variant 2 (what the engine uses): a work item is 256 second SNPs computed by a CTA PAIR

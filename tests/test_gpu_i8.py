@@ -181,23 +181,60 @@ def test_i8_monomorphic_snps_and_small_batches(eng, tmp_path, monkeypatch):
 
 
 def test_engine_selection(eng, tmp_path, monkeypatch):
-    """auto = int8 engine without missing genotypes, FP64 DMMA kernel otherwise; the int8 engine refuses a store
-    with missing genotypes instead of computing something else."""
-    import torch
+    """auto = i8 = the int8 tensor-core engine, f64 = the DMMA kernel, anything else is an error."""
     p0, _ = _dataset(tmp_path, 40, 12, seed=5)
     s0 = eng.GenotypeStore(p0)
-    p1 = str(tmp_path / "miss")
-    from gmat_b200 import synth
-    synth.write_dataset(p1, 40, 12, seed=5, missing_rate=0.1)
-    s1 = eng.GenotypeStore(p1)
     monkeypatch.delenv("GMAT_B200_EXACT_ENGINE", raising=False)
-    assert eng.exact_engine(s0) == "i8" and eng.exact_engine(s1) == "f64"
+    assert eng.exact_engine(s0) == "i8"
     monkeypatch.setenv("GMAT_B200_EXACT_ENGINE", "f64")
     assert eng.exact_engine(s0) == "f64"
     monkeypatch.setenv("GMAT_B200_EXACT_ENGINE", "bogus")
     with pytest.raises(ValueError):
         eng.exact_engine(s0)
-    pymat, pvp = _random_model(40, 2)
-    with pytest.raises(ValueError):
-        eng.I8Exact(s1, s1.lut(eng.ADD), s1.lut(eng.ADD), eng.ADD, torch.as_tensor(pymat.ravel().copy()).cuda(),
-                    torch.as_tensor(pvp).cuda())
+
+
+@pytest.mark.parametrize("kind", ["AA", "AD"])
+def test_i8_missing_calls_are_nan_like_the_reference(eng, tmp_path, kind):
+    """A missing call makes the coded column NaN in the reference's numpy path, so every statistic of a pair that
+    involves such a SNP is NaN (never reported); all other pairs are untouched.  Same NaN pattern and same numbers
+    as the DMMA kernel and the oracle."""
+    import torch
+    from gmat_b200 import synth
+    n, m = 150, 70
+    g = synth.random_genotypes(n, m, 9, 0.0)
+    for snp, ids in ((3, [0, 7]), (20, [149]), (41, [5, 6, 77]), (69, [10])):
+        g[snp, ids] = -1
+    prefix, _ = _dataset(tmp_path, n, m, seed=2, geno=g)
+    pymat, pvp = _random_model(n, 6)
+    store = eng.GenotypeStore(prefix)
+    assert store.n_missing() == 7
+    cu, cv = _codings(eng, kind)
+    lu, lv = store.lut(cu), store.lut(cv)
+    pyd = torch.as_tensor(pymat.ravel().copy()).cuda()
+    pvd = torch.as_tensor(pvp).cuda().contiguous()
+    packed = eng.pack_pvp(pvd)
+    space = eng.PAIRS_ALL if kind == "AD" else eng.PAIRS_UPPER
+    first = np.arange(m if kind == "AD" else m - 1)
+    ref = eng.epi_exact_scan(store, lu, lv, pyd, packed, first, space, -1.0)
+    got = eng.I8Exact(store, lu, lv, cv, pyd, pvd).scan(first, space, -1.0)
+    key = lambda h: h["snp_0"].astype(np.int64) * m + h["snp_1"]
+    ref, got = ref[np.argsort(key(ref))], got[np.argsort(key(got))]
+    assert np.array_equal(key(ref), key(got))
+    dead = np.isin(ref["snp_0"], [3, 20, 41, 69]) | np.isin(ref["snp_1"], [3, 20, 41, 69])
+    for col in ("eff", "var", "chi"):
+        assert np.all(np.isnan(ref[col][dead])) and np.all(np.isnan(got[col][dead]))
+        assert not np.isnan(got[col][~dead]).any()
+    np.testing.assert_allclose(got["eff"][~dead], ref["eff"][~dead], rtol=RTOL, atol=1e-12)
+    np.testing.assert_allclose(got["var"][~dead], ref["var"][~dead], rtol=RTOL)
+    # thresholded: no pair with a missing call is ever reported
+    hits = eng.I8Exact(store, lu, lv, cv, pyd, pvd).scan(first, space, 0.5)
+    assert len(hits) == int(np.nansum(ref["chi"] > 0.5)) and not (np.isin(hits["snp_0"], [3, 20, 41, 69]).any()
+                                                                  or np.isin(hits["snp_1"], [3, 20, 41, 69]).any())
+    U, V = oracle.coded_pair(kind, oracle.read_plink(prefix))
+    js, e, v, c, _ = oracle.exact_first_snp(U, V, 5, pymat, pvp, kind == "AD")
+    mine = got[got["snp_0"] == 5]
+    assert np.array_equal(mine["snp_1"], js)
+    assert np.array_equal(np.isnan(v), np.isnan(mine["var"]))
+    ok = ~np.isnan(v)
+    np.testing.assert_allclose(mine["var"][ok], v[ok], rtol=RTOL)
+    np.testing.assert_allclose(mine["eff"][ok], e[ok], rtol=RTOL, atol=1e-11)
