@@ -113,6 +113,43 @@ def test_exact_scan_full_shape_sampled_against_oracle(eng, n, m, kind):
     assert np.array_equal(res2["var"], res["var"])
 
 
+@pytest.mark.parametrize("n,m,kind", [(2000, 20000, "AA"), (5000, 50000, "AA"), (5000, 50000, "DD"),
+                                      (5000, 50000, "AD")])
+def test_i8_scan_full_shape_sampled_against_oracle(eng, n, m, kind):
+    """The int8 tensor-core engine at BASELINE's shapes: same hit set as the DMMA kernel on the same first SNPs, and
+    a sample of its rows (plus unreported pairs) recomputed by the numpy oracle to 1e-9."""
+    import torch
+    from gmat_b200 import synth
+    dev = eng.current_device()
+    payload = synth.device_payload(n, m, 20201013 + n, dev, eng.row_stride(n))
+    store = eng.GenotypeStore.from_device_payload(payload, n)
+    host = payload.cpu().numpy()
+    pvp, py = _model(n, 5, torch, dev)
+    pvp = pvp.contiguous()
+    cu, cv = kind[0], kind[1]
+    code = {"A": eng.ADD, "D": eng.DOM}
+    lu, lv = store.lut(code[cu]), store.lut(code[cv])
+    space = eng.PAIRS_ALL if kind == "AD" else eng.PAIRS_UPPER
+    first = np.array([3, 4, 5, 6, 7, 8, 9, 10, m // 2, m // 2 + 1, m - 3, m - 2], dtype=np.int64)
+    chi_cut = 9.0
+    hits = eng.I8Exact(store, lu, lv, code[cv], py, pvp).scan(first, space, chi_cut)
+    ref = eng.epi_exact_scan(store, lu, lv, py, eng.pack_pvp(pvp), first, space, chi_cut)
+    key = lambda h: h["snp_0"].astype(np.int64) * m + h["snp_1"]
+    hits, ref = hits[np.argsort(key(hits))], ref[np.argsort(key(ref))]
+    border = set(key(ref)[np.abs(ref["chi"] / chi_cut - 1) < 1e-7].tolist())
+    assert len(ref) > 100 and (set(key(hits).tolist()) ^ set(key(ref).tolist())) <= border
+    if len(hits) == len(ref):
+        np.testing.assert_allclose(hits["var"], ref["var"], rtol=RTOL)
+        np.testing.assert_allclose(hits["eff"], ref["eff"], rtol=RTOL, atol=1e-9 * np.abs(ref["eff"]).max())
+    rng = np.random.Generator(np.random.PCG64(n + m + 1))
+    pick = rng.choice(len(hits), size=min(48, len(hits)), replace=False)
+    sample = np.stack([hits["snp_0"][pick], hits["snp_1"][pick]], axis=1).astype(np.int64)
+    eff, var = _oracle_pairs(host, n, sample, cu, cv, py.cpu().numpy(), pvp.cpu().numpy())
+    np.testing.assert_allclose(hits["eff"][pick], eff, rtol=RTOL, atol=1e-9 * np.abs(eff).max())
+    np.testing.assert_allclose(hits["var"][pick], var, rtol=RTOL)
+    assert np.all(eff * eff / var > chi_cut * (1 - 1e-7))
+
+
 def test_screen_full_c3_shape_subset_equals_oracle(eng):
     import torch
     from gmat_b200 import synth
