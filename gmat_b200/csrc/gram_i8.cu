@@ -1,0 +1,298 @@
+// GRM on the INT8 tensor cores (sm_100a: tcgen05.mma cta_group::2 kind::i8, TMEM, TMA).
+//
+// agmat / dgmat_as (gmat/gmatrix/gmatrix.py:53-66, 116-130): K = X X' / scale with X[k][s] = a_ks - o_s, a the
+// integer dosage (additive) or the heterozygote indicator (dominance), o_s = 2 p_s or 2 p_s q_s.  Expanding,
+//
+//     (X X')_kl = sum_s a_ks a_ls  -  c_k  -  c_l  +  d ,      c_k = sum_s o_s a_ks ,   d = sum_s o_s^2
+//
+// and the only n^2 m term, G G' with G = [a_ks], is a product of small integers: ONE exact int8 x int8 -> int32
+// GEMM (|sum| <= 4 m), no digit planes needed.  c (n x m FP64 multiply-adds) and d are cheap.  The FP64 DMMA
+// kernel (grm.cu) needs n(n+1)m FP64 flop at 34 TFLOP/s; this kernel does n(n+1)m/2 int8 MACs at > 1 PMAC/s.
+//
+// Layout: G is re-coded once per call from the 2-bit store into Gt[id][snp] int8 (K = SNP contiguous, what the
+// K-major UMMA operands need), zero padded to 256 ids.  Tiles of 256 x 256 ids (lower block triangle) x all SNPs;
+// work is cut stream-K style into equal contiguous ranges of (tile, 128-SNP slab) units per CTA pair, partial tiles
+// are added with integer atomics -- exact, hence reproducible whatever the order.
+#include "tc5.cuh"
+
+namespace gb {
+
+constexpr int GI_NS = 6;
+constexpr int GI_THREADS = 192;                                     // producer, issuer, 4 epilogue warps
+constexpr int GI_HALF = I8_TK / 2;
+constexpr int GI_STAGE_BYTES = I8_A_BYTES + GI_HALF * I8_SLAB;      // 32 KB per CTA: its 128 rows + half of the columns
+
+struct GramBars {
+    uint64_t full[GI_NS], empty[GI_NS], tfull[2], tempty[2];
+    uint32_t tmem_base;
+};
+
+struct GramParams {
+    int n, np, ms, n_slab, nt;
+    long long units;               // tiles * n_slab
+    int *S;                        // [np][np] int32, zero-initialised
+};
+
+__device__ __forceinline__ void gram_tile_of(int t, int &rt, int &ct) {
+    int r = (int)((sqrtf(8.0f * (float)t + 1.0f) - 1.0f) * 0.5f);
+    while ((r + 1) * (r + 2) / 2 <= t) ++r;
+    while (r * (r + 1) / 2 > t) --r;
+    rt = r; ct = t - r * (r + 1) / 2;
+}
+
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GI_THREADS, 1)
+i8_gram_pair_kernel(const __grid_constant__ CUtensorMap map_gt, const GramParams p) {
+    extern __shared__ unsigned char smem_raw[];
+    unsigned char *smem = reinterpret_cast<unsigned char *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                                           ~static_cast<uintptr_t>(1023));
+    GramBars *bars = reinterpret_cast<GramBars *>(smem + GI_NS * GI_STAGE_BYTES);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int rank = (int)cluster_ctarank();
+    const long long cluster_id = blockIdx.x >> 1, n_clusters = gridDim.x >> 1;
+    const long long u_begin = p.units * cluster_id / n_clusters, u_end = p.units * (cluster_id + 1) / n_clusters;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < GI_NS; ++s) { mbar_init(&bars->full[s], 1); mbar_init(&bars->empty[s], 1); }
+        for (int b = 0; b < 2; ++b) { mbar_init(&bars->tfull[b], 1); mbar_init(&bars->tempty[b], 8); }
+        mbar_fence_init();
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;\n" ::"r"(
+                         smem_u32(&bars->tmem_base)), "r"(512)
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;\n" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync_all();
+    tc_fence_after();
+    const uint32_t tmem_base = bars->tmem_base;
+
+    if (warp == 0) {
+        // ================================ TMA producer (both CTAs) ===============================
+        if (lane == 0) {
+            int stage = 0; unsigned phase = 0;
+            for (long long u = u_begin; u < u_end;) {
+                const int t = (int)(u / p.n_slab), l0 = (int)(u % p.n_slab);
+                const int cnt = (int)min((long long)(p.n_slab - l0), u_end - u);
+                int rt, ct;
+                gram_tile_of(t, rt, ct);
+                for (int l = l0; l < l0 + cnt; ++l) {
+                    mbar_wait(&bars->empty[stage], phase ^ 1u);
+                    if (rank == 0) mbar_expect_tx(&bars->full[stage], 2 * GI_STAGE_BYTES);
+                    unsigned char *sa = smem + stage * GI_STAGE_BYTES;
+                    tma_load_2d_pair(sa, &map_gt, l * I8_SLAB, rt * I8_TK + rank * I8_TJ, &bars->full[stage]);
+                    tma_load_2d_pair(sa + I8_A_BYTES, &map_gt, l * I8_SLAB, ct * I8_TK + rank * GI_HALF,
+                                     &bars->full[stage]);
+                    if (++stage == GI_NS) { stage = 0; phase ^= 1u; }
+                }
+                u += cnt;
+            }
+        }
+    } else if (warp == 1) {
+        // ================================ MMA issuer (leader CTA, one lane) ======================
+        if (lane == 0 && rank == 0) {
+            int stage = 0; unsigned phase = 0;
+            int abuf = 0; unsigned aphase = 0;
+            for (long long u = u_begin; u < u_end;) {
+                const int l0 = (int)(u % p.n_slab);
+                const int cnt = (int)min((long long)(p.n_slab - l0), u_end - u);
+                mbar_wait(&bars->tempty[abuf], aphase ^ 1u);
+                tc_fence_after();
+                const uint32_t tmem_d = tmem_base + (uint32_t)(abuf * I8_TK);
+                for (int l = 0; l < cnt; ++l) {
+                    mbar_wait(&bars->full[stage], phase);
+                    tc_fence_after();
+                    const uint32_t sa = smem_u32(smem + stage * GI_STAGE_BYTES);
+                    const uint64_t da = umma_desc_sw128(sa), db = umma_desc_sw128(sa + I8_A_BYTES);
+#pragma unroll
+                    for (int k = 0; k < I8_SLAB / 32; ++k)
+                        umma_i8_pair(tmem_d, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), I8P_IDESC,
+                                     (uint32_t)((l | k) != 0));
+                    tc_commit_pair(&bars->empty[stage]);
+                    if (++stage == GI_NS) { stage = 0; phase ^= 1u; }
+                }
+                tc_commit_pair(&bars->tfull[abuf]);
+                if (++abuf == 2) { abuf = 0; aphase ^= 1u; }
+                u += cnt;
+            }
+        }
+    } else {
+        // ================================ epilogue (both CTAs): TMEM -> S ========================
+        const int q = warp & 3;
+        int abuf = 0; unsigned aphase = 0;
+        for (long long u = u_begin; u < u_end;) {
+            const int t = (int)(u / p.n_slab), l0 = (int)(u % p.n_slab);
+            const int cnt = (int)min((long long)(p.n_slab - l0), u_end - u);
+            int rt, ct;
+            gram_tile_of(t, rt, ct);
+            const bool whole = cnt == p.n_slab;                       // the tile was not cut: plain stores
+            const int k = rt * I8_TK + rank * I8_TJ + q * 32 + lane;  // this lane's row of S
+            int *dst = p.S + (size_t)k * p.np + ct * I8_TK;
+            mbar_wait_warp(&bars->tfull[abuf], aphase);
+            tc_fence_after();
+            const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(abuf * I8_TK);
+#pragma unroll 1
+            for (int ch = 0; ch < I8_TK / 32; ++ch) {
+                int v[32];
+                tmem_ld32(taddr + ch * 32, v);
+                tmem_ld_wait();
+                if (k < p.n) {
+                    if (whole) {
+#pragma unroll
+                        for (int g = 0; g < 8; ++g)
+                            *reinterpret_cast<int4 *>(dst + ch * 32 + 4 * g) =
+                                make_int4(v[4 * g], v[4 * g + 1], v[4 * g + 2], v[4 * g + 3]);
+                    } else {
+#pragma unroll
+                        for (int c = 0; c < 32; ++c) atomicAdd(dst + ch * 32 + c, v[c]);
+                    }
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive_leader(&bars->tempty[abuf]);
+            if (++abuf == 2) { abuf = 0; aphase ^= 1u; }
+            u += cnt;
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync_all();
+    if (warp == 1) {
+        asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;\n" ::"r"(tmem_base), "r"(512) : "memory");
+    }
+}
+
+// 2-bit store [snp][id] -> Gt[id][snp - s0] int8 (zero outside [0,n) x [s0,s1)); tile = 64 SNPs x 256 ids
+__global__ void __launch_bounds__(256)
+i8_dosage_t_kernel(const unsigned char *__restrict__ bed, int n, long long row_bytes, long long s0, long long s1,
+                   unsigned table, signed char *__restrict__ gt, long long mld) {
+    __shared__ __align__(16) unsigned char tile[256][80];
+    const long long sblk = (long long)blockIdx.x * 64;
+    const int k0 = blockIdx.y * 256;
+    {
+        const int sl = threadIdx.x >> 2, chunk = threadIdx.x & 3;         // SNP in the tile, 64-id chunk
+        const long long snp = s0 + sblk + sl;
+        uint4 w = make_uint4(0u, 0u, 0u, 0u);
+        const long long off = (long long)(k0 / 4) + chunk * 16;
+        if (snp < s1 && off + 16 <= row_bytes) w = *reinterpret_cast<const uint4 *>(bed + snp * row_bytes + off);
+        const unsigned ww[4] = {w.x, w.y, w.z, w.w};
+#pragma unroll
+        for (int e = 0; e < 64; ++e) {
+            const unsigned code = (ww[e >> 4] >> (2 * (e & 15))) & 3u;
+            const int k = k0 + chunk * 64 + e;
+            tile[chunk * 64 + e][sl] = (k < n && snp < s1) ? (unsigned char)((table >> (8 * code)) & 0xffu) : 0;
+        }
+    }
+    __syncthreads();
+    signed char *dst = gt + (size_t)(k0 + threadIdx.x) * mld + sblk;
+#pragma unroll
+    for (int g = 0; g < 4; ++g)
+        if (sblk + 16 * g < mld)
+            *reinterpret_cast<uint4 *>(dst + 16 * g) = *reinterpret_cast<const uint4 *>(&tile[threadIdx.x][16 * g]);
+}
+
+// c[k] = sum_s o_s a_ks (block k < n), d = sum_s o_s^2 (block n); fixed summation order
+__global__ void __launch_bounds__(256)
+i8_rowdot_kernel(const signed char *__restrict__ gt, long long mld, const double *__restrict__ lut, long long s0,
+                 long long ms, int n, double *__restrict__ c_out) {
+    __shared__ double red[8];
+    const int k = blockIdx.x;
+    double acc = 0.0;
+    if (k < n) {
+        const signed char *row = gt + (size_t)k * mld;
+        for (long long s = threadIdx.x; s < ms; s += 256) acc += (double)row[s] * -lut[(s0 + s) * 4];
+    } else {
+        for (long long s = threadIdx.x; s < ms; s += 256) { const double o = lut[(s0 + s) * 4]; acc += o * o; }
+    }
+#pragma unroll
+    for (int d = 16; d >= 1; d >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, d);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double t = 0.0;
+        for (int w = 0; w < 8; ++w) t += red[w];
+        c_out[k] = t;
+    }
+}
+
+__global__ void i8_gram_finish_kernel(const int *__restrict__ S, int np, const double *__restrict__ c, int n,
+                                      double scale, double small_val, int accumulate, double *__restrict__ K) {
+    const long long total = (long long)n * n;
+    const double d = c[n];
+    for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
+         idx += (long long)gridDim.x * blockDim.x) {
+        const int k = (int)(idx / n), l = (int)(idx % n);
+        const int hi = k > l ? k : l, lo = k > l ? l : k;
+        double v = ((double)S[(size_t)hi * np + lo] - c[k]) - c[l] + d;
+        if (accumulate) {
+            K[idx] += v;
+        } else {
+            v /= scale;
+            if (k == l) v += v * small_val;
+            K[idx] = v;
+        }
+    }
+}
+
+}  // namespace gb
+
+using namespace gb;
+
+extern "C" int gmat_b200_grm_i8(const unsigned char *bed_dev, long long n, long long m, long long row_bytes,
+                                const double *lut_dev, int coding, long long snp_begin, long long snp_end,
+                                double scale, double small_val, int accumulate, double *K_dev, void *stream) {
+    GB_CHECK_ARG(bed_dev && lut_dev && K_dev, "null buffer");
+    GB_CHECK_ARG(n > 0 && m > 0 && row_bytes % 16 == 0 && row_bytes * 4 >= n, "shape");
+    GB_CHECK_ARG(snp_begin >= 0 && snp_begin <= snp_end && snp_end <= m, "snp range");
+    GB_CHECK_ARG(coding == GMAT_B200_CODING_ADD || coding == GMAT_B200_CODING_DOM, "coding");
+    GB_CHECK_ARG(accumulate || scale != 0.0, "scale");
+    GB_CHECK_ARG(snp_end - snp_begin < (1LL << 28) && n < (1 << 20), "shape too large for int32 sums / tensor maps");
+    cudaStream_t st = (cudaStream_t)stream;
+    const long long ms = snp_end - snp_begin;
+    const int np = (int)round_up(n, I8_TK);
+    const long long mld = round_up(ms > 0 ? ms : 1, 128);
+    keep_scratch_pool();
+    signed char *gt = nullptr; int *S = nullptr; double *c = nullptr;
+    GB_CUDA(cudaMallocAsync((void **)&gt, (size_t)np * mld, st));
+    GB_CUDA(cudaMallocAsync((void **)&S, (size_t)np * np * sizeof(int), st));
+    GB_CUDA(cudaMallocAsync((void **)&c, (size_t)(n + 1) * sizeof(double), st));
+    GB_CUDA(cudaMemsetAsync(S, 0, (size_t)np * np * sizeof(int), st));
+    int rc = GMAT_B200_OK;
+    if (ms > 0) {
+        const unsigned table = coding == GMAT_B200_CODING_DOM ? 0x00010000u : 0x02010000u;
+        dim3 tg((unsigned)((mld + 63) / 64), (unsigned)(np / 256));
+        i8_dosage_t_kernel<<<tg, 256, 0, st>>>(bed_dev, (int)n, row_bytes, snp_begin, snp_end, table, gt, mld);
+        count_launch();
+        GramParams p;
+        p.n = (int)n; p.np = np; p.ms = (int)ms; p.n_slab = (int)((ms + I8_SLAB - 1) / I8_SLAB); p.nt = np / I8_TK;
+        p.units = (long long)p.nt * (p.nt + 1) / 2 * p.n_slab; p.S = S;
+        CUtensorMap map_gt;
+        rc = make_map(&map_gt, gt, ms, np, mld, I8_TJ);
+        if (rc == GMAT_B200_OK) {
+            const int smem_bytes = GI_NS * GI_STAGE_BYTES + 1024 + (int)sizeof(GramBars);
+            cudaError_t e = cudaFuncSetAttribute(i8_gram_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                 smem_bytes);
+            if (e != cudaSuccess) { set_error("cudaFuncSetAttribute: %s", cudaGetErrorString(e)); rc = GMAT_B200_ERR_CUDA; }
+            else {
+                long long pairs = sm_count() / 2;
+                if (pairs > p.units) pairs = p.units;
+                i8_gram_pair_kernel<<<(unsigned)(2 * pairs), GI_THREADS, smem_bytes, st>>>(map_gt, p);
+                count_launch();
+            }
+        }
+    }
+    if (rc == GMAT_B200_OK) {
+        i8_rowdot_kernel<<<(unsigned)(n + 1), 256, 0, st>>>(gt, mld, lut_dev, snp_begin, ms, (int)n, c);
+        count_launch();
+        i8_gram_finish_kernel<<<sm_count() * 8, 256, 0, st>>>(S, np, c, (int)n, scale, small_val, accumulate, K_dev);
+        count_launch();
+        cudaError_t e = cudaGetLastError();
+        if (e != cudaSuccess) { set_error("kernel launch failed: %s", cudaGetErrorString(e)); rc = GMAT_B200_ERR_CUDA; }
+    }
+    cudaFreeAsync(gt, st);
+    cudaFreeAsync(S, st);
+    cudaFreeAsync(c, st);
+    return rc;
+}

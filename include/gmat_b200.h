@@ -210,6 +210,16 @@ int gmat_b200_i8_scan(const signed char *g8_dev, long long n, long long m, const
 /* int8 tensor-core issue-rate microbenchmark (tcgen05.mma kind::i8 128x256x32 on resident tiles, all SMs): TOPS  */
 int gmat_b200_i8_peak(int iters, double *tops);
 
+/* The same GRM on the INT8 tensor cores (gmat_b200/csrc/gram_i8.cu): X X' = G G' - c 1' - 1 c' + d with G the
+ * integer dosage / heterozygote indicator matrix, so the n^2 m term is ONE exact int8 x int8 -> int32 GEMM
+ * (tcgen05.mma cta_group::2 kind::i8); c_k = sum_s o_s a_ks and d = sum_s o_s^2 in FP64.  Same arguments and
+ * semantics as gmat_b200_grm plus the coding (GMAT_B200_CODING_ADD / _DOM) the LUT was built for; the SNP range
+ * must not contain a missing genotype (callers use gmat_b200_grm then).  Scratch (n x m bytes + 4 n^2 bytes)
+ * comes from the stream-ordered pool.                                                                          */
+int gmat_b200_grm_i8(const unsigned char *bed_dev, long long n, long long m, long long row_bytes,
+                     const double *lut_dev, int coding, long long snp_begin, long long snp_end,
+                     double scale, double small_val, int accumulate, double *K_dev, void *stream);
+
 /* Host text writer, byte-identical to np.savetxt(path, mat) as used by output_mat (gmat/gmatrix/gmatrix.py:10-14:
  * '%.18e', ' ' delimiter, '\n'): rows formatted in parallel by `threads` host threads (<= 0: all).  No GPU work. */
 int gmat_b200_savetxt_host(const char *path, const double *mat /* HOST [rows][cols] */, long long rows,
