@@ -225,7 +225,7 @@ __global__ void i8_gram_finish_kernel(const int *__restrict__ S, int np, const d
          idx += (long long)gridDim.x * blockDim.x) {
         const int k = (int)(idx / n), l = (int)(idx % n);
         const int hi = k > l ? k : l, lo = k > l ? l : k;
-        double v = ((double)S[(size_t)hi * np + lo] - c[k]) - c[l] + d;
+        double v = ((double)S[(size_t)hi * np + lo] - c[hi]) - c[lo] + d;     // same expression for (k,l) and (l,k)
         if (accumulate) {
             K[idx] += v;
         } else {

@@ -259,9 +259,12 @@ def test_exact_scan_hit_buffer_overflow_retry(eng, tmp_path):
 
 
 # ------------------------------------------------------------------------------------------ GRM
-@pytest.mark.parametrize("n,m", [(131, 300), (128, 16), (260, 1000), (5, 3)])
-def test_grm_vs_oracle_synthetic(eng, tmp_path, n, m):
+@pytest.mark.parametrize("which", ["i8", "f64"])
+@pytest.mark.parametrize("n,m", [(131, 300), (128, 16), (260, 1000), (5, 3), (513, 130)])
+def test_grm_vs_oracle_synthetic(eng, tmp_path, monkeypatch, n, m, which):
+    """Both GRM kernels (int8 tensor cores: gram_i8.cu; FP64 DMMA: grm.cu) against the numpy oracle."""
     from gmat_b200.gmatrix.gmatrix import grm_device
+    monkeypatch.setenv("GMAT_B200_GRM_ENGINE", which)
     prefix, _ = _dataset(tmp_path, n, m, seed=n + 3 * m)
     store = eng.GenotypeStore(prefix)
     for coding, fn in ((eng.ADD, oracle.agmat), (eng.DOM, oracle.dgmat_as)):
@@ -281,10 +284,13 @@ def test_grm_vs_oracle_synthetic(eng, tmp_path, n, m):
     assert np.abs(acc.cpu().numpy() / scale - want).max() <= RTOL * np.abs(want).max()
 
 
-def test_grm_streamk_many_tiles_reproducible(eng, tmp_path):
+@pytest.mark.parametrize("which", ["i8", "f64"])
+def test_grm_streamk_many_tiles_reproducible(eng, tmp_path, monkeypatch, which):
     """n large enough for more tiles than SMs (the equal-range stream-K split with atomically added partial tiles):
-    parity with the oracle and bit-identical results run to run (a tile never has more than two parts)."""
+    parity with the oracle and bit-identical results run to run (FP64: a tile never has more than two parts;
+    int8: the partial sums are integers)."""
     from gmat_b200.gmatrix.gmatrix import grm_device
+    monkeypatch.setenv("GMAT_B200_GRM_ENGINE", which)
     n, m = 2300, 200                      # 18 blocks -> 171 tiles > 148 SMs; 4 stages of 64 SNPs (last one ragged)
     prefix, _ = _dataset(tmp_path, n, m, seed=99)
     store = eng.GenotypeStore(prefix)
@@ -297,6 +303,26 @@ def test_grm_streamk_many_tiles_reproducible(eng, tmp_path):
     for _ in range(3):
         again, _ = grm_device(store, eng.ADD)
         assert np.array_equal(again.cpu().numpy(), got)
+
+
+def test_grm_engine_selection_and_missing_calls(eng, tmp_path, monkeypatch):
+    """auto = int8 kernel for SNP ranges without a missing call, DMMA kernel otherwise (same result as forcing f64);
+    forcing i8 on data with missing calls is refused."""
+    from gmat_b200.gmatrix.gmatrix import grm_device
+    prefix, _ = _dataset(tmp_path, 90, 150, seed=4, missing=0.02)
+    store = eng.GenotypeStore(prefix)
+    monkeypatch.delenv("GMAT_B200_GRM_ENGINE", raising=False)
+    assert eng.grm_engine(store) == "f64"
+    clean = [s for s in range(150) if int(store.counts[s, 1]) == 0]
+    if clean:
+        assert eng.grm_engine(store, clean[0], clean[0] + 1) == "i8"
+    a, _ = grm_device(store, eng.ADD)
+    monkeypatch.setenv("GMAT_B200_GRM_ENGINE", "f64")
+    b, _ = grm_device(store, eng.ADD)
+    assert np.array_equal(a.cpu().numpy(), b.cpu().numpy(), equal_nan=True)
+    monkeypatch.setenv("GMAT_B200_GRM_ENGINE", "i8")
+    with pytest.raises(ValueError):
+        grm_device(store, eng.ADD)
 
 
 def test_screen_chunked_operand_scratch(eng, tmp_path, monkeypatch):
