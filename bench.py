@@ -60,13 +60,18 @@ def var_com_for(pheno):
     return [float(v * np.var(yv)) for v in VAR_PROP]
 
 
-def i8_ops_per_pair(n, planes):
+def i8_ops_per_pair(n, planes, variant=3):
     """int8 tensor-core ops (2 per MAC) per pair: (algorithmic, issued).  Algorithmic = the lower triangle of the
     symmetric B_i once per digit plane, planes * n(n+1); issued = what the kernel's tiling launches: per plane and per
-    256-row tile kt the id slabs 0..min(2kt+2, ceil(n/128))-1, each 256 x 128 MACs per pair."""
+    256-row tile kt the id slabs 0..min(2kt+2, ceil(n/128))-1, each N x 128 MACs per pair with N = 256 plane rows,
+    or (variant 3, ozaki.cu::i8p_shape) N = the tile's rows below n rounded up to 16, minus 128 for slab 2kt+1."""
     n_kt, n_slab = (n + 255) // 256, (n + 127) // 128
-    slabs = sum(min(2 * kt + 2, n_slab) for kt in range(n_kt))
-    return planes * float(n) * (n + 1), planes * slabs * 256.0 * 128.0 * 2.0
+    macs = 0.0
+    for kt in range(n_kt):
+        rows = 256 if variant != 3 else min(256, (n - 256 * kt + 15) // 16 * 16)
+        for l in range(min(2 * kt + 2, n_slab)):
+            macs += (rows - 128 if variant == 3 and l == 2 * kt + 1 else rows) * 128.0
+    return planes * float(n) * (n + 1), planes * macs * 2.0
 
 
 def f_exact(n):
@@ -365,7 +370,7 @@ def run_gpu(args):
         }
         if i8 is not None:
             planes = i8.n_planes
-            alg, iss = i8_ops_per_pair(n, planes)
+            alg, iss = i8_ops_per_pair(n, planes, i8.wide)
             launches_per_step = kern_n / float(args.steps)
             pairs_per_launch = pairs_rank / launches_per_step
             achieved = pairs_per_launch * alg / (kern_ms * 1e-3) / 1e12
@@ -382,7 +387,7 @@ def run_gpu(args):
             line["dtype"] = "f64 results; n^2 term as exact int8 x int8 -> int32 tensor-core products of an error-free %d-plane split (%d bits), rest f64" % (planes, 7 * planes)
             line["roofline"] = {
                 "bound": "tensor", "achieved": achieved, "unit": "TOP/s", "peak": peak, "frac": achieved / peak,
-                "traffic": I8_TRAFFIC_BYTES, "kernel": {0: "i8_scan_kernel (tcgen05.mma cta_group::1 kind::i8, 128x256x32)", 2: "i8_scan_pair_kernel (tcgen05.mma cta_group::2 kind::i8, 256x256x32 per CTA pair)"}[i8.wide],
+                "traffic": I8_TRAFFIC_BYTES, "kernel": {0: "i8_scan_kernel (tcgen05.mma cta_group::1 kind::i8, 128x256x32)", 2: "i8_scan_pair_kernel (tcgen05.mma cta_group::2 kind::i8, 256x256x32 per CTA pair)", 3: "i8_scan_pair_kernel (tcgen05.mma cta_group::2 kind::i8, 256xNx32 per CTA pair, N = the plane rows that can be non-zero)"}[i8.wide],
                 "kernel_ms_per_launch": kern_ms, "kernel_launches_per_step": launches_per_step,
                 "kernel_share_of_step": kern_ms * launches_per_step / ms_local,
                 "ops_per_pair_algorithmic": alg, "ops_per_pair_issued": iss, "issued_tops": issued,
@@ -516,11 +521,28 @@ def extras(engine, torch, synth, store, model, lut, args, prefix, pymat, e2e_f64
         st2 = engine.GenotypeStore.from_device_payload(payload, n2)
         st2.lut(engine.ADD)
         kin = torch.empty((n2, n2), dtype=torch.float64, device=store.device)
-        t = timed(lambda: engine.grm(st2, engine.ADD, 1.0, 0.001, out=kin), reps=2)
-        out["agmat"] = {"tflops_full_gemm_convention_2n2m": 2.0 * n2 * n2 * m2 / t / 1e12,
+        # the engine agmat() selects for this data (no missing calls -> the int8 tensor-core GEMM G G' with FP64
+        # rank-one corrections, gram_i8.cu), then the FP64 DMMA kernel (grm.cu) north_star names, same output buffer
+        which = engine.grm_engine(st2)
+        t = timed(lambda: engine.grm(st2, engine.ADD, 1.0, 0.001, out=kin, which=which), reps=2)
+        out["agmat"] = {"engine": which,
+                        "tflops_full_gemm_convention_2n2m": 2.0 * n2 * n2 * m2 / t / 1e12,
                         "tflops_algorithmic_n(n+1)m": float(n2) * (n2 + 1) * m2 / t / 1e12,
-                        "seconds": t, "workload": "agmat GRM kernel, synthetic n=%d x m=%d generated in HBM "
+                        "seconds": t, "workload": "agmat GRM, synthetic n=%d x m=%d generated in HBM "
                                                   "(BASELINE configs[1])" % (n2, m2)}
+        if which == "i8":
+            i8_peak = engine.i8_peak(20000)
+            out["agmat"]["roofline"] = {
+                "bound": "tensor", "unit": "TOP/s", "achieved": float(n2) * (n2 + 1) * m2 / t / 1e12,
+                "peak": i8_peak, "frac": float(n2) * (n2 + 1) * m2 / t / 1e12 / i8_peak,
+                "note": "n(n+1)m int8 ops (lower triangle of G G', 2 ops per MAC) / the whole call (2-bit -> int8 "
+                        "transpose, i8_gram_pair_kernel, FP64 corrections); peak = int8 MMA issue rate measured live"}
+            t64 = timed(lambda: engine.grm(st2, engine.ADD, 1.0, 0.001, out=kin, which="f64"), reps=1)
+            out["agmat"]["f64_engine"] = {"seconds": t64,
+                                          "tflops_algorithmic_n(n+1)m": float(n2) * (n2 + 1) * m2 / t64 / 1e12,
+                                          "fp64_peak_tflops": peak,
+                                          "frac": float(n2) * (n2 + 1) * m2 / t64 / 1e12 / peak,
+                                          "kernel": "grm_kernel (FP64 DMMA, 2-bit codes staged by TMA)"}
         if args.agmat_e2e:
             # the public call on files: agmat(bed_file) = .bed/.bim/.fam read + H2D + counts + GRM kernel + D2H +
             # the 2.5 GB '%.18e' text file the reference format demands (written by all host threads)

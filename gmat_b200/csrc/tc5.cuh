@@ -70,6 +70,10 @@ __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.
 
 constexpr uint32_t I8P_IDESC = (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(I8_TK >> 3) << 17) |
                                ((uint32_t)((2 * I8_TJ) >> 4) << 24);
+// the same with N = nn plane rows (a multiple of 16 in [16, 256] for M = 256)
+__device__ __forceinline__ uint32_t i8p_idesc(int nn) {
+    return (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(nn >> 3) << 17) | ((uint32_t)((2 * I8_TJ) >> 4) << 24);
+}
 constexpr uint32_t I8P_PEER_MASK = 0xFEFFFFFFu;                   // shared::cluster address of the same offset in CTA 0
 
 __device__ __forceinline__ uint32_t cluster_ctarank() {

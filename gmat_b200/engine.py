@@ -253,10 +253,11 @@ class I8Exact(object):
         self.planes = [torch.zeros((self.batch * per_first,), dtype=torch.int8, device=dev) for _ in range(2)]
         self._prep_stream = torch.cuda.Stream(device=dev)
         self._shifts = torch.tensor([0, 2, 4, 6], dtype=torch.uint8, device=dev)
-        # kernel variant: 2 = CTA pair (tcgen05 cta_group::2, default), 0 = one CTA per 128-SNP tile (cta_group::1)
-        self.wide = int(os.environ.get("GMAT_B200_I8_VARIANT", "2"))
-        if self.wide not in (0, 2):
-            raise ValueError("GMAT_B200_I8_VARIANT must be 0 or 2")
+        # kernel variant: 3 = CTA pair (tcgen05 cta_group::2) issuing only the plane rows that can be non-zero
+        # (default), 2 = CTA pair with full 256-row MMAs, 0 = one CTA per 128-SNP tile (cta_group::1)
+        self.wide = int(os.environ.get("GMAT_B200_I8_VARIANT", "3"))
+        if self.wide not in (0, 2, 3):
+            raise ValueError("GMAT_B200_I8_VARIANT must be 0, 2 or 3")
         self.kernel_events = None      # bench.py: list of (start, end) CUDA events around every i8_scan launch
 
     def _coded_first(self, il):

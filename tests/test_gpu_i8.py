@@ -238,3 +238,42 @@ def test_i8_missing_calls_are_nan_like_the_reference(eng, tmp_path, kind):
     ok = ~np.isnan(v)
     np.testing.assert_allclose(mine["var"][ok], v[ok], rtol=RTOL)
     np.testing.assert_allclose(mine["eff"][ok], e[ok], rtol=RTOL, atol=1e-11)
+
+
+@pytest.mark.parametrize("n,m", [(257, 300), (400, 270), (520, 130), (900, 515), (1100, 64)])
+def test_i8_kernel_variants_are_bit_identical(eng, tmp_path, n, m):
+    """The CTA-pair kernel that issues only the plane rows that can be non-zero (variant 3, the default: last row
+    tile trimmed to n, zero block right of the diagonal skipped) must give the SAME BITS as the full-tile CTA-pair
+    kernel (2) and the single-CTA kernel (0): the integer sums are exact, the FP64 finish is the same expression.
+    Shapes put n just past a 256-row tile (N = 16), past the half tile (half-slab N = 16) and in between."""
+    import torch
+    prefix, _ = _dataset(tmp_path, n, m, seed=n + m)
+    pymat, pvp = _random_model(n, n * 3 + m)
+    store = eng.GenotypeStore(prefix)
+    lu = store.lut(eng.ADD)
+    pyd = torch.as_tensor(pymat.ravel().copy()).cuda()
+    pvd = torch.as_tensor(pvp).cuda().contiguous()
+    first = np.arange(0, m - 1, 2)
+    res = {}
+    for variant in (3, 2, 0):
+        sc = eng.I8Exact(store, lu, lu, eng.ADD, pyd, pvd)
+        sc.wide = variant
+        h, q = sc.scan(first, eng.PAIRS_UPPER, -1.0, q_debug=True)
+        key = h["snp_0"].astype(np.int64) * m + h["snp_1"]
+        res[variant] = (h[np.argsort(key)], q.cpu().numpy())
+    for variant in (2, 0):
+        assert np.array_equal(res[3][0]["snp_0"], res[variant][0]["snp_0"])
+        assert np.array_equal(res[3][0]["snp_1"], res[variant][0]["snp_1"])
+        assert np.array_equal(res[3][0]["var"], res[variant][0]["var"]), "variant %d: var differs" % variant
+        assert np.array_equal(res[3][0]["eff"], res[variant][0]["eff"])
+    # a_j' B_i a_j itself (only the entries of scanned pairs j > i are written by every variant)
+    q3, q2 = res[3][1], res[2][1]
+    for r, i in enumerate(first):
+        assert np.array_equal(q3[r, i + 1:], q2[r, i + 1:])
+    # and against the oracle, like every other engine test
+    U, V = oracle.coded_pair("AA", oracle.read_plink(prefix))
+    h = res[3][0]
+    pairs = np.stack([h["snp_0"], h["snp_1"]], axis=1)
+    eff, var, _, _ = oracle.exact_pairs(U, V, pairs, pymat, pvp)
+    np.testing.assert_allclose(h["eff"], eff, rtol=RTOL, atol=1e-11)
+    np.testing.assert_allclose(h["var"], var, rtol=RTOL, atol=1e-13 * np.abs(var).max())
