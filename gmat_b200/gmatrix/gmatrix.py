@@ -22,17 +22,33 @@ def output_mat(mat, id, out_file, out_fmt):
         mat = np.ascontiguousarray(mat, dtype=np.float64)
         check(lib.gmat_b200_savetxt_host((out_file + '0').encode(), ffi.cast("double *", mat.ctypes.data),
                                          mat.shape[0], mat.shape[1], 0), "gmat_b200_savetxt_host")
-    elif out_fmt == 'row_col_val':
-        ind = np.tril_indices_from(mat)
-        df = pd.DataFrame({"row": ind[0] + 1, "col": ind[1] + 1, "val": mat[ind]})
-        df.to_csv(out_file + '1', sep=' ', index=False, header=False, columns=["row", "col", "val"])
-    elif out_fmt == 'id_id_val':
-        ind = np.tril_indices_from(mat)
-        df = pd.DataFrame({"id0": id[ind[0]], "id1": id[ind[1]], "val": mat[ind]})
-        df.to_csv(out_file + '2', sep=' ', index=False, header=False, columns=["id0", "id1", "val"])
+    elif out_fmt in ('row_col_val', 'id_id_val'):
+        # gmatrix.py:15-29: pandas to_csv of the lower triangle (np.tril_indices order).  Same bytes, written by
+        # all host threads (gmat_b200_write_tril_host: repr(float) values, labels as pandas prints them).
+        mat = np.ascontiguousarray(mat, dtype=np.float64)
+        if out_fmt == 'row_col_val':
+            ids, off, path = ffi.NULL, ffi.NULL, out_file + '1'
+        else:
+            labels = _csv_labels(id)
+            blob = "".join(labels).encode()
+            lens = np.array([len(x.encode()) for x in labels], dtype=np.int64)
+            offs = np.concatenate([[0], np.cumsum(lens)]).astype(np.int64)
+            ids, off, path = ffi.from_buffer(blob), ffi.cast("long long *", offs.ctypes.data), out_file + '2'
+        check(lib.gmat_b200_write_tril_host(path.encode(), ffi.cast("double *", mat.ctypes.data), mat.shape[0],
+                                            ids, off, 0), "gmat_b200_write_tril_host")
     else:
         return 0
     return 1
+
+
+def _csv_labels(id):
+    """The n individual labels exactly as ``DataFrame.to_csv(sep=' ')`` prints them (ints, floats, strings, quoting
+    of labels that hold the separator): pandas itself formats the n labels once, the n(n+1)/2 lines reuse them."""
+    text = pd.DataFrame({"id": np.asarray(id)}).to_csv(sep=' ', index=False, header=False)
+    labels = text.split("\n")[:-1]
+    if len(labels) != len(id):                                   # a label with an embedded newline: not a .fam id
+        raise ValueError("individual ids must not contain line breaks")
+    return labels
 
 
 def _read_ids(bed_file):

@@ -226,6 +226,17 @@ int gmat_b200_grm_i8(const unsigned char *bed_dev, long long n, long long m, lon
  * '%.18e', ' ' delimiter, '\n'): rows formatted in parallel by `threads` host threads (<= 0: all).  No GPU work. */
 int gmat_b200_savetxt_host(const char *path, const double *mat /* HOST [rows][cols] */, long long rows,
                            long long cols, int threads);
+/* The two list formats of output_mat (gmat/gmatrix/gmatrix.py:15-29: pandas to_csv of the lower triangle in
+ * np.tril_indices order, sep ' ', no header): "<row> <col> <val>" with 1-based indices when ids == NULL
+ * ('row_col_val'), "<id_r> <id_c> <val>" otherwise ('id_id_val'; ids = the n labels as pandas prints them,
+ * concatenated, label k = ids[id_off[k] .. id_off[k+1])).  <val> is repr(float) -- shortest round-trip digits in
+ * CPython's layout, NaN as the empty string -- so the files are byte-identical to the reference's; rows are
+ * formatted in parallel by `threads` host threads (<= 0: all).  No GPU work.                                   */
+int gmat_b200_write_tril_host(const char *path, const double *mat /* HOST [n][n] */, long long n,
+                              const char *ids, const long long *id_off, int threads);
+/* repr(float) of one value into out32 (NUL-terminated, <= 32 bytes): the formatter of the list writer, exported so
+ * that it can be pinned against CPython on its own.                                                            */
+int gmat_b200_repr_host(double v, char *out32);
 
 #ifdef __cplusplus
 }

@@ -207,6 +207,50 @@ def test_savetxt_host_is_byte_identical_to_numpy(tmp_path):
     assert lib.gmat_b200_savetxt_host(str(tmp_path / "no" / "dir.txt").encode(), ffi.NULL, 0, 0, 1) == -2
 
 
+def _reference_output_mat(mat, id, out_file, out_fmt):
+    """The two list branches of the reference's output_mat, restated verbatim in behaviour (gmatrix.py:15-29)."""
+    import pandas as pd
+    ind = np.tril_indices_from(mat)
+    if out_fmt == 'row_col_val':
+        df = pd.DataFrame({"row": ind[0] + 1, "col": ind[1] + 1, "val": mat[ind]})
+        df.to_csv(out_file + '1', sep=' ', index=False, header=False, columns=["row", "col", "val"])
+    else:
+        df = pd.DataFrame({"id0": id[ind[0]], "id1": id[ind[1]], "val": mat[ind]})
+        df.to_csv(out_file + '2', sep=' ', index=False, header=False, columns=["id0", "id1", "val"])
+
+
+def test_list_format_writers_are_byte_identical_to_pandas(tmp_path):
+    """output_mat(..., 'row_col_val' / 'id_id_val') == the reference's pandas to_csv of the lower triangle
+    (gmatrix.py:15-29): repr(float) values incl. exponent forms, integers, zeros, NaN as the empty string; integer,
+    string and float individual ids; one thread and all threads; no GPU."""
+    from gmat_b200._ffi import ffi, lib
+    from gmat_b200.gmatrix.gmatrix import output_mat
+    rng = np.random.Generator(np.random.PCG64(8))
+    n = 483                                                    # 116,886 lines: more than one chunk per thread
+    mat = rng.normal(size=(n, n)) * 10.0 ** rng.integers(-12, 20, size=(n, n))
+    mat[0, 0], mat[1, 0], mat[1, 1], mat[2, 0], mat[2, 1] = 0.0, -0.0, 1.0, 1e16, 1e-5
+    mat[3, 0], mat[3, 1], mat[3, 2] = np.nan, np.inf, 123456.0
+    id_sets = [np.arange(1000, 1000 + n), np.array(["id%d_x" % k for k in range(n)], dtype=object),
+               np.arange(n) + 0.5]
+    for k, ids in enumerate(id_sets):
+        a, b = str(tmp_path / ("ref%d" % k)), str(tmp_path / ("got%d" % k))
+        for fmt, ext in (("row_col_val", "1"), ("id_id_val", "2")):
+            _reference_output_mat(mat, ids, a, fmt)
+            assert output_mat(mat, ids, b, fmt) == 1
+            assert open(a + ext, "rb").read() == open(b + ext, "rb").read(), (k, fmt)
+    small = np.ascontiguousarray(mat[:5, :5])
+    p1 = str(tmp_path / "t1")
+    assert lib.gmat_b200_write_tril_host(p1.encode(), ffi.cast("double *", small.ctypes.data), 5, ffi.NULL, ffi.NULL,
+                                         1) == 1
+    _reference_output_mat(small, None, str(tmp_path / "t1ref"), "row_col_val")
+    assert open(p1, "rb").read() == open(str(tmp_path / "t1ref") + "1", "rb").read()
+    assert lib.gmat_b200_write_tril_host(str(tmp_path / "no" / "dir").encode(), ffi.NULL, 0, ffi.NULL, ffi.NULL, 1) == -2
+    buf = ffi.new("char[40]")
+    for v in [0.1, 1e-4, 9.9e-5, 1e15, 1e16, 2.0 ** 53, 5e-324, 1.7976931348623157e308, -1 / 3, 1e22, 1e23]:
+        lib.gmat_b200_repr_host(v, buf)
+        assert ffi.string(buf).decode() == repr(v)
+
+
 def test_annotation_snp_pos_matches_reference(tmp_path):
     """annotation_snp_pos (README step 4, gmat/remma/annotation.py:22-74) against files written by the unmodified
     reference (fixtures made in the build container: p_cut filter, distance filter, LD filter)."""
