@@ -24,21 +24,20 @@ def read_plink(bed_file):
     return out
 
 
+GENOTYPES = [0.0, 1.0, 2.0]
+
+
 def impute_geno(snp_mat):
-    """Random imputation by observed genotype frequency, column by column, with the global numpy RNG
-    (restated from process_plink.py:12-25 -- same column order, same draws for the same RNG state)."""
-    ind_na = np.where(np.isnan(snp_mat))
-    col_na = set(ind_na[1])
-    for i in col_na:
-        snpi = snp_mat[:, i]
-        code0 = np.sum(np.absolute(snpi - 0.0) < 1e-10)
-        code1 = np.sum(np.absolute(snpi - 1.0) < 1e-10)
-        code2 = np.sum(np.absolute(snpi - 2.0) < 1e-10)
-        code_count = code0 + code1 + code2
-        p_lst = [code0 / code_count, code1 / code_count, code2 / code_count]
-        icol_na = np.where(np.isnan(snpi))
-        snpi[icol_na] = np.random.choice([0.0, 1.0, 2.0], len(icol_na[0]), p=p_lst)
-        snp_mat[:, i] = snpi
+    """Random imputation by observed genotype frequency, in place (reference: process_plink.py:12-25).  Reproduces
+    the reference's draws for the same state of the global numpy RNG: columns are visited in the iteration order
+    of ``set(column indices of the NaNs)`` (row-major NaN order, as ``np.where`` lists them), and each column makes
+    ONE ``np.random.choice`` call for all of its holes with p = the observed frequencies of 0 / 1 / 2."""
+    holes = np.isnan(snp_mat)
+    for col in set(np.nonzero(holes)[1]):
+        gap = holes[:, col]
+        seen = snp_mat[~gap, col]
+        tally = np.array([np.count_nonzero(np.abs(seen - g) < 1e-10) for g in GENOTYPES])
+        snp_mat[gap, col] = np.random.choice(GENOTYPES, int(gap.sum()), p=tally / tally.sum())
     return snp_mat
 
 

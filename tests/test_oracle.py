@@ -119,3 +119,18 @@ def test_reml_restatement_matches_reference(golden, mouse_model):
     vc = oracle.wemai_multi_gmat(M["y"], M["xmat"], M["zmat"], M["gl_aa"])
     np.testing.assert_allclose(vc, golden["var_com_ag_agag"], rtol=1e-7)
     assert [round(float(v), 8) for v in vc] == [0.06289206, 0.07641075, 0.08121168]
+
+
+def test_impute_geno_reproduces_the_reference_draws():
+    """gmat_b200's impute_geno against the unmodified reference's (fixture by oracle/make_golden_impute.py): same
+    imputed matrix under the same state of the global numpy RNG, and the same RNG state afterwards."""
+    import json
+    from gmat_b200.process_plink.process_plink import impute_geno
+    g = json.load(open(os.path.join(GOLD, "impute_geno.json")))
+    src = np.array(g["input"], dtype=np.float64)
+    src[src < 0] = np.nan
+    np.random.seed(g["seed"])
+    out = impute_geno(src.copy())
+    assert not np.isnan(out).any()
+    assert np.array_equal(out, np.array(g["output"], dtype=np.float64))
+    assert float(np.random.random()) == g["next_random"]
