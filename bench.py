@@ -64,13 +64,13 @@ def i8_ops_per_pair(n, planes, variant=3):
     """int8 tensor-core ops (2 per MAC) per pair: (algorithmic, issued).  Algorithmic = the lower triangle of the
     symmetric B_i once per digit plane, planes * n(n+1); issued = what the kernel's tiling launches: per plane and per
     256-row tile kt the id slabs 0..min(2kt+2, ceil(n/128))-1, each N x 128 MACs per pair with N = 256 plane rows,
-    or (variant 3, ozaki.cu::i8p_shape) N = the tile's rows below n rounded up to 16, minus 128 for slab 2kt+1."""
+    or (variants 3 and 4, ozaki.cu::i8p_shape) N = the tile's rows below n rounded up to 16, minus 128 for slab 2kt+1."""
     n_kt, n_slab = (n + 255) // 256, (n + 127) // 128
     macs = 0.0
     for kt in range(n_kt):
-        rows = 256 if variant != 3 else min(256, (n - 256 * kt + 15) // 16 * 16)
+        rows = 256 if variant < 3 else min(256, (n - 256 * kt + 15) // 16 * 16)
         for l in range(min(2 * kt + 2, n_slab)):
-            macs += (rows - 128 if variant == 3 and l == 2 * kt + 1 else rows) * 128.0
+            macs += (rows - 128 if variant >= 3 and l == 2 * kt + 1 else rows) * 128.0
     return planes * float(n) * (n + 1), planes * macs * 2.0
 
 
@@ -387,7 +387,7 @@ def run_gpu(args):
             line["dtype"] = "f64 results; n^2 term as exact int8 x int8 -> int32 tensor-core products of an error-free %d-plane split (%d bits), rest f64" % (planes, 7 * planes)
             line["roofline"] = {
                 "bound": "tensor", "achieved": achieved, "unit": "TOP/s", "peak": peak, "frac": achieved / peak,
-                "traffic": I8_TRAFFIC_BYTES, "kernel": {0: "i8_scan_kernel (tcgen05.mma cta_group::1 kind::i8, 128x256x32)", 2: "i8_scan_pair_kernel (tcgen05.mma cta_group::2 kind::i8, 256x256x32 per CTA pair)", 3: "i8_scan_pair_kernel (tcgen05.mma cta_group::2 kind::i8, 256xNx32 per CTA pair, N = the plane rows that can be non-zero)"}[i8.wide],
+                "traffic": I8_TRAFFIC_BYTES, "kernel": {0: "i8_scan_kernel (tcgen05.mma cta_group::1 kind::i8, 128x256x32)", 2: "i8_scan_pair_kernel (tcgen05.mma cta_group::2 kind::i8, 256x256x32 per CTA pair)", 3: "i8_scan_pair_kernel (tcgen05.mma cta_group::2 kind::i8, 256xNx32 per CTA pair, N = the plane rows that can be non-zero)", 4: "i8_scan_pair2_kernel (tcgen05.mma cta_group::2 kind::i8, 256xNx32 per CTA pair, two digit planes per genotype tile, N = the plane rows that can be non-zero)"}[i8.wide],
                 "kernel_ms_per_launch": kern_ms, "kernel_launches_per_step": launches_per_step,
                 "kernel_share_of_step": kern_ms * launches_per_step / ms_local,
                 "ops_per_pair_algorithmic": alg, "ops_per_pair_issued": iss, "issued_tops": issued,

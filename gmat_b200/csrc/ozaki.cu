@@ -76,6 +76,37 @@ __device__ __forceinline__ void i8_load_dosage(const signed char *row, int4 (&a)
     for (int q = 0; q < I8_TK / 16; ++q) a[q] = __ldg(ap + q);
 }
 
+// Finish one pair (first SNP ii of the launch, second SNP j) from qacc = sum_s 128^-(s+1) sum_k a_jk Y_s[j][k]: the
+// FP64 side terms, chi, threshold, warp-ballot compaction, 32-byte hit record (remma_epiAA.py:75-82).  Called by
+// all 32 lanes of an epilogue warp.
+__device__ __forceinline__ void i8_finish_pair(const I8Params &p, int ii, int j, int lane, double qacc) {
+    const int i = (int)p.ilist[ii];
+    const bool valid = j < p.m && (p.pair_space == GMAT_B200_PAIRS_ALL || j > i);
+    const int jc = j < p.m ? j : p.m - 1;
+    const double quad = 2.0 * p.scale[ii] * qacc;                   // a_j' B_i a_j
+    const double o = p.offs[jc];
+    const size_t at = (size_t)ii * p.m + jc;
+    double var = quad - 2.0 * o * p.t1[at] + o * o * p.s_i[ii];
+    double eff = p.e[at] - o * p.upy[ii];
+    if (o != o) { var = 0.0; eff = 0.0; }                          // monomorphic second SNP: w == 0 exactly
+    else if (o > 1.0e300) { var = o - o; eff = var; }             // missing genotype in the second SNP: NaN, as numpy
+    const double chi = eff * eff / var;
+    if (p.q_debug != nullptr && j < p.m) p.q_debug[at] = quad;
+    gmat_b200_hit h;
+    h.snp_0 = i; h.snp_1 = j; h.eff = eff; h.var = var; h.chi = chi;
+    const bool hit = valid && (p.chi_cut < 0.0 || chi > p.chi_cut);
+    const unsigned ballot = __ballot_sync(0xffffffffu, hit);
+    if (ballot) {
+        unsigned long long base = 0;
+        if (lane == 0) base = atomicAdd(p.count, (unsigned long long)__popc(ballot));
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (hit) {
+            const unsigned long long pos = base + __popc(ballot & ((1u << lane) - 1u));
+            if ((long long)pos < p.cap) p.hits[pos] = h;
+        }
+    }
+}
+
 struct I8Bars {
     uint64_t full[I8_NS], empty[I8_NS], tfull[2], tempty[2];
     uint32_t tmem_base;
@@ -199,32 +230,7 @@ i8_scan_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_constant_
                 }
                 qacc += (double)plane_sum * wgt;                         // the only FP64 work per plane
             }
-            // ---- finish the pair: FP64 terms, test, emit (remma_epiAA.py:75-82) ----
-            const int i = (int)p.ilist[ii];
-            const bool valid = j < p.m && (p.pair_space == GMAT_B200_PAIRS_ALL || j > i);
-            const int jc = j < p.m ? j : p.m - 1;
-            const double quad = 2.0 * p.scale[ii] * qacc;                   // a_j' B_i a_j
-            const double o = p.offs[jc];
-            const size_t at = (size_t)ii * p.m + jc;
-            double var = quad - 2.0 * o * p.t1[at] + o * o * p.s_i[ii];
-            double eff = p.e[at] - o * p.upy[ii];
-            if (o != o) { var = 0.0; eff = 0.0; }                          // monomorphic second SNP: w == 0 exactly
-            else if (o > 1.0e300) { var = o - o; eff = var; }             // missing genotype in the second SNP: NaN, as numpy
-            const double chi = eff * eff / var;
-            if (p.q_debug != nullptr && j < p.m) p.q_debug[at] = quad;
-            gmat_b200_hit h;
-            h.snp_0 = i; h.snp_1 = j; h.eff = eff; h.var = var; h.chi = chi;
-            const bool hit = valid && (p.chi_cut < 0.0 || chi > p.chi_cut);
-            const unsigned ballot = __ballot_sync(0xffffffffu, hit);
-            if (ballot) {
-                unsigned long long base = 0;
-                if (lane == 0) base = atomicAdd(p.count, (unsigned long long)__popc(ballot));
-                base = __shfl_sync(0xffffffffu, base, 0);
-                if (hit) {
-                    const unsigned long long pos = base + __popc(ballot & ((1u << lane) - 1u));
-                    if ((long long)pos < p.cap) p.hits[pos] = h;
-                }
-            }
+            i8_finish_pair(p, ii, j, lane, qacc);
         }
     }
     tc_fence_before();
@@ -375,36 +381,173 @@ i8_scan_pair_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_cons
                 }
                 qacc += (double)plane_sum * wgt;                         // the only FP64 work per plane
             }
-            const int i = (int)p.ilist[ii];
-            const bool valid = j < p.m && (p.pair_space == GMAT_B200_PAIRS_ALL || j > i);
-            const int jc = j < p.m ? j : p.m - 1;
-            const double quad = 2.0 * p.scale[ii] * qacc;
-            const double o = p.offs[jc];
-            const size_t at = (size_t)ii * p.m + jc;
-            double var = quad - 2.0 * o * p.t1[at] + o * o * p.s_i[ii];
-            double eff = p.e[at] - o * p.upy[ii];
-            if (o != o) { var = 0.0; eff = 0.0; }                          // monomorphic second SNP: w == 0 exactly
-            else if (o > 1.0e300) { var = o - o; eff = var; }             // missing genotype in the second SNP: NaN, as numpy
-            const double chi = eff * eff / var;
-            if (p.q_debug != nullptr && j < p.m) p.q_debug[at] = quad;
-            gmat_b200_hit h;
-            h.snp_0 = i; h.snp_1 = j; h.eff = eff; h.var = var; h.chi = chi;
-            const bool hit = valid && (p.chi_cut < 0.0 || chi > p.chi_cut);
-            const unsigned ballot = __ballot_sync(0xffffffffu, hit);
-            if (ballot) {
-                unsigned long long base = 0;
-                if (lane == 0) base = atomicAdd(p.count, (unsigned long long)__popc(ballot));
-                base = __shfl_sync(0xffffffffu, base, 0);
-                if (hit) {
-                    const unsigned long long pos = base + __popc(ballot & ((1u << lane) - 1u));
-                    if ((long long)pos < p.cap) p.hits[pos] = h;
-                }
-            }
+            i8_finish_pair(p, ii, j, lane, qacc);
         }
     }
     tc_fence_before();
     __syncthreads();
     cluster_sync_all();                       // nobody frees TMEM / exits while the peer may still touch this CTA
+    if (warp == 1) {
+        asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;\n" ::"r"(tmem_base), "r"(512) : "memory");
+    }
+}
+
+// ---- dual-plane CTA-pair variant (variant 4) ---------------------------------------------------------------------
+// ncu on the kernel above: 97.5 GB of TMA loads in 7.1 ms = 13.7 TB/s, the L2 -> SM ceiling of the chip (the
+// guide's ~6300 B/clk LTS cap); trimming MMAs (variant 3) left the time unchanged.  A 256 x 256 tile per CTA pair
+// needs 64 B/clk/SM at the full MMA rate, 148 SMs 9.5 KB/clk -- the kernel is bound by operand bytes, not by the
+// tensor pipe.  This variant multiplies every genotype tile with the tiles of TWO digit planes (s, s+1) while it is in
+// shared memory: 48 KB per CTA and stage feed 8 instead of 4 MMAs (47 B/clk/SM).  The two accumulators take all
+// 512 TMEM columns, so there is no second buffer: accumulator a of the next row tile starts when group a of the
+// epilogue warps (two groups of four warps, one per accumulator, draining in parallel) has released it, which
+// exposes about one drain minus one slab of MMAs per row tile.  Both groups leave their exact integer plane sums in
+// shared memory; group 0 adds the planes in the same order as the other variants (same bits) and finishes the pair.
+constexpr int I8Q_NS = 4;
+constexpr int I8Q_THREADS = 320;                                  // producer, issuer, 2 x 4 epilogue warps
+constexpr int I8Q_STAGE_BYTES = I8_A_BYTES + 2 * I8P_HALF * I8_SLAB;   // 48 KB per CTA
+struct I8QBars {
+    uint64_t full[I8Q_NS], empty[I8Q_NS], tfull[2], tempty[2];
+    uint32_t tmem_base;
+    long long handoff[2][I8_MAX_PLANES][I8_TJ];                  // [item parity][plane][TMEM lane]: exact plane sums
+};
+
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(I8Q_THREADS, 1)
+i8_scan_pair2_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_constant__ CUtensorMap map_ph,
+                     const I8Params p) {
+    extern __shared__ unsigned char smem_raw[];
+    unsigned char *smem = reinterpret_cast<unsigned char *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                                           ~static_cast<uintptr_t>(1023));
+    I8QBars *bars = reinterpret_cast<I8QBars *>(smem + I8Q_NS * I8Q_STAGE_BYTES);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int rank = (int)cluster_ctarank();
+    const int cluster_id = blockIdx.x >> 1, n_clusters = gridDim.x >> 1;
+    const int n_sp = p.n_planes >> 1;                             // plane pairs (n_planes is even)
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < I8Q_NS; ++s) { mbar_init(&bars->full[s], 1); mbar_init(&bars->empty[s], 1); }
+        for (int b = 0; b < 2; ++b) { mbar_init(&bars->tfull[b], 1); mbar_init(&bars->tempty[b], 8); }
+        mbar_fence_init();
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;\n" ::"r"(
+                         smem_u32(&bars->tmem_base)), "r"(512)
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;\n" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync_all();
+    tc_fence_after();
+    const uint32_t tmem_base = bars->tmem_base;
+
+    if (warp == 0) {
+        // ================================ TMA producer (both CTAs) ===============================
+        if (lane == 0) {
+            int stage = 0; unsigned phase = 0;
+            for (int item = cluster_id; item < p.total_items; item += n_clusters) {
+                const int ii = i8_find_first(p.item_prefix, p.n_i, item);
+                const int jt = 2 * (p.jt0[ii] + (item - p.item_prefix[ii])) + rank;
+                for (int sp = 0; sp < n_sp; ++sp) {
+                    const int prow = (ii * p.n_planes + 2 * sp) * p.np;     // plane 2sp; plane 2sp+1 is np rows on
+                    for (int kt = 0; kt < p.n_kt; ++kt) {
+                        const int nl = i8_slabs_of(kt, p.n_slab);
+                        for (int l = 0; l < nl; ++l) {
+                            int row_off, nn;
+                            i8p_shape(p, kt, l, row_off, nn);
+                            const int brow = prow + kt * I8_TK + row_off + rank * (nn >> 1);
+                            mbar_wait(&bars->empty[stage], phase ^ 1u);
+                            if (rank == 0) mbar_expect_tx(&bars->full[stage], 2 * I8Q_STAGE_BYTES);
+                            unsigned char *sa = smem + stage * I8Q_STAGE_BYTES;
+                            tma_load_2d_pair(sa, &map_g, l * I8_SLAB, jt * I8_TJ, &bars->full[stage]);
+                            tma_load_2d_pair(sa + I8_A_BYTES, &map_ph, l * I8_SLAB, brow, &bars->full[stage]);
+                            tma_load_2d_pair(sa + I8_A_BYTES + I8P_HALF * I8_SLAB, &map_ph, l * I8_SLAB, brow + p.np,
+                                             &bars->full[stage]);
+                            if (++stage == I8Q_NS) { stage = 0; phase ^= 1u; }
+                        }
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ================================ MMA issuer (leader CTA, one lane) ======================
+        if (lane == 0 && rank == 0) {
+            int stage = 0; unsigned phase = 0;
+            unsigned aphase = 0;                                  // both accumulators are used once per row tile
+            for (int item = cluster_id; item < p.total_items; item += n_clusters) {
+                for (int sp = 0; sp < n_sp; ++sp) {
+                    for (int kt = 0; kt < p.n_kt; ++kt) {
+                        const int nl = i8_slabs_of(kt, p.n_slab);
+                        for (int l = 0; l < nl; ++l) {
+                            mbar_wait(&bars->full[stage], phase);
+                            tc_fence_after();
+                            const uint32_t sa = smem_u32(smem + stage * I8Q_STAGE_BYTES);
+                            const uint64_t da = umma_desc_sw128(sa);
+                            int row_off, nn;
+                            i8p_shape(p, kt, l, row_off, nn);
+                            const uint32_t idesc = i8p_idesc(nn);
+#pragma unroll
+                            for (int a = 0; a < 2; ++a) {
+                                if (l == 0) {                     // epilogue group a drained accumulator a
+                                    mbar_wait(&bars->tempty[a], aphase ^ 1u);
+                                    tc_fence_after();
+                                }
+                                const uint64_t db = umma_desc_sw128(sa + I8_A_BYTES + a * I8P_HALF * I8_SLAB);
+                                const uint32_t tmem_d = tmem_base + (uint32_t)(a * I8_TK + row_off);
+#pragma unroll
+                                for (int k = 0; k < I8_SLAB / 32; ++k)
+                                    umma_i8_pair(tmem_d, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc,
+                                                 (uint32_t)((l | k) != 0));
+                                if (l == nl - 1) tc_commit_pair(&bars->tfull[a]);
+                            }
+                            tc_commit_pair(&bars->empty[stage]);
+                            if (++stage == I8Q_NS) { stage = 0; phase ^= 1u; }
+                        }
+                        aphase ^= 1u;
+                    }
+                }
+            }
+        }
+    } else {
+        // ================================ epilogue: group a = (warp - 2) / 4 drains accumulator a ========
+        const int q = warp & 3;                                   // TMEM lane quarter this warp may read
+        const int grp = (warp - 2) >> 2;
+        unsigned aphase = 0;
+        int parity = 0;
+        for (int item = cluster_id; item < p.total_items; item += n_clusters, parity ^= 1) {
+            const int ii = i8_find_first(p.item_prefix, p.n_i, item);
+            const int jt = 2 * (p.jt0[ii] + (item - p.item_prefix[ii])) + rank;
+            const int j = jt * I8_TJ + q * 32 + lane;
+            const signed char *arow = p.g8 + (size_t)(j < p.m ? j : p.m - 1) * p.ld;
+            for (int sp = 0; sp < n_sp; ++sp) {
+                long long plane_sum = 0;                          // exact; plane 2sp + grp
+                for (int kt = 0; kt < p.n_kt; ++kt) {
+                    int4 abytes[I8_TK / 16];
+                    i8_load_dosage(arow + kt * I8_TK, abytes);
+                    mbar_wait_warp(&bars->tfull[grp], aphase);
+                    tc_fence_after();
+                    const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(grp * I8_TK);
+                    plane_sum += i8_drain_tile(taddr, abytes);
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive_leader(&bars->tempty[grp]);
+                    aphase ^= 1u;
+                }
+                bars->handoff[parity][2 * sp + grp][q * 32 + lane] = plane_sum;
+            }
+            named_bar_sync(1, 256);                               // the eight epilogue warps of this CTA
+            if (grp == 0) {
+                double qacc = 0.0, wgt = 1.0;
+                for (int s = 0; s < p.n_planes; ++s) {            // planes in the order 0, 1, 2, ... like the other variants
+                    wgt *= 0.0078125;                             // 128^-(s+1)
+                    qacc += (double)bars->handoff[parity][s][q * 32 + lane] * wgt;
+                }
+                i8_finish_pair(p, ii, j, lane, qacc);
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync_all();
     if (warp == 1) {
         asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;\n" ::"r"(tmem_base), "r"(512) : "memory");
     }
@@ -599,10 +742,21 @@ extern "C" int gmat_b200_i8_scan(const signed char *g8_dev, long long n, long lo
     if (rc == GMAT_B200_OK) rc = make_map(&map_p, planes_dev, p.ld, (long long)n_i * n_planes * p.np, p.ld, I8_TK);
     if (rc != GMAT_B200_OK) return rc;
     const int grid = (int)(total_items < sm_count() ? total_items : sm_count());
-    GB_CHECK_ARG(wide == 0 || wide == 2 || wide == 3,
-                 "variant must be 0 (one CTA per 128-SNP tile), 2 (CTA pair) or 3 (CTA pair, trimmed MMAs)");
-    p.trim = wide == 3;
-    if (wide >= 2) {
+    GB_CHECK_ARG(wide == 0 || wide == 2 || wide == 3 || wide == 4,
+                 "variant must be 0 (one CTA per 128-SNP tile), 2 (CTA pair), 3 (CTA pair, trimmed MMAs) or 4 (CTA "
+                 "pair, trimmed MMAs, two digit planes per genotype tile)");
+    GB_CHECK_ARG(wide != 4 || n_planes % 2 == 0, "variant 4 multiplies the digit planes two at a time: n_planes must be even");
+    p.trim = wide >= 3;
+    if (wide == 4) {
+        CUtensorMap map_ph;
+        rc = make_map(&map_ph, planes_dev, p.ld, (long long)n_i * n_planes * p.np, p.ld, I8P_HALF);
+        if (rc != GMAT_B200_OK) return rc;
+        const int smem_bytes = I8Q_NS * I8Q_STAGE_BYTES + 1024 + (int)sizeof(I8QBars);
+        GB_CUDA(cudaFuncSetAttribute(i8_scan_pair2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
+        const int pairs_of_sms = sm_count() / 2;
+        const int grid2 = 2 * (int)(total_items < pairs_of_sms ? total_items : pairs_of_sms);
+        i8_scan_pair2_kernel<<<grid2, I8Q_THREADS, smem_bytes, st>>>(map_g, map_ph, p);
+    } else if (wide >= 2) {
         CUtensorMap map_ph;                                       // plane map with 128-row boxes (one half per CTA)
         rc = make_map(&map_ph, planes_dev, p.ld, (long long)n_i * n_planes * p.np, p.ld, I8P_HALF);
         if (rc != GMAT_B200_OK) return rc;

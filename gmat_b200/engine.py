@@ -253,11 +253,16 @@ class I8Exact(object):
         self.planes = [torch.zeros((self.batch * per_first,), dtype=torch.int8, device=dev) for _ in range(2)]
         self._prep_stream = torch.cuda.Stream(device=dev)
         self._shifts = torch.tensor([0, 2, 4, 6], dtype=torch.uint8, device=dev)
-        # kernel variant: 3 = CTA pair (tcgen05 cta_group::2) issuing only the plane rows that can be non-zero
-        # (default), 2 = CTA pair with full 256-row MMAs, 0 = one CTA per 128-SNP tile (cta_group::1)
-        self.wide = int(os.environ.get("GMAT_B200_I8_VARIANT", "3"))
-        if self.wide not in (0, 2, 3):
-            raise ValueError("GMAT_B200_I8_VARIANT must be 0, 2 or 3")
+        # kernel variant: 4 = CTA pair (tcgen05 cta_group::2), every genotype tile multiplied with the tiles of two
+        # digit planes while it is in shared memory (the scan is bound by L2 -> SM operand bytes, not by the tensor
+        # pipe), only the plane rows that can be non-zero issued (default; needs an even number of planes, else 3);
+        # 3 = CTA pair, one plane at a time, trimmed MMAs; 2 = CTA pair with full 256-row MMAs;
+        # 0 = one CTA per 128-SNP tile (cta_group::1)
+        self.wide = int(os.environ.get("GMAT_B200_I8_VARIANT", "4"))
+        if self.wide not in (0, 2, 3, 4):
+            raise ValueError("GMAT_B200_I8_VARIANT must be 0, 2, 3 or 4")
+        if self.wide == 4 and self.n_planes % 2:
+            self.wide = 3
         self.kernel_events = None      # bench.py: list of (start, end) CUDA events around every i8_scan launch
 
     def _coded_first(self, il):

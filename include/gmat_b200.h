@@ -197,10 +197,13 @@ int gmat_b200_i8_split(const double *pvp_dev /* [n][n] */, long long n, const do
  * (a_j . r_i and a_j . (u_i o Z'Py)); offs_dev[m] = o_j (NaN = monomorphic second SNP, +inf = SNP with a missing call);
  * q_debug_dev (optional, [n_i][m]) receives a_j' B_i a_j.  Hits are appended at *count_dev as in
  * gmat_b200_epi_exact_scan (count keeps counting beyond cap).  variant 0: one CTA per work item of 128 second SNPs
- * (tcgen05 cta_group::1); variant 2 (what the engine uses): a work item is 256 second SNPs computed by a CTA PAIR
+ * (tcgen05 cta_group::1); variant 2: a work item is 256 second SNPs computed by a CTA PAIR
  * (cluster of 2, tcgen05 cta_group::2) -- jt0 and the item counts are then in units of 256 second SNPs; variant 3 =
  * variant 2 issuing only the plane rows that can be non-zero (last row tile trimmed to n, the zero 128 x 128 block
- * right of the diagonal skipped): same results bit for bit, fewer MMAs.                                         */
+ * right of the diagonal skipped): same results bit for bit, fewer MMAs; variant 4 (what the engine uses, n_planes
+ * even) = variant 3 with every genotype tile multiplied by the tiles of two digit planes while it sits in shared
+ * memory (two TMEM accumulators, two groups of epilogue warps): a third fewer operand bytes from L2 per MMA, which
+ * is what bounds the scan; same bits again.                                                                     */
 int gmat_b200_i8_scan(const signed char *g8_dev, long long n, long long m, const signed char *planes_dev,
                       int n_planes, const long long *ilist_dev, long long n_i,
                       const int *item_prefix_dev, const int *jt0_dev, long long total_items,

@@ -242,9 +242,10 @@ def test_i8_missing_calls_are_nan_like_the_reference(eng, tmp_path, kind):
 
 @pytest.mark.parametrize("n,m", [(257, 300), (400, 270), (520, 130), (900, 515), (1100, 64)])
 def test_i8_kernel_variants_are_bit_identical(eng, tmp_path, n, m):
-    """The CTA-pair kernel that issues only the plane rows that can be non-zero (variant 3, the default: last row
-    tile trimmed to n, zero block right of the diagonal skipped) must give the SAME BITS as the full-tile CTA-pair
-    kernel (2) and the single-CTA kernel (0): the integer sums are exact, the FP64 finish is the same expression.
+    """The CTA-pair kernels that issue only the plane rows that can be non-zero (last row tile trimmed to n, zero
+    block right of the diagonal skipped) -- variant 4 (the default: two digit planes per genotype tile) and variant 3
+    (one plane at a time) -- must give the SAME BITS as the full-tile CTA-pair kernel (2) and the single-CTA kernel
+    (0): the integer sums are exact, the FP64 finish is the same expression in the same order.
     Shapes put n just past a 256-row tile (N = 16), past the half tile (half-slab N = 16) and in between."""
     import torch
     prefix, _ = _dataset(tmp_path, n, m, seed=n + m)
@@ -255,21 +256,21 @@ def test_i8_kernel_variants_are_bit_identical(eng, tmp_path, n, m):
     pvd = torch.as_tensor(pvp).cuda().contiguous()
     first = np.arange(0, m - 1, 2)
     res = {}
-    for variant in (3, 2, 0):
+    for variant in (4, 3, 2, 0):
         sc = eng.I8Exact(store, lu, lu, eng.ADD, pyd, pvd)
         sc.wide = variant
         h, q = sc.scan(first, eng.PAIRS_UPPER, -1.0, q_debug=True)
         key = h["snp_0"].astype(np.int64) * m + h["snp_1"]
         res[variant] = (h[np.argsort(key)], q.cpu().numpy())
-    for variant in (2, 0):
+    for variant in (4, 2, 0):
         assert np.array_equal(res[3][0]["snp_0"], res[variant][0]["snp_0"])
         assert np.array_equal(res[3][0]["snp_1"], res[variant][0]["snp_1"])
         assert np.array_equal(res[3][0]["var"], res[variant][0]["var"]), "variant %d: var differs" % variant
         assert np.array_equal(res[3][0]["eff"], res[variant][0]["eff"])
     # a_j' B_i a_j itself (only the entries of scanned pairs j > i are written by every variant)
-    q3, q2 = res[3][1], res[2][1]
+    q4, q3, q2 = res[4][1], res[3][1], res[2][1]
     for r, i in enumerate(first):
-        assert np.array_equal(q3[r, i + 1:], q2[r, i + 1:])
+        assert np.array_equal(q3[r, i + 1:], q2[r, i + 1:]) and np.array_equal(q4[r, i + 1:], q2[r, i + 1:])
     # and against the oracle, like every other engine test
     U, V = oracle.coded_pair("AA", oracle.read_plink(prefix))
     h = res[3][0]
