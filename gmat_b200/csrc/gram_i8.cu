@@ -10,9 +10,15 @@
 // kernel (grm.cu) needs n(n+1)m FP64 flop at 34 TFLOP/s; this kernel does n(n+1)m/2 int8 MACs at > 1 PMAC/s.
 //
 // Layout: G is re-coded once per call from the 2-bit store into Gt[id][snp] int8 (K = SNP contiguous, what the
-// K-major UMMA operands need), zero padded to 256 ids.  Tiles of 256 x 256 ids (lower block triangle) x all SNPs;
-// work is cut stream-K style into equal contiguous ranges of (tile, 128-SNP slab) units per CTA pair, partial tiles
-// are added with integer atomics -- exact, hence reproducible whatever the order.
+// K-major UMMA operands need), zero padded to 256 ids.  Tiles of 256 x 256 ids (lower block triangle) x all SNPs.
+// Schedule (gram_segment): Gt is far larger than L2 at scale (5 GB at n = 10,000 x m = 500,000), so WHICH slabs the
+// CTA pairs touch at the same time decides the DRAM traffic.  Full waves of tiles run in lockstep -- wave w = tiles
+// [w C, (w+1) C) for C CTA pairs, every pair sweeps the SNP axis of ITS tile from slab 0, all at the same pace, so
+// the ~40 id bands a wave needs are read from DRAM once and shared through L2 (the first version cut the (tile,
+// slab) space into equal contiguous ranges from the start: every pair sat at a different SNP position, each
+// re-read its bands from DRAM, 210 GB of DRAM reads = 32 of the 38 ms at that shape).  Only the tiles of the last,
+// partial wave are cut stream-K style into equal contiguous (tile, 128-SNP slab) ranges; their parts are added with
+// integer atomics -- exact, hence reproducible whatever the order.
 #include "tc5.cuh"
 
 namespace gb {
@@ -29,9 +35,27 @@ struct GramBars {
 
 struct GramParams {
     int n, np, ms, n_slab, nt;
-    long long units;               // tiles * n_slab
+    int tiles;                     // nt (nt + 1) / 2 lower-triangle tiles
     int *S;                        // [np][np] int32, zero-initialised
 };
+
+// idx-th piece of work of CTA pair c out of C: tile t, slabs [l0, l0 + cnt).  Pieces 0 .. W-1 (W = tiles / C) are the
+// whole tiles t = idx C + c of the lockstep waves; then the (tile, slab) units of the remaining tiles % C tiles, cut
+// into C equal contiguous ranges, one piece per tile a range touches.  Returns false past the last piece.
+__device__ __forceinline__ bool gram_segment(const GramParams &p, int c, int C, int idx, int &t, int &l0, int &cnt) {
+    const int W = p.tiles / C;
+    if (idx < W) { t = idx * C + c; l0 = 0; cnt = p.n_slab; return true; }
+    const long long units = (long long)(p.tiles - W * C) * p.n_slab;
+    const long long u0 = units * c / C, u1 = units * (c + 1) / C;
+    long long u = u0;
+    for (int k = W; ; ++k) {                                   // at most a few pieces: walk them
+        if (u >= u1) return false;
+        const int rem_t = (int)(u / p.n_slab), l = (int)(u % p.n_slab);
+        const int len = (int)min((long long)(p.n_slab - l), u1 - u);
+        if (k == idx) { t = W * C + rem_t; l0 = l; cnt = len; return true; }
+        u += len;
+    }
+}
 
 __device__ __forceinline__ void gram_tile_of(int t, int &rt, int &ct) {
     int r = (int)((sqrtf(8.0f * (float)t + 1.0f) - 1.0f) * 0.5f);
@@ -46,10 +70,10 @@ i8_gram_pair_kernel(const __grid_constant__ CUtensorMap map_gt, const GramParams
     unsigned char *smem = reinterpret_cast<unsigned char *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                                            ~static_cast<uintptr_t>(1023));
     GramBars *bars = reinterpret_cast<GramBars *>(smem + GI_NS * GI_STAGE_BYTES);
+    const uint32_t smem_base = smem_u32(smem);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int rank = (int)cluster_ctarank();
-    const long long cluster_id = blockIdx.x >> 1, n_clusters = gridDim.x >> 1;
-    const long long u_begin = p.units * cluster_id / n_clusters, u_end = p.units * (cluster_id + 1) / n_clusters;
+    const int cluster_id = blockIdx.x >> 1, n_clusters = gridDim.x >> 1;
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < GI_NS; ++s) { mbar_init(&bars->full[s], 1); mbar_init(&bars->empty[s], 1); }
@@ -68,62 +92,61 @@ i8_gram_pair_kernel(const __grid_constant__ CUtensorMap map_gt, const GramParams
     tc_fence_after();
     const uint32_t tmem_base = bars->tmem_base;
 
+    // Producer and issuer warps run their loops converged; one elected lane issues the single-thread instructions
+    // (elect_one, tc5.cuh), so addresses and descriptors stay in uniform registers.
     if (warp == 0) {
         // ================================ TMA producer (both CTAs) ===============================
-        if (lane == 0) {
-            int stage = 0; unsigned phase = 0;
-            for (long long u = u_begin; u < u_end;) {
-                const int t = (int)(u / p.n_slab), l0 = (int)(u % p.n_slab);
-                const int cnt = (int)min((long long)(p.n_slab - l0), u_end - u);
-                int rt, ct;
-                gram_tile_of(t, rt, ct);
-                for (int l = l0; l < l0 + cnt; ++l) {
-                    mbar_wait(&bars->empty[stage], phase ^ 1u);
+        int stage = 0; unsigned phase = 0;
+        int t, l0, cnt;
+        for (int idx = 0; gram_segment(p, cluster_id, n_clusters, idx, t, l0, cnt); ++idx) {
+            int rt, ct;
+            gram_tile_of(t, rt, ct);
+            for (int l = l0; l < l0 + cnt; ++l) {
+                mbar_wait(&bars->empty[stage], phase ^ 1u);
+                if (elect_one()) {
                     if (rank == 0) mbar_expect_tx(&bars->full[stage], 2 * GI_STAGE_BYTES);
                     unsigned char *sa = smem + stage * GI_STAGE_BYTES;
                     tma_load_2d_pair(sa, &map_gt, l * I8_SLAB, rt * I8_TK + rank * I8_TJ, &bars->full[stage]);
                     tma_load_2d_pair(sa + I8_A_BYTES, &map_gt, l * I8_SLAB, ct * I8_TK + rank * GI_HALF,
                                      &bars->full[stage]);
-                    if (++stage == GI_NS) { stage = 0; phase ^= 1u; }
                 }
-                u += cnt;
+                if (++stage == GI_NS) { stage = 0; phase ^= 1u; }
             }
         }
     } else if (warp == 1) {
-        // ================================ MMA issuer (leader CTA, one lane) ======================
-        if (lane == 0 && rank == 0) {
+        // ================================ MMA issuer (leader CTA) ================================
+        if (rank == 0) {
             int stage = 0; unsigned phase = 0;
             int abuf = 0; unsigned aphase = 0;
-            for (long long u = u_begin; u < u_end;) {
-                const int l0 = (int)(u % p.n_slab);
-                const int cnt = (int)min((long long)(p.n_slab - l0), u_end - u);
+            int t, l0, cnt;
+            for (int idx = 0; gram_segment(p, cluster_id, n_clusters, idx, t, l0, cnt); ++idx) {
                 mbar_wait(&bars->tempty[abuf], aphase ^ 1u);
                 tc_fence_after();
                 const uint32_t tmem_d = tmem_base + (uint32_t)(abuf * I8_TK);
                 for (int l = 0; l < cnt; ++l) {
                     mbar_wait(&bars->full[stage], phase);
                     tc_fence_after();
-                    const uint32_t sa = smem_u32(smem + stage * GI_STAGE_BYTES);
+                    const uint32_t sa = smem_base + (uint32_t)(stage * GI_STAGE_BYTES);
                     const uint64_t da = umma_desc_sw128(sa), db = umma_desc_sw128(sa + I8_A_BYTES);
+                    if (elect_one()) {
 #pragma unroll
-                    for (int k = 0; k < I8_SLAB / 32; ++k)
-                        umma_i8_pair(tmem_d, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), I8P_IDESC,
-                                     (uint32_t)((l | k) != 0));
-                    tc_commit_pair(&bars->empty[stage]);
+                        for (int k = 0; k < I8_SLAB / 32; ++k)
+                            umma_i8_pair(tmem_d, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), I8P_IDESC,
+                                         (uint32_t)((l | k) != 0));
+                        tc_commit_pair(&bars->empty[stage]);
+                        if (l == cnt - 1) tc_commit_pair(&bars->tfull[abuf]);
+                    }
                     if (++stage == GI_NS) { stage = 0; phase ^= 1u; }
                 }
-                tc_commit_pair(&bars->tfull[abuf]);
                 if (++abuf == 2) { abuf = 0; aphase ^= 1u; }
-                u += cnt;
             }
         }
     } else {
         // ================================ epilogue (both CTAs): TMEM -> S ========================
         const int q = warp & 3;
         int abuf = 0; unsigned aphase = 0;
-        for (long long u = u_begin; u < u_end;) {
-            const int t = (int)(u / p.n_slab), l0 = (int)(u % p.n_slab);
-            const int cnt = (int)min((long long)(p.n_slab - l0), u_end - u);
+        int t, l0, cnt;
+        for (int idx = 0; gram_segment(p, cluster_id, n_clusters, idx, t, l0, cnt); ++idx) {
             int rt, ct;
             gram_tile_of(t, rt, ct);
             const bool whole = cnt == p.n_slab;                       // the tile was not cut: plain stores
@@ -153,7 +176,6 @@ i8_gram_pair_kernel(const __grid_constant__ CUtensorMap map_gt, const GramParams
             __syncwarp();
             if (lane == 0) mbar_arrive_leader(&bars->tempty[abuf]);
             if (++abuf == 2) { abuf = 0; aphase ^= 1u; }
-            u += cnt;
         }
     }
     tc_fence_before();
@@ -164,57 +186,105 @@ i8_gram_pair_kernel(const __grid_constant__ CUtensorMap map_gt, const GramParams
     }
 }
 
-// 2-bit store [snp][id] -> Gt[id][snp - s0] int8 (zero outside [0,n) x [s0,s1)); tile = 64 SNPs x 256 ids
+// 2-bit store [snp][id] -> Gt[id][snp - s0] int8 (zero outside [0,n) x [s0,s1)); block = 128 SNPs x 128 ids.
+// Pass 1: the block's 128 x 32 bytes of codes into shared memory (16-byte loads).  Pass 2: thread (sg, ig) turns the
+// code words of 4 SNPs x 16 ids into 16 words "4 SNPs of one id" (a 4 x 16 byte transpose in registers) and stores
+// them conflict-free (row stride 33 words).  Pass 3: full 128-byte lines of Gt are written, 8 lanes per id row.
+// The first version (64 x 256 tile, byte stores into shared memory, 64-byte row pieces) ran at 1.3 TB/s.
 __global__ void __launch_bounds__(256)
 i8_dosage_t_kernel(const unsigned char *__restrict__ bed, int n, long long row_bytes, long long s0, long long s1,
                    unsigned table, signed char *__restrict__ gt, long long mld) {
-    __shared__ __align__(16) unsigned char tile[256][80];
-    const long long sblk = (long long)blockIdx.x * 64;
-    const int k0 = blockIdx.y * 256;
+    __shared__ unsigned raw[128][9];                               // codes of 128 ids per SNP (8 words) + 1 pad
+    __shared__ unsigned tile[128][33];                             // [id][4-SNP group] + 1 pad
+    const long long sblk = (long long)blockIdx.x * 128;
+    const int k0 = blockIdx.y * 128;
     {
-        const int sl = threadIdx.x >> 2, chunk = threadIdx.x & 3;         // SNP in the tile, 64-id chunk
+        const int sl = threadIdx.x >> 1, half = threadIdx.x & 1;
         const long long snp = s0 + sblk + sl;
+        const long long off = (long long)(k0 / 4) + half * 16;
         uint4 w = make_uint4(0u, 0u, 0u, 0u);
-        const long long off = (long long)(k0 / 4) + chunk * 16;
         if (snp < s1 && off + 16 <= row_bytes) w = *reinterpret_cast<const uint4 *>(bed + snp * row_bytes + off);
-        const unsigned ww[4] = {w.x, w.y, w.z, w.w};
+        raw[sl][half * 4 + 0] = w.x; raw[sl][half * 4 + 1] = w.y; raw[sl][half * 4 + 2] = w.z; raw[sl][half * 4 + 3] = w.w;
+    }
+    __syncthreads();
+    {
+        const int sg = threadIdx.x & 31, ig = threadIdx.x >> 5;   // SNPs 4 sg .. 4 sg + 3, ids 16 ig .. 16 ig + 15
+        unsigned w[4];
 #pragma unroll
-        for (int e = 0; e < 64; ++e) {
-            const unsigned code = (ww[e >> 4] >> (2 * (e & 15))) & 3u;
-            const int k = k0 + chunk * 64 + e;
-            tile[chunk * 64 + e][sl] = (k < n && snp < s1) ? (unsigned char)((table >> (8 * code)) & 0xffu) : 0;
+        for (int q = 0; q < 4; ++q) w[q] = raw[4 * sg + q][ig];
+#pragma unroll
+        for (int e = 0; e < 16; ++e) {
+            unsigned o = 0;
+#pragma unroll
+            for (int q = 0; q < 4; ++q) o |= ((table >> (8 * ((w[q] >> (2 * e)) & 3u))) & 0xffu) << (8 * q);
+            tile[16 * ig + e][sg] = (k0 + 16 * ig + e < n) ? o : 0u;
         }
     }
     __syncthreads();
-    signed char *dst = gt + (size_t)(k0 + threadIdx.x) * mld + sblk;
 #pragma unroll
-    for (int g = 0; g < 4; ++g)
-        if (sblk + 16 * g < mld)
-            *reinterpret_cast<uint4 *>(dst + 16 * g) = *reinterpret_cast<const uint4 *>(&tile[threadIdx.x][16 * g]);
+    for (int pass = 0; pass < 4; ++pass) {
+        const int row = pass * 32 + (threadIdx.x >> 3), seg = threadIdx.x & 7;
+        const uint4 v = make_uint4(tile[row][4 * seg], tile[row][4 * seg + 1], tile[row][4 * seg + 2],
+                                   tile[row][4 * seg + 3]);
+        *reinterpret_cast<uint4 *>(gt + (size_t)(k0 + row) * mld + sblk + 16 * seg) = v;
+    }
 }
 
-// c[k] = sum_s o_s a_ks (block k < n), d = sum_s o_s^2 (block n); fixed summation order
+// c[k] = sum_s o_s a_ks (k < n) and d = sum_s o_s^2 (slot n), o_s = -lut[s][code 0], in a fixed summation order.
+// Gt (n x m bytes: 5 GB at the C2 shape) is streamed ONCE: block (chunk, row group) stages the chunk's 4096 offsets
+// in shared memory -- transposed, ot[b][i] = o[4 i + b], so that lanes reading consecutive 4-byte words of a row hit
+// consecutive doubles -- and its 8 warps walk 128 rows, a warp per row, 128 coalesced bytes per load.  Partials go
+// to part[chunk][k]; i8_rowsum_kernel adds the chunks in order.  (The first version ran one block per row over all
+// SNPs and re-read the whole offset vector through L2 for every row: 4 ms at n = 10,000 x m = 500,000.)
+constexpr int GI_DOT_CHUNK = 4096;
+constexpr int GI_DOT_ROWS = 128;
 __global__ void __launch_bounds__(256)
 i8_rowdot_kernel(const signed char *__restrict__ gt, long long mld, const double *__restrict__ lut, long long s0,
-                 long long ms, int n, double *__restrict__ c_out) {
+                 long long ms, int n, double *__restrict__ part) {
+    __shared__ double ot[4][GI_DOT_CHUNK / 4];
     __shared__ double red[8];
-    const int k = blockIdx.x;
-    double acc = 0.0;
-    if (k < n) {
-        const signed char *row = gt + (size_t)k * mld;
-        for (long long s = threadIdx.x; s < ms; s += 256) acc += (double)row[s] * -lut[(s0 + s) * 4];
-    } else {
-        for (long long s = threadIdx.x; s < ms; s += 256) { const double o = lut[(s0 + s) * 4]; acc += o * o; }
-    }
-#pragma unroll
-    for (int d = 16; d >= 1; d >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, d);
-    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
+    const long long c0 = (long long)blockIdx.x * GI_DOT_CHUNK;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    for (int t = threadIdx.x; t < GI_DOT_CHUNK; t += 256)
+        ot[t & 3][t >> 2] = c0 + t < ms ? -lut[(s0 + c0 + t) * 4] : 0.0;
     __syncthreads();
-    if (threadIdx.x == 0) {
-        double t = 0.0;
-        for (int w = 0; w < 8; ++w) t += red[w];
-        c_out[k] = t;
+    double *out = part + (size_t)blockIdx.x * (n + 1);
+    if (blockIdx.y == 0) {                                        // d: this chunk's share of sum o^2
+        double acc = 0.0;
+        for (int t = threadIdx.x; t < GI_DOT_CHUNK; t += 256) { const double o = ot[t & 3][t >> 2]; acc += o * o; }
+#pragma unroll
+        for (int d = 16; d >= 1; d >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, d);
+        if (lane == 0) red[warp] = acc;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            double t = 0.0;
+            for (int w = 0; w < 8; ++w) t += red[w];
+            out[n] = t;
+        }
     }
+    const int words = (int)(min((long long)GI_DOT_CHUNK, mld - c0) >> 2);   // mld is a multiple of 128
+    for (int r = warp; r < GI_DOT_ROWS; r += 8) {
+        const int k = blockIdx.y * GI_DOT_ROWS + r;
+        if (k >= n) break;
+        const unsigned *row = reinterpret_cast<const unsigned *>(gt + (size_t)k * mld + c0);
+        double acc = 0.0;
+#pragma unroll 4
+        for (int i = lane; i < words; i += 32) {
+            const unsigned w = __ldg(row + i);
+            acc += (double)(int)(w & 0xffu) * ot[0][i] + (double)(int)((w >> 8) & 0xffu) * ot[1][i] +
+                   (double)(int)((w >> 16) & 0xffu) * ot[2][i] + (double)(int)(w >> 24) * ot[3][i];
+        }
+#pragma unroll
+        for (int d = 16; d >= 1; d >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, d);
+        if (lane == 0) out[k] = acc;
+    }
+}
+__global__ void i8_rowsum_kernel(const double *__restrict__ part, int chunks, int n, double *__restrict__ c_out) {
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k > n) return;
+    double t = 0.0;
+    for (int ch = 0; ch < chunks; ++ch) t += part[(size_t)ch * (n + 1) + k];
+    c_out[k] = t;
 }
 
 __global__ void i8_gram_finish_kernel(const int *__restrict__ S, int np, const double *__restrict__ c, int n,
@@ -254,20 +324,22 @@ extern "C" int gmat_b200_grm_i8(const unsigned char *bed_dev, long long n, long 
     const int np = (int)round_up(n, I8_TK);
     const long long mld = round_up(ms > 0 ? ms : 1, 128);
     keep_scratch_pool();
-    signed char *gt = nullptr; int *S = nullptr; double *c = nullptr;
+    signed char *gt = nullptr; int *S = nullptr; double *c = nullptr, *part = nullptr;
+    const int chunks = (int)((mld + GI_DOT_CHUNK - 1) / GI_DOT_CHUNK);
     GB_CUDA(cudaMallocAsync((void **)&gt, (size_t)np * mld, st));
     GB_CUDA(cudaMallocAsync((void **)&S, (size_t)np * np * sizeof(int), st));
     GB_CUDA(cudaMallocAsync((void **)&c, (size_t)(n + 1) * sizeof(double), st));
+    GB_CUDA(cudaMallocAsync((void **)&part, (size_t)chunks * (n + 1) * sizeof(double), st));
     GB_CUDA(cudaMemsetAsync(S, 0, (size_t)np * np * sizeof(int), st));
     int rc = GMAT_B200_OK;
     if (ms > 0) {
         const unsigned table = coding == GMAT_B200_CODING_DOM ? 0x00010000u : 0x02010000u;
-        dim3 tg((unsigned)((mld + 63) / 64), (unsigned)(np / 256));
+        dim3 tg((unsigned)(mld / 128), (unsigned)(np / 128));
         i8_dosage_t_kernel<<<tg, 256, 0, st>>>(bed_dev, (int)n, row_bytes, snp_begin, snp_end, table, gt, mld);
         count_launch();
         GramParams p;
         p.n = (int)n; p.np = np; p.ms = (int)ms; p.n_slab = (int)((ms + I8_SLAB - 1) / I8_SLAB); p.nt = np / I8_TK;
-        p.units = (long long)p.nt * (p.nt + 1) / 2 * p.n_slab; p.S = S;
+        p.tiles = p.nt * (p.nt + 1) / 2; p.S = S;
         CUtensorMap map_gt;
         rc = make_map(&map_gt, gt, ms, np, mld, I8_TJ);
         if (rc == GMAT_B200_OK) {
@@ -277,14 +349,17 @@ extern "C" int gmat_b200_grm_i8(const unsigned char *bed_dev, long long n, long 
             if (e != cudaSuccess) { set_error("cudaFuncSetAttribute: %s", cudaGetErrorString(e)); rc = GMAT_B200_ERR_CUDA; }
             else {
                 long long pairs = sm_count() / 2;
-                if (pairs > p.units) pairs = p.units;
+                if (pairs > (long long)p.tiles * p.n_slab) pairs = (long long)p.tiles * p.n_slab;
                 i8_gram_pair_kernel<<<(unsigned)(2 * pairs), GI_THREADS, smem_bytes, st>>>(map_gt, p);
                 count_launch();
             }
         }
     }
     if (rc == GMAT_B200_OK) {
-        i8_rowdot_kernel<<<(unsigned)(n + 1), 256, 0, st>>>(gt, mld, lut_dev, snp_begin, ms, (int)n, c);
+        dim3 dg((unsigned)chunks, (unsigned)((n + GI_DOT_ROWS - 1) / GI_DOT_ROWS));
+        i8_rowdot_kernel<<<dg, 256, 0, st>>>(gt, mld, lut_dev, snp_begin, ms, (int)n, part);
+        count_launch();
+        i8_rowsum_kernel<<<(unsigned)((n + 256) / 256), 256, 0, st>>>(part, chunks, (int)n, c);
         count_launch();
         i8_gram_finish_kernel<<<sm_count() * 8, 256, 0, st>>>(S, np, c, (int)n, scale, small_val, accumulate, K_dev);
         count_launch();
@@ -294,5 +369,6 @@ extern "C" int gmat_b200_grm_i8(const unsigned char *bed_dev, long long n, long 
     cudaFreeAsync(gt, st);
     cudaFreeAsync(S, st);
     cudaFreeAsync(c, st);
+    cudaFreeAsync(part, st);
     return rc;
 }

@@ -277,6 +277,7 @@ i8_scan_pair_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_cons
     unsigned char *smem = reinterpret_cast<unsigned char *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                                            ~static_cast<uintptr_t>(1023));
     I8PBars *bars = reinterpret_cast<I8PBars *>(smem + I8P_NS * I8P_STAGE_BYTES);
+    const uint32_t smem_base = smem_u32(smem);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int rank = (int)cluster_ctarank();
     const int cluster_id = blockIdx.x >> 1, n_clusters = gridDim.x >> 1;
@@ -298,33 +299,35 @@ i8_scan_pair_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_cons
     tc_fence_after();
     const uint32_t tmem_base = bars->tmem_base;
 
+    // The producer and issuer warps run their loops CONVERGED and hand only the single-thread instructions to one
+    // elected lane (elect_one, tc5.cuh): addresses and descriptors then live in uniform registers.
     if (warp == 0) {
-        if (lane == 0) {
-            int stage = 0; unsigned phase = 0;
-            for (int item = cluster_id; item < p.total_items; item += n_clusters) {
-                const int ii = i8_find_first(p.item_prefix, p.n_i, item);
-                const int jt = 2 * (p.jt0[ii] + (item - p.item_prefix[ii])) + rank;
-                for (int s = 0; s < p.n_planes; ++s) {
-                    const int prow = (ii * p.n_planes + s) * p.np;
-                    for (int kt = 0; kt < p.n_kt; ++kt) {
-                        const int nl = i8_slabs_of(kt, p.n_slab);
-                        for (int l = 0; l < nl; ++l) {
-                            int row_off, nn;
-                            i8p_shape(p, kt, l, row_off, nn);
-                            mbar_wait(&bars->empty[stage], phase ^ 1u);
+        int stage = 0; unsigned phase = 0;
+        for (int item = cluster_id; item < p.total_items; item += n_clusters) {
+            const int ii = i8_find_first(p.item_prefix, p.n_i, item);
+            const int jt = 2 * (p.jt0[ii] + (item - p.item_prefix[ii])) + rank;
+            for (int s = 0; s < p.n_planes; ++s) {
+                const int prow = (ii * p.n_planes + s) * p.np;
+                for (int kt = 0; kt < p.n_kt; ++kt) {
+                    const int nl = i8_slabs_of(kt, p.n_slab);
+                    for (int l = 0; l < nl; ++l) {
+                        int row_off, nn;
+                        i8p_shape(p, kt, l, row_off, nn);
+                        mbar_wait(&bars->empty[stage], phase ^ 1u);
+                        if (elect_one()) {
                             if (rank == 0) mbar_expect_tx(&bars->full[stage], 2 * I8P_STAGE_BYTES);
                             unsigned char *sa = smem + stage * I8P_STAGE_BYTES;
                             tma_load_2d_pair(sa, &map_g, l * I8_SLAB, jt * I8_TJ, &bars->full[stage]);
                             tma_load_2d_pair(sa + I8_A_BYTES, &map_ph, l * I8_SLAB,
                                              prow + kt * I8_TK + row_off + rank * (nn >> 1), &bars->full[stage]);
-                            if (++stage == I8P_NS) { stage = 0; phase ^= 1u; }
                         }
+                        if (++stage == I8P_NS) { stage = 0; phase ^= 1u; }
                     }
                 }
             }
         }
     } else if (warp == 1) {
-        if (lane == 0 && rank == 0) {
+        if (rank == 0) {
             int stage = 0; unsigned phase = 0;
             int abuf = 0; unsigned aphase = 0;
             for (int item = cluster_id; item < p.total_items; item += n_clusters) {
@@ -337,19 +340,21 @@ i8_scan_pair_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_cons
                         for (int l = 0; l < nl; ++l) {
                             mbar_wait(&bars->full[stage], phase);
                             tc_fence_after();
-                            const uint32_t sa = smem_u32(smem + stage * I8P_STAGE_BYTES);
+                            const uint32_t sa = smem_base + (uint32_t)(stage * I8P_STAGE_BYTES);
                             const uint64_t da = umma_desc_sw128(sa), db = umma_desc_sw128(sa + I8_A_BYTES);
                             int row_off, nn;
                             i8p_shape(p, kt, l, row_off, nn);
                             const uint32_t idesc = i8p_idesc(nn);
+                            if (elect_one()) {
 #pragma unroll
-                            for (int k = 0; k < I8_SLAB / 32; ++k)
-                                umma_i8_pair(tmem_d + (uint32_t)row_off, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k),
-                                             idesc, (uint32_t)((l | k) != 0));
-                            tc_commit_pair(&bars->empty[stage]);
+                                for (int k = 0; k < I8_SLAB / 32; ++k)
+                                    umma_i8_pair(tmem_d + (uint32_t)row_off, da + (uint64_t)(2 * k),
+                                                 db + (uint64_t)(2 * k), idesc, (uint32_t)((l | k) != 0));
+                                tc_commit_pair(&bars->empty[stage]);
+                                if (l == nl - 1) tc_commit_pair(&bars->tfull[abuf]);
+                            }
                             if (++stage == I8P_NS) { stage = 0; phase ^= 1u; }
                         }
-                        tc_commit_pair(&bars->tfull[abuf]);
                         if (++abuf == 2) { abuf = 0; aphase ^= 1u; }
                     }
                 }
@@ -418,6 +423,7 @@ i8_scan_pair2_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_con
     unsigned char *smem = reinterpret_cast<unsigned char *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                                            ~static_cast<uintptr_t>(1023));
     I8QBars *bars = reinterpret_cast<I8QBars *>(smem + I8Q_NS * I8Q_STAGE_BYTES);
+    const uint32_t smem_base = smem_u32(smem);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int rank = (int)cluster_ctarank();
     const int cluster_id = blockIdx.x >> 1, n_clusters = gridDim.x >> 1;
@@ -441,36 +447,36 @@ i8_scan_pair2_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_con
     const uint32_t tmem_base = bars->tmem_base;
 
     if (warp == 0) {
-        // ================================ TMA producer (both CTAs) ===============================
-        if (lane == 0) {
-            int stage = 0; unsigned phase = 0;
-            for (int item = cluster_id; item < p.total_items; item += n_clusters) {
-                const int ii = i8_find_first(p.item_prefix, p.n_i, item);
-                const int jt = 2 * (p.jt0[ii] + (item - p.item_prefix[ii])) + rank;
-                for (int sp = 0; sp < n_sp; ++sp) {
-                    const int prow = (ii * p.n_planes + 2 * sp) * p.np;     // plane 2sp; plane 2sp+1 is np rows on
-                    for (int kt = 0; kt < p.n_kt; ++kt) {
-                        const int nl = i8_slabs_of(kt, p.n_slab);
-                        for (int l = 0; l < nl; ++l) {
-                            int row_off, nn;
-                            i8p_shape(p, kt, l, row_off, nn);
-                            const int brow = prow + kt * I8_TK + row_off + rank * (nn >> 1);
-                            mbar_wait(&bars->empty[stage], phase ^ 1u);
+        // ================================ TMA producer (both CTAs; converged warp, elected lane issues) ====
+        int stage = 0; unsigned phase = 0;
+        for (int item = cluster_id; item < p.total_items; item += n_clusters) {
+            const int ii = i8_find_first(p.item_prefix, p.n_i, item);
+            const int jt = 2 * (p.jt0[ii] + (item - p.item_prefix[ii])) + rank;
+            for (int sp = 0; sp < n_sp; ++sp) {
+                const int prow = (ii * p.n_planes + 2 * sp) * p.np;         // plane 2sp; plane 2sp+1 is np rows on
+                for (int kt = 0; kt < p.n_kt; ++kt) {
+                    const int nl = i8_slabs_of(kt, p.n_slab);
+                    for (int l = 0; l < nl; ++l) {
+                        int row_off, nn;
+                        i8p_shape(p, kt, l, row_off, nn);
+                        const int brow = prow + kt * I8_TK + row_off + rank * (nn >> 1);
+                        mbar_wait(&bars->empty[stage], phase ^ 1u);
+                        if (elect_one()) {
                             if (rank == 0) mbar_expect_tx(&bars->full[stage], 2 * I8Q_STAGE_BYTES);
                             unsigned char *sa = smem + stage * I8Q_STAGE_BYTES;
                             tma_load_2d_pair(sa, &map_g, l * I8_SLAB, jt * I8_TJ, &bars->full[stage]);
                             tma_load_2d_pair(sa + I8_A_BYTES, &map_ph, l * I8_SLAB, brow, &bars->full[stage]);
                             tma_load_2d_pair(sa + I8_A_BYTES + I8P_HALF * I8_SLAB, &map_ph, l * I8_SLAB, brow + p.np,
                                              &bars->full[stage]);
-                            if (++stage == I8Q_NS) { stage = 0; phase ^= 1u; }
                         }
+                        if (++stage == I8Q_NS) { stage = 0; phase ^= 1u; }
                     }
                 }
             }
         }
     } else if (warp == 1) {
-        // ================================ MMA issuer (leader CTA, one lane) ======================
-        if (lane == 0 && rank == 0) {
+        // ================================ MMA issuer (leader CTA; converged warp, elected lane issues) =====
+        if (rank == 0) {
             int stage = 0; unsigned phase = 0;
             unsigned aphase = 0;                                  // both accumulators are used once per row tile
             for (int item = cluster_id; item < p.total_items; item += n_clusters) {
@@ -480,7 +486,7 @@ i8_scan_pair2_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_con
                         for (int l = 0; l < nl; ++l) {
                             mbar_wait(&bars->full[stage], phase);
                             tc_fence_after();
-                            const uint32_t sa = smem_u32(smem + stage * I8Q_STAGE_BYTES);
+                            const uint32_t sa = smem_base + (uint32_t)(stage * I8Q_STAGE_BYTES);
                             const uint64_t da = umma_desc_sw128(sa);
                             int row_off, nn;
                             i8p_shape(p, kt, l, row_off, nn);
@@ -493,13 +499,15 @@ i8_scan_pair2_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_con
                                 }
                                 const uint64_t db = umma_desc_sw128(sa + I8_A_BYTES + a * I8P_HALF * I8_SLAB);
                                 const uint32_t tmem_d = tmem_base + (uint32_t)(a * I8_TK + row_off);
+                                if (elect_one()) {
 #pragma unroll
-                                for (int k = 0; k < I8_SLAB / 32; ++k)
-                                    umma_i8_pair(tmem_d, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc,
-                                                 (uint32_t)((l | k) != 0));
-                                if (l == nl - 1) tc_commit_pair(&bars->tfull[a]);
+                                    for (int k = 0; k < I8_SLAB / 32; ++k)
+                                        umma_i8_pair(tmem_d, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc,
+                                                     (uint32_t)((l | k) != 0));
+                                    if (l == nl - 1) tc_commit_pair(&bars->tfull[a]);
+                                    if (a == 1) tc_commit_pair(&bars->empty[stage]);
+                                }
                             }
-                            tc_commit_pair(&bars->empty[stage]);
                             if (++stage == I8Q_NS) { stage = 0; phase ^= 1u; }
                         }
                         aphase ^= 1u;

@@ -21,6 +21,22 @@ __device__ __forceinline__ void tma_load_2d(void *smem_dst, const CUtensorMap *m
         ::"r"(smem_u32(smem_dst)), "l"(map), "r"(c0), "r"(c1), "r"(smem_u32(bar))
         : "memory");
 }
+// one lane of a CONVERGED warp (elect.sync): the single-thread tcgen05 instructions are issued under this predicate
+// while the loop around them stays warp-uniform, so that ptxas keeps descriptors / addresses in uniform registers
+// instead of re-deriving them per MMA through an ELECT + R2UR.BROADCAST + BRA.U.ANY waterfall (12 dependent
+// instructions per MMA when the whole loop runs under `if (lane == 0)`: the issuing thread, not the tensor pipe,
+// was the limit of the int8 kernels -- profiles/r01_kernels_v8.md)
+__device__ __forceinline__ bool elect_one() {
+    uint32_t pred;
+    asm volatile(
+        "{\n"
+        ".reg .pred P;\n"
+        "elect.sync _|P, 0xffffffff;\n"
+        "selp.b32 %0, 1, 0, P;\n"
+        "}\n"
+        : "=r"(pred));
+    return pred != 0;
+}
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;\n" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;\n" ::: "memory"); }
 __device__ __forceinline__ void tc_commit(uint64_t *bar) {
