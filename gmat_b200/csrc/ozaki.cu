@@ -47,24 +47,31 @@ struct I8Params {
 // rows of the tile, all in INTEGER registers.  No FP64 instruction may sit in this loop: DADD / I2F.F64 issue into
 // the pipe the tensor MMAs occupy (ncu: 37 % of all stall samples sat on the one DADD of the first version and the
 // tensor pipe idled 37 % of the time).  |Y| <= 2*127*n, so a 32-column partial fits int32 for n < 1.3e5.
+__device__ __forceinline__ int i8_dot_chunk(const int (&v)[32], const int4 &lo, const int4 &hi) {
+    const int aw[8] = {lo.x, lo.y, lo.z, lo.w, hi.x, hi.y, hi.z, hi.w};
+    int c0 = 0, c1 = 0, c2 = 0, c3 = 0;                           // four independent chains
+#pragma unroll
+    for (int w = 0; w < 8; ++w) {
+        c0 += (aw[w] & 0xff) * v[4 * w];
+        c1 += ((aw[w] >> 8) & 0xff) * v[4 * w + 1];
+        c2 += ((aw[w] >> 16) & 0xff) * v[4 * w + 2];
+        c3 += ((aw[w] >> 24) & 0xff) * v[4 * w + 3];
+    }
+    return (c0 + c1) + (c2 + c3);                                 // |.| <= 32 * 2 * 2*127*n: int32 for n < 1.3e5
+}
+// The TMEM load of chunk ch+1 is in flight while chunk ch is multiplied (two register buffers).
 __device__ __forceinline__ long long i8_drain_tile(uint32_t taddr, const int4 (&a)[I8_TK / 16]) {
     long long total = 0;
+    int v0[32], v1[32];
+    tmem_ld32(taddr, v0);
 #pragma unroll
-    for (int ch = 0; ch < I8_TK / 32; ++ch) {
-        int v[32];
-        tmem_ld32(taddr + ch * 32, v);
+    for (int ch = 0; ch < I8_TK / 32; ch += 2) {
         tmem_ld_wait();
-        const int aw[8] = {a[2 * ch].x, a[2 * ch].y, a[2 * ch].z, a[2 * ch].w,
-                           a[2 * ch + 1].x, a[2 * ch + 1].y, a[2 * ch + 1].z, a[2 * ch + 1].w};
-        int c0 = 0, c1 = 0, c2 = 0, c3 = 0;                       // four independent chains
-#pragma unroll
-        for (int w = 0; w < 8; ++w) {
-            c0 += (aw[w] & 0xff) * v[4 * w];
-            c1 += ((aw[w] >> 8) & 0xff) * v[4 * w + 1];
-            c2 += ((aw[w] >> 16) & 0xff) * v[4 * w + 2];
-            c3 += ((aw[w] >> 24) & 0xff) * v[4 * w + 3];
-        }
-        total += (long long)(c0 + c1) + (long long)(c2 + c3);
+        tmem_ld32(taddr + (ch + 1) * 32, v1);
+        total += i8_dot_chunk(v0, a[2 * ch], a[2 * ch + 1]);
+        tmem_ld_wait();
+        if (ch + 2 < I8_TK / 32) tmem_ld32(taddr + (ch + 2) * 32, v0);
+        total += i8_dot_chunk(v1, a[2 * ch + 2], a[2 * ch + 3]);
     }
     return total;
 }

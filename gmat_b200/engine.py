@@ -253,12 +253,12 @@ class I8Exact(object):
         self.planes = [torch.zeros((self.batch * per_first,), dtype=torch.int8, device=dev) for _ in range(2)]
         self._prep_stream = torch.cuda.Stream(device=dev)
         self._shifts = torch.tensor([0, 2, 4, 6], dtype=torch.uint8, device=dev)
-        # kernel variant: 4 = CTA pair (tcgen05 cta_group::2), every genotype tile multiplied with the tiles of two
-        # digit planes while it is in shared memory (the scan is bound by L2 -> SM operand bytes, not by the tensor
-        # pipe), only the plane rows that can be non-zero issued (default; needs an even number of planes, else 3);
-        # 3 = CTA pair, one plane at a time, trimmed MMAs; 2 = CTA pair with full 256-row MMAs;
-        # 0 = one CTA per 128-SNP tile (cta_group::1)
-        self.wide = int(os.environ.get("GMAT_B200_I8_VARIANT", "4"))
+        # kernel variant: 3 = CTA pair (tcgen05 cta_group::2), one digit plane at a time, TMEM double-buffered, only
+        # the plane rows that can be non-zero issued (default: fastest measured, 8.1e7 pairs/s at n=2000);
+        # 4 = the same with every genotype tile multiplied by the tiles of TWO digit planes while it is in shared
+        # memory (-25 % L2 -> SM bytes, but both TMEM accumulators are busy, so the drain of a row tile is exposed:
+        # 7.5e7; needs an even number of planes); 2 = CTA pair with full 256-row MMAs; 0 = one CTA per 128-SNP tile
+        self.wide = int(os.environ.get("GMAT_B200_I8_VARIANT", "3"))
         if self.wide not in (0, 2, 3, 4):
             raise ValueError("GMAT_B200_I8_VARIANT must be 0, 2, 3 or 4")
         if self.wide == 4 and self.n_planes % 2:

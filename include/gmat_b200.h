@@ -200,10 +200,10 @@ int gmat_b200_i8_split(const double *pvp_dev /* [n][n] */, long long n, const do
  * (tcgen05 cta_group::1); variant 2: a work item is 256 second SNPs computed by a CTA PAIR
  * (cluster of 2, tcgen05 cta_group::2) -- jt0 and the item counts are then in units of 256 second SNPs; variant 3 =
  * variant 2 issuing only the plane rows that can be non-zero (last row tile trimmed to n, the zero 128 x 128 block
- * right of the diagonal skipped): same results bit for bit, fewer MMAs; variant 4 (what the engine uses, n_planes
+ * right of the diagonal skipped): same results bit for bit, fewer MMAs -- what the engine uses; variant 4 (n_planes
  * even) = variant 3 with every genotype tile multiplied by the tiles of two digit planes while it sits in shared
- * memory (two TMEM accumulators, two groups of epilogue warps): a third fewer operand bytes from L2 per MMA, which
- * is what bounds the scan; same bits again.                                                                     */
+ * memory (two TMEM accumulators, two groups of epilogue warps): a quarter fewer operand bytes from L2, but no
+ * second accumulator buffer to hide the drain of a row tile behind; same bits again.                            */
 int gmat_b200_i8_scan(const signed char *g8_dev, long long n, long long m, const signed char *planes_dev,
                       int n_planes, const long long *ilist_dev, long long n_i,
                       const int *item_prefix_dev, const int *jt0_dev, long long total_items,
