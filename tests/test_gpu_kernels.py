@@ -305,6 +305,37 @@ def test_grm_streamk_many_tiles_reproducible(eng, tmp_path, monkeypatch, which):
         assert np.array_equal(again.cpu().numpy(), got)
 
 
+@pytest.mark.parametrize("n,m", [(3300, 300), (4200, 140), (300, 9000)])
+def test_grm_i8_wave_schedule_and_chunked_corrections(eng, monkeypatch, n, m):
+    """The int8 GRM's schedule beyond one wave of tiles -- n=3300: 91 tiles of 256 x 256 = one lockstep wave of
+    whole tiles (plain stores) + 17 tiles cut stream-K style (integer atomics); n=4200: two waves + 5 -- and its
+    FP64 corrections over more than one 4096-SNP chunk (m=9000), against numpy on genotypes generated in HBM, and
+    against the FP64 DMMA kernel; bit-identical run to run."""
+    import torch
+    from gmat_b200 import synth
+    from gmat_b200.gmatrix.gmatrix import grm_device
+    payload = synth.device_payload(n, m, 4242 + n, "cuda", eng.row_stride(n))
+    store = eng.GenotypeStore.from_device_payload(payload, n)
+    g = store.decode(None).t().contiguous().cpu().numpy()               # [n][m] dosages 0/1/2 (decode is bit-exact)
+    assert not np.any(np.abs(g - 1.0 / 3) < 1e-3)
+    freq = g.sum(axis=0) / (2.0 * n)
+    x = g - 2.0 * freq                                                    # gmatrix.py:53-66
+    scale = np.sum(2.0 * freq * (1.0 - freq))
+    want = x @ x.T / scale
+    want[np.diag_indices(n)] *= 1.001
+    monkeypatch.setenv("GMAT_B200_GRM_ENGINE", "i8")
+    kin, s = grm_device(store, eng.ADD)
+    got = kin.cpu().numpy()
+    assert abs(s - scale) <= 1e-12 * scale
+    assert np.abs(got - want).max() <= RTOL * np.abs(want).max()
+    assert np.array_equal(got, got.T)
+    again, _ = grm_device(store, eng.ADD)
+    assert np.array_equal(again.cpu().numpy(), got)
+    monkeypatch.setenv("GMAT_B200_GRM_ENGINE", "f64")
+    ref, _ = grm_device(store, eng.ADD)
+    assert np.abs(ref.cpu().numpy() - got).max() <= 1e-12 * np.abs(want).max()
+
+
 def test_grm_engine_selection_and_missing_calls(eng, tmp_path, monkeypatch):
     """auto = int8 kernel for SNP ranges without a missing call, DMMA kernel otherwise (same result as forcing f64);
     forcing i8 on data with missing calls is refused."""
