@@ -37,6 +37,12 @@ def main():
     ap.add_argument("--workdir", default="/tmp/gmat_northstar")
     ap.add_argument("--out", default="gpurun_out/northstar.json")
     ap.add_argument("--kind", default="AA", choices=["AA", "DD", "AD"])
+    ap.add_argument("--records", type=int, default=1,
+                    help="records per individual (> 1: repeated measures, BASELINE configs[4]: GRM list gets an "
+                         "identity for the permanent environment and Z is a real N x n incidence matrix)")
+    ap.add_argument("--first", type=int, default=0,
+                    help="scan only this many first SNPs (evenly spread, plus the first SNP of every planted pair) "
+                         "through snp_lst_0 -- a single-GPU sample of the full shape; 0 = exhaustive")
     args = ap.parse_args()
     import torch
     import torch.distributed as dist
@@ -61,14 +67,19 @@ def main():
         torch.cuda.synchronize()
 
     n, m = args.n, args.m
-    prefix = os.path.join(args.workdir, "ns_n%d_m%d" % (n, m))
+    prefix = os.path.join(args.workdir, "ns_n%d_m%d_r%d_%s" % (n, m, args.records, args.kind))
     t0 = time.perf_counter()
     planted = None
     if rank == 0:
         os.makedirs(args.workdir, exist_ok=True)
-        ds = synth.write_dataset(prefix, n, m, seed=20201013 + 4, n_planted=10, planted_kind=args.kind)
+        ds = synth.write_dataset(prefix, n, m, seed=20201013 + 4, n_planted=10, planted_kind=args.kind,
+                                 records_per_id=args.records)
         planted = ds["planted"]
         del ds
+    if world > 1:
+        box = [planted]
+        dist.broadcast_object_list(box, src=0)
+        planted = box[0]
     barrier()
     t_data = time.perf_counter() - t0
 
@@ -84,6 +95,14 @@ def main():
     else:
         dg = grm_device(store, engine.DOM)[0].cpu().numpy()
         gmat_lst, var_com = [ag, dg, ag * ag], [0.30 * s2, 0.05 * s2, 0.10 * s2, 0.55 * s2]
+    if args.records > 1:                                      # permanent-environment component (SURVEY config C5)
+        gmat_lst = gmat_lst + [np.eye(n)]
+        var_com = [v * 0.8 for v in var_com[:-1]] + [0.15 * s2, var_com[-1] * 0.8]
+    snp_lst_0 = None
+    if args.first > 0:
+        last = m if args.kind == "AD" else m - 1
+        pick = set(np.linspace(0, last - 1, args.first).astype(np.int64).tolist()) | {int(a) for a, _ in planted}
+        snp_lst_0 = sorted(pick)
     del store
     barrier()
     t_grm = time.perf_counter() - t0
@@ -91,10 +110,13 @@ def main():
     out_file = os.path.join(args.workdir, "epi%s_full" % args.kind)
     barrier()
     t0 = time.perf_counter()
-    scan(prefix + ".pheno", prefix, gmat_lst, var_com, p_cut=args.p_cut, out_file=out_file)
+    scan(prefix + ".pheno", prefix, gmat_lst, var_com, snp_lst_0=snp_lst_0, p_cut=args.p_cut, out_file=out_file)
     barrier()
     t_scan = time.perf_counter() - t0
-    n_tests = m * m if args.kind == "AD" else m * (m - 1) // 2
+    if snp_lst_0 is None:
+        n_tests = m * m if args.kind == "AD" else m * (m - 1) // 2
+    else:
+        n_tests = len(snp_lst_0) * m if args.kind == "AD" else int(sum(m - 1 - i for i in snp_lst_0))
 
     if rank == 0:
         # ------------------------------ verification against the oracle (host numpy) ------------------------
@@ -148,9 +170,12 @@ def main():
                 msgs.append("planted %s: oracle p %.3e, in file: %s" % (pr, pv, tuple(pr) in got))
         rng = np.random.Generator(np.random.PCG64(1))
         rnd = []
+        firsts = np.asarray(snp_lst_0 if snp_lst_0 is not None else np.arange(m))
         while len(rnd) < 2000:
-            a, b = sorted(rng.integers(0, m, size=2).tolist())
-            if a != b and (a, b) not in got:
+            a, b = int(firsts[rng.integers(0, len(firsts))]), int(rng.integers(0, m))
+            if args.kind != "AD" and b <= a:
+                continue
+            if (a, b) not in got:
                 rnd.append((a, b))
         _, _, rp = stats(rnd)
         if not np.all(rp >= args.p_cut):
@@ -158,8 +183,11 @@ def main():
             msgs.append("unreported random pairs below p_cut: %d" % int(np.sum(rp < args.p_cut)))
         t_verify = time.perf_counter() - t0
         res = {
-            "what": "remma_epi%s exact, exhaustive, synthetic n=%d x m=%d, p_cut=%g, through the drop-in API "
-                    "(files in, file out), %d x B200" % (args.kind, n, m, args.p_cut, world),
+            "what": "remma_epi%s exact, %s, synthetic n=%d x m=%d, %d record(s) per individual, %d GRMs, p_cut=%g, "
+                    "through the drop-in API (files in, file out), %d x B200"
+                    % (args.kind, "exhaustive" if snp_lst_0 is None else "%d first SNPs (snp_lst_0)" % len(snp_lst_0),
+                       n, m, args.records, len(gmat_lst), args.p_cut, world),
+            "records": n * args.records,
             "n_gpus": world, "tests": n_tests, "seconds_scan_call": t_scan, "pairs_per_s_e2e": n_tests / t_scan,
             "seconds_dataset": t_data, "seconds_grm": t_grm, "seconds_verify": t_verify,
             "rows_in_file": len(got), "var_com": var_com, "host_cores": os.cpu_count(), "planted": planted, "planted_significant": planted_sig,
