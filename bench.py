@@ -43,9 +43,9 @@ METRIC = "snp_pairs_per_sec_remma_epiAA_exact"
 # 10 MB + LUTs, read once; the capture ran 128 first-SNPs of the same data shape, the compulsory bytes are the same)
 EXACT_TRAFFIC_BYTES = 28.9e6
 # dram__bytes_read.sum + dram__bytes_write.sum of one i8_scan_pair_kernel launch (64 first SNPs of this shape), from the
-# committed ncu --set full capture (profiles/r01_kernels_v6.md): 2.141 GB read + 4.7 MB written; the compulsory bytes
+# committed ncu --set full capture (profiles/r01_kernels_v9.md): 1.793 GB read + 3.9 MB written; the compulsory bytes
 # are the digit planes once (1.07 GB, written by i8_split_kernel just before) + G8 40 MB + side terms 20 MB
-I8_TRAFFIC_BYTES = 2.146e9
+I8_TRAFFIC_BYTES = 1.797e9
 CONFIG = {"workload": "remma_epiAA exact test, synthetic n=%d x m=%d, GRMs [A, A*A] (BASELINE configs[2])"
                       % (N_ID, N_SNP),
           "step": "one batch of %d first-SNPs (evenly spread blocks of 8), all j>i (~1.0e7 pairs) per rank" % BATCH,
