@@ -96,6 +96,18 @@ int run_screen(char *bed_file, long long num_id, long long num_snp, long long *s
         GB_CUDA(cudaMemcpy(table.p, cut_table, sizeof(double) * 111, cudaMemcpyHostToDevice));
     }
 
+    // engine of the screen: int8 tensor cores when no genotype is missing (GMAT_B200_SCREEN_ENGINE=f64 forces DMMA)
+    const char *f64_only = getenv("GMAT_B200_SCREEN_ENGINE");
+    if (f64_only != nullptr && strcmp(f64_only, "f64") != 0) f64_only = nullptr;
+    bool clean = false;
+    {
+        std::vector<int> hc((size_t)(4 * num_snp));
+        GB_CUDA(cudaMemcpy(hc.data(), st.counts.p, sizeof(int) * hc.size(), cudaMemcpyDeviceToHost));
+        long long missing = 0;
+        for (long long s = 0; s < num_snp; ++s) missing += hc[(size_t)(4 * s + 1)];
+        clean = missing == 0;
+    }
+
     std::vector<gmat_b200_hit> all;
     std::vector<int> dir;
     for (int q = 0; q < n_pass; ++q) {
@@ -122,10 +134,17 @@ int run_screen(char *bed_file, long long num_id, long long num_snp, long long *s
             DevBuf h;
             GB_TRY(h.alloc(sizeof(gmat_b200_hit) * (size_t)cap));
             GB_CUDA(cudaMemset(count.p, 0, sizeof(unsigned long long)));
-            GB_TRY(gmat_b200_epi_eff(st.bed.as<unsigned char>(), st.n, st.m, st.row_bytes, lu, lv,
-                                     py.as<double>(), ilist.as<long long>(), len_snp_lst_0, ps.flags, eff_cut,
-                                     cut_table ? table.as<double>() : nullptr, bI.as<int>(), bJ.as<int>(),
-                                     h.as<gmat_b200_hit>(), cap, count.as<unsigned long long>(), nullptr));
+            if (clean && f64_only == nullptr)              // no missing call: int8 prefilter + FP64 re-test (screen_i8.cu)
+                GB_TRY(gmat_b200_epi_eff_i8(st.bed.as<unsigned char>(), st.n, st.m, st.row_bytes, lu, lv, ps.codingU,
+                                            ps.codingV, py.as<double>(), ilist.as<long long>(), len_snp_lst_0,
+                                            ps.flags, eff_cut, cut_table ? table.as<double>() : nullptr, bI.as<int>(),
+                                            bJ.as<int>(), h.as<gmat_b200_hit>(), cap,
+                                            count.as<unsigned long long>(), nullptr, nullptr));
+            else
+                GB_TRY(gmat_b200_epi_eff(st.bed.as<unsigned char>(), st.n, st.m, st.row_bytes, lu, lv,
+                                         py.as<double>(), ilist.as<long long>(), len_snp_lst_0, ps.flags, eff_cut,
+                                         cut_table ? table.as<double>() : nullptr, bI.as<int>(), bJ.as<int>(),
+                                         h.as<gmat_b200_hit>(), cap, count.as<unsigned long long>(), nullptr));
             unsigned long long cnt = 0;
             GB_CUDA(cudaMemcpy(&cnt, count.p, sizeof(cnt), cudaMemcpyDeviceToHost));
             if ((long long)cnt > cap) { cap = (long long)cnt; continue; }   // exact count known: retry once

@@ -402,9 +402,29 @@ def epi_exact_pairs(store, lutU, lutV, py_dev, packed, pairs):
     return hits_to_numpy(out, k)
 
 
+def screen_engine(store):
+    """Which engine runs the approximate screen: "i8" (int8 tensor-core prefilter + FP64 re-test of the survivors;
+    needs a store without missing calls) or "f64" (DMMA).  GMAT_B200_SCREEN_ENGINE = auto (default) | i8 | f64."""
+    want = os.environ.get("GMAT_B200_SCREEN_ENGINE", "auto").lower()
+    if want not in ("auto", "i8", "f64"):
+        raise ValueError("GMAT_B200_SCREEN_ENGINE must be auto, i8 or f64")
+    if want == "f64":
+        return "f64"
+    clean = store.n_missing() == 0
+    if want == "i8" and not clean:
+        raise ValueError("the int8 screen needs genotypes without missing calls")
+    return "i8" if clean else "f64"
+
+
+LAST_SCREEN_ENGINE = None      # "i8" / "f64": what the last epi_eff call actually ran (tests, bench)
+
+
 def epi_eff(store, lutU, lutV, py_dev, ilist, flags, eff_cut, cut_table=None, binI=None, binJ=None,
-            cap=1 << 20):
-    """Approximate screen on device buffers; returns HIT_DTYPE array (unordered)."""
+            cap=1 << 20, codings=None):
+    """Approximate screen on device buffers; returns HIT_DTYPE array (unordered).  ``codings`` = (coding of lutU,
+    coding of lutV): with it (and a store without missing calls) the int8 tensor-core engine runs, see
+    screen_engine; without it the FP64 DMMA kernel."""
+    global LAST_SCREEN_ENGINE
     dev = store.device
     il = torch.as_tensor(np.ascontiguousarray(ilist, dtype=np.int64)).to(dev)
     count = torch.zeros((1,), dtype=torch.int64, device=dev)
@@ -413,16 +433,29 @@ def epi_eff(store, lutU, lutV, py_dev, ilist, flags, eff_cut, cut_table=None, bi
         tab = torch.as_tensor(np.ascontiguousarray(cut_table, dtype=np.float64)).to(dev)
         bI = torch.as_tensor(np.ascontiguousarray(binI, dtype=np.int32)).to(dev)
         bJ = torch.as_tensor(np.ascontiguousarray(binJ, dtype=np.int32)).to(dev)
+    which = screen_engine(store) if codings is not None else "f64"
+    used = ffi.new("int *")
     while True:
         hits = alloc_hits(cap, dev)
         count.zero_()
-        check(lib.gmat_b200_epi_eff(
-            _p(store.bed, "unsigned char *"), store.n, store.m, store.row_bytes,
-            _p(lutU, "double *"), _p(lutV, "double *"), _p(py_dev, "double *"),
-            _p(il, "long long *"), il.numel(), flags, float(eff_cut),
-            _p(tab, "double *"), _p(bI, "int *"), _p(bJ, "int *"),
-            ffi.cast("gmat_b200_hit *", hits.data_ptr()), cap,
-            ffi.cast("unsigned long long *", count.data_ptr()), _stream()), "gmat_b200_epi_eff")
+        if which == "i8":
+            check(lib.gmat_b200_epi_eff_i8(
+                _p(store.bed, "unsigned char *"), store.n, store.m, store.row_bytes,
+                _p(lutU, "double *"), _p(lutV, "double *"), int(codings[0]), int(codings[1]), _p(py_dev, "double *"),
+                _p(il, "long long *"), il.numel(), flags, float(eff_cut),
+                _p(tab, "double *"), _p(bI, "int *"), _p(bJ, "int *"),
+                ffi.cast("gmat_b200_hit *", hits.data_ptr()), cap,
+                ffi.cast("unsigned long long *", count.data_ptr()), used, _stream()), "gmat_b200_epi_eff_i8")
+            LAST_SCREEN_ENGINE = "i8" if used[0] == 1 else "f64"
+        else:
+            check(lib.gmat_b200_epi_eff(
+                _p(store.bed, "unsigned char *"), store.n, store.m, store.row_bytes,
+                _p(lutU, "double *"), _p(lutV, "double *"), _p(py_dev, "double *"),
+                _p(il, "long long *"), il.numel(), flags, float(eff_cut),
+                _p(tab, "double *"), _p(bI, "int *"), _p(bJ, "int *"),
+                ffi.cast("gmat_b200_hit *", hits.data_ptr()), cap,
+                ffi.cast("unsigned long long *", count.data_ptr()), _stream()), "gmat_b200_epi_eff")
+            LAST_SCREEN_ENGINE = "f64"
         cnt = int(count.item())
         if cnt <= cap:
             return hits_to_numpy(hits, cnt)

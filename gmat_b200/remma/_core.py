@@ -438,15 +438,17 @@ class Prepared(object):
         la = st.lut(engine.ADD, engine.FREQ_CLOOP)
         ld = st.lut(engine.DOM, engine.FREQ_CLOOP)
         ilist = np.asarray(list(snp_lst_0), dtype=np.int64)
+        A, D = engine.ADD, engine.DOM
         if k.name == 'AD':
-            passes = [(la, ld, engine.EFF_GE), (ld, la, engine.EFF_SWAP)]
+            passes = [(la, ld, engine.EFF_GE, (A, D)), (ld, la, engine.EFF_SWAP, (D, A))]
         elif k.name == 'AA':
-            passes = [(la, la, 0)]
+            passes = [(la, la, 0, (A, A))]
         else:
-            passes = [(ld, ld, 0)]
+            passes = [(ld, ld, 0, (D, D))]
         rows = []
-        for d, (lu, lv, flags) in enumerate(passes):
-            h = engine.epi_eff(st, lu, lv, self.model.py, ilist, flags, eff_cut, cut_table, bin_i, bin_j)
+        for d, (lu, lv, flags, codings) in enumerate(passes):
+            h = engine.epi_eff(st, lu, lv, self.model.py, ilist, flags, eff_cut, cut_table, bin_i, bin_j,
+                               codings=codings)
             swap = bool(flags & engine.EFF_SWAP)
             for s0, s1, e in zip(h['snp_0'].tolist(), h['snp_1'].tolist(), h['eff'].tolist()):
                 rows.append(((s1, s0, d) if swap else (s0, s1, d), s0, s1, e))

@@ -142,6 +142,23 @@ int gmat_b200_epi_eff(const unsigned char *bed_dev, long long n, long long m, lo
                       gmat_b200_hit *hits_dev, long long cap, unsigned long long *count_dev,
                       void *stream);
 
+/* The same screen with the INT8 tensor cores deciding which pairs are worth the FP64 arithmetic
+ * (gmat_b200/csrc/screen_i8.cu).  Stage 1: eff = Q - o_j t_i - o_i (t_j - o_j P) with Q_ij = sum_k a_ik a_jk py_k
+ * evaluated for every pair from two exact int8 GEMMs (py cut into two base-128 digits, tcgen05.mma cta_group::2
+ * kind::i8) in FP32; pairs with |eff~| >= cut - margin survive, margin a rigorous bound of everything stage 1 drops.
+ * Stage 2: eff of the survivors in FP64 from the LUT values (the arithmetic of gmat_b200_epi_eff) and the reference's
+ * threshold -- so the reported set and the reported values are FP64 results.  codingU / codingV: the codings the two
+ * LUTs were built for (GMAT_B200_CODING_ADD / _DOM); the store must not contain a missing call (callers use
+ * gmat_b200_epi_eff then).  Falls back to gmat_b200_epi_eff by itself when the margin is not small against the cut
+ * (e.g. eff_cut = 0) or the survivors do not fit its candidate buffer; *engine_used (optional) = 1 when the int8
+ * path produced the result, 0 after a fallback.  Synchronises the stream (it reads two scalars back).            */
+int gmat_b200_epi_eff_i8(const unsigned char *bed_dev, long long n, long long m, long long row_bytes,
+                         const double *lutU_dev, const double *lutV_dev, int codingU, int codingV,
+                         const double *py_dev, const long long *ilist_dev, long long n_i, int flags, double eff_cut,
+                         const double *cut_table_dev, const int *binI_dev, const int *binJ_dev,
+                         gmat_b200_hit *hits_dev, long long cap, unsigned long long *count_dev,
+                         int *engine_used, void *stream);
+
 /* Z'PZ re-tiled for the exact kernel: lower block-triangle, 128-row blocks, DMMA fragment order.
  * gmat_b200_pvp_packed_elems(n) doubles are needed.                                            */
 long long gmat_b200_pvp_packed_elems(long long n);
