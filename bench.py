@@ -483,14 +483,34 @@ def extras(engine, torch, synth, store, model, lut, args, prefix, pymat, e2e_f64
                                **peaks}
     if e2e_f64 is not None:
         out["exact_f64_engine"]["e2e_pairs_per_s"] = e2e_f64
-    # approximate screen: full scan of the C3 data (1.9999e8 pairs), F_approx = 2n flop per pair
+    # approximate screen: full scan of the C3 data (1.9999e8 pairs).  Default engine (no missing call): int8
+    # tensor-core prefilter (2 planes x 2n int8 ops per pair) + FP64 re-test of the survivors (screen_i8.cu); the
+    # FP64 DMMA kernel (F_approx = 2n flop per pair, eff.cu) beside it.  The cut is a real one (p_cut = 1e-5 on a
+    # variance of the size random pairs show), so the survivors, the re-test and the hit records are in the time.
     la = store.lut(engine.ADD, engine.FREQ_CLOOP)
     full = np.arange(N_SNP - 1, dtype=np.int64)
-    t = timed(lambda: engine.epi_eff(store, la, la, model.py, full, 0, 1e30))
     pairs = N_SNP * (N_SNP - 1) // 2
-    out["approx_screen"] = {"pairs_per_s": pairs / t, "seconds": t, "pairs": pairs,
-                            "tflops_algorithmic": pairs * 2.0 * N_ID / t / 1e12,
-                            "workload": "remma_epiAA_eff_cpu formulation, full scan n=%d x m=%d" % (N_ID, N_SNP)}
+    sample = engine.epi_eff(store, la, la, model.py, np.arange(0, N_SNP - 1, 97, dtype=np.int64), 0, 0.0)
+    from scipy.stats import chi2
+    cut = float(np.sqrt(chi2.isf(P_CUT, 1) * np.median(sample["eff"] ** 2) / chi2.ppf(0.5, 1)))
+    box = {}
+
+    def run_screen(codings):
+        box["hits"] = engine.epi_eff(store, la, la, model.py, full, 0, cut, codings=codings)
+    t = timed(lambda: run_screen((engine.ADD, engine.ADD)))
+    which = engine.LAST_SCREEN_ENGINE
+    n_hits = len(box["hits"])
+    out["approx_screen"] = {"engine": which, "pairs_per_s": pairs / t, "seconds": t, "pairs": pairs, "hits": n_hits,
+                            "eff_cut": cut,
+                            "int8_tops_algorithmic": pairs * 4.0 * N_ID / t / 1e12 if which == "i8" else None,
+                            "fp64_equivalent_tflops": pairs * 2.0 * N_ID / t / 1e12,
+                            "workload": "remma_epiAA_eff_cpu formulation, full scan n=%d x m=%d, whole call "
+                                        "(operand build, prefilter, FP64 re-test, hit records)" % (N_ID, N_SNP)}
+    t64 = timed(lambda: run_screen(None))
+    out["approx_screen"]["f64_engine"] = {"pairs_per_s": pairs / t64, "seconds": t64, "hits": len(box["hits"]),
+                                          "same_hit_count": len(box["hits"]) == n_hits,
+                                          "tflops_algorithmic": pairs * 2.0 * N_ID / t64 / 1e12,
+                                          "kernel": "epi_eff_kernel (FP64 DMMA)"}
     if not args.no_cpu:
         # the reference's own C screen (oracle/_ref, compiled from gmat/remma/_remma_epi_eff_cpu.c) on the same
         # files with all host threads; bounded sample of first-SNPs.  It re-reads and re-codes the whole .bed into

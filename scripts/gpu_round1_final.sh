@@ -25,10 +25,10 @@ echo "bench ref rc=$?"; cut -c1-300 gpurun_out/bench_ref.json
 timeout 900 python -m pytest tests -m gpu -q --maxfail=20 --timeout=300 --ignore=tests/test_gpu_i8.py \
     > gpurun_out/pytest_gpu.log 2>&1
 echo "pytest rc=$?"; tail -8 gpurun_out/pytest_gpu.log
-PK="python scripts/profile_kernels.py --reps 0 --only i8,grm"
+PK="python scripts/profile_kernels.py --reps 0 --only i8,grm,eff"
 timeout 300 $PK > gpurun_out/prof_plain.log 2>&1 &&
 timeout 600 ncu --set full --clock-control none --import-source on \
-    -k regex:'i8_scan_pair|i8_gram_pair|i8_dosage_t|i8_split' -c 6 \
+    -k regex:'i8_scan_pair|i8_gram_pair|i8_dosage_t|i8_split|i8_screen_pair|sc_planes|screen_exact' -c 10 \
     -f -o gpurun_out/prof_kernels $PK > gpurun_out/prof_ncu.log 2>&1
 echo "profile rc=$?"; tail -2 gpurun_out/prof_plain.log; tail -2 gpurun_out/prof_ncu.log
 BN="python bench.py --steps 2 --warmup 1 --no-cpu --no-extra"

@@ -89,6 +89,12 @@ def main():
         t = timed(lambda: engine.epi_eff(store, la, la, py, full, 0, 1e30))
         out["eff"] = {"seconds": t, "pairs": pairs, "pairs_per_s": pairs / t,
                       "tflops_algorithmic": pairs * 2.0 * n / t / 1e12}
+        # the int8 tensor-core screen (prefilter + FP64 re-test) at a cut that keeps ~1e-5 of the pairs
+        smp = engine.epi_eff(store, la, la, py, np.arange(0, m - 1, 97, dtype=np.int64), 0, 0.0)
+        cut = float(np.quantile(np.abs(smp["eff"]), 1.0 - 1e-5))
+        t = timed(lambda: engine.epi_eff(store, la, la, py, full, 0, cut, codings=(engine.ADD, engine.ADD)))
+        out["eff_i8"] = {"seconds": t, "pairs": pairs, "pairs_per_s": pairs / t, "engine": engine.LAST_SCREEN_ENGINE,
+                         "int8_tops_algorithmic": pairs * 4.0 * n / t / 1e12}
     if "decode" in only:
         n2, m2 = args.dec_n, args.dec_m
         st2 = engine.GenotypeStore.from_device_payload(synth.device_payload(n2, m2, 12, dev, engine.row_stride(n2)), n2)
