@@ -20,6 +20,7 @@
 // Tiles: M = 256 second SNPs (two CTAs x 128 TMEM lanes) x N = 128 first SNPs x K = all ids in slabs of 128; the S
 // plane accumulators of a tile sit side by side in TMEM (S x 128 columns), double-buffered (2 x 256 columns).
 #include "tc5.cuh"
+#include <cstdlib>
 #include <vector>
 
 namespace gb {
@@ -493,15 +494,21 @@ extern "C" int gmat_b200_epi_eff_i8(const unsigned char *bed_dev, long long n, l
     GB_CUDA(cudaFuncSetAttribute(i8_screen_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
 
     // ---- first SNPs in chunks (plane buffer <= 1 GiB) ----
-    long long chunk = (1LL << 30) / ((long long)SC_S * ld);
+    long long budget = 1LL << 30;
+    if (const char *e = getenv("GMAT_B200_SCREEN_SCRATCH_BYTES")) {     // tests force several chunks with this
+        const long long v = atoll(e);
+        if (v > 0) budget = v;
+    }
+    long long chunk = budget / ((long long)SC_S * ld);
     chunk = chunk / SC_TI * SC_TI;
     if (chunk < SC_TI) chunk = SC_TI;
     for (long long c0 = 0; c0 < n_i; c0 += chunk) {
         const int ni = (int)((n_i - c0 < chunk) ? n_i - c0 : chunk);
         const int n_ib = (ni + SC_TI - 1) / SC_TI, plane_rows = n_ib * SC_TI;
-        signed char *pu = sc.get<signed char>((size_t)SC_S * plane_rows * ld);
-        float *tU = sc.get<float>((size_t)plane_rows), *oU = sc.get<float>((size_t)plane_rows);
-        int *tiles = sc.get<int>((size_t)2 * n_ib + 2);
+        Scratch csc(st);                                          // this chunk's buffers: freed (stream-ordered) per chunk
+        signed char *pu = csc.get<signed char>((size_t)SC_S * plane_rows * ld);
+        float *tU = csc.get<float>((size_t)plane_rows), *oU = csc.get<float>((size_t)plane_rows);
+        int *tiles = csc.get<int>((size_t)2 * n_ib + 2);
         GB_CHECK_ARG(pu && tU && oU && tiles, "out of device memory");
         sc_planes_kernel<<<(unsigned)plane_rows, 256, 0, st>>>(g8U, ld, ilist_dev + c0, ni, plane_rows, dig, lutU_dev,
                                                                tUall, pu, tU, oU);

@@ -104,6 +104,13 @@ def test_i8_screen_maf_table_small_cuts_and_forced_engines(eng, tmp_path, monkey
     # hit buffer smaller than the number of hits: counted, retried with the exact capacity
     small = eng.epi_eff(store, la, la, pyd, lst, 0, base, cap=16, codings=(eng.ADD, eng.ADD))
     assert eng.LAST_SCREEN_ENGINE == "i8" and len(small) == int(np.sum(np.abs(every["eff"]) > base))
+    # first SNPs in several chunks (plane-buffer budget of one 128-SNP block): same hits
+    whole = eng.epi_eff(store, la, la, pyd, lst, 0, base, codings=(eng.ADD, eng.ADD))
+    monkeypatch.setenv("GMAT_B200_SCREEN_SCRATCH_BYTES", "1")
+    parts = eng.epi_eff(store, la, la, pyd, lst, 0, base, codings=(eng.ADD, eng.ADD))
+    monkeypatch.delenv("GMAT_B200_SCREEN_SCRATCH_BYTES")
+    assert eng.LAST_SCREEN_ENGINE == "i8" and key(whole) == key(parts) and len(whole) == len(small)
+    assert sorted(whole["eff"].tolist()) == sorted(parts["eff"].tolist())
     monkeypatch.setenv("GMAT_B200_SCREEN_ENGINE", "f64")
     eng.epi_eff(store, la, la, pyd, lst, 0, base, codings=(eng.ADD, eng.ADD))
     assert eng.LAST_SCREEN_ENGINE == "f64"
