@@ -416,7 +416,7 @@ extern "C" int gmat_b200_epi_eff_i8(const unsigned char *bed_dev, long long n, l
                                     const int *binJ_dev, gmat_b200_hit *hits_dev, long long cap,
                                     unsigned long long *count_dev, int *engine_used, void *stream) {
     GB_CHECK_ARG(bed_dev && lutU_dev && lutV_dev && py_dev && ilist_dev && count_dev, "NULL pointer");
-    GB_CHECK_ARG(n > 0 && m > 0 && n_i >= 0 && m < (1LL << 31) && n < 60000, "sizes");
+    GB_CHECK_ARG(n > 0 && m > 0 && n_i >= 0, "sizes");
     GB_CHECK_ARG(row_bytes >= (n + 3) / 4 && row_bytes % 16 == 0, "row_bytes");
     GB_CHECK_ARG((codingU == GMAT_B200_CODING_ADD || codingU == GMAT_B200_CODING_DOM) &&
                  (codingV == GMAT_B200_CODING_ADD || codingV == GMAT_B200_CODING_DOM), "coding");
@@ -429,6 +429,8 @@ extern "C" int gmat_b200_epi_eff_i8(const unsigned char *bed_dev, long long n, l
 #define SC_FALLBACK()                                                                                            \
     return gmat_b200_epi_eff(bed_dev, n, m, row_bytes, lutU_dev, lutV_dev, py_dev, ilist_dev, n_i, flags, eff_cut,   \
                              cut_table_dev, binI_dev, binJ_dev, hits_dev, cap, count_dev, stream)
+    // int32 plane sums must convert to FP32 exactly (|Y| <= 256 n < 2^24) and SNP indices are ints in the kernels
+    if (n >= 60000 || m >= (1LL << 31) || n_i >= (1LL << 31)) SC_FALLBACK();
     Scratch sc(st);
     // ---- scale of py, margin of stage 1, is the int8 path worth it? ----
     double *stats = sc.get<double>(2);
