@@ -22,7 +22,16 @@ static void format_rows(const double *mat, long long cols, long long r0, long lo
     for (long long r = r0; r < r1; ++r) {
         const double *row = mat + r * cols;
         for (long long c = 0; c < cols; ++c) {
-            const int len = snprintf(buf, sizeof(buf), "%.18e", row[c]);
+            // "%.18e": std::to_chars with a precision is correctly rounded like printf and prints the same
+            // two-digit-minimum exponent, several times faster; non-finite values keep printf's spelling
+            int len;
+            if (std::isfinite(row[c])) {
+                len = (int)(std::to_chars(buf, buf + sizeof(buf), row[c], std::chars_format::scientific, 18).ptr - buf);
+            } else {                                             // Python's '%.18e' % x: nan (never -nan), inf, -inf
+                const char *t = std::isnan(row[c]) ? "nan" : (row[c] < 0 ? "-inf" : "inf");
+                len = (int)strlen(t);
+                memcpy(buf, t, (size_t)len);
+            }
             out.append(buf, (size_t)len);
             out.push_back(c + 1 < cols ? ' ' : '\n');
         }
@@ -113,6 +122,36 @@ static void format_tril(const double *mat, long long n, long long r0, long long 
     }
 }
 
+// Row chunks [first[c], first[c+1]) are formatted by `nt` threads a round at a time and written in order; the
+// threads of round k+1 format while the caller's thread writes round k (two sets of buffers).
+template <class Fmt>
+static bool write_chunks_pipelined(FILE *f, const std::vector<long long> &first, int nt, Fmt fmt) {
+    const long long n_chunks = (long long)first.size() - 1;
+    std::vector<std::string> bufs[2] = {std::vector<std::string>((size_t)nt), std::vector<std::string>((size_t)nt)};
+    std::vector<std::thread> pool[2];
+    auto launch = [&](long long round) {
+        const int set = (int)(round & 1);
+        for (int t = 0; t < nt; ++t) {
+            const long long c = round * nt + t;
+            if (c >= n_chunks) break;
+            pool[set].emplace_back([&, c, t, set] { fmt(first[(size_t)c], first[(size_t)c + 1], bufs[set][(size_t)t]); });
+        }
+    };
+    const long long rounds = (n_chunks + nt - 1) / nt;
+    bool ok = true;
+    if (rounds > 0) launch(0);
+    for (long long r = 0; r < rounds; ++r) {
+        const int set = (int)(r & 1);
+        const size_t used = pool[set].size();
+        for (auto &th : pool[set]) th.join();
+        pool[set].clear();
+        if (r + 1 < rounds) launch(r + 1);
+        for (size_t t = 0; t < used && ok; ++t)
+            ok = fwrite(bufs[set][t].data(), 1, bufs[set][t].size(), f) == bufs[set][t].size();
+    }
+    return ok;
+}
+
 }  // namespace gb
 
 using namespace gb;
@@ -135,24 +174,15 @@ extern "C" int gmat_b200_write_tril_host(const char *path, const double *mat, lo
     }
     int nt = threads > 0 ? threads : (int)std::thread::hardware_concurrency();
     nt = std::max(1, std::min(nt, 256));
-    std::vector<std::string> bufs((size_t)nt);
-    bool ok = true;
-    long long r = 0;
-    while (r < n && ok) {
-        // a round = nt chunks of ~100k lines each (row r holds r + 1 lines), written in order
-        std::vector<std::thread> pool;
-        int used = 0;
-        for (int t = 0; t < nt && r < n; ++t) {
-            long long r1 = r, lines = 0;
-            while (r1 < n && lines < 100000) { lines += r1 + 1; ++r1; }
-            pool.emplace_back(format_tril, mat, n, r, r1, ids, id_off, std::ref(bufs[(size_t)t]));
-            ++used;
-            r = r1;
-        }
-        for (auto &th : pool) th.join();
-        for (int t = 0; t < used && ok; ++t)
-            ok = fwrite(bufs[(size_t)t].data(), 1, bufs[(size_t)t].size(), f) == bufs[(size_t)t].size();
+    std::vector<long long> first{0};                            // chunks of ~100k lines each (row r holds r + 1 lines)
+    for (long long r = 0; r < n;) {
+        long long lines = 0;
+        while (r < n && lines < 100000) { lines += r + 1; ++r; }
+        first.push_back(r);
     }
+    bool ok = write_chunks_pipelined(f, first, nt, [&](long long r0, long long r1, std::string &out) {
+        format_tril(mat, n, r0, r1, ids, id_off, out);
+    });
     if (fclose(f) != 0) ok = false;
     if (!ok) {
         set_error("write to %s failed", path);
@@ -174,21 +204,11 @@ extern "C" int gmat_b200_savetxt_host(const char *path, const double *mat, long 
     nt = std::max(1, std::min(nt, 256));
     // rows per thread per round: ~4 MB of text each
     long long per = std::max(1LL, (4LL << 20) / std::max(1LL, cols * 26));
-    std::vector<std::string> bufs((size_t)nt);
-    bool ok = true;
-    for (long long base = 0; base < rows && ok; base += per * nt) {
-        std::vector<std::thread> pool;
-        int used = 0;
-        for (int t = 0; t < nt; ++t) {
-            const long long r0 = base + t * per, r1 = std::min(rows, r0 + per);
-            if (r0 >= rows) break;
-            ++used;
-            pool.emplace_back(format_rows, mat, cols, r0, r1, std::ref(bufs[(size_t)t]));
-        }
-        for (auto &th : pool) th.join();
-        for (int t = 0; t < used && ok; ++t)
-            ok = fwrite(bufs[(size_t)t].data(), 1, bufs[(size_t)t].size(), f) == bufs[(size_t)t].size();
-    }
+    std::vector<long long> first{0};
+    for (long long r = 0; r < rows; r += per) first.push_back(std::min(rows, r + per));
+    bool ok = write_chunks_pipelined(f, first, nt, [&](long long r0, long long r1, std::string &out) {
+        format_rows(mat, cols, r0, r1, out);
+    });
     if (fclose(f) != 0) ok = false;
     if (!ok) {
         set_error("write to %s failed", path);

@@ -195,6 +195,8 @@ def test_savetxt_host_is_byte_identical_to_numpy(tmp_path):
     rng = np.random.Generator(np.random.PCG64(4))
     mats = [rng.normal(size=(37, 53)) * 10.0 ** rng.integers(-30, 30, size=(37, 53)),
             np.array([[0.0, -0.0, 1.0, -1.0, 1e-310, 1.7976931348623157e308, 5e-324, 0.1, 1 / 3]]),
+            np.array([[np.nan, -np.nan, np.inf, -np.inf, np.copysign(np.nan, -1.0)]]),
+            rng.integers(0, 2 ** 64, size=(400, 25), dtype=np.uint64).view(np.float64),   # any bit pattern
             rng.normal(size=(1300, 7)), np.zeros((0, 4)), rng.normal(size=(5, 1))]
     for k, mat in enumerate(mats):
         mat = np.ascontiguousarray(mat)
