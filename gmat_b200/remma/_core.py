@@ -308,6 +308,26 @@ def _screen_defaults(kind, maf, snp_lst_0, num_snp):
     return snp_lst_0
 
 
+def _append_p_app(temp_file, out_file, deno_of):
+    """The 'Add the approximate P values' step of the screen front ends (remma_epiAA_eff.py:85-95,
+    remma_epiAA_maf_eff.py:88-101): every row of the C screen's text file gets chi_app = eff^2 / deno -- eff re-read
+    from the %g-truncated text, like the reference -- and p_app = chi2.sf(chi_app, 1).  Same bytes as the reference's
+    per-line loop (same IEEE operations, same str() of the same doubles), evaluated as arrays: the loop costs 70 us a
+    row in scipy's scalar path, more than the whole GPU screen for a few hundred rows."""
+    with open(temp_file) as fin:
+        head_line = fin.readline().strip() + ' chi_app p_app\n'
+        rows = [line.split() for line in fin]
+    with open(out_file, 'w') as fout:
+        fout.write(head_line)
+        if rows:
+            eff = np.array([float(r[-1]) for r in rows], dtype=np.float64)
+            chi_app = eff * eff / deno_of(rows)
+            p_app = chi2.sf(chi_app, 1)
+            fout.write(''.join(' '.join(r + [str(c), str(q)]) + '\n'
+                               for r, c, q in zip(rows, chi_app.tolist(), p_app)))
+    os.remove(temp_file)
+
+
 def eff_screen(kind, y, xmat, zmat, gmat_lst, var_com, bed_file, snp_lst_0=None, var_app=1.0, p_cut=1.0e-5,
                out_file='epi_eff'):
     logging.info("Calculate the phenotypic covariance matrix and inversion")
@@ -336,15 +356,7 @@ def eff_screen(kind, y, xmat, zmat, gmat_lst, var_com, bed_file, snp_lst_0=None,
     logging.info("Running time: Clock time, {:.5f} sec; CPU time, {:.5f} sec.".format(clock_t1 - clock_t0,
                                                                                    cpu_t1 - cpu_t0))
     logging.info('Add the approximate P values')
-    with open(temp_file) as fin, open(out_file, 'w') as fout:
-        head_line = fin.readline().strip() + ' chi_app p_app\n'
-        fout.write(head_line)
-        for line in fin:
-            arr = line.split()
-            chi_app = float(arr[-1]) * float(arr[-1]) / var_app      # from the %g-truncated text, like the reference
-            p_app = chi2.sf(chi_app, 1)
-            fout.write(' '.join(arr + [str(chi_app), str(p_app)]) + '\n')
-    os.remove(temp_file)
+    _append_p_app(temp_file, out_file, lambda rows: var_app)
     return 0
 
 
@@ -396,16 +408,9 @@ def maf_eff_screen(kind, y, xmat, zmat, gmat_lst, var_com, bed_file, snp_lst_0=N
         rc = fn(pbed_file, num_id, num_snp, psnp_lst_0, len(snp_lst_0), ppymat, pf, peff_cut, pout_file)
     check(rc, 'remma_epi%s_maf_eff_cpu' % kind.name)
     logging.info('Add the approximate P values')
-    with open(temp_file) as fin, open(out_file, 'w') as fout:
-        head_line = fin.readline().strip() + ' chi_app p_app\n'
-        fout.write(head_line)
-        for line in fin:
-            arr = line.split()
-            deno = freq_deno[freq[int(arr[0])] * 10 + freq2[int(arr[1])]]
-            chi_app = float(arr[-1]) * float(arr[-1]) / deno
-            p_app = chi2.sf(chi_app, 1)
-            fout.write(' '.join(arr + [str(chi_app), str(p_app)]) + '\n')
-    os.remove(temp_file)
+    freq_deno = np.asarray(freq_deno, dtype=np.float64)
+    _append_p_app(temp_file, out_file,
+                  lambda rows: freq_deno[freq[[int(r[0]) for r in rows]] * 10 + freq2[[int(r[1]) for r in rows]]])
     return 0
 
 
@@ -575,13 +580,15 @@ def approx(kind, pheno_file, bed_file, gmat_lst, var_com, p_cut=1.0e-5, num_rand
         hits = ctx.screen(snp_lst_0, cut_table=np.sqrt(chi_cut * freq_deno), bin_i=bi, bin_j=bj)
         deno = lambda s0, s1: freq_deno[bi[s0] * 10 + bj[s1]]              # noqa: E731
     # approximate p from the %g-truncated effect, exactly like the text round trip of the reference
+    # (as arrays: the same IEEE operations and the same str() of the same doubles as a per-row loop, without scipy's
+    # 70 us scalar call per row)
+    surv = [(s0, s1) for s0, s1, _ in hits]
     p_dct = {}
-    surv = []
-    for s0, s1, e in hits:
-        e_txt = '%g' % e
-        chi_app = float(e_txt) * float(e_txt) / deno(s0, s1)
-        p_dct['%d %d' % (s0, s1)] = str(chi2.sf(chi_app, 1))
-        surv.append((s0, s1))
+    if hits:
+        e_trunc = np.array([float('%g' % e) for _, _, e in hits], dtype=np.float64)
+        den = np.array([deno(s0, s1) for s0, s1 in surv], dtype=np.float64)
+        p_app = chi2.sf(e_trunc * e_trunc / den, 1)
+        p_dct = {'%d %d' % k: str(q) for k, q in zip(surv, p_app)}
     logging.info("\n\n#####Calculate exact p values for top SNP pairs#####")
     with open(out_file + sfx, 'w') as fout:
         # header of .exact_p with the token p_app spliced in (remma_epiAA_approx.py:41-50)

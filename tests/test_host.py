@@ -267,3 +267,33 @@ def test_annotation_snp_pos_matches_reference(tmp_path):
     assert annotation_snp_pos(res, bed, p_cut=1, dis=5.0e7, ld_file=os.path.join(out, "epiAD.ld_table"), r2=0.2) == 0
     assert open(res + ".anno").read() == open(os.path.join(out, "epiAD.anno_dis5e7")).read()
     assert open(res + ".anno.ld").read() == open(os.path.join(out, "epiAD.anno_dis5e7.ld")).read()
+
+
+def test_p_app_step_is_byte_identical_to_the_reference_loop(tmp_path):
+    """The 'Add the approximate P values' step of the screen front ends, evaluated as arrays, writes the bytes the
+    reference's per-line loop writes (remma_epiAA_eff.py:85-95 scalar var_app; remma_epiAA_maf_eff.py:88-101 table)."""
+    from scipy.stats import chi2
+    from gmat_b200.remma import _core
+    rng = np.random.Generator(np.random.PCG64(3))
+    m, k = 300, 2500
+    rows = [(int(a), int(b), "%g" % e) for a, b, e in
+            zip(rng.integers(0, m, k), rng.integers(0, m, k), rng.normal(size=k) * 10.0 ** rng.integers(-4, 5, k))]
+    freq, freq2 = rng.integers(0, 11, m).astype(np.longlong), rng.integers(0, 11, m).astype(np.longlong)
+    table = rng.uniform(0.5, 5.0, 111)
+    for mode in ("scalar", "table", "empty"):
+        tmp, out = str(tmp_path / "t.temp"), str(tmp_path / "t.out")
+        use = [] if mode == "empty" else rows
+        with open(tmp, "w") as f:
+            f.write("snp_0 snp_1 eff\n")
+            f.writelines("%d %d %s\n" % r for r in use)
+        want = ["snp_0 snp_1 eff chi_app p_app\n"]
+        for a, b, e in use:                                              # the reference's loop, verbatim in behaviour
+            deno = 2.37 if mode == "scalar" else table[freq[a] * 10 + freq2[b]]
+            chi_app = float(e) * float(e) / deno
+            want.append(' '.join([str(a), str(b), e, str(chi_app), str(chi2.sf(chi_app, 1))]) + '\n')
+        if mode == "table":
+            _core._append_p_app(tmp, out, lambda rr: table[freq[[int(r[0]) for r in rr]] * 10
+                                                           + freq2[[int(r[1]) for r in rr]]])
+        else:
+            _core._append_p_app(tmp, out, lambda rr: 2.37)
+        assert open(out).read() == ''.join(want) and not os.path.exists(tmp)
