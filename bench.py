@@ -64,11 +64,13 @@ def i8_ops_per_pair(n, planes, variant=3):
     """int8 tensor-core ops (2 per MAC) per pair: (algorithmic, issued).  Algorithmic = the lower triangle of the
     symmetric B_i once per digit plane, planes * n(n+1); issued = what the kernel's tiling launches: per plane and per
     256-row tile kt the id slabs 0..min(2kt+2, ceil(n/128))-1, each N x 128 MACs per pair with N = 256 plane rows,
-    or (variants 3 and 4, ozaki.cu::i8p_shape) N = the tile's rows below n rounded up to 16, minus 128 for slab 2kt+1."""
-    n_kt, n_slab = (n + 255) // 256, (n + 127) // 128
+    or (variant 3, ozaki.cu::i8p_shape) N = the tile's rows up to the four extra rows (n rounded up to 4, + 4),
+    rounded up to 16, minus 128 for slab 2kt+1."""
+    rows_all = (n + 3) // 4 * 4 + 4
+    n_kt, n_slab = (rows_all + 255) // 256, (n + 127) // 128
     macs = 0.0
     for kt in range(n_kt):
-        rows = 256 if variant < 3 else min(256, (n - 256 * kt + 15) // 16 * 16)
+        rows = 256 if variant < 3 else min(256, (rows_all - 256 * kt + 15) // 16 * 16)
         for l in range(min(2 * kt + 2, n_slab)):
             macs += (rows - 128 if variant >= 3 and l == 2 * kt + 1 else rows) * 128.0
     return planes * float(n) * (n + 1), planes * macs * 2.0
@@ -217,8 +219,9 @@ def run_reference(args):
 def measure_fp64_peaks(engine, torch):
     """Roofline denominators for FP64 (absent from MEASURED_PEAKS.json): the library's DMMA issue-rate
     microbenchmark and cuBLAS DGEMM 4096^3 (torch.matmul float64), best of a few runs, CUDA events."""
-    dmma = engine.fp64_peak(0, 20000)
-    dfma = engine.fp64_peak(1, 20000)
+    import probe
+    dmma = probe.fp64_peak(0, 20000)
+    dfma = probe.fp64_peak(1, 20000)
     a = torch.randn((4096, 4096), dtype=torch.float64, device="cuda")
     b = torch.randn((4096, 4096), dtype=torch.float64, device="cuda")
     best = 1e30
@@ -375,7 +378,8 @@ def run_gpu(args):
             pairs_per_launch = pairs_rank / launches_per_step
             achieved = pairs_per_launch * alg / (kern_ms * 1e-3) / 1e12
             issued = pairs_per_launch * iss / (kern_ms * 1e-3) / 1e12
-            peaks = {"i8_mma_issue_tops": engine.i8_peak(20000)}
+            import probe
+            peaks = {"i8_mma_issue_tops": probe.i8_peak(20000)}
             mp = {}
             try:
                 mp = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "MEASURED_PEAKS.json")))
@@ -384,10 +388,10 @@ def run_gpu(args):
             peaks["int8_from_measured_bf16_sustained_x2"] = 2.0 * mp["bf16_tflops_sustained"] if mp else None
             peaks["int8_from_measured_bf16_burst_x2"] = 2.0 * mp["bf16_tflops"] if mp else None
             peak = peaks["i8_mma_issue_tops"]
-            line["dtype"] = "f64 results; n^2 term as exact int8 x int8 -> int32 tensor-core products of an error-free %d-plane split (%d bits), rest f64" % (planes, 7 * planes)
+            line["dtype"] = "f64 results; n^2 term as exact int8 x int8 -> int32 tensor-core products of an error-free %d-plane base-256 split (%d bits), rest f64" % (planes, 8 * planes - 1)
             line["roofline"] = {
                 "bound": "tensor", "achieved": achieved, "unit": "TOP/s", "peak": peak, "frac": achieved / peak,
-                "traffic": I8_TRAFFIC_BYTES, "kernel": {0: "i8_scan_kernel (tcgen05.mma cta_group::1 kind::i8, 128x256x32)", 2: "i8_scan_pair_kernel (tcgen05.mma cta_group::2 kind::i8, 256x256x32 per CTA pair)", 3: "i8_scan_pair_kernel (tcgen05.mma cta_group::2 kind::i8, 256xNx32 per CTA pair, N = the plane rows that can be non-zero)", 4: "i8_scan_pair2_kernel (tcgen05.mma cta_group::2 kind::i8, 256xNx32 per CTA pair, two digit planes per genotype tile, N = the plane rows that can be non-zero)"}[i8.wide],
+                "traffic": I8_TRAFFIC_BYTES, "kernel": {2: "i8_scan_pair_kernel (tcgen05.mma cta_group::2 kind::i8, 256x256x32 per CTA pair)", 3: "i8_scan_pair_kernel (tcgen05.mma cta_group::2 kind::i8, 256xNx32 per CTA pair, N = the plane rows that can be non-zero)"}[i8.wide],
                 "kernel_ms_per_launch": kern_ms, "kernel_launches_per_step": launches_per_step,
                 "kernel_share_of_step": kern_ms * launches_per_step / ms_local,
                 "ops_per_pair_algorithmic": alg, "ops_per_pair_issued": iss, "issued_tops": issued,
@@ -551,7 +555,8 @@ def extras(engine, torch, synth, store, model, lut, args, prefix, pymat, e2e_f64
                         "seconds": t, "workload": "agmat GRM, synthetic n=%d x m=%d generated in HBM "
                                                   "(BASELINE configs[1])" % (n2, m2)}
         if which == "i8":
-            i8_peak = engine.i8_peak(20000)
+            import probe
+            i8_peak = probe.i8_peak(20000)
             out["agmat"]["roofline"] = {
                 "bound": "tensor", "unit": "TOP/s", "achieved": float(n2) * (n2 + 1) * m2 / t / 1e12,
                 "peak": i8_peak, "frac": float(n2) * (n2 + 1) * m2 / t / 1e12 / i8_peak,

@@ -7,60 +7,87 @@
 //     var_ij = a_j' B_i a_j  -  2 o_j a_j.r_i  +  o_j^2 s_i,      r_i = u_i o (A u_i),  s_i = sum(r_i)
 //     eff_ij = a_j.(u_i o Z'Py) - o_j (u_i . Z'Py)
 //
-// Only a_j' B_i a_j costs n^2 per pair, and a_j is an exact small-integer vector.  B_i is split error-free into
-// S signed base-128 digit planes (int8); "plane x genotype" products are exact int8 x int8 -> int32 tensor-core
-// GEMMs, recombined in FP64 (S = 8 carries 56 bits: the split is finer than the FP64 rounding of B_i itself).
+// Only a_j' B_i a_j costs n^2 per pair, and a_j is an exact small-integer vector.  B_i / scale_i is split error-free
+// into S signed base-256 digit planes (int8: every digit in [-128, 127]); "plane x genotype" products are exact
+// int8 x int8 -> int32 tensor-core GEMMs, recombined in FP64.  S planes carry 8S - 1 bits of max|B_i| (S = 6: 47
+// bits, S = 7: 55 bits -- finer than the FP64 rounding of B_i itself).  The two O(n)-per-pair terms a_j.r_i and
+// a_j.(u_i o Z'Py) ride in the SAME tensor-core stream: r_i and u_i o Z'Py are split into digits as well (a high and
+// a low part, 2S digits, so they lose nothing against FP64) and stored as four extra rows of every plane, below the
+// n rows of B_i; their integer dot products with a_j come out of the accumulator as four extra TMEM columns.
+// Nothing on this path is a library call: decode of the first SNPs, A u_i, the reductions, the digit split and the
+// scan are the kernels of this file (remma_epiAA.py:72-74 is what they replace).
+//
 // The FP64 DMMA kernel (exact.cu) issues 2 n^2 FP64 flop per pair at 37 TFLOP/s; this path issues S n^2 / 2
 // int8 MACs per pair (block-lower-triangle of the symmetric B_i, diagonal blocks halved, result doubled) on a
 // pipe that is two orders of magnitude faster.
 //
-// Kernel roles (one CTA per SM, 192 threads): warp 0 = TMA producer, warp 1 = tcgen05.mma issuer (one lane),
-// warps 2..5 = epilogue (TMEM -> registers -> a_jk-weighted row sums, kept per thread: the TMEM lane IS the
-// pair, so no cross-lane reduction exists anywhere).  MMA shape M=128 (second SNPs j) x N=256 (rows k of a
-// plane) x K=32 ids; accumulators double-buffered in TMEM (2 x 256 columns).
+// A-posteriori guard: the split drops at most half a unit of the last digit per element of B_i, i.e. a random-walk
+// error of ~0.41 * 256^-S * scale_i * sum_k a_jk^2 on a_j' B_i a_j.  Every pair checks 4 * 256^-S * scale_i * sum a^2
+// (ten standard deviations) against recheck_tol * |var_ij|; a pair that fails (a variance that is tiny against
+// max|u_i|^2 max|A|: two very rare variants) is not decided here but appended to a re-check list, which the caller
+// evaluates with the FP64 pair kernel (exact.cu).  So the number of planes is a speed knob, not an accuracy risk.
 #include "tc5.cuh"
 
 namespace gb {
 
 constexpr int I8_THREADS = 192;
-constexpr int I8_MAX_PLANES = 8;
+constexpr int I8_MAX_PLANES = 7;          // 8 base-256 digits would not fit the int64 the split rounds into
+constexpr int I8_SIDE = 8;                // doubles per first SNP in the side table (see i8_side_kernel)
+constexpr int I8_XROWS = 4;               // extra plane rows: r hi, r lo, (u o py) hi, (u o py) lo
+
+__host__ __device__ inline long long i8_xrow(long long n) { return round_up(n, 4); }            // first extra row
+__host__ __device__ inline long long i8_rows(long long n) { return round_up(i8_xrow(n) + I8_XROWS, I8_TK); }
 
 struct I8Params {
     int n, m, ld, np, n_planes, n_kt, n_slab;
     int n_i, total_items, pair_space;
+    int xkt, xcol;               // row tile and TMEM column of the four extra rows
     const long long *ilist;
     const int *item_prefix;      // [n_i+1] first work item of every first SNP
     const int *jt0;              // [n_i]   first j tile of every first SNP
-    const signed char *g8;       // [m][ld] integer coded second SNPs
-    const double *scale, *s_i, *upy;      // [n_i]
-    const double *t1, *e;        // [n_i][m]  a_j.r_i  and  a_j.(u_i o py)
+    const signed char *g8;       // [m][ld] integer coded second SNPs (the MMA operand, read by TMA)
+    const unsigned char *g2;     // [m][ld/4] the same values packed 2 bits each (the epilogue's copy: 16 registers per 256 ids)
+    const double *side;          // [n_i][I8_SIDE]
     const double *offs;          // [m]   o_j
-    double chi_cut;
+    const double *asq;           // [m]   sum_k a_jk^2
+    double chi_cut, wlo, recheck_tol;
     gmat_b200_hit *hits;
     long long cap;
     unsigned long long *count;
+    int *recheck;                // [recheck_cap][2] pairs the split cannot decide (see header comment)
+    long long recheck_cap;
+    unsigned long long *recheck_count;
     double *q_debug;             // optional [n_i][m]: a_j' B_i a_j
-    int trim;                    // CTA-pair kernel: issue only the plane rows that can be non-zero (i8p_shape)
+    int trim;                    // issue only the plane rows that can be non-zero (i8p_shape)
 };
 
 // Epilogue of one accumulator tile for one TMEM lane (= one second SNP): sum_k a_jk * Y[j][k] over the 256 plane
 // rows of the tile, all in INTEGER registers.  No FP64 instruction may sit in this loop: DADD / I2F.F64 issue into
 // the pipe the tensor MMAs occupy (ncu: 37 % of all stall samples sat on the one DADD of the first version and the
-// tensor pipe idled 37 % of the time).  |Y| <= 2*127*n, so a 32-column partial fits int32 for n < 1.3e5.
-__device__ __forceinline__ int i8_dot_chunk(const int (&v)[32], const int4 &lo, const int4 &hi) {
-    const int aw[8] = {lo.x, lo.y, lo.z, lo.w, hi.x, hi.y, hi.z, hi.w};
+// tensor pipe idled 37 % of the time).  |Y| <= 2*128*n, so a 32-column partial fits int32 for n < 1.3e5.
+__device__ __forceinline__ int i8_dot_chunk(const int (&v)[32], unsigned w0, unsigned w1) {
     int c0 = 0, c1 = 0, c2 = 0, c3 = 0;                           // four independent chains
 #pragma unroll
-    for (int w = 0; w < 8; ++w) {
-        c0 += (aw[w] & 0xff) * v[4 * w];
-        c1 += ((aw[w] >> 8) & 0xff) * v[4 * w + 1];
-        c2 += ((aw[w] >> 16) & 0xff) * v[4 * w + 2];
-        c3 += ((aw[w] >> 24) & 0xff) * v[4 * w + 3];
+    for (int q = 0; q < 16; q += 4) {
+        c0 += (int)((w0 >> (2 * q)) & 3u) * v[q];
+        c1 += (int)((w0 >> (2 * q + 2)) & 3u) * v[q + 1];
+        c2 += (int)((w0 >> (2 * q + 4)) & 3u) * v[q + 2];
+        c3 += (int)((w0 >> (2 * q + 6)) & 3u) * v[q + 3];
     }
-    return (c0 + c1) + (c2 + c3);                                 // |.| <= 32 * 2 * 2*127*n: int32 for n < 1.3e5
+#pragma unroll
+    for (int q = 0; q < 16; q += 4) {
+        c0 += (int)((w1 >> (2 * q)) & 3u) * v[16 + q];
+        c1 += (int)((w1 >> (2 * q + 2)) & 3u) * v[17 + q];
+        c2 += (int)((w1 >> (2 * q + 4)) & 3u) * v[18 + q];
+        c3 += (int)((w1 >> (2 * q + 6)) & 3u) * v[19 + q];
+    }
+    return (c0 + c1) + (c2 + c3);                                 // |.| <= 32 * 2 * 2*128*n: int32 for n < 1.3e5
 }
-// The TMEM load of chunk ch+1 is in flight while chunk ch is multiplied (two register buffers).
-__device__ __forceinline__ long long i8_drain_tile(uint32_t taddr, const int4 (&a)[I8_TK / 16]) {
+// The TMEM load of chunk ch+1 is in flight while chunk ch is multiplied (two register buffers).  a[] = the 256
+// integer codes of this lane's SNP for the row tile, 2 bits each (16 per word).
+__device__ __forceinline__ long long i8_drain_tile(uint32_t taddr, const uint4 (&a)[I8_TK / 64]) {
+    const unsigned aw[16] = {a[0].x, a[0].y, a[0].z, a[0].w, a[1].x, a[1].y, a[1].z, a[1].w,
+                             a[2].x, a[2].y, a[2].z, a[2].w, a[3].x, a[3].y, a[3].z, a[3].w};
     long long total = 0;
     int v0[32], v1[32];
     tmem_ld32(taddr, v0);
@@ -68,40 +95,48 @@ __device__ __forceinline__ long long i8_drain_tile(uint32_t taddr, const int4 (&
     for (int ch = 0; ch < I8_TK / 32; ch += 2) {
         tmem_ld_wait();
         tmem_ld32(taddr + (ch + 1) * 32, v1);
-        total += i8_dot_chunk(v0, a[2 * ch], a[2 * ch + 1]);
+        total += i8_dot_chunk(v0, aw[2 * ch], aw[2 * ch + 1]);
         tmem_ld_wait();
         if (ch + 2 < I8_TK / 32) tmem_ld32(taddr + (ch + 2) * 32, v0);
-        total += i8_dot_chunk(v1, a[2 * ch + 2], a[2 * ch + 3]);
+        total += i8_dot_chunk(v1, aw[2 * ch + 2], aw[2 * ch + 3]);
     }
     return total;
 }
-// the 256 dosage bytes of this lane's SNP for one row tile: issued BEFORE the wait on the accumulator, so the L2
-// latency (the first version prefetched one 32-byte chunk ahead and stalled on it: 23 % of all samples) is hidden
-__device__ __forceinline__ void i8_load_dosage(const signed char *row, int4 (&a)[I8_TK / 16]) {
-    const int4 *ap = reinterpret_cast<const int4 *>(row);
+// the 256 codes (64 bytes) of this lane's SNP for one row tile: issued BEFORE the wait on the accumulator, so the L2
+// latency (the first version prefetched one chunk ahead and stalled on it: 23 % of all samples) is hidden.  Packed
+// 2 bits per code they take 16 registers; as bytes (the MMA operand's layout) they took 64 and pushed the kernel to
+// 247 registers -- two such warps fill an SM sub-partition's register file, and no operand kernel of the next batch
+// could co-reside with the scan.
+__device__ __forceinline__ void i8_load_dosage(const unsigned char *row, uint4 (&a)[I8_TK / 64]) {
+    const uint4 *ap = reinterpret_cast<const uint4 *>(row);
 #pragma unroll
-    for (int q = 0; q < I8_TK / 16; ++q) a[q] = __ldg(ap + q);
+    for (int q = 0; q < I8_TK / 64; ++q) a[q] = __ldg(ap + q);
 }
 
-// Finish one pair (first SNP ii of the launch, second SNP j) from qacc = sum_s 128^-(s+1) sum_k a_jk Y_s[j][k]: the
-// FP64 side terms, chi, threshold, warp-ballot compaction, 32-byte hit record (remma_epiAA.py:75-82).  Called by
-// all 32 lanes of an epilogue warp.
-__device__ __forceinline__ void i8_finish_pair(const I8Params &p, int ii, int j, int lane, double qacc) {
+// Finish one pair (first SNP ii of the launch, second SNP j).  qacc = sum_s 256^-(s+1) sum_k a_jk Y_s[j][k];
+// t1acc / eacc = the digit sums of a_j.r_i and a_j.(u_i o py) in units of their scales.  The FP64 side terms, chi,
+// the a-posteriori guard, threshold, warp-ballot compaction, 32-byte hit record (remma_epiAA.py:75-82).  Called by all
+// 32 lanes of an epilogue warp.
+__device__ __forceinline__ void i8_finish_pair(const I8Params &p, int ii, int j, int lane, double qacc, double t1acc,
+                                               double eacc) {
     const int i = (int)p.ilist[ii];
     const bool valid = j < p.m && (p.pair_space == GMAT_B200_PAIRS_ALL || j > i);
     const int jc = j < p.m ? j : p.m - 1;
-    const double quad = 2.0 * p.scale[ii] * qacc;                   // a_j' B_i a_j
+    const double *sd = p.side + (size_t)ii * I8_SIDE;
+    const double quad = 2.0 * sd[0] * qacc;                         // a_j' B_i a_j
     const double o = p.offs[jc];
-    const size_t at = (size_t)ii * p.m + jc;
-    double var = quad - 2.0 * o * p.t1[at] + o * o * p.s_i[ii];
-    double eff = p.e[at] - o * p.upy[ii];
-    if (o != o) { var = 0.0; eff = 0.0; }                          // monomorphic second SNP: w == 0 exactly
-    else if (o > 1.0e300) { var = o - o; eff = var; }             // missing genotype in the second SNP: NaN, as numpy
+    double var = quad - 2.0 * o * (sd[3] * t1acc) + o * o * sd[1];
+    double eff = sd[4] * eacc - o * sd[2];
+    bool plain = true;
+    if (o != o) { var = 0.0; eff = 0.0; plain = false; }           // monomorphic second SNP: w == 0 exactly
+    else if (o > 1.0e300) { var = o - o; eff = var; plain = false; }   // missing genotype in the second SNP: NaN, as numpy
     const double chi = eff * eff / var;
-    if (p.q_debug != nullptr && j < p.m) p.q_debug[at] = quad;
+    if (p.q_debug != nullptr && j < p.m) p.q_debug[(size_t)ii * p.m + jc] = quad;
+    // what the split may have dropped (ten standard deviations) against the variance itself; NaN compares false
+    const bool weak = valid && plain && sd[5] * p.asq[jc] > p.recheck_tol * fabs(var);
     gmat_b200_hit h;
     h.snp_0 = i; h.snp_1 = j; h.eff = eff; h.var = var; h.chi = chi;
-    const bool hit = valid && (p.chi_cut < 0.0 || chi > p.chi_cut);
+    const bool hit = valid && !weak && (p.chi_cut < 0.0 || chi > p.chi_cut);
     const unsigned ballot = __ballot_sync(0xffffffffu, hit);
     if (ballot) {
         unsigned long long base = 0;
@@ -112,12 +147,17 @@ __device__ __forceinline__ void i8_finish_pair(const I8Params &p, int ii, int j,
             if ((long long)pos < p.cap) p.hits[pos] = h;
         }
     }
+    const unsigned wballot = __ballot_sync(0xffffffffu, weak);
+    if (wballot) {                                                  // rare: two very rare variants
+        unsigned long long base = 0;
+        if (lane == 0) base = atomicAdd(p.recheck_count, (unsigned long long)__popc(wballot));
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (weak) {
+            const unsigned long long pos = base + __popc(wballot & ((1u << lane) - 1u));
+            if ((long long)pos < p.recheck_cap) { p.recheck[2 * pos] = i; p.recheck[2 * pos + 1] = j; }
+        }
+    }
 }
-
-struct I8Bars {
-    uint64_t full[I8_NS], empty[I8_NS], tfull[2], tempty[2];
-    uint32_t tmem_base;
-};
 
 __device__ __forceinline__ int i8_slabs_of(int kt, int n_slab) {
     const int want = 2 * kt + 2;              // block-lower-triangle: id slabs 0 .. (last 128-row block of the tile)
@@ -132,127 +172,14 @@ __device__ __forceinline__ int i8_find_first(const int *prefix, int n_i, int ite
     return lo;
 }
 
-__global__ void __launch_bounds__(I8_THREADS, 1)
-i8_scan_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_constant__ CUtensorMap map_p,
-               const I8Params p) {
-    extern __shared__ unsigned char smem_raw[];
-    unsigned char *smem = reinterpret_cast<unsigned char *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
-                                                           ~static_cast<uintptr_t>(1023));
-    I8Bars *bars = reinterpret_cast<I8Bars *>(smem + I8_NS * I8_STAGE_BYTES);
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-
-    if (threadIdx.x == 0) {
-        for (int s = 0; s < I8_NS; ++s) { mbar_init(&bars->full[s], 1); mbar_init(&bars->empty[s], 1); }
-        for (int b = 0; b < 2; ++b) { mbar_init(&bars->tfull[b], 1); mbar_init(&bars->tempty[b], 4); }
-        mbar_fence_init();
-    }
-    if (warp == 1) {                          // TMEM: all 512 columns (two 256-column accumulators)
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;\n" ::"r"(
-                         smem_u32(&bars->tmem_base)), "r"(512)
-                     : "memory");
-        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;\n" ::: "memory");
-    }
-    tc_fence_before();
-    __syncthreads();
-    tc_fence_after();
-    const uint32_t tmem_base = bars->tmem_base;
-
-    if (warp == 0) {
-        // ================================ TMA producer ==========================================
-        if (lane == 0) {
-            int stage = 0; unsigned phase = 0;
-            for (int item = blockIdx.x; item < p.total_items; item += gridDim.x) {
-                const int ii = i8_find_first(p.item_prefix, p.n_i, item);
-                const int jt = p.jt0[ii] + (item - p.item_prefix[ii]);
-                for (int s = 0; s < p.n_planes; ++s) {
-                    const int prow = (ii * p.n_planes + s) * p.np;
-                    for (int kt = 0; kt < p.n_kt; ++kt) {
-                        const int nl = i8_slabs_of(kt, p.n_slab);
-                        for (int l = 0; l < nl; ++l) {
-                            mbar_wait(&bars->empty[stage], phase ^ 1u);
-                            mbar_expect_tx(&bars->full[stage], I8_STAGE_BYTES);
-                            unsigned char *sa = smem + stage * I8_STAGE_BYTES;
-                            tma_load_2d(sa, &map_g, l * I8_SLAB, jt * I8_TJ, &bars->full[stage]);
-                            tma_load_2d(sa + I8_A_BYTES, &map_p, l * I8_SLAB, prow + kt * I8_TK, &bars->full[stage]);
-                            if (++stage == I8_NS) { stage = 0; phase ^= 1u; }
-                        }
-                    }
-                }
-            }
-        }
-    } else if (warp == 1) {
-        // ================================ MMA issuer (one thread) ================================
-        if (lane == 0) {
-            int stage = 0; unsigned phase = 0;
-            int abuf = 0; unsigned aphase = 0;
-            for (int item = blockIdx.x; item < p.total_items; item += gridDim.x) {
-                for (int s = 0; s < p.n_planes; ++s) {
-                    for (int kt = 0; kt < p.n_kt; ++kt) {
-                        const int nl = i8_slabs_of(kt, p.n_slab);
-                        mbar_wait(&bars->tempty[abuf], aphase ^ 1u);       // epilogue drained this accumulator
-                        tc_fence_after();
-                        const uint32_t tmem_d = tmem_base + (uint32_t)(abuf * I8_TK);
-                        for (int l = 0; l < nl; ++l) {
-                            mbar_wait(&bars->full[stage], phase);           // TMA bytes have landed
-                            tc_fence_after();
-                            const uint32_t sa = smem_u32(smem + stage * I8_STAGE_BYTES);
-                            const uint64_t da = umma_desc_sw128(sa), db = umma_desc_sw128(sa + I8_A_BYTES);
-#pragma unroll
-                            for (int k = 0; k < I8_SLAB / 32; ++k)          // K = 32 ids per MMA: +32 B in the atom
-                                umma_i8(tmem_d, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), I8_IDESC,
-                                        (uint32_t)((l | k) != 0));
-                            tc_commit(&bars->empty[stage]);                 // frees the smem slot when the MMAs retire
-                            if (++stage == I8_NS) { stage = 0; phase ^= 1u; }
-                        }
-                        tc_commit(&bars->tfull[abuf]);                      // accumulator complete
-                        if (++abuf == 2) { abuf = 0; aphase ^= 1u; }
-                    }
-                }
-            }
-        }
-    } else {
-        // ================================ epilogue warps =========================================
-        const int q = warp & 3;                                             // TMEM lane quarter of this warp
-        int abuf = 0; unsigned aphase = 0;
-        for (int item = blockIdx.x; item < p.total_items; item += gridDim.x) {
-            const int ii = i8_find_first(p.item_prefix, p.n_i, item);
-            const int jt = p.jt0[ii] + (item - p.item_prefix[ii]);
-            const int j = jt * I8_TJ + q * 32 + lane;
-            const signed char *arow = p.g8 + (size_t)(j < p.m ? j : p.m - 1) * p.ld;
-            double qacc = 0.0, wgt = 1.0;
-            for (int s = 0; s < p.n_planes; ++s) {
-                wgt *= 0.0078125;                                           // 128^-(s+1)
-                long long plane_sum = 0;                                    // exact
-                for (int kt = 0; kt < p.n_kt; ++kt) {
-                    int4 abytes[I8_TK / 16];
-                    i8_load_dosage(arow + kt * I8_TK, abytes);
-                    mbar_wait_warp(&bars->tfull[abuf], aphase);
-                    tc_fence_after();
-                    const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(abuf * I8_TK);
-                    plane_sum += i8_drain_tile(taddr, abytes);
-                    tc_fence_before();
-                    __syncwarp();
-                    if (lane == 0) mbar_arrive(&bars->tempty[abuf]);
-                    if (++abuf == 2) { abuf = 0; aphase ^= 1u; }
-                }
-                qacc += (double)plane_sum * wgt;                         // the only FP64 work per plane
-            }
-            i8_finish_pair(p, ii, j, lane, qacc);
-        }
-    }
-    tc_fence_before();
-    __syncthreads();
-    if (warp == 1) {
-        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;\n" ::"r"(tmem_base), "r"(512) : "memory");
-    }
-}
-
-// ---- CTA-pair variant: tcgen05.mma.cta_group::2 ---------------------------------------------------------------
-// Two CTAs of a cluster (one TPC) own the two 128-SNP tiles of a work item and HALF of every plane tile each
-// (128 of its 256 rows); one MMA of the leader CTA computes M = 256 SNPs x N = 256 plane rows across both SMs,
-// each tensor core reading its own genotype tile and the two plane halves.  Per SM and per 512 MMA cycles the
-// shared memory sees 32 KB of TMA writes and 32 KB of operand reads instead of 48 + 48, which is what holds the
-// single-CTA kernel at ~60 % of the issue rate.  Accumulators stay double-buffered (2 x 256 TMEM columns per CTA).
+// ---- the scan kernel: CTA pairs, tcgen05.mma.cta_group::2 -----------------------------------------------------
+// Persistent CTA pairs (cluster of 2 = one TPC), 192 threads per CTA: warp 0 = TMA producer, warp 1 of the leader =
+// tcgen05.mma issuer (one elected lane), warps 2..5 = epilogue (TMEM -> registers -> a_jk-weighted row sums, kept per
+// thread: the TMEM lane IS the pair, so no cross-lane reduction exists anywhere).  A work item is (first SNP, 256
+// second SNPs); the two CTAs own the two 128-SNP tiles of the item and HALF of every plane tile each (128 of its 256
+// rows); one MMA of the leader CTA computes M = 256 SNPs x N = 256 plane rows x K = 32 ids across both SMs, each
+// tensor core reading its own genotype tile and the two plane halves.  Accumulators are double-buffered in TMEM
+// (2 x 256 columns per CTA).
 constexpr int I8P_NS = 6;
 constexpr int I8P_HALF = I8_TK / 2;                               // plane rows each CTA loads
 constexpr int I8P_STAGE_BYTES = I8_A_BYTES + I8P_HALF * I8_SLAB;  // 32 KB per CTA
@@ -262,9 +189,10 @@ struct I8PBars {
 };
 
 // Plane rows of tile kt that slab l (128 ids) can touch: MMA N = nn rows starting row_off rows into the tile.
-//  * the last tile holds only n - 256 kt rows of data (rounded up to the UMMA N granularity of 16);
+//  * the last tile holds only the rows up to the four extra rows (rounded up to the UMMA N granularity of 16);
 //  * slab 2kt+1 lies right of the diagonal for the tile's first 128 rows (the split kernel leaves that 128 x 128
-//    block zero), so only rows 128.. of the tile are multiplied and accumulated into TMEM columns 128.. .
+//    block zero), so only rows 128.. of the tile are multiplied and accumulated into TMEM columns 128.. .  (The
+//    extra rows need every slab: when slab 2kt+1 exists in their tile, n > 256 kt + 128, so they sit in rows 128.. .)
 // The two CTAs supply nn/2 rows each (tcgen05 cta_group::2 takes the first half of N from the leader's shared
 // memory, the second from the peer's), so CTA r loads the 128-row box starting at row_off + r nn/2 and the MMA reads
 // its first nn/2 rows.  TMEM columns that a trimmed MMA does not write keep stale integers; the epilogue multiplies
@@ -272,12 +200,13 @@ struct I8PBars {
 __device__ __forceinline__ void i8p_shape(const I8Params &p, int kt, int l, int &row_off, int &nn) {
     row_off = 0; nn = I8_TK;
     if (!p.trim) return;
-    const int rows = p.n - kt * I8_TK;
+    const int rows = p.xkt * I8_TK + p.xcol + I8_XROWS - kt * I8_TK;
     if (rows < I8_TK) nn = (rows + 15) & ~15;
     if (l == 2 * kt + 1) { row_off = I8_TK / 2; nn -= I8_TK / 2; }
 }
 
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(I8_THREADS, 1)
+// (192 registers: 2 x 192 x 32 leave 4096 of a sub-partition's 16384 for a warp of an operand kernel of the next batch)
+__global__ void __cluster_dims__(2, 1, 1) __maxnreg__(192)
 i8_scan_pair_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_constant__ CUtensorMap map_ph,
                     const I8Params p) {
     extern __shared__ unsigned char smem_raw[];
@@ -374,26 +303,34 @@ i8_scan_pair_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_cons
             const int ii = i8_find_first(p.item_prefix, p.n_i, item);
             const int jt = 2 * (p.jt0[ii] + (item - p.item_prefix[ii])) + rank;
             const int j = jt * I8_TJ + q * 32 + lane;
-            const signed char *arow = p.g8 + (size_t)(j < p.m ? j : p.m - 1) * p.ld;
+            const unsigned char *arow = p.g2 + (size_t)(j < p.m ? j : p.m - 1) * (p.ld >> 2);
             double qacc = 0.0, wgt = 1.0;
+            double rh = 0.0, rl = 0.0, eh = 0.0, el = 0.0;                  // digit sums of the four extra rows
             for (int s = 0; s < p.n_planes; ++s) {
-                wgt *= 0.0078125;
+                wgt *= 0.00390625;                                          // 256^-(s+1)
                 long long plane_sum = 0;                                    // exact
+                int x[4] = {0, 0, 0, 0};
                 for (int kt = 0; kt < p.n_kt; ++kt) {
-                    int4 abytes[I8_TK / 16];
-                    i8_load_dosage(arow + kt * I8_TK, abytes);
+                    uint4 abytes[I8_TK / 64];
+                    i8_load_dosage(arow + kt * (I8_TK / 4), abytes);
                     mbar_wait_warp(&bars->tfull[abuf], aphase);
                     tc_fence_after();
                     const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(abuf * I8_TK);
                     plane_sum += i8_drain_tile(taddr, abytes);
+                    if (kt == p.xkt) {                                      // a_j . digits of r_i and of u_i o py
+                        tmem_ld4(taddr + (uint32_t)p.xcol, x);
+                        tmem_ld_wait();
+                    }
                     tc_fence_before();
                     __syncwarp();
                     if (lane == 0) mbar_arrive_leader(&bars->tempty[abuf]);
                     if (++abuf == 2) { abuf = 0; aphase ^= 1u; }
                 }
                 qacc += (double)plane_sum * wgt;                         // the only FP64 work per plane
+                rh += (double)x[0] * wgt; rl += (double)x[1] * wgt;
+                eh += (double)x[2] * wgt; el += (double)x[3] * wgt;
             }
-            i8_finish_pair(p, ii, j, lane, qacc);
+            i8_finish_pair(p, ii, j, lane, qacc, rh + p.wlo * rl, eh + p.wlo * el);
         }
     }
     tc_fence_before();
@@ -404,214 +341,10 @@ i8_scan_pair_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_cons
     }
 }
 
-// ---- dual-plane CTA-pair variant (variant 4) ---------------------------------------------------------------------
-// ncu on the kernel above: 97.5 GB of TMA loads in 7.1 ms = 13.7 TB/s, the L2 -> SM ceiling of the chip (the
-// guide's ~6300 B/clk LTS cap); trimming MMAs (variant 3) left the time unchanged.  A 256 x 256 tile per CTA pair
-// needs 64 B/clk/SM at the full MMA rate, 148 SMs 9.5 KB/clk -- the kernel is bound by operand bytes, not by the
-// tensor pipe.  This variant multiplies every genotype tile with the tiles of TWO digit planes (s, s+1) while it is in
-// shared memory: 48 KB per CTA and stage feed 8 instead of 4 MMAs (47 B/clk/SM).  The two accumulators take all
-// 512 TMEM columns, so there is no second buffer: accumulator a of the next row tile starts when group a of the
-// epilogue warps (two groups of four warps, one per accumulator, draining in parallel) has released it, which
-// exposes about one drain minus one slab of MMAs per row tile.  Both groups leave their exact integer plane sums in
-// shared memory; group 0 adds the planes in the same order as the other variants (same bits) and finishes the pair.
-constexpr int I8Q_NS = 4;
-constexpr int I8Q_THREADS = 320;                                  // producer, issuer, 2 x 4 epilogue warps
-constexpr int I8Q_STAGE_BYTES = I8_A_BYTES + 2 * I8P_HALF * I8_SLAB;   // 48 KB per CTA
-struct I8QBars {
-    uint64_t full[I8Q_NS], empty[I8Q_NS], tfull[2], tempty[2];
-    uint32_t tmem_base;
-    long long handoff[2][I8_MAX_PLANES][I8_TJ];                  // [item parity][plane][TMEM lane]: exact plane sums
-};
-
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(I8Q_THREADS, 1)
-i8_scan_pair2_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_constant__ CUtensorMap map_ph,
-                     const I8Params p) {
-    extern __shared__ unsigned char smem_raw[];
-    unsigned char *smem = reinterpret_cast<unsigned char *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
-                                                           ~static_cast<uintptr_t>(1023));
-    I8QBars *bars = reinterpret_cast<I8QBars *>(smem + I8Q_NS * I8Q_STAGE_BYTES);
-    const uint32_t smem_base = smem_u32(smem);
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int rank = (int)cluster_ctarank();
-    const int cluster_id = blockIdx.x >> 1, n_clusters = gridDim.x >> 1;
-    const int n_sp = p.n_planes >> 1;                             // plane pairs (n_planes is even)
-
-    if (threadIdx.x == 0) {
-        for (int s = 0; s < I8Q_NS; ++s) { mbar_init(&bars->full[s], 1); mbar_init(&bars->empty[s], 1); }
-        for (int b = 0; b < 2; ++b) { mbar_init(&bars->tfull[b], 1); mbar_init(&bars->tempty[b], 8); }
-        mbar_fence_init();
-    }
-    if (warp == 1) {
-        asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;\n" ::"r"(
-                         smem_u32(&bars->tmem_base)), "r"(512)
-                     : "memory");
-        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;\n" ::: "memory");
-    }
-    tc_fence_before();
-    __syncthreads();
-    cluster_sync_all();
-    tc_fence_after();
-    const uint32_t tmem_base = bars->tmem_base;
-
-    if (warp == 0) {
-        // ================================ TMA producer (both CTAs; converged warp, elected lane issues) ====
-        int stage = 0; unsigned phase = 0;
-        for (int item = cluster_id; item < p.total_items; item += n_clusters) {
-            const int ii = i8_find_first(p.item_prefix, p.n_i, item);
-            const int jt = 2 * (p.jt0[ii] + (item - p.item_prefix[ii])) + rank;
-            for (int sp = 0; sp < n_sp; ++sp) {
-                const int prow = (ii * p.n_planes + 2 * sp) * p.np;         // plane 2sp; plane 2sp+1 is np rows on
-                for (int kt = 0; kt < p.n_kt; ++kt) {
-                    const int nl = i8_slabs_of(kt, p.n_slab);
-                    for (int l = 0; l < nl; ++l) {
-                        int row_off, nn;
-                        i8p_shape(p, kt, l, row_off, nn);
-                        const int brow = prow + kt * I8_TK + row_off + rank * (nn >> 1);
-                        mbar_wait(&bars->empty[stage], phase ^ 1u);
-                        if (elect_one()) {
-                            if (rank == 0) mbar_expect_tx(&bars->full[stage], 2 * I8Q_STAGE_BYTES);
-                            unsigned char *sa = smem + stage * I8Q_STAGE_BYTES;
-                            tma_load_2d_pair(sa, &map_g, l * I8_SLAB, jt * I8_TJ, &bars->full[stage]);
-                            tma_load_2d_pair(sa + I8_A_BYTES, &map_ph, l * I8_SLAB, brow, &bars->full[stage]);
-                            tma_load_2d_pair(sa + I8_A_BYTES + I8P_HALF * I8_SLAB, &map_ph, l * I8_SLAB, brow + p.np,
-                                             &bars->full[stage]);
-                        }
-                        if (++stage == I8Q_NS) { stage = 0; phase ^= 1u; }
-                    }
-                }
-            }
-        }
-    } else if (warp == 1) {
-        // ================================ MMA issuer (leader CTA; converged warp, elected lane issues) =====
-        if (rank == 0) {
-            int stage = 0; unsigned phase = 0;
-            unsigned aphase = 0;                                  // both accumulators are used once per row tile
-            for (int item = cluster_id; item < p.total_items; item += n_clusters) {
-                for (int sp = 0; sp < n_sp; ++sp) {
-                    for (int kt = 0; kt < p.n_kt; ++kt) {
-                        const int nl = i8_slabs_of(kt, p.n_slab);
-                        for (int l = 0; l < nl; ++l) {
-                            mbar_wait(&bars->full[stage], phase);
-                            tc_fence_after();
-                            const uint32_t sa = smem_base + (uint32_t)(stage * I8Q_STAGE_BYTES);
-                            const uint64_t da = umma_desc_sw128(sa);
-                            int row_off, nn;
-                            i8p_shape(p, kt, l, row_off, nn);
-                            const uint32_t idesc = i8p_idesc(nn);
-#pragma unroll
-                            for (int a = 0; a < 2; ++a) {
-                                if (l == 0) {                     // epilogue group a drained accumulator a
-                                    mbar_wait(&bars->tempty[a], aphase ^ 1u);
-                                    tc_fence_after();
-                                }
-                                const uint64_t db = umma_desc_sw128(sa + I8_A_BYTES + a * I8P_HALF * I8_SLAB);
-                                const uint32_t tmem_d = tmem_base + (uint32_t)(a * I8_TK + row_off);
-                                if (elect_one()) {
-#pragma unroll
-                                    for (int k = 0; k < I8_SLAB / 32; ++k)
-                                        umma_i8_pair(tmem_d, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc,
-                                                     (uint32_t)((l | k) != 0));
-                                    if (l == nl - 1) tc_commit_pair(&bars->tfull[a]);
-                                    if (a == 1) tc_commit_pair(&bars->empty[stage]);
-                                }
-                            }
-                            if (++stage == I8Q_NS) { stage = 0; phase ^= 1u; }
-                        }
-                        aphase ^= 1u;
-                    }
-                }
-            }
-        }
-    } else {
-        // ================================ epilogue: group a = (warp - 2) / 4 drains accumulator a ========
-        const int q = warp & 3;                                   // TMEM lane quarter this warp may read
-        const int grp = (warp - 2) >> 2;
-        unsigned aphase = 0;
-        int parity = 0;
-        for (int item = cluster_id; item < p.total_items; item += n_clusters, parity ^= 1) {
-            const int ii = i8_find_first(p.item_prefix, p.n_i, item);
-            const int jt = 2 * (p.jt0[ii] + (item - p.item_prefix[ii])) + rank;
-            const int j = jt * I8_TJ + q * 32 + lane;
-            const signed char *arow = p.g8 + (size_t)(j < p.m ? j : p.m - 1) * p.ld;
-            for (int sp = 0; sp < n_sp; ++sp) {
-                long long plane_sum = 0;                          // exact; plane 2sp + grp
-                for (int kt = 0; kt < p.n_kt; ++kt) {
-                    int4 abytes[I8_TK / 16];
-                    i8_load_dosage(arow + kt * I8_TK, abytes);
-                    mbar_wait_warp(&bars->tfull[grp], aphase);
-                    tc_fence_after();
-                    const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(grp * I8_TK);
-                    plane_sum += i8_drain_tile(taddr, abytes);
-                    tc_fence_before();
-                    __syncwarp();
-                    if (lane == 0) mbar_arrive_leader(&bars->tempty[grp]);
-                    aphase ^= 1u;
-                }
-                bars->handoff[parity][2 * sp + grp][q * 32 + lane] = plane_sum;
-            }
-            named_bar_sync(1, 256);                               // the eight epilogue warps of this CTA
-            if (grp == 0) {
-                double qacc = 0.0, wgt = 1.0;
-                for (int s = 0; s < p.n_planes; ++s) {            // planes in the order 0, 1, 2, ... like the other variants
-                    wgt *= 0.0078125;                             // 128^-(s+1)
-                    qacc += (double)bars->handoff[parity][s][q * 32 + lane] * wgt;
-                }
-                i8_finish_pair(p, ii, j, lane, qacc);
-            }
-        }
-    }
-    tc_fence_before();
-    __syncthreads();
-    cluster_sync_all();
-    if (warp == 1) {
-        asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;\n" ::"r"(tmem_base), "r"(512) : "memory");
-    }
-}
-
-// Issue-rate microbenchmark of the int8 MMA (the roofline denominator of the engine): one thread per CTA issues
-// back-to-back 128x256x32 MMAs on a resident (pseudo-random) smem tile pair, alternating two TMEM accumulators.
-__global__ void __launch_bounds__(128, 1) i8_peak_kernel(int iters) {
-    extern __shared__ unsigned char smem_raw[];
-    unsigned char *smem = reinterpret_cast<unsigned char *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
-                                                           ~static_cast<uintptr_t>(1023));
-    __shared__ uint64_t bar;
-    __shared__ uint32_t tbase_slot;
-    for (int k = threadIdx.x; k < I8_STAGE_BYTES / 4; k += blockDim.x)
-        reinterpret_cast<unsigned *>(smem)[k] = (unsigned)(k * 2654435761u) ^ (blockIdx.x * 40503u);
-    if (threadIdx.x == 0) { mbar_init(&bar, 1); mbar_fence_init(); }
-    if (threadIdx.x < 32) {
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;\n" ::"r"(smem_u32(&tbase_slot)),
-                     "r"(512)
-                     : "memory");
-        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;\n" ::: "memory");
-    }
-    fence_proxy_async();
-    tc_fence_before();
-    __syncthreads();
-    tc_fence_after();
-    const uint32_t tbase = tbase_slot;
-    if (threadIdx.x == 0) {
-        const uint32_t sa = smem_u32(smem);
-        const uint64_t da = umma_desc_sw128(sa), db = umma_desc_sw128(sa + I8_A_BYTES);
-        for (int it = 0; it < iters; ++it) {
-#pragma unroll
-            for (int k = 0; k < 4; ++k)
-                umma_i8(tbase + (uint32_t)((it & 1) * I8_TK), da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), I8_IDESC,
-                        (uint32_t)(it > 1));
-        }
-        tc_commit(&bar);
-        mbar_wait(&bar, 0);
-    }
-    tc_fence_before();
-    __syncthreads();
-    if (threadIdx.x < 32)
-        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;\n" ::"r"(tbase), "r"(512) : "memory");
-}
-
 // ------------------------------------------------------------------------------------------ operand builders
 // integer code of the second SNP: additive dosage {0,miss->0,1,2}; dominance indicator {0,miss->0,1,0}
 __global__ void i8_dosage_kernel(const unsigned char *__restrict__ bed, int n, long long m, long long row_bytes,
-                                 int coding, signed char *__restrict__ g8, int ld) {
+                                 int coding, signed char *__restrict__ g8, unsigned char *__restrict__ g2, int ld) {
     const long long groups = ld / 16;
     const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= m * groups) return;
@@ -620,7 +353,7 @@ __global__ void i8_dosage_kernel(const unsigned char *__restrict__ bed, int n, l
     const unsigned tab = coding == GMAT_B200_CODING_DOM ? 0x00010000u : 0x02010000u;   // byte[code]
     unsigned w = 0;
     if (k0 / 4 + 3 < row_bytes) w = *reinterpret_cast<const unsigned *>(bed + snp * row_bytes + k0 / 4);
-    unsigned out[4];
+    unsigned out[4], packed = 0;
 #pragma unroll
     for (int g = 0; g < 4; ++g) {
         unsigned o = 0;
@@ -630,52 +363,263 @@ __global__ void i8_dosage_kernel(const unsigned char *__restrict__ bed, int n, l
             const unsigned code = (w >> (2 * (g * 4 + c))) & 3u;
             const unsigned val = k < n ? ((tab >> (8 * code)) & 0xffu) : 0u;
             o |= val << (8 * c);
+            packed |= val << (2 * (g * 4 + c));
         }
         out[g] = o;
     }
     *reinterpret_cast<uint4 *>(g8 + snp * ld + k0) = make_uint4(out[0], out[1], out[2], out[3]);
+    if (g2 != nullptr) *reinterpret_cast<unsigned *>(g2 + snp * (ld >> 2) + (k0 >> 2)) = packed;
 }
 
-// B_i = diag(u_i) A diag(u_i) / scale_i -> S signed base-128 digits.  Lower block-triangle of 128 x 128 blocks,
-// diagonal blocks halved (the kernel doubles the sum); everything else in the plane buffer stays zero.
+// Per second SNP: o_j = -lut[j][code 0] with the two flags of the engine, and sum_k a_jk^2 (from the exact genotype
+// counts).  A SNP whose integer code is the same for everybody has w == 0 exactly (eff = var = 0, chi = NaN in the
+// reference); the expanded form would return rounding noise instead, so it is flagged o_j = NaN.  A missing call
+// makes the coded column NaN in the reference's numpy path (remma_epiAA.py:59-61 on read_plink's NaN), so every
+// statistic of such a SNP is NaN and it is never reported: flagged o_j = +inf.
+__global__ void i8_offs_kernel(const int *__restrict__ counts, const double *__restrict__ lutV, long long m, int coding,
+                               double *__restrict__ offs, double *__restrict__ asq) {
+    const long long j = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= m) return;
+    const int c0 = counts[4 * j], c1 = counts[4 * j + 1], c2 = counts[4 * j + 2], c3 = counts[4 * j + 3];
+    const int v3 = coding == GMAT_B200_CODING_DOM ? 0 : 2;         // integer value of code 11
+    int hi = -1, lo = 9;
+    if (c0 > 0) { hi = max(hi, 0); lo = min(lo, 0); }
+    if (c2 > 0) { hi = max(hi, 1); lo = min(lo, 1); }
+    if (c3 > 0) { hi = max(hi, v3); lo = min(lo, v3); }
+    double o = -lutV[4 * j];
+    if (hi <= lo) o = __longlong_as_double(0x7ff8000000000000LL);
+    if (c1 > 0) o = __longlong_as_double(0x7ff0000000000000LL);
+    offs[j] = o;
+    asq[j] = (double)c2 + (double)(v3 * v3) * (double)c3;
+}
+
+// max |x| over a device array, as the bit pattern of a non-negative double (monotone in the value; a NaN wins)
+__global__ void absmax_kernel(const double *__restrict__ x, long long len, unsigned long long *out) {
+    double mx = 0.0;
+    bool bad = false;
+    for (long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x; k < len; k += (long long)gridDim.x * blockDim.x) {
+        const double v = fabs(x[k]);
+        bad |= v != v;
+        mx = fmax(mx, v);
+    }
+    unsigned long long bits = bad ? 0x7ff8000000000000ULL : (unsigned long long)__double_as_longlong(mx);
+#pragma unroll
+    for (int d = 16; d >= 1; d >>= 1) {
+        const unsigned long long other = __shfl_xor_sync(0xffffffffu, bits, d);
+        bits = other > bits ? other : bits;
+    }
+    if ((threadIdx.x & 31) == 0 && bits) atomicMax(out, bits);
+}
+
+// coded first SNPs: u[ii][k] = lutU[i][code of individual k]
+__global__ void i8_first_decode_kernel(const unsigned char *__restrict__ bed, int n, long long row_bytes,
+                                       const double *__restrict__ lutU, const long long *__restrict__ ilist,
+                                       double *__restrict__ u) {
+    const int ii = blockIdx.x;
+    const long long i = ilist[ii];
+    const unsigned char *row = bed + i * row_bytes;
+    const double l0 = lutU[4 * i], l1 = lutU[4 * i + 1], l2 = lutU[4 * i + 2], l3 = lutU[4 * i + 3];
+    for (int k = threadIdx.x; k < n; k += blockDim.x) {
+        const int c = code_at(row, k);
+        u[(size_t)ii * n + k] = c == 0 ? l0 : (c == 1 ? l1 : (c == 2 ? l2 : l3));
+    }
+}
+
+// r[ii][k] = u[ii][k] * sum_l A[k][l] u[ii][l]   (A symmetric: row k of A).  Tile = 32 rows k x 64 first SNPs, the l
+// axis in steps of 32 through shared memory; every thread owns 2 x 4 outputs and sums over l in ascending order, so
+// the result does not depend on the launch shape.  n^2 flop per first SNP against S n^2 / 2 int8 MACs per PAIR.
+constexpr int AU_BK = 32, AU_BI = 64, AU_BL = 32;
+__global__ void __launch_bounds__(256) i8_au_kernel(const double *__restrict__ A, int n, const double *__restrict__ u,
+                                                    int n_i, double *__restrict__ r) {
+    __shared__ double As[AU_BL][AU_BK + 1];
+    __shared__ double Us[AU_BL][AU_BI + 1];
+    const int k0 = blockIdx.x * AU_BK, i0 = blockIdx.y * AU_BI;
+    const int tk = (threadIdx.x >> 4) * 2, ti = (threadIdx.x & 15) * 4;
+    double acc[2][4] = {{0, 0, 0, 0}, {0, 0, 0, 0}};
+    for (int l0 = 0; l0 < n; l0 += AU_BL) {
+        {   // A tile: 32 rows x 32 columns, 4 per thread
+            const int row = threadIdx.x >> 3, c0 = (threadIdx.x & 7) * 4;
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                const int k = k0 + row, l = l0 + c0 + c;
+                As[c0 + c][row] = (k < n && l < n) ? A[(size_t)k * n + l] : 0.0;
+            }
+        }
+        {   // u tile: 64 first SNPs x 32 columns, 8 per thread
+            const int row = threadIdx.x >> 2, c0 = (threadIdx.x & 3) * 8;
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+                const int ii = i0 + row, l = l0 + c0 + c;
+                Us[c0 + c][row] = (ii < n_i && l < n) ? u[(size_t)ii * n + l] : 0.0;
+            }
+        }
+        __syncthreads();
+#pragma unroll 8
+        for (int l = 0; l < AU_BL; ++l) {
+            const double a0 = As[l][tk], a1 = As[l][tk + 1];
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                const double uv = Us[l][ti + c];
+                acc[0][c] = fma(a0, uv, acc[0][c]);
+                acc[1][c] = fma(a1, uv, acc[1][c]);
+            }
+        }
+        __syncthreads();
+    }
+#pragma unroll
+    for (int a = 0; a < 2; ++a)
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            const int k = k0 + tk + a, ii = i0 + ti + c;
+            if (k < n && ii < n_i) r[(size_t)ii * n + k] = u[(size_t)ii * n + k] * acc[a][c];
+        }
+}
+
+// Balanced base-256 digits of t, all S at once: with e_s = d_s + 128 in [0, 255], sum_s e_s 256^s = t + 128 sum_s 256^s,
+// so the BYTES of t + 0x80..80 are the e_s, and e_s - 128 as an int8 bit pattern is e_s ^ 0x80: one 64-bit add and one
+// 64-bit xor give every digit (byte s = digit s, least significant first; |t| <= 126.5 * 256^(S-1) by the choice of
+// scale, so nothing carries out of byte S-1).  The shift-and-mask loop this replaces cost ~8 instructions per digit.
 template <int S>
-__global__ void __launch_bounds__(256)
+__device__ __forceinline__ unsigned long long i8_digits(long long t) {
+    constexpr unsigned long long BIAS = 0x8080808080808080ULL >> (8 * (8 - S));
+    return ((unsigned long long)t + BIAS) ^ BIAS;
+}
+// digit bytes of 4 neighbouring columns -> one word per plane (plane q = digit S-1-q: most significant first)
+template <int S>
+__device__ __forceinline__ void i8_pack4(const unsigned long long (&e)[4], int g, unsigned (&dg)[S][4]) {
+#pragma unroll
+    for (int q = 0; q < S; ++q) {
+        const int b = S - 1 - q;
+        const unsigned x0 = b < 4 ? (unsigned)e[0] : (unsigned)(e[0] >> 32), x1 = b < 4 ? (unsigned)e[1] : (unsigned)(e[1] >> 32);
+        const unsigned x2 = b < 4 ? (unsigned)e[2] : (unsigned)(e[2] >> 32), x3 = b < 4 ? (unsigned)e[3] : (unsigned)(e[3] >> 32);
+        const unsigned sel = (unsigned)(b & 3) | ((unsigned)(4 + (b & 3)) << 4);
+        dg[q][g] = __byte_perm(__byte_perm(x0, x1, sel), __byte_perm(x2, x3, sel), 0x5410);
+    }
+}
+
+// Per first SNP (one block): the scalars of the side table and the four extra plane rows.
+//   side[0] = scale_i   >= max|B_i| / 0.49      (max|u_i|^2 max|A| / 0.49)
+//   side[1] = s_i = sum_k r_ik,   side[2] = u_i . py
+//   side[3] = scale_r (max|r_i| / 0.49),  side[4] = scale_e (max|u_i o py| / 0.49)
+//   side[5] = 4 * 256^-S * scale_i   (the a-posteriori guard's error unit; 0 for a monomorphic first SNP)
+// Sums run in a fixed order (per-thread strided partials, then a tree), so they are run-to-run identical.  A first SNP
+// with a missing call has NaN in u_i (lut[i][code 01]); s_i and u_i.py are then NaN and so is every statistic.
+// Extra rows (xrow .. xrow+3 of every plane): y = x / scale as t + f, t = rn(y 256^S) (the "high" S digits),
+// f = y 256^S - t exactly, |f| <= 1/2, and rn(f 256^S / 2) (the "low" S digits): y = 256^-S (t + 2 256^-S t_low).
+constexpr int I8_PREP_THREADS = 128;    // operand kernels: small CTAs (<= 16 K registers) so that they co-reside with the
+                                        // persistent scan kernel (248 registers x 192 threads per SM) of the previous batch
+template <int S>
+__global__ void __launch_bounds__(I8_PREP_THREADS)
+i8_side_kernel(const double *__restrict__ u, const double *__restrict__ r, const double *__restrict__ py, int n,
+               const unsigned long long *__restrict__ amax_bits, int np, int ld, int xrow,
+               double *__restrict__ side, signed char *__restrict__ planes) {
+    constexpr int NT = I8_PREP_THREADS;
+    __shared__ double red[5][NT];
+    __shared__ double sc[2];
+    const int ii = blockIdx.x, t = threadIdx.x;
+    const double *ui = u + (size_t)ii * n, *ri = r + (size_t)ii * n;
+    double s = 0.0, upy = 0.0, rmax = 0.0, emax = 0.0, umax = 0.0;
+    for (int k = t; k < n; k += NT) {
+        const double uu = ui[k], rr = ri[k], e = uu * py[k];
+        s += rr; upy += e;
+        rmax = fmax(rmax, fabs(rr)); emax = fmax(emax, fabs(e)); umax = fmax(umax, fabs(uu));
+    }
+    red[0][t] = s; red[1][t] = upy; red[2][t] = rmax; red[3][t] = emax; red[4][t] = umax;
+    __syncthreads();
+    for (int d = NT / 2; d >= 1; d >>= 1) {
+        if (t < d) {
+            red[0][t] += red[0][t + d]; red[1][t] += red[1][t + d];
+            red[2][t] = fmax(red[2][t], red[2][t + d]); red[3][t] = fmax(red[3][t], red[3][t + d]);
+            red[4][t] = fmax(red[4][t], red[4][t + d]);
+        }
+        __syncthreads();
+    }
+    double pw = 1.0;
+#pragma unroll
+    for (int q = 0; q < S; ++q) pw *= 256.0;                       // 256^S
+    if (t == 0) {
+        const double amax = __longlong_as_double((long long)*amax_bits);
+        const double um = red[4][0];
+        double *sd = side + (size_t)ii * I8_SIDE;
+        const double scale = fmax(um * um * (amax / 0.49), 1e-200);
+        sd[0] = scale; sd[1] = red[0][0]; sd[2] = red[1][0];
+        const double scale_r = red[2][0] > 0.0 ? red[2][0] / 0.49 : 1.0;
+        const double scale_e = red[3][0] > 0.0 ? red[3][0] / 0.49 : 1.0;
+        sd[3] = scale_r; sd[4] = scale_e;
+        sd[5] = um > 0.0 ? 4.0 * scale / pw : 0.0;
+        sd[6] = 0.0; sd[7] = 0.0;
+        sc[0] = pw / scale_r; sc[1] = pw / scale_e;
+    }
+    __syncthreads();
+    const double mr = sc[0], me = sc[1];
+    for (int g = t; g < ld / 16; g += NT) {
+        const int k0 = g * 16;
+#pragma unroll
+        for (int which = 0; which < 2; ++which) {
+            unsigned hi[S][4], lo[S][4];
+#pragma unroll
+            for (int g4 = 0; g4 < 4; ++g4) {
+                unsigned long long eh[4], el[4];
+#pragma unroll
+                for (int c = 0; c < 4; ++c) {
+                    const int k = k0 + 4 * g4 + c;
+                    double x = 0.0;
+                    if (k < n) x = which == 0 ? ri[k] * mr : (ui[k] * py[k]) * me;
+                    const long long th = __double2ll_rn(x);
+                    const double f = x - (double)th;                // exact, |f| <= 1/2
+                    eh[c] = i8_digits<S>(th);
+                    el[c] = i8_digits<S>(__double2ll_rn(f * (0.5 * pw)));
+                }
+                i8_pack4<S>(eh, g4, hi);
+                i8_pack4<S>(el, g4, lo);
+            }
+#pragma unroll
+            for (int q = 0; q < S; ++q) {
+                signed char *base = planes + ((size_t)(ii * S + q) * np + xrow + 2 * which) * ld + k0;
+                *reinterpret_cast<uint4 *>(base) = make_uint4(hi[q][0], hi[q][1], hi[q][2], hi[q][3]);
+                *reinterpret_cast<uint4 *>(base + ld) = make_uint4(lo[q][0], lo[q][1], lo[q][2], lo[q][3]);
+            }
+        }
+    }
+}
+
+// B_i = diag(u_i) A diag(u_i) / scale_i -> S signed base-256 digits.  Lower block-triangle of 128 x 128 blocks,
+// diagonal blocks halved (the kernel doubles the sum); rows >= n are not touched (they hold the extra rows of
+// i8_side_kernel and zeros), everything else in the plane buffer stays zero.
+template <int S>
+__global__ void __launch_bounds__(I8_PREP_THREADS)
 i8_split_kernel(const double *__restrict__ A, int n, const double *__restrict__ U, int n_i, int i_per_block,
-                const double *__restrict__ scale, int np, int ld, signed char *__restrict__ planes) {
+                const double *__restrict__ side, int np, int ld, signed char *__restrict__ planes) {
     int pk = 0, rem = blockIdx.x;                       // blockIdx.x -> (pk, pl), pl <= pk
     while (rem > pk) { rem -= pk + 1; ++pk; }
     const int pl = rem;
     const int cg = threadIdx.x & 7, r0 = threadIdx.x >> 3;
     const int l0 = pl * 128 + cg * 16;
-    const double half = pk == pl ? 0.5 : 1.0;
-    const double big = 72057594037927936.0;             // 128^8 = 2^56
-    double top = 1.0;
-    for (int s = S; s < 8; ++s) top *= 128.0;
-    const double mul = half * (big / top);              // 128^S (x 1/2 on the diagonal blocks)
+    double mul = pk == pl ? 0.5 : 1.0;                  // 256^S (x 1/2 on the diagonal blocks)
+#pragma unroll
+    for (int q = 0; q < S; ++q) mul *= 256.0;
     const int i_begin = blockIdx.y * i_per_block;
     const int i_end = min(n_i, i_begin + i_per_block);
-    for (int pass = 0; pass < 4; ++pass) {
-        const int k = pk * 128 + pass * 32 + r0;
+    for (int pass = 0; pass < 128 / (I8_PREP_THREADS / 8); ++pass) {
+        const int k = pk * 128 + pass * (I8_PREP_THREADS / 8) + r0;
+        if (k >= n) continue;
         double a[16];
 #pragma unroll
-        for (int c = 0; c < 16; ++c) a[c] = (k < n && l0 + c < n) ? A[(size_t)k * n + l0 + c] : 0.0;
+        for (int c = 0; c < 16; ++c) a[c] = l0 + c < n ? A[(size_t)k * n + l0 + c] : 0.0;
         for (int ii = i_begin; ii < i_end; ++ii) {
             const double *u = U + (size_t)ii * n;
-            const double uk = k < n ? u[k] * (mul / scale[ii]) : 0.0;
+            const double uk = u[k] * (mul / side[(size_t)ii * I8_SIDE]);
             unsigned dg[S][4];
 #pragma unroll
-            for (int s = 0; s < S; ++s) dg[s][0] = dg[s][1] = dg[s][2] = dg[s][3] = 0u;
+            for (int g4 = 0; g4 < 4; ++g4) {
+                unsigned long long e[4];
 #pragma unroll
-            for (int c = 0; c < 16; ++c) {
-                const double ul = l0 + c < n ? u[l0 + c] : 0.0;
-                long long t = __double2ll_rn(uk * a[c] * ul);
-#pragma unroll
-                for (int s = S - 1; s >= 1; --s) {
-                    const long long d = ((t + 64) & 127) - 64;          // balanced digit in [-64, 63]
-                    t = (t - d) >> 7;
-                    dg[s][c >> 2] |= ((unsigned)d & 0xffu) << (8 * (c & 3));
+                for (int c = 0; c < 4; ++c) {
+                    const int col = 4 * g4 + c;
+                    const double ul = l0 + col < n ? u[l0 + col] : 0.0;
+                    e[c] = i8_digits<S>(__double2ll_rn(uk * a[col] * ul));
                 }
-                dg[0][c >> 2] |= ((unsigned)t & 0xffu) << (8 * (c & 3));  // |t| <= 127 by the choice of scale
+                i8_pack4<S>(e, g4, dg);
             }
 #pragma unroll
             for (int s = 0; s < S; ++s) {
@@ -690,25 +634,76 @@ i8_split_kernel(const double *__restrict__ A, int n, const double *__restrict__ 
 
 using namespace gb;
 
-extern "C" long long gmat_b200_i8_ld(long long n) { return round_up(n, I8_TK); }
+extern "C" long long gmat_b200_i8_ld(long long n) { return i8_rows(n); }
 
 extern "C" int gmat_b200_i8_dosage(const unsigned char *bed_dev, long long n, long long m, long long row_bytes,
-                                   int coding, signed char *g8_dev, long long ld, void *stream) {
+                                   int coding, signed char *g8_dev, unsigned char *g2_dev, long long ld, void *stream) {
     GB_CHECK_ARG(bed_dev && g8_dev && n > 0 && m > 0, "null buffer or empty shape");
-    GB_CHECK_ARG(ld == round_up(n, I8_TK) && row_bytes % 4 == 0, "ld must be gmat_b200_i8_ld(n)");
+    GB_CHECK_ARG(ld >= n && ld % 16 == 0 && row_bytes % 4 == 0, "ld must be a multiple of 16 not below n");
     GB_CHECK_ARG(coding == GMAT_B200_CODING_ADD || coding == GMAT_B200_CODING_DOM, "coding");
     const long long work = m * (ld / 16);
     i8_dosage_kernel<<<(unsigned)((work + 255) / 256), 256, 0, (cudaStream_t)stream>>>(bed_dev, (int)n, m, row_bytes,
-                                                                                      coding, g8_dev, (int)ld);
+                                                                                      coding, g8_dev, g2_dev, (int)ld);
+    GB_LAUNCH_CHECK();
+    return GMAT_B200_OK;
+}
+
+extern "C" int gmat_b200_i8_offs(const int *counts_dev, const double *lutV_dev, long long m, int coding,
+                                 double *offs_dev, double *asq_dev, void *stream) {
+    GB_CHECK_ARG(counts_dev && lutV_dev && offs_dev && asq_dev && m > 0, "null buffer or empty shape");
+    GB_CHECK_ARG(coding == GMAT_B200_CODING_ADD || coding == GMAT_B200_CODING_DOM, "coding");
+    i8_offs_kernel<<<(unsigned)((m + 255) / 256), 256, 0, (cudaStream_t)stream>>>(counts_dev, lutV_dev, m, coding,
+                                                                                 offs_dev, asq_dev);
+    GB_LAUNCH_CHECK();
+    return GMAT_B200_OK;
+}
+
+extern "C" int gmat_b200_absmax(const double *x_dev, long long len, double *out_dev, void *stream) {
+    GB_CHECK_ARG(x_dev && out_dev && len > 0, "null buffer or empty array");
+    cudaStream_t st = (cudaStream_t)stream;
+    GB_CUDA(cudaMemsetAsync(out_dev, 0, sizeof(double), st));
+    const long long want = (len + 1023) / 1024;
+    const int grid = (int)(want < 4LL * sm_count() ? want : 4LL * sm_count());
+    absmax_kernel<<<grid, 256, 0, st>>>(x_dev, len, reinterpret_cast<unsigned long long *>(out_dev));
+    GB_LAUNCH_CHECK();
+    return GMAT_B200_OK;
+}
+
+#define GB_PLANES_SWITCH(n_planes, MACRO)                                                                     \
+    switch (n_planes) {                                                                                       \
+        case 2: MACRO(2); break; case 3: MACRO(3); break; case 4: MACRO(4); break; case 5: MACRO(5); break;   \
+        case 6: MACRO(6); break; default: MACRO(7); break;                                                    \
+    }
+
+extern "C" int gmat_b200_i8_first(const unsigned char *bed_dev, long long n, long long m, long long row_bytes,
+                                  const double *lutU_dev, const double *py_dev, const double *pvp_dev,
+                                  const double *amax_dev, const long long *ilist_dev, long long n_i, int n_planes,
+                                  double *u_dev, double *r_dev, double *side_dev, signed char *planes_dev,
+                                  void *stream) {
+    GB_CHECK_ARG(bed_dev && lutU_dev && py_dev && pvp_dev && amax_dev && ilist_dev && u_dev && r_dev && side_dev &&
+                 planes_dev, "null buffer");
+    GB_CHECK_ARG(n > 0 && m > 0 && n_i > 0, "empty shape");
+    GB_CHECK_ARG(n_planes >= 2 && n_planes <= I8_MAX_PLANES, "n_planes must be in [2, 7]");
+    cudaStream_t st = (cudaStream_t)stream;
+    const int ld = (int)i8_rows(n), np = ld, xrow = (int)i8_xrow(n);
+    i8_first_decode_kernel<<<(unsigned)n_i, 256, 0, st>>>(bed_dev, (int)n, row_bytes, lutU_dev, ilist_dev, u_dev);
+    GB_LAUNCH_CHECK();
+    dim3 grid((unsigned)((n + AU_BK - 1) / AU_BK), (unsigned)((n_i + AU_BI - 1) / AU_BI));
+    i8_au_kernel<<<grid, 256, 0, st>>>(pvp_dev, (int)n, u_dev, (int)n_i, r_dev);
+    GB_LAUNCH_CHECK();
+    const unsigned long long *amax_bits = reinterpret_cast<const unsigned long long *>(amax_dev);
+#define GB_SIDE(SV) i8_side_kernel<SV><<<(unsigned)n_i, I8_PREP_THREADS, 0, st>>>(u_dev, r_dev, py_dev, (int)n, amax_bits, np, ld, xrow, side_dev, planes_dev)
+    GB_PLANES_SWITCH(n_planes, GB_SIDE)
+#undef GB_SIDE
     GB_LAUNCH_CHECK();
     return GMAT_B200_OK;
 }
 
 extern "C" int gmat_b200_i8_split(const double *pvp_dev, long long n, const double *u_dev, long long n_i,
-                                  const double *scale_dev, int n_planes, signed char *planes_dev, void *stream) {
-    GB_CHECK_ARG(pvp_dev && u_dev && scale_dev && planes_dev && n > 0 && n_i > 0, "null buffer or empty shape");
-    GB_CHECK_ARG(n_planes >= 2 && n_planes <= I8_MAX_PLANES, "n_planes must be in [2, 8]");
-    const int ld = (int)round_up(n, I8_TK), np = ld;
+                                  const double *side_dev, int n_planes, signed char *planes_dev, void *stream) {
+    GB_CHECK_ARG(pvp_dev && u_dev && side_dev && planes_dev && n > 0 && n_i > 0, "null buffer or empty shape");
+    GB_CHECK_ARG(n_planes >= 2 && n_planes <= I8_MAX_PLANES, "n_planes must be in [2, 7]");
+    const int ld = (int)i8_rows(n), np = ld;
     const int nb = (int)((n + 127) / 128);
     const int blocks = nb * (nb + 1) / 2;
     // enough CTAs for the chip; each keeps its 16 A values per thread across its share of the first SNPs
@@ -718,95 +713,62 @@ extern "C" int gmat_b200_i8_split(const double *pvp_dev, long long n, const doub
     const int per = (int)((n_i + ysplit - 1) / ysplit);
     dim3 grid(blocks, (unsigned)((n_i + per - 1) / per));
     cudaStream_t st = (cudaStream_t)stream;
-#define GB_SPLIT(SV) i8_split_kernel<SV><<<grid, 256, 0, st>>>(pvp_dev, (int)n, u_dev, (int)n_i, per, scale_dev, np, ld, planes_dev)
-    switch (n_planes) {
-        case 2: GB_SPLIT(2); break; case 3: GB_SPLIT(3); break; case 4: GB_SPLIT(4); break; case 5: GB_SPLIT(5); break;
-        case 6: GB_SPLIT(6); break; case 7: GB_SPLIT(7); break; default: GB_SPLIT(8); break;
-    }
+#define GB_SPLIT(SV) i8_split_kernel<SV><<<grid, I8_PREP_THREADS, 0, st>>>(pvp_dev, (int)n, u_dev, (int)n_i, per, side_dev, np, ld, planes_dev)
+    GB_PLANES_SWITCH(n_planes, GB_SPLIT)
 #undef GB_SPLIT
     GB_LAUNCH_CHECK();
     return GMAT_B200_OK;
 }
 
-extern "C" int gmat_b200_i8_scan(const signed char *g8_dev, long long n, long long m, const signed char *planes_dev,
+extern "C" int gmat_b200_i8_scan(const signed char *g8_dev, const unsigned char *g2_dev, long long n, long long m,
+                                 const signed char *planes_dev,
                                  int n_planes, const long long *ilist_dev, long long n_i,
                                  const int *item_prefix_dev, const int *jt0_dev, long long total_items,
-                                 const double *scale_dev, const double *s_dev, const double *upy_dev,
-                                 const double *t1_dev, const double *e_dev, const double *offs_dev,
+                                 const double *side_dev, const double *offs_dev, const double *asq_dev,
                                  int pair_space, double chi_cut, gmat_b200_hit *hits_dev, long long cap,
-                                 unsigned long long *count_dev, double *q_debug_dev, int wide, void *stream) {
-    GB_CHECK_ARG(g8_dev && planes_dev && ilist_dev && item_prefix_dev && jt0_dev && scale_dev && s_dev && upy_dev &&
-                 t1_dev && e_dev && offs_dev && count_dev, "null buffer");
+                                 unsigned long long *count_dev, int *recheck_dev, long long recheck_cap,
+                                 unsigned long long *recheck_count_dev, double recheck_tol, double *q_debug_dev,
+                                 int variant, void *stream) {
+    GB_CHECK_ARG(g8_dev && g2_dev && planes_dev && ilist_dev && item_prefix_dev && jt0_dev && side_dev && offs_dev && asq_dev &&
+                 count_dev && recheck_count_dev, "null buffer");
     GB_CHECK_ARG(n > 0 && m > 0 && n_i > 0 && total_items >= 0 && total_items < (1LL << 31), "shape");
-    GB_CHECK_ARG(n_planes >= 2 && n_planes <= I8_MAX_PLANES, "n_planes must be in [2, 8]");
+    GB_CHECK_ARG(n_planes >= 2 && n_planes <= I8_MAX_PLANES, "n_planes must be in [2, 7]");
     GB_CHECK_ARG(pair_space == GMAT_B200_PAIRS_UPPER || pair_space == GMAT_B200_PAIRS_ALL, "pair_space");
     GB_CHECK_ARG(cap == 0 || hits_dev, "hits buffer");
+    GB_CHECK_ARG(recheck_cap == 0 || recheck_dev, "re-check buffer");
+    GB_CHECK_ARG(variant == 2 || variant == 3, "variant must be 2 (full 256-row MMAs) or 3 (trimmed MMAs)");
     if (total_items == 0) return GMAT_B200_OK;
     cudaStream_t st = (cudaStream_t)stream;
     I8Params p;
-    p.n = (int)n; p.m = (int)m; p.ld = (int)round_up(n, I8_TK); p.np = p.ld;
+    p.n = (int)n; p.m = (int)m; p.ld = (int)i8_rows(n); p.np = p.ld;
     p.n_planes = n_planes; p.n_kt = p.ld / I8_TK; p.n_slab = (int)((n + I8_SLAB - 1) / I8_SLAB);
     p.n_i = (int)n_i; p.pair_space = pair_space;
+    p.xkt = (int)(i8_xrow(n) / I8_TK); p.xcol = (int)(i8_xrow(n) % I8_TK);
     GB_CHECK_ARG((long long)n_i * n_planes * p.np < (1LL << 31), "plane buffer has too many rows for one tensor map");
     p.total_items = (int)total_items; p.item_prefix = item_prefix_dev; p.jt0 = jt0_dev;
-    p.ilist = ilist_dev; p.g8 = g8_dev; p.scale = scale_dev; p.s_i = s_dev; p.upy = upy_dev; p.t1 = t1_dev; p.e = e_dev;
-    p.offs = offs_dev; p.chi_cut = chi_cut; p.hits = hits_dev; p.cap = cap; p.count = count_dev; p.q_debug = q_debug_dev;
+    p.ilist = ilist_dev; p.g8 = g8_dev; p.g2 = g2_dev; p.side = side_dev; p.offs = offs_dev; p.asq = asq_dev;
+    p.chi_cut = chi_cut; p.hits = hits_dev; p.cap = cap; p.count = count_dev;
+    p.recheck = recheck_dev; p.recheck_cap = recheck_cap; p.recheck_count = recheck_count_dev;
+    p.recheck_tol = recheck_tol;
+    p.wlo = 2.0;
+    for (int q = 0; q < n_planes; ++q) p.wlo *= 0.00390625;      // 2 * 256^-S: weight of the low digit rows
+    p.q_debug = q_debug_dev;
+    p.trim = variant >= 3;
 
-    CUtensorMap map_g, map_p;
+    CUtensorMap map_g, map_ph;                                    // plane map with 128-row boxes (one half per CTA)
     int rc = make_map(&map_g, g8_dev, p.ld, m, p.ld, I8_TJ);
-    if (rc == GMAT_B200_OK) rc = make_map(&map_p, planes_dev, p.ld, (long long)n_i * n_planes * p.np, p.ld, I8_TK);
+    if (rc == GMAT_B200_OK) rc = make_map(&map_ph, planes_dev, p.ld, (long long)n_i * n_planes * p.np, p.ld, I8P_HALF);
     if (rc != GMAT_B200_OK) return rc;
-    const int grid = (int)(total_items < sm_count() ? total_items : sm_count());
-    GB_CHECK_ARG(wide == 0 || wide == 2 || wide == 3 || wide == 4,
-                 "variant must be 0 (one CTA per 128-SNP tile), 2 (CTA pair), 3 (CTA pair, trimmed MMAs) or 4 (CTA "
-                 "pair, trimmed MMAs, two digit planes per genotype tile)");
-    GB_CHECK_ARG(wide != 4 || n_planes % 2 == 0, "variant 4 multiplies the digit planes two at a time: n_planes must be even");
-    p.trim = wide >= 3;
-    if (wide == 4) {
-        CUtensorMap map_ph;
-        rc = make_map(&map_ph, planes_dev, p.ld, (long long)n_i * n_planes * p.np, p.ld, I8P_HALF);
-        if (rc != GMAT_B200_OK) return rc;
-        const int smem_bytes = I8Q_NS * I8Q_STAGE_BYTES + 1024 + (int)sizeof(I8QBars);
-        GB_CUDA(cudaFuncSetAttribute(i8_scan_pair2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
-        const int pairs_of_sms = sm_count() / 2;
-        const int grid2 = 2 * (int)(total_items < pairs_of_sms ? total_items : pairs_of_sms);
-        i8_scan_pair2_kernel<<<grid2, I8Q_THREADS, smem_bytes, st>>>(map_g, map_ph, p);
-    } else if (wide >= 2) {
-        CUtensorMap map_ph;                                       // plane map with 128-row boxes (one half per CTA)
-        rc = make_map(&map_ph, planes_dev, p.ld, (long long)n_i * n_planes * p.np, p.ld, I8P_HALF);
-        if (rc != GMAT_B200_OK) return rc;
-        const int smem_bytes = I8P_NS * I8P_STAGE_BYTES + 1024 + (int)sizeof(I8PBars);
-        GB_CUDA(cudaFuncSetAttribute(i8_scan_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
-        const int pairs_of_sms = sm_count() / 2;
-        const int grid2 = 2 * (int)(total_items < pairs_of_sms ? total_items : pairs_of_sms);
-        i8_scan_pair_kernel<<<grid2, I8_THREADS, smem_bytes, st>>>(map_g, map_ph, p);
-    } else {
-        const int smem_bytes = I8_NS * I8_STAGE_BYTES + 1024 + (int)sizeof(I8Bars);
-        GB_CUDA(cudaFuncSetAttribute(i8_scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
-        i8_scan_kernel<<<grid, I8_THREADS, smem_bytes, st>>>(map_g, map_p, p);
-    }
+    const int smem_bytes = I8P_NS * I8P_STAGE_BYTES + 1024 + (int)sizeof(I8PBars);
+    GB_CUDA(cudaFuncSetAttribute(i8_scan_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
+    // the whole 228 KB as shared memory: with the next smaller carveout (196 KB) nothing is left beside this kernel's
+    // 194 KB and the operand kernels of the next batch could not co-reside with it (they then ran AFTER the scan:
+    // 2 ms of every 11)
+    GB_CUDA(cudaFuncSetAttribute(i8_scan_pair_kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                 cudaSharedmemCarveoutMaxShared));
+    const int pairs_of_sms = sm_count() / 2;
+    const int grid2 = 2 * (int)(total_items < pairs_of_sms ? total_items : pairs_of_sms);
+    i8_scan_pair_kernel<<<grid2, I8_THREADS, smem_bytes, st>>>(map_g, map_ph, p);
     GB_LAUNCH_CHECK();
-    return GMAT_B200_OK;
-}
-
-extern "C" int gmat_b200_i8_peak(int iters, double *tops) {
-    GB_CHECK_ARG(iters > 0 && tops, "iters/tops");
-    const int smem_bytes = I8_STAGE_BYTES + 1024;
-    GB_CUDA(cudaFuncSetAttribute(i8_peak_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
-    cudaEvent_t e0, e1;
-    GB_CUDA(cudaEventCreate(&e0));
-    GB_CUDA(cudaEventCreate(&e1));
-    const int grid = sm_count();
-    i8_peak_kernel<<<grid, 128, smem_bytes>>>(iters / 8 + 1);          // warm-up
-    GB_CUDA(cudaEventRecord(e0));
-    i8_peak_kernel<<<grid, 128, smem_bytes>>>(iters);
-    GB_CUDA(cudaEventRecord(e1));
-    GB_CUDA(cudaEventSynchronize(e1));
-    GB_LAUNCH_CHECK();
-    float ms = 0.f;
-    GB_CUDA(cudaEventElapsedTime(&ms, e0, e1));
-    cudaEventDestroy(e0);
-    cudaEventDestroy(e1);
-    *tops = 2.0 * grid * (double)iters * 4.0 * I8_TJ * I8_TK * 32.0 / (ms * 1e-3) / 1e12;
     return GMAT_B200_OK;
 }

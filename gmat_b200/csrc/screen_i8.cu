@@ -385,8 +385,6 @@ __global__ void __launch_bounds__(256) screen_exact_kernel(
 
 using namespace gb;
 
-extern "C" int gmat_b200_i8_dosage(const unsigned char *bed_dev, long long n, long long m, long long row_bytes,
-                                   int coding, signed char *g8_dev, long long ld, void *stream);
 extern "C" int gmat_b200_epi_eff(const unsigned char *bed_dev, long long n, long long m, long long row_bytes,
                                  const double *lutU_dev, const double *lutV_dev, const double *py_dev,
                                  const long long *ilist_dev, long long n_i, int flags, double eff_cut,
@@ -460,7 +458,7 @@ extern "C" int gmat_b200_epi_eff_i8(const unsigned char *bed_dev, long long n, l
     double *tV = sc.get<double>((size_t)m), *tUall = tV;
     float *oV = sc.get<float>((size_t)m), *cV = sc.get<float>((size_t)m), *tab32 = sc.get<float>(112);
     GB_CHECK_ARG(g8V && dig && tV && oV && cV && tab32, "out of device memory");
-    int rc = gmat_b200_i8_dosage(bed_dev, n, m, row_bytes, codingV, g8V, ld, stream);
+    int rc = gmat_b200_i8_dosage(bed_dev, n, m, row_bytes, codingV, g8V, nullptr, ld, stream);
     if (rc != GMAT_B200_OK) return rc;
     sc_dot_kernel<<<(unsigned)((m + 7) / 8), 256, 0, st>>>(g8V, ld, (int)n, m, py_dev, tV);
     GB_LAUNCH_CHECK();
@@ -468,7 +466,7 @@ extern "C" int gmat_b200_epi_eff_i8(const unsigned char *bed_dev, long long n, l
         g8U = sc.get<signed char>((size_t)m * ld);
         tUall = sc.get<double>((size_t)m);
         GB_CHECK_ARG(g8U && tUall, "out of device memory");
-        rc = gmat_b200_i8_dosage(bed_dev, n, m, row_bytes, codingU, g8U, ld, stream);
+        rc = gmat_b200_i8_dosage(bed_dev, n, m, row_bytes, codingU, g8U, nullptr, ld, stream);
         if (rc != GMAT_B200_OK) return rc;
         sc_dot_kernel<<<(unsigned)((m + 7) / 8), 256, 0, st>>>(g8U, ld, (int)n, m, py_dev, tUall);
         GB_LAUNCH_CHECK();

@@ -212,86 +212,69 @@ def exact_engine(store):
 
 
 def i8_planes():
-    """Digit planes of the int8 engine (GMAT_B200_I8_PLANES, 2..8; 8 = 56 bits, finer than FP64 itself)."""
-    return int(os.environ.get("GMAT_B200_I8_PLANES", "8"))
+    """Digit planes of the int8 engine (GMAT_B200_I8_PLANES, 2..7).  S base-256 planes carry 8S - 1 bits of
+    max|diag(u) Z'PZ diag(u)|: 6 (default) = 47 bits, var within ~1e-12 of FP64 on real Z'PZ; 7 = 55 bits, finer
+    than the FP64 rounding of the matrix itself.  Pairs whose variance is too small for the planes in use are
+    re-evaluated in FP64 (I8Exact.RECHECK_TOL), so this is a speed knob."""
+    return int(os.environ.get("GMAT_B200_I8_PLANES", "6"))
 
 
 class I8Exact(object):
     """INT8 tensor-core engine of the exact scan (gmat_b200/csrc/ozaki.cu): same statistics as
     ``epi_exact_scan`` (remma_epiAA.py:72-82), the n^2-per-pair quadratic form evaluated with tcgen05 int8 MMAs on
-    an error-free digit-plane split of diag(u_i) Z'PZ diag(u_i).  Built once per scan (operands of the second SNPs
-    stay resident: integer codes [m][ld] int8, their FP64 copy for the two O(n)-per-pair GEMM terms)."""
+    an error-free digit-plane split of diag(u_i) Z'PZ diag(u_i); the two O(n)-per-pair terms ride in the same MMAs as
+    four extra plane rows.  Every step is a kernel of libgmat_b200.so; torch owns the buffers, streams and events.
+    Built once per scan (operands of the second SNPs stay resident: integer codes [m][ld] int8, o_j, sum a_j^2)."""
 
     PLANE_BYTES = 4 << 30          # budget of ONE digit-plane buffer (first SNPs per launch follow from it); two exist
+    MAX_BATCH = 128                # first SNPs per launch at most
+    RECHECK_TOL = 2.5e-10          # a pair is re-evaluated in FP64 when 10 sigma of the split error > this x |var|
+    RECHECK_CAP = 1 << 20
+    FIRST_BATCH = 16               # the first launch of a scan is small: its operands cannot be built behind a scan
 
-    def __init__(self, store, lutU, lutV, coding_v, py_dev, pvp_dev, n_planes=None):
-        self.store, self.lutU, self.py = store, lutU, py_dev.reshape(-1)
+    def __init__(self, store, lutU, lutV, coding_v, py_dev, pvp_dev, n_planes=None, packed=None):
+        self.store, self.lutU, self.lutV, self.py = store, lutU, lutV, py_dev.reshape(-1).contiguous()
         self.A = pvp_dev
+        self._packed = packed          # Z'PZ in the FP64 pair kernel's order (built on first use: re-checks are rare)
         self.n_planes = int(i8_planes() if n_planes is None else n_planes)
+        if not 2 <= self.n_planes <= 7:
+            raise ValueError("GMAT_B200_I8_PLANES must be in [2, 7]")
         n, m, dev = store.n, store.m, store.device
         self.ld = int(lib.gmat_b200_i8_ld(n))
         self.g8 = torch.empty((m, self.ld), dtype=torch.int8, device=dev)
+        self.g2 = torch.empty((m, self.ld // 4), dtype=torch.uint8, device=dev)
         check(lib.gmat_b200_i8_dosage(_p(store.bed, "unsigned char *"), n, m, store.row_bytes, coding_v,
-                                      _p(self.g8, "signed char *"), self.ld, _stream()), "gmat_b200_i8_dosage")
-        self.offs = (-lutV[:, 0]).contiguous()                     # lut[j][code 0] = 0 - o_j
-        # second SNPs whose integer code is the same for everybody have w == 0 exactly (eff = var = 0, chi = NaN in
-        # the reference); the expanded form would return rounding noise instead, so they are flagged (o_j = NaN)
-        tabv = torch.tensor([0, 0, 1, 2] if coding_v == ADD else [0, 0, 1, 0], dtype=torch.int32, device=dev)
-        present = store.counts > 0
-        present[:, 1] = False
-        hi = torch.where(present, tabv, torch.full_like(tabv, -1)).amax(dim=1)
-        lo = torch.where(present, tabv, torch.full_like(tabv, 9)).amin(dim=1)
-        self.offs[hi <= lo] = float("nan")
-        # a missing call makes the coded column NaN in the reference's numpy path (remma_epiAA.py:59-61 on
-        # read_plink's NaN), so every statistic of such a SNP is NaN and it is never reported: second SNPs are
-        # flagged (o_j = +inf -> eff = var = chi = NaN); for a FIRST SNP the NaN of lutU[i][code 01] propagates
-        self.offs[store.counts[:, 1] > 0] = float("inf")
-        self.amax = float(pvp_dev.abs().max())
+                                      _p(self.g8, "signed char *"), _p(self.g2, "unsigned char *"), self.ld,
+                                      _stream()), "gmat_b200_i8_dosage")
+        self.offs = torch.empty((m,), dtype=torch.float64, device=dev)
+        self.asq = torch.empty((m,), dtype=torch.float64, device=dev)
+        check(lib.gmat_b200_i8_offs(_p(store.counts, "int *"), _p(lutV, "double *"), m, coding_v,
+                                    _p(self.offs, "double *"), _p(self.asq, "double *"), _stream()),
+              "gmat_b200_i8_offs")
+        self.amax = torch.empty((1,), dtype=torch.float64, device=dev)
+        check(lib.gmat_b200_absmax(_p(self.A, "double *"), self.A.numel(), _p(self.amax, "double *"), _stream()),
+              "gmat_b200_absmax")
         per_first = self.n_planes * self.ld * self.ld
-        self.batch = int(max(1, min(64, self.PLANE_BYTES // per_first)))
-        # two plane buffers: the split of batch k+1 (side stream) overlaps the scan of batch k
+        self.batch = int(max(1, min(self.MAX_BATCH, self.PLANE_BYTES // per_first)))
+        # two plane buffers (and two sets of per-batch scratch): the operands of batch k+1 are built on a side
+        # stream while the scan of batch k is running
         self.planes = [torch.zeros((self.batch * per_first,), dtype=torch.int8, device=dev) for _ in range(2)]
+        self.u = [torch.empty((self.batch, n), dtype=torch.float64, device=dev) for _ in range(2)]
+        self.r = [torch.empty((self.batch, n), dtype=torch.float64, device=dev) for _ in range(2)]
+        self.side = [torch.empty((self.batch, 8), dtype=torch.float64, device=dev) for _ in range(2)]
         self._prep_stream = torch.cuda.Stream(device=dev)
-        self._shifts = torch.tensor([0, 2, 4, 6], dtype=torch.uint8, device=dev)
-        # kernel variant: 3 = CTA pair (tcgen05 cta_group::2), one digit plane at a time, TMEM double-buffered, only
-        # the plane rows that can be non-zero issued (default: fastest measured, 8.1e7 pairs/s at n=2000);
-        # 4 = the same with every genotype tile multiplied by the tiles of TWO digit planes while it is in shared
-        # memory (-25 % L2 -> SM bytes, but both TMEM accumulators are busy, so the drain of a row tile is exposed:
-        # 7.5e7; needs an even number of planes); 2 = CTA pair with full 256-row MMAs; 0 = one CTA per 128-SNP tile
+        # kernel variant: 3 = only the plane rows that can be non-zero are issued (default); 2 = full 256-row MMAs
+        # (same bits, kept for A/B)
         self.wide = int(os.environ.get("GMAT_B200_I8_VARIANT", "3"))
-        if self.wide not in (0, 2, 3, 4):
-            raise ValueError("GMAT_B200_I8_VARIANT must be 0, 2, 3 or 4")
-        if self.wide == 4 and self.n_planes % 2:
-            self.wide = 3
+        if self.wide not in (2, 3):
+            raise ValueError("GMAT_B200_I8_VARIANT must be 2 or 3")
         self.kernel_events = None      # bench.py: list of (start, end) CUDA events around every i8_scan launch
-
-    def _coded_first(self, il):
-        """[len(il)][n] FP64 coded first SNPs: lutU[i][code] (missing calls of a FIRST SNP are fine: they code 0)."""
-        rows = self.store.bed[il]
-        codes = ((rows[:, :, None] >> self._shifts) & 3).reshape(len(il), -1)[:, :self.store.n]
-        return torch.gather(self.lutU[il], 1, codes.long())
-
-    M_CHUNK = 65536    # second SNPs whose integer codes are widened to FP64 at a time for the side-term GEMMs
-
-    def _side_terms(self, r, upy_vec):
-        """The two O(n)-per-pair FP64 terms for a chunk of first SNPs: [nc][m] each (library DGEMMs)."""
-        n, m = self.store.n, self.store.m
-        nc = r.shape[0]
-        t1 = torch.empty((nc, m), dtype=torch.float64, device=r.device)
-        e = torch.empty((nc, m), dtype=torch.float64, device=r.device)
-        lhs = torch.cat([r, upy_vec])
-        for j0 in range(0, m, self.M_CHUNK):
-            j1 = min(m, j0 + self.M_CHUNK)
-            gd = self.g8[j0:j1, :n].to(torch.float64)                      # integer codes as FP64, [chunk][n]
-            both = lhs @ gd.T
-            t1[:, j0:j1] = both[:nc]
-            e[:, j0:j1] = both[nc:]
-        return t1, e
+        self.last_rechecked = 0        # pairs of the last scan that were re-evaluated in FP64
 
     def _work_items(self, ih, pair_space):
-        """(item_prefix[n_i+1], jt0[n_i]) int32 host arrays: tiles of 128 second SNPs every first SNP needs."""
+        """(item_prefix[n_i+1], jt0[n_i]) int32 host arrays: tiles of 256 second SNPs every first SNP needs."""
         m = self.store.m
-        tj = 256 if self.wide else 128                 # second SNPs per work item
+        tj = 256                                       # second SNPs per work item (a CTA pair)
         n_jt = (m + tj - 1) // tj
         if pair_space == PAIRS_ALL:
             jt0 = np.zeros(len(ih), dtype=np.int64)
@@ -302,89 +285,106 @@ class I8Exact(object):
         prefix = np.concatenate([[0], np.cumsum(cnt)])
         return prefix.astype(np.int32), jt0.astype(np.int32)
 
-    SUPER = 1024       # first SNPs whose O(n)-per-pair terms are formed by one pair of library GEMMs
+    def packed(self):
+        if self._packed is None:
+            self._packed = pack_pvp(self.A)
+        return self._packed
 
     def scan(self, ilist, pair_space, chi_cut, cap=1 << 20, q_debug=False):
         """All launches of the scan are queued back to back (one hit buffer, one counter, no host synchronisation
-        between first-SNP batches); the counter is read once at the end and the scan repeated with the exact
-        capacity in the rare case the buffer was too small.  Per chunk of SUPER first SNPs the FP64 side terms come
-        from one stacked GEMM; per batch (plane-buffer budget) the digit-plane split runs on a side stream into
-        the other plane buffer while the tensor-core scan of the previous batch is still running."""
+        between first-SNP batches); the counters are read once at the end and the scan repeated with the exact
+        capacity in the rare case a buffer was too small.  Per batch (plane-buffer budget) the operand kernels
+        (first-SNP decode, Z'PZ u, side table, digit split) run on a side stream into the other plane buffer while
+        the tensor-core scan of the previous batch is still running."""
         store, dev = self.store, self.store.device
         n, m = store.n, store.m
         ilist = np.ascontiguousarray(ilist, dtype=np.int64)
         if len(ilist) and (ilist.min() < 0 or ilist.max() >= m):
             raise ValueError("first SNP out of range")
-        count = torch.zeros((1,), dtype=torch.int64, device=dev)
+        count = torch.zeros((2,), dtype=torch.int64, device=dev)          # [hits, re-checks]
         main = torch.cuda.current_stream()
         prep = self._prep_stream
+        il_dev = torch.as_tensor(ilist).to(dev, non_blocking=True)
+        # batches: a short one first (nothing hides its operand kernels), then full plane buffers
+        bounds, b0 = [], 0
+        while b0 < len(ilist):
+            ni = min(self.FIRST_BATCH if not bounds else self.batch, self.batch, len(ilist) - b0)
+            bounds.append((b0, ni))
+            b0 += ni
+        # work tables of every batch in one upload: [prefix (ni+1), jt0 (ni)] per batch, back to back
+        tabs, offs, totals = [], [], []
+        at = 0
+        for b0, ni in bounds:
+            prefix, jt0 = self._work_items(ilist[b0:b0 + ni], pair_space)
+            tabs += [prefix, jt0]
+            offs.append(at)
+            totals.append(int(prefix[-1]))
+            at += len(prefix) + len(jt0)
+        tab_dev = torch.as_tensor(np.concatenate(tabs) if tabs else np.zeros(1, np.int32)).to(dev, non_blocking=True)
+        rcap = self.RECHECK_CAP
         while True:
             hits = alloc_hits(cap, dev)
+            recheck = torch.empty((max(rcap, 1), 2), dtype=torch.int32, device=dev)
             count.zero_()
-            dbg, keep = [], []
+            inputs_ready = main.record_event()
+            dbg = []
             scan_done = [None, None]                                        # event per plane buffer
             k = 0
-            for c0 in range(0, len(ilist), self.SUPER):
-                ic = ilist[c0:c0 + self.SUPER]
-                il_all = torch.as_tensor(ic).to(dev, non_blocking=True)
-                u_all = self._coded_first(il_all)                           # [nc][n]
-                r = u_all * (u_all @ self.A)                                # u o (A u)   (A symmetric)
-                upy_vec = u_all * self.py
-                s_all = r.sum(dim=1).contiguous()
-                upy_all = upy_vec.sum(dim=1).contiguous()
-                t1_all, e_all = self._side_terms(r, upy_vec)                # [nc][m] a_j . r_i, a_j . (u_i o py)
-                scale_all = (u_all.abs().amax(dim=1) ** 2 * (self.amax / 0.99)).clamp_min(1e-200).contiguous()
-                del r, upy_vec
-                side_ready = main.record_event()
-                keep.append((il_all, u_all, s_all, upy_all, t1_all, e_all, scale_all))
-                for b0 in range(0, len(ic), self.batch):
-                    ih = ic[b0:b0 + self.batch]
-                    ni = len(ih)
-                    prefix, jt0 = self._work_items(ih, pair_space)
-                    total = int(prefix[-1])
-                    if total == 0:
-                        continue
-                    tab = torch.as_tensor(np.concatenate([prefix, jt0])).to(dev, non_blocking=True)
-                    planes = self.planes[k & 1]
-                    u, scale = u_all[b0:b0 + ni], scale_all[b0:b0 + ni]
-                    with torch.cuda.stream(prep):
-                        prep.wait_event(side_ready)
-                        if scan_done[k & 1] is not None:
-                            prep.wait_event(scan_done[k & 1])               # the scan that last read this buffer
-                        check(lib.gmat_b200_i8_split(_p(self.A, "double *"), n, _p(u, "double *"), ni,
-                                                     _p(scale, "double *"), self.n_planes,
-                                                     _p(planes, "signed char *"), _stream()), "gmat_b200_i8_split")
-                        split_done = prep.record_event()
-                    main.wait_event(split_done)
-                    qd = torch.zeros((ni, m), dtype=torch.float64, device=dev) if q_debug else None
-                    if self.kernel_events is not None:
-                        ev = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
-                        ev[0].record()
-                    check(lib.gmat_b200_i8_scan(
-                        _p(self.g8, "signed char *"), n, m, _p(planes, "signed char *"), self.n_planes,
-                        _p(il_all[b0:b0 + ni], "long long *"), ni, _p(tab, "int *"),
-                        ffi.cast("int *", tab.data_ptr() + 4 * (ni + 1)), total,
-                        _p(scale, "double *"), _p(s_all[b0:b0 + ni], "double *"), _p(upy_all[b0:b0 + ni], "double *"),
-                        _p(t1_all[b0:b0 + ni], "double *"), _p(e_all[b0:b0 + ni], "double *"),
-                        _p(self.offs, "double *"), pair_space, float(chi_cut),
-                        ffi.cast("gmat_b200_hit *", hits.data_ptr()), cap,
-                        ffi.cast("unsigned long long *", count.data_ptr()), _p(qd, "double *"), int(self.wide),
-                        _stream()), "gmat_b200_i8_scan")
-                    if self.kernel_events is not None:
-                        ev[1].record()
-                        self.kernel_events.append(ev)
-                    scan_done[k & 1] = main.record_event()
-                    keep.append(tab)
-                    if q_debug:
-                        dbg.append(qd)
-                    k += 1
-            cnt = int(count.item())                                         # the one synchronisation of the scan
+            for bi, (b0, ni) in enumerate(bounds):
+                total = totals[bi]
+                if total == 0:
+                    continue
+                slot = k & 1
+                planes, u, r, side = self.planes[slot], self.u[slot], self.r[slot], self.side[slot]
+                il_ptr = ffi.cast("long long *", il_dev.data_ptr() + 8 * b0)
+                with torch.cuda.stream(prep):
+                    prep.wait_event(inputs_ready)
+                    if scan_done[slot] is not None:
+                        prep.wait_event(scan_done[slot])                    # the scan that last read this buffer
+                    check(lib.gmat_b200_i8_first(
+                        _p(store.bed, "unsigned char *"), n, m, store.row_bytes, _p(self.lutU, "double *"),
+                        _p(self.py, "double *"), _p(self.A, "double *"), _p(self.amax, "double *"), il_ptr, ni,
+                        self.n_planes, _p(u, "double *"), _p(r, "double *"), _p(side, "double *"),
+                        _p(planes, "signed char *"), _stream()), "gmat_b200_i8_first")
+                    check(lib.gmat_b200_i8_split(_p(self.A, "double *"), n, _p(u, "double *"), ni,
+                                                 _p(side, "double *"), self.n_planes,
+                                                 _p(planes, "signed char *"), _stream()), "gmat_b200_i8_split")
+                    split_done = prep.record_event()
+                main.wait_event(split_done)
+                qd = torch.zeros((ni, m), dtype=torch.float64, device=dev) if q_debug else None
+                if self.kernel_events is not None:
+                    ev = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+                    ev[0].record()
+                tab_ptr = tab_dev.data_ptr() + 4 * offs[bi]
+                check(lib.gmat_b200_i8_scan(
+                    _p(self.g8, "signed char *"), _p(self.g2, "unsigned char *"), n, m, _p(planes, "signed char *"),
+                    self.n_planes, il_ptr, ni,
+                    ffi.cast("int *", tab_ptr), ffi.cast("int *", tab_ptr + 4 * (ni + 1)), total,
+                    _p(side, "double *"), _p(self.offs, "double *"), _p(self.asq, "double *"),
+                    pair_space, float(chi_cut), ffi.cast("gmat_b200_hit *", hits.data_ptr()), cap,
+                    ffi.cast("unsigned long long *", count.data_ptr()), _p(recheck, "int *"), rcap,
+                    ffi.cast("unsigned long long *", count.data_ptr() + 8), float(self.RECHECK_TOL),
+                    _p(qd, "double *"), int(self.wide), _stream()), "gmat_b200_i8_scan")
+                if self.kernel_events is not None:
+                    ev[1].record()
+                    self.kernel_events.append(ev)
+                scan_done[slot] = main.record_event()
+                if q_debug:
+                    dbg.append(qd)
+                k += 1
+            cnt, rcnt = (int(v) for v in count.tolist())                    # the one synchronisation of the scan
             prep.synchronize()
-            del keep
-            if cnt <= cap:
+            if cnt <= cap and rcnt <= rcap:
                 break
-            cap = cnt
+            cap, rcap = max(cap, cnt), max(rcap, rcnt)
         res = hits_to_numpy(hits, cnt)
+        self.last_rechecked = rcnt
+        if rcnt:
+            # pairs the digit planes could not decide: FP64 DMMA pair kernel, then the same threshold
+            pairs = recheck[:rcnt].cpu().numpy()
+            ex = epi_exact_pairs(store, self.lutU, self.lutV, self.py, self.packed(), pairs)
+            ex = ex[ex["chi"] > chi_cut] if chi_cut >= 0.0 else ex
+            res = np.concatenate([res, ex])
         return (res, torch.cat(dbg)) if q_debug else res
 
 
@@ -502,18 +502,3 @@ def decode_into(store, coding, out, freq_mode=FREQ_NUMPY):
     check(lib.gmat_b200_decode(_p(store.bed, "unsigned char *"), store.n, store.m, store.row_bytes,
                                _p(lut, "double *"), _p(out, "double *"), _stream()), "gmat_b200_decode")
     return out
-
-
-def i8_peak(iters=20000):
-    """Measured issue rate of the int8 tensor-core MMA on this GPU, TOPS (2 ops per MAC)."""
-    require_cuda()
-    out = ffi.new("double *")
-    check(lib.gmat_b200_i8_peak(iters, out), "gmat_b200_i8_peak")
-    return float(out[0])
-
-
-def fp64_peak(kind=0, iters=20000):
-    require_cuda()
-    out = ffi.new("double *")
-    check(lib.gmat_b200_fp64_peak(kind, iters, out), "gmat_b200_fp64_peak")
-    return float(out[0])

@@ -141,7 +141,7 @@ class DeviceModel(object):
         GMAT_B200_EXACT_ENGINE = auto (default: the INT8 tensor-core engine) | i8 | f64 (the FP64 DMMA kernel)."""
         which = engine.exact_engine(store)
         if which == "i8":
-            eng = engine.I8Exact(store, lut_u, lut_v, coding_v, self.py, self.pvp)
+            eng = engine.I8Exact(store, lut_u, lut_v, coding_v, self.py, self.pvp, packed=self.packed)
             return eng.scan
         return lambda ilist, pair_space, chi_cut: engine.epi_exact_scan(store, lut_u, lut_v, self.py, self.packed,
                                                                         ilist, pair_space, chi_cut)

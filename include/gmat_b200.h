@@ -70,19 +70,6 @@ int         gmat_b200_set_device(int device);
 int         gmat_b200_device_info(int *sm_count, int *cc_major, int *cc_minor, long long *hbm_bytes);
 long long   gmat_b200_kernel_launches(void);       /* kernels launched by this library so far   */
 
-/* FP64 issue-rate microbenchmarks (used by bench.py for the roofline denominator).
- * kind 0: DMMA (mma.sync m8n8k4 f64) ; kind 1: DFMA.  Writes TFLOP/s.  */
-int gmat_b200_fp64_peak(int kind, int iters, double *tflops);
-/* DMMA issue-model probe: `ctas_per_sm` CTAs of `warps` warps per SM, each warp an (ia x ib) register tile of
- * independent m8n8k4 accumulators with distinct A/B fragments, no memory traffic.  Writes TFLOP/s.           */
-int gmat_b200_dmma_probe(int warps, int ia, int ib, int ctas_per_sm, int iters, double *tflops);
-/* same, with every k-step's fragments re-loaded from shared memory (shape 0: 4x4 tile, B as LDS.64; 1: 4x4, B as
- * LDS.128; 2: 8x4, LDS.64; 3: 8x4, LDS.128; 4: 4x2, LDS.128): the LDS + DMMA issue mix without any barrier.   */
-int gmat_b200_dmma_lds_probe(int warps, int shape, int ctas_per_sm, int iters, double *tflops);
-/* 8x4 tile (32 DMMAs per step) + nmul DMULs per step; mode 0 grouped/independent, 1 spread/independent,
- * 2 grouped and feeding the step's B fragments.  Writes the DMMA-only TFLOP/s.                               */
-int gmat_b200_dmma_dmul_probe(int warps, int nmul, int mode, int iters, double *tflops);
-
 /* ------------------------------------------------------------------ (1) drop-in symbols ---- */
 /* gmat/process_plink/_read_plink_bed.c:5 -- marker_mat is HOST double[num_snp][num_id]        */
 int read_plink_bed(char *bed_file, long long num_id, long long num_snp, double *marker_mat);
@@ -198,39 +185,56 @@ int gmat_b200_grm(const unsigned char *bed_dev, long long n, long long m, long l
  *   var_ij = a_j' B_i a_j - 2 o_j (a_j . r_i) + o_j^2 s_i ,  r_i = u_i o (Z'PZ u_i), s_i = sum r_i
  *   eff_ij = a_j . (u_i o Z'Py) - o_j (u_i . Z'Py)
  * a_j' B_i a_j is evaluated on the INT8 tensor cores from an error-free split of B_i/scale_i into n_planes signed
- * base-128 digit planes (exact int8 x int8 -> int32 products, recombined in FP64; 8 planes = 56 bits).  A SNP
- * with a missing call has NaN statistics in the reference's numpy path; callers flag such second SNPs with
- * offs = +inf (eff = var = chi = NaN) and monomorphic ones with offs = NaN (eff = var = 0, chi = NaN).          */
-long long gmat_b200_i8_ld(long long n);      /* bytes per row (and rows per plane) of the int8 operands       */
+ * base-256 digit planes (exact int8 x int8 -> int32 products, recombined in FP64; S planes = 8S-1 bits of
+ * max|B_i|, n_planes in [2, 7]).  a_j.r_i and a_j.(u_i o Z'Py) come out of the same MMAs: r_i and u_i o Z'Py are
+ * split into 2S digits each (high and low part: no loss against FP64) and stored as four extra rows of every plane.
+ * Every step below is a kernel of this library (no library GEMM, no host arithmetic); all calls are asynchronous on
+ * `stream`.  A SNP with a missing call has NaN statistics in the reference's numpy path: such second SNPs are flagged
+ * offs = +inf (eff = var = chi = NaN), monomorphic ones offs = NaN (eff = var = 0, chi = NaN), by gmat_b200_i8_offs. */
+long long gmat_b200_i8_ld(long long n);      /* bytes per row AND rows per plane of the int8 operands: n rounded up
+                                              * to 4, plus the 4 extra rows, rounded up to 256                   */
+/* integer code of every SNP: g8[snp][k] = dosage {0,1,2} (ADD) or heterozygote indicator (DOM), 0 for a missing
+ * call and for k >= n; ld a multiple of 16, >= n.  g2_dev (optional, [m][ld/4]): the same values packed 2 bits each,
+ * low bits first (what the scan kernel's epilogue reads)                                                       */
 int gmat_b200_i8_dosage(const unsigned char *bed_dev, long long n, long long m, long long row_bytes, int coding,
-                        signed char *g8_dev /* [m][ld] */, long long ld, void *stream);
-/* planes_dev: [n_i][n_planes][ld][ld] int8, ZERO-initialised by the caller once (blocks above the block diagonal
- * are never written); u_dev [n_i][n] coded first SNPs; scale_dev[i] >= max|B_i| / 0.99                          */
+                        signed char *g8_dev /* [m][ld] */, unsigned char *g2_dev /* [m][ld/4] or NULL */,
+                        long long ld, void *stream);
+/* per second SNP: offs[j] = o_j = -lutV[j][0] with the two flags above, asq[j] = sum_k a_jk^2 (from the counts)   */
+int gmat_b200_i8_offs(const int *counts_dev /* [m][4] */, const double *lutV_dev /* [m][4] */, long long m,
+                      int coding, double *offs_dev /* [m] */, double *asq_dev /* [m] */, void *stream);
+/* *out_dev = max |x[k]| (NaN if any x is NaN)                                                                    */
+int gmat_b200_absmax(const double *x_dev, long long len, double *out_dev, void *stream);
+/* Per batch of n_i first SNPs (ilist_dev): u[ii][k] = lutU[i][code] (coded first SNPs), r = u o (Z'PZ u)
+ * (scratch, [n_i][n]), the side table side[ii][8] = {scale_i, s_i, u_i.Z'Py, scale_r, scale_e, guard unit, 0, 0}
+ * and the four extra rows (n rounded up to 4, +0..3) of every plane of every first SNP.  amax_dev = max|Z'PZ|
+ * (gmat_b200_absmax).  planes_dev: [n_i][n_planes][ld][ld] int8, ZERO-initialised by the caller once.           */
+int gmat_b200_i8_first(const unsigned char *bed_dev, long long n, long long m, long long row_bytes,
+                       const double *lutU_dev, const double *py_dev, const double *pvp_dev /* [n][n] */,
+                       const double *amax_dev, const long long *ilist_dev, long long n_i, int n_planes,
+                       double *u_dev /* [n_i][n] */, double *r_dev /* [n_i][n] */, double *side_dev /* [n_i][8] */,
+                       signed char *planes_dev, void *stream);
+/* rows 0..n-1 of every plane: the digits of B_i / side[ii][0], lower block-triangle of 128 x 128 blocks, diagonal
+ * blocks halved (blocks above the block diagonal are never written and stay zero)                              */
 int gmat_b200_i8_split(const double *pvp_dev /* [n][n] */, long long n, const double *u_dev, long long n_i,
-                       const double *scale_dev, int n_planes, signed char *planes_dev, void *stream);
-/* Work items of one launch are (first SNP ii, tile of 128 second SNPs): item_prefix_dev[n_i+1] = first item of
- * every first SNP, jt0_dev[n_i] = its first tile (UPPER: (i+1)/128, ALL: 0), total_items = item_prefix[n_i]; all
- * device arrays, so that successive launches queue without a host synchronisation.  t1_dev/e_dev: [n_i][m] FP64
- * (a_j . r_i and a_j . (u_i o Z'Py)); offs_dev[m] = o_j (NaN = monomorphic second SNP, +inf = SNP with a missing call);
- * q_debug_dev (optional, [n_i][m]) receives a_j' B_i a_j.  Hits are appended at *count_dev as in
- * gmat_b200_epi_exact_scan (count keeps counting beyond cap).  variant 0: one CTA per work item of 128 second SNPs
- * (tcgen05 cta_group::1); variant 2: a work item is 256 second SNPs computed by a CTA PAIR
- * (cluster of 2, tcgen05 cta_group::2) -- jt0 and the item counts are then in units of 256 second SNPs; variant 3 =
- * variant 2 issuing only the plane rows that can be non-zero (last row tile trimmed to n, the zero 128 x 128 block
- * right of the diagonal skipped): same results bit for bit, fewer MMAs -- what the engine uses; variant 4 (n_planes
- * even) = variant 3 with every genotype tile multiplied by the tiles of two digit planes while it sits in shared
- * memory (two TMEM accumulators, two groups of epilogue warps): a quarter fewer operand bytes from L2, but no
- * second accumulator buffer to hide the drain of a row tile behind; same bits again.                            */
-int gmat_b200_i8_scan(const signed char *g8_dev, long long n, long long m, const signed char *planes_dev,
-                      int n_planes, const long long *ilist_dev, long long n_i,
+                       const double *side_dev, int n_planes, signed char *planes_dev, void *stream);
+/* Work items of one launch are (first SNP ii, tile of 256 second SNPs, computed by a CTA PAIR -- cluster of 2,
+ * tcgen05 cta_group::2): item_prefix_dev[n_i+1] = first item of every first SNP, jt0_dev[n_i] = its first tile
+ * (UPPER: (i+1)/256, ALL: 0), total_items = item_prefix[n_i]; all device arrays, so that successive launches queue
+ * without a host synchronisation.  Hits are appended at *count_dev as in gmat_b200_epi_exact_scan (count keeps
+ * counting beyond cap).  A-posteriori guard: a pair whose variance is so small against scale_i that the digits the
+ * split dropped could matter (side[ii][5] * asq[j] > recheck_tol * |var|) is NOT decided here; it is appended to
+ * recheck_dev ([recheck_cap][2] ints, counter *recheck_count_dev, counting beyond the cap) for the caller to
+ * evaluate with gmat_b200_epi_exact_pairs.  q_debug_dev (optional, [n_i][m]) receives a_j' B_i a_j.
+ * variant 3 issues only the plane rows that can be non-zero (last row tile trimmed, the zero 128 x 128 block right
+ * of the diagonal skipped) -- what the engine uses; variant 2 issues full 256-row MMAs: same results bit for bit. */
+int gmat_b200_i8_scan(const signed char *g8_dev, const unsigned char *g2_dev, long long n, long long m,
+                      const signed char *planes_dev, int n_planes, const long long *ilist_dev, long long n_i,
                       const int *item_prefix_dev, const int *jt0_dev, long long total_items,
-                      const double *scale_dev, const double *s_dev, const double *upy_dev,
-                      const double *t1_dev, const double *e_dev, const double *offs_dev,
+                      const double *side_dev, const double *offs_dev, const double *asq_dev,
                       int pair_space, double chi_cut, gmat_b200_hit *hits_dev, long long cap,
-                      unsigned long long *count_dev, double *q_debug_dev, int variant, void *stream);
-
-/* int8 tensor-core issue-rate microbenchmark (tcgen05.mma kind::i8 128x256x32 on resident tiles, all SMs): TOPS  */
-int gmat_b200_i8_peak(int iters, double *tops);
+                      unsigned long long *count_dev, int *recheck_dev, long long recheck_cap,
+                      unsigned long long *recheck_count_dev, double recheck_tol, double *q_debug_dev,
+                      int variant, void *stream);
 
 /* The same GRM on the INT8 tensor cores (gmat_b200/csrc/gram_i8.cu): X X' = G G' - c 1' - 1 c' + d with G the
  * integer dosage / heterozygote indicator matrix, so the n^2 m term is ONE exact int8 x int8 -> int32 GEMM

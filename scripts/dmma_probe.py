@@ -3,7 +3,11 @@
 import json, os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from gmat_b200 import engine
-from gmat_b200._ffi import check, ffi, lib
+from probe import ffi, lib
+
+
+def check(rc):
+    assert rc >= 1, ffi.string(lib.gmat_b200_last_error())
 engine.current_device()
 out = ffi.new("double *")
 res = []
