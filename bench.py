@@ -1,14 +1,21 @@
 #!/usr/bin/env python
 """bench.py -- headline benchmark of the REMMAX hot path on B200 (contract: see DESIGN.md section 6).
 
-    python bench.py --gpus N --steps K --warmup W            # CUDA engine (this repo)
-    python bench.py --impl reference --gpus N --steps K --warmup W   # reference CPU path on host cores
+    python bench.py --gpus N --steps K --warmup W                    # CUDA engine (this repo)
+    python bench.py --impl reference --gpus N --steps K --warmup W   # the UNMODIFIED reference on the host cores
 
-Workload (config.workload): BASELINE.json configs[2] -- remma_epiAA EXACT test, synthetic n=2,000 x m=20,000
-(the largest exact-scan configuration that fits one GPU; configs[1] (agmat GRM n=10,000 x m=500,000) is
-reported in the same line under "extra").  One step = one pass of the hot path over one batch of first-SNPs
-(256 first-SNPs spread over the range, all j > i: ~2.56e6 pairs); under torchrun every rank takes its own
-batch (weak scaling), value = pairs of all ranks / max-over-ranks device time.
+Headline workload (config.workload): BASELINE.json configs[2] -- remma_epiAA EXACT test, synthetic n=2,000 x m=20,000.
+One step = one pass of the hot path over one batch of 1024 first-SNPs (all j > i: ~1.0e7 pairs); under torchrun
+every rank takes its own batch (weak scaling), value = pairs of all ranks / max-over-ranks device time.
+
+Also in the same JSON line:
+  e2e              the public drop-in call remma_epiAA(files in, file out) on the same data
+  extra (N=1)      approximate screen, agmat (configs[1]), decode, the FP64 DMMA engine
+  extra.northstar  the north-star shape n=5,000 x m=50,000 through the drop-in API, every reported row re-derived by the
+                   numpy oracle in the run: a FIXED sub-problem (every 8th first SNP of the exact AA scan) at every N
+                   (strong scaling), remma_epiAD / remma_epiDD (configs[3]) and the 15,000-record repeated-measures
+                   model (configs[4]) -- exhaustive at N=8 (or --northstar-full), on first-SNP subsets below that
+  extra.multi_gpu_parity (N>=2)   sharded output file == single-GPU output file, byte for byte (data with missing calls)
 """
 import argparse
 import json
@@ -37,27 +44,24 @@ VAR_PROP = [0.35, 0.10, 0.55]           # [A, A*A, residual] proportions of the 
 P_CUT = 1.0e-5
 BATCH = 1024                            # first-SNPs per step
 E2E_FIRST = 4096                        # first-SNPs per GPU of the end-to-end call (~4.1e7 pairs)
+REF_FIRST = 4                           # first-SNPs per step of the reference arm (~5.0e4 pairs, ~1 s of numpy/BLAS)
+NS_N, NS_M, NS_P_CUT = 5000, 50000, 1.0e-7     # the north-star shape (BASELINE configs[3]/[4])
 METRIC = "snp_pairs_per_sec_remma_epiAA_exact"
-# dram__bytes_read.sum + dram__bytes_write.sum of one exact-kernel launch of this step, from the committed
-# ncu --set full capture (profiles/r01_kernels_v3.md: 28.87 MB read + ~0 written = packed Z'PZ 17.8 MB + .bed
-# 10 MB + LUTs, read once; the capture ran 128 first-SNPs of the same data shape, the compulsory bytes are the same)
-EXACT_TRAFFIC_BYTES = 28.9e6
-# dram__bytes_read.sum + dram__bytes_write.sum of one i8_scan_pair_kernel launch (64 first SNPs of this shape), from the
-# committed ncu --set full capture (profiles/r01_kernels_v9.md): 1.793 GB read + 3.9 MB written; the compulsory bytes
-# are the digit planes once (1.07 GB, written by i8_split_kernel just before) + G8 40 MB + side terms 20 MB
-I8_TRAFFIC_BYTES = 1.797e9
+# dram__bytes_read.sum + dram__bytes_write.sum of one i8_scan_pair_kernel launch (128 first SNPs of this shape), from the
+# committed ncu --set full capture (profiles/r02_kernels.md); filled in once that capture exists
+I8_TRAFFIC_BYTES = None
 CONFIG = {"workload": "remma_epiAA exact test, synthetic n=%d x m=%d, GRMs [A, A*A] (BASELINE configs[2])"
                       % (N_ID, N_SNP),
           "step": "one batch of %d first-SNPs (evenly spread blocks of 8), all j>i (~1.0e7 pairs) per rank" % BATCH,
           "p_cut": P_CUT, "l2": "flushed (256 MB write) between timed iterations"}
 
 
-def var_com_for(pheno):
-    """Fixed variance components (REML is not on the timed path): VAR_PROP scaled to the phenotypic variance of the
+def var_com_for(pheno, props=VAR_PROP):
+    """Fixed variance components (REML is not on the timed path): proportions scaled to the phenotypic variance of the
     data set, so that the test statistics are calibrated and the output file holds the handful of rows a real scan
     yields (unscaled components made every chi-square anti-conservative: ~0.3 % of all pairs were written)."""
     yv = np.array([float(line.split()[-1]) for line in open(pheno)])
-    return [float(v * np.var(yv)) for v in VAR_PROP]
+    return [float(v * np.var(yv)) for v in props]
 
 
 def i8_ops_per_pair(n, planes, variant=3):
@@ -153,72 +157,69 @@ class ClockSampler(threading.Thread):
 
 
 def make_dataset(workdir, n=N_ID, m=N_SNP):
-    from gmat_b200 import synth
+    import synth
     prefix = os.path.join(workdir, "c3_n%d_m%d" % (n, m))
     ds = synth.write_dataset(prefix, n, m, seed=SEED, n_planted=10, planted_kind="AA")
     return prefix, ds["pheno"]
 
 
-class CpuExact(object):
-    """The reference formulation of the exact scan on the host cores: numpy restatement (oracle.py) of
-    remma_epiAA.py:72-77 -- the reference's exact path IS numpy, so this is what its users run.  The model
-    (GRM, preamble, coded genotypes) is built once, outside the timed region, exactly like on the GPU arm."""
+# ----------------------------------------------------------------------------------------------------------------
+# reference arm: the unmodified reference on the host cores (baseline/reference_arm.py)
+# ----------------------------------------------------------------------------------------------------------------
+REF_SAMPLE = ("one call of the unmodified reference's _remma_epiAA(y, xmat, zmat, gmat_lst, var_com, bed_file, "
+              "snp_lst_0=%d evenly spread first-SNPs, p_cut, out_file) (gmat/remma/remma_epiAA/remma_epiAA.py:16-86, "
+              "pip-installed into baseline/_ref) on the same synthetic files, all host threads (numpy/BLAS); timed: its "
+              "scan loop by its own clock ('Running time: Clock time', remma_epiAA.py:83-85), i.e. without its preamble "
+              "and .bed read" % REF_FIRST)
 
-    def __init__(self, prefix, pheno, ag=None):
-        from oracle import oracle
-        from gmat_b200.uvlmm.design_matrix import design_matrix_wemai_multi_gmat
-        self.oracle = oracle
-        if ag is None:
-            ag, _ = oracle.agmat(prefix)
-        y, xmat, zmat = design_matrix_wemai_multi_gmat(pheno, prefix)
-        self.py, self.pvp = oracle.preamble(y, xmat, zmat, [ag, ag * ag], var_com_for(pheno))
-        self.U, self.V = oracle.coded_pair("AA", oracle.read_plink(prefix))
-        self.m = self.U.shape[1]
 
-    def sample(self, n_first):
-        """Time ``n_first`` evenly spread first-SNPs (all j > i).  Returns (pairs, seconds)."""
-        lst = batch_first_snps(self.m, 0, 1, n_first)
-        t0 = time.perf_counter()
-        hits = 0
-        for i in lst:
-            js, eff, var, chi, p = self.oracle.exact_first_snp(self.U, self.V, i, self.py, self.pvp, False)
-            hits += int(np.sum(p < P_CUT))
-        return n_pairs(lst, self.m), time.perf_counter() - t0
+def reference_sample(prefix, pheno, arm=None):
+    """(pairs, loop seconds, whole-call seconds, arm) of one bounded sample of the reference's exact scan."""
+    from baseline import reference_arm
+    if arm is None:
+        arm = reference_arm.ExactArm(prefix, pheno, var_com_for(pheno), P_CUT)
+    lst = batch_first_snps(N_SNP, 0, 1, REF_FIRST)
+    pairs, loop_s, whole_s, rows = arm.sample(lst)
+    return pairs, loop_s, whole_s, arm
 
 
 def run_reference(args):
-    """--impl reference: the reference's CPU formulation on the host cores, bounded sample per step."""
+    """--impl reference: the UNMODIFIED reference (baseline/_ref) on the host cores, bounded sample per step."""
     if int(os.environ.get("RANK", "0")) != 0:
         return 0
-    n_first = 4
+    from baseline import reference_arm
+    if not reference_arm.available():
+        print(json.dumps({"impl": "reference", "unavailable": "baseline/_ref is missing (run baseline/install_ref.sh "
+                                                              "where /root/reference exists)"}))
+        return 0
     with tempfile.TemporaryDirectory() as d:
         prefix, pheno = make_dataset(d)
-        cpu = CpuExact(prefix, pheno)
-        times, pairs = [], 0
+        arm = None
+        times, whole, pairs = [], [], 0
         for it in range(args.warmup + args.steps):
-            pairs, dt = cpu.sample(n_first)
+            pairs, loop_s, whole_s, arm = reference_sample(prefix, pheno, arm)
             if it >= args.warmup:
-                times.append(dt)
+                times.append(loop_s)
+                whole.append(whole_s)
     t = float(np.mean(times))
     value = pairs / t
-    sample = "%d evenly spread first-SNPs, all j>i = %d pairs per step" % (n_first, pairs)
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": "pairs/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": t * 1e3,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": dict(CONFIG, sample=sample),
-        "cpu_baseline": {"value": value, "unit": "pairs/s", "cores": os.cpu_count(), "kind": "port",
-                         "sample": "numpy restatement of remma_epiAA.py:72-77 (the reference's exact path is "
-                                   "numpy/BLAS, all host threads); " + sample},
+        "config": CONFIG,
+        "cpu_baseline": {"value": value, "unit": "pairs/s", "cores": os.cpu_count(), "kind": "reference",
+                         "sample": REF_SAMPLE + "; %d pairs per step; whole call incl. preamble and file read: %.2f s"
+                                   % (pairs, float(np.mean(whole)))},
         "e2e": {"value": value, "unit": "pairs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     print(json.dumps(line))
     return 0
 
 
-def measure_fp64_peaks(engine, torch):
-    """Roofline denominators for FP64 (absent from MEASURED_PEAKS.json): the library's DMMA issue-rate
-    microbenchmark and cuBLAS DGEMM 4096^3 (torch.matmul float64), best of a few runs, CUDA events."""
+def measure_fp64_peaks(torch):
+    """Roofline denominators for FP64 (absent from MEASURED_PEAKS.json): the DMMA issue-rate microbenchmark of
+    probe/ and cuBLAS DGEMM 4096^3 (torch.matmul float64), best of a few runs, CUDA events."""
     import probe
     dmma = probe.fp64_peak(0, 20000)
     dfma = probe.fp64_peak(1, 20000)
@@ -237,11 +238,24 @@ def measure_fp64_peaks(engine, torch):
     return {"dmma_tflops": dmma, "dfma_tflops": dfma, "cublas_dgemm_tflops": dgemm}
 
 
+def i8_peak_sustained(seconds=1.5):
+    """The int8 MMA issue-rate microbenchmark back to back for ``seconds``: the power-capped rate of the part
+    (mean of the second half of the window)."""
+    import probe
+    t0, rates = time.time(), []
+    while time.time() - t0 < seconds:
+        rates.append(probe.i8_peak(200000))
+    tail = rates[len(rates) // 2:]
+    return float(sum(tail) / len(tail))
+
+
 def run_gpu(args):
     import torch
     import torch.distributed as dist
     from scipy.stats import chi2
-    from gmat_b200 import engine, synth
+    import synth
+    import probe
+    from gmat_b200 import engine
     from gmat_b200._ffi import lib
     from gmat_b200.gmatrix.gmatrix import grm_device
     from gmat_b200.remma import _core
@@ -280,11 +294,20 @@ def run_gpu(args):
         dist.all_reduce(t, op=op)
         return float(t.item())
 
+    MAX = dist.ReduceOp.MAX if world > 1 else None
+    SUM = dist.ReduceOp.SUM if world > 1 else None
+
+    # ONE int8 denominator for every tensor-roofline fraction of this run: the issue-rate microbenchmark on a cold,
+    # unthrottled part, measured before anything else (the sustained, power-capped rate is measured after the timed
+    # steps and reported beside it)
+    i8_peak_burst = probe.i8_peak(20000) if rank == 0 else None
+
     workdir = tempfile.mkdtemp(prefix="gmat_bench_r%d_" % rank)
     prefix, pheno = make_dataset(workdir)            # every rank writes its own identical copy (seeded)
     # ------------- setup, outside the timed region: GRM on the GPU, preamble on the host, upload -------------
     store = engine.GenotypeStore(prefix)
-    ag_dev, _ = grm_device(store, engine.ADD)
+    with _core.par.single_rank():                    # every rank needs the full GRM of its own copy here
+        ag_dev, _ = grm_device(store, engine.ADD)
     ag = ag_dev.cpu().numpy()
     gmat_lst = [ag, ag * ag]
     y, xmat, zmat = design_matrix_wemai_multi_gmat(pheno, prefix)
@@ -299,7 +322,7 @@ def run_gpu(args):
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)       # > 126 MB L2
     # the engine the drop-in runs for this data (GMAT_B200_EXACT_ENGINE, default auto -> int8 tensor cores)
     which = engine.exact_engine(store)
-    i8 = engine.I8Exact(store, lut, lut, engine.ADD, model.py, model.pvp) if which == "i8" else None
+    i8 = engine.I8Exact(store, lut, lut, engine.ADD, model.py, model.pvp, packed=model.packed) if which == "i8" else None
 
     def step():
         if i8 is not None:
@@ -316,24 +339,27 @@ def run_gpu(args):
     if i8 is not None:
         i8.kernel_events = []
     hits = None
+    rechecked = 0
     for k in range(args.steps):
         flush.zero_()                                # L2 flush between timed iterations
         ev[k][0].record()
         hits = step()
         ev[k][1].record()
+        rechecked += i8.last_rechecked if i8 is not None else 0
     barrier()
     launches = lib.gmat_b200_kernel_launches() - launches0
+    i8_peak_load = i8_peak_sustained() if rank == 0 else None          # right after the load, still power-capped
     clocks = sampler.result()
     ms_local = sum(a.elapsed_time(b) for a, b in ev) / args.steps
     kern_ms = kern_n = None
     if i8 is not None:
         kern_n = len(i8.kernel_events)
-        kern_ms = sum(a.elapsed_time(b) for a, b in i8.kernel_events) / max(kern_n, 1)   # per i8_scan launch
+        kern_ms = sum(a.elapsed_time(b) for a, b in i8.kernel_events)     # all i8_scan launches of the timed steps
         i8.kernel_events = None
     print("[bench] rank %d: %.1f ms/step, per-step %s" % (rank, ms_local, [round(a.elapsed_time(b), 1) for a, b in ev]),
           file=sys.stderr)
-    ms = reduce(ms_local, dist.ReduceOp.MAX if world > 1 else None)
-    total_pairs = reduce(float(pairs_rank), dist.ReduceOp.SUM if world > 1 else None)
+    ms = reduce(ms_local, MAX)
+    total_pairs = reduce(float(pairs_rank), SUM)
     value = total_pairs / (ms * 1e-3)
 
     # ------------- e2e: the public drop-in call, HOST buffers, files in / file out, copies inside -------------
@@ -350,16 +376,32 @@ def run_gpu(args):
         barrier()
         if it:
             e2e_t.append(time.perf_counter() - t0)
-    e2e_s = reduce(float(np.mean(e2e_t)), dist.ReduceOp.MAX if world > 1 else None)
+    e2e_phases = {k: round(v, 4) for k, v in _core.PHASES.items()}
+    e2e_s = reduce(float(np.mean(e2e_t)), MAX)
     e2e_value = float(e2e_pairs) / e2e_s
     e2e_rows = sum(1 for _ in open(out_file)) - 1 if rank == 0 else 0
-    # every rank uploads its own copy of the .bed payload, the GRMs (GPU preamble), y and X
-    h2d = world * (store.h2d_bytes + sum(g.nbytes for g in gmat_lst) + y.nbytes + xmat.nbytes) + len(e2e_lst) * 8
-    d2h = 8 + 32 * e2e_rows
+    # rank 0 uploads the GRMs, y and X (the preamble is computed once and broadcast); every rank its .bed payload
+    h2d = world * store.h2d_bytes + sum(g.nbytes for g in gmat_lst) + y.nbytes + xmat.nbytes + len(e2e_lst) * 8
+    d2h = 16 + 32 * e2e_rows
+
+    extra = {}
+    if world > 1 and not args.no_parity:
+        extra["multi_gpu_parity"] = multi_gpu_parity(torch, dist, engine, synth, remma_epiAA, rank, world, workdir,
+                                                     barrier)
+    if not args.no_northstar:
+        extra["northstar"] = northstar(args, torch, dist, engine, _core, synth, rank, world, barrier, reduce, MAX)
 
     line = None
     if rank == 0:
         n = N_ID
+        mp = {}
+        try:
+            mp = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        i8_peaks = {"i8_mma_issue_tops": i8_peak_burst, "i8_mma_issue_tops_sustained": i8_peak_load,
+                    "int8_from_measured_bf16_burst_x2": 2.0 * mp["bf16_tflops"] if mp else None,
+                    "int8_from_measured_bf16_sustained_x2": 2.0 * mp["bf16_tflops_sustained"] if mp else None}
         line = {
             "metric": METRIC, "value": value, "unit": "pairs/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
@@ -367,6 +409,7 @@ def run_gpu(args):
             "clocks": clocks, "gpu_launches": int(launches),
             "e2e": {"value": e2e_value, "unit": "pairs/s", "h2d_bytes_per_step": int(h2d),
                     "d2h_bytes_per_step": int(d2h), "seconds": e2e_s, "pairs": e2e_pairs, "rows_in_file": e2e_rows,
+                    "phases_rank0_s": e2e_phases,
                     "what": "gmat_b200.remma.remma_epiAA(pheno_file, bed_file, gmat_lst, var_com, snp_lst_0=%d "
                             "first-SNPs): phenotype parse + GRM upload + GPU preamble + .bed read + H2D + scan + D2H "
                             "+ file" % len(e2e_lst)},
@@ -375,34 +418,37 @@ def run_gpu(args):
             planes = i8.n_planes
             alg, iss = i8_ops_per_pair(n, planes, i8.wide)
             launches_per_step = kern_n / float(args.steps)
-            pairs_per_launch = pairs_rank / launches_per_step
-            achieved = pairs_per_launch * alg / (kern_ms * 1e-3) / 1e12
-            issued = pairs_per_launch * iss / (kern_ms * 1e-3) / 1e12
-            import probe
-            peaks = {"i8_mma_issue_tops": probe.i8_peak(20000)}
-            mp = {}
-            try:
-                mp = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "MEASURED_PEAKS.json")))
-            except Exception:
-                pass
-            peaks["int8_from_measured_bf16_sustained_x2"] = 2.0 * mp["bf16_tflops_sustained"] if mp else None
-            peaks["int8_from_measured_bf16_burst_x2"] = 2.0 * mp["bf16_tflops"] if mp else None
-            peak = peaks["i8_mma_issue_tops"]
-            line["dtype"] = "f64 results; n^2 term as exact int8 x int8 -> int32 tensor-core products of an error-free %d-plane base-256 split (%d bits), rest f64" % (planes, 8 * planes - 1)
+            kern_s = kern_ms * 1e-3 / args.steps                              # scan-kernel seconds per step
+            achieved = pairs_rank * alg / kern_s / 1e12
+            issued = pairs_rank * iss / kern_s / 1e12
+            peak = i8_peak_burst
+            line["dtype"] = ("f64 results; n^2 term as exact int8 x int8 -> int32 tensor-core products of an error-free "
+                             "%d-plane base-256 split (%d bits), weak pairs re-checked in FP64, rest f64"
+                             % (planes, 8 * planes - 1))
             line["roofline"] = {
                 "bound": "tensor", "achieved": achieved, "unit": "TOP/s", "peak": peak, "frac": achieved / peak,
-                "traffic": I8_TRAFFIC_BYTES, "kernel": {2: "i8_scan_pair_kernel (tcgen05.mma cta_group::2 kind::i8, 256x256x32 per CTA pair)", 3: "i8_scan_pair_kernel (tcgen05.mma cta_group::2 kind::i8, 256xNx32 per CTA pair, N = the plane rows that can be non-zero)"}[i8.wide],
-                "kernel_ms_per_launch": kern_ms, "kernel_launches_per_step": launches_per_step,
-                "kernel_share_of_step": kern_ms * launches_per_step / ms_local,
+                "frac_of_sustained_peak": achieved / i8_peak_load,
+                "traffic": I8_TRAFFIC_BYTES,
+                "kernel": "i8_scan_pair_kernel (tcgen05.mma cta_group::2 kind::i8, 256xNx32 per CTA pair, N = the plane "
+                          "rows that can be non-zero)" if i8.wide == 3 else
+                          "i8_scan_pair_kernel (tcgen05.mma cta_group::2 kind::i8, 256x256x32 per CTA pair)",
+                "kernel_ms_per_launch": kern_ms / max(kern_n, 1), "kernel_launches_per_step": launches_per_step,
+                "kernel_share_of_step": kern_ms / args.steps / ms_local,
                 "ops_per_pair_algorithmic": alg, "ops_per_pair_issued": iss, "issued_tops": issued,
-                "frac_issued": issued / peak,
+                "frac_issued": issued / peak, "frac_issued_of_sustained_peak": issued / i8_peak_load,
+                "pairs_rechecked_in_fp64_per_step": rechecked / float(args.steps),
                 "fp64_equivalent_tflops": pairs_rank * f_exact(n) / (ms * 1e-3) / 1e12,
-                "peak_source": "measured live on rank 0: issue rate of back-to-back tcgen05.mma kind::i8 128x256x32 on "
-                               "resident tiles, all SMs (gmat_b200_i8_peak); MEASURED_PEAKS.json has no int8 figure, "
-                               "2 x its dense bf16 numbers are listed beside it", **peaks,
+                "peak_source": "ONE denominator for every tensor-roofline fraction of this line: the issue rate of "
+                               "back-to-back tcgen05.mma kind::i8 128x256x32 on resident tiles, all SMs "
+                               "(probe/libgmat_b200_probe.so), measured on rank 0 at the start of the run on the cold "
+                               "part; i8_mma_issue_tops_sustained = the same microbenchmark for 1.5 s right after the "
+                               "timed steps (the power-capped rate, what *_of_sustained_peak divides by); "
+                               "MEASURED_PEAKS.json has no int8 figure, 2 x its dense bf16 numbers are listed beside",
+                **i8_peaks,
                 "note": "achieved = planes x n(n+1) int8 ops per pair (lower triangle of the symmetric quadratic form, "
-                        "once per digit plane) / the kernel's own launch time; issued adds the tiling's padding and "
-                        "the zero half of the diagonal 256x256 blocks"}
+                        "once per digit plane) / the scan kernel's own launch time (the operand kernels of the next "
+                        "batch run beside it on spare SM resources); issued adds the tiling's padding and the zero "
+                        "half of the diagonal 256x256 blocks"}
         else:
             achieved = (pairs_rank * f_exact(n)) / (ms * 1e-3) / 1e12          # per GPU, algorithmic flops
             from gmat_b200._ffi import ffi
@@ -410,50 +456,275 @@ def run_gpu(args):
             lib.gmat_b200_exact_config(cfg, cfg + 1, cfg + 2)
             bm, bn = int(cfg[0]), int(cfg[1])
             issued = pairs_rank * exact_issued_flop_per_pair(n, bm) / (ms * 1e-3) / 1e12
-            line["roofline"] = {"bound": "tensor", "achieved": achieved, "unit": "TFLOP/s", "peak": None, "frac": None,
-                                "traffic": EXACT_TRAFFIC_BYTES, "kernel": "epi_exact_rb_kernel<%d,..,scan>" % bn,
-                                "flops_per_pair_algorithmic": f_exact(n), "issued_tflops": issued,
-                                "note": "achieved = pairs/s x (2n^2+5n), the reference formulation's flop; the kernel exploits the "
-                                        "symmetry of Z'PZ and issues ~51.5 % of them, so frac > 1 is expected: read "
-                                        "frac_issued (DMMA flop actually issued / measured DMMA peak) as pipe utilisation"}
-            peaks = measure_fp64_peaks(engine, torch)
+            peaks = measure_fp64_peaks(torch)
             peak = max(peaks["dmma_tflops"], peaks["cublas_dgemm_tflops"])
-            line["roofline"].update({"peak": peak, "frac": achieved / peak, "frac_issued": issued / peak,
-                                     "peak_source": "measured live on rank 0: max(DMMA issue-rate microbenchmark, cuBLAS "
-                                                    "DGEMM 4096^3); FP64 is absent from MEASURED_PEAKS.json; achieved "
-                                                    "and issued are per GPU", **peaks})
-        if world == 1:
-            if not args.no_extra:
-                e2e_f64 = None
-                if i8 is not None:
-                    # the same drop-in call on the FP64 DMMA engine (one timed call after one warm call)
-                    os.environ["GMAT_B200_EXACT_ENGINE"] = "f64"
-                    try:
-                        for it in range(2):
-                            torch.cuda.synchronize()
-                            t0 = time.perf_counter()
-                            remma_epiAA(pheno, prefix, gmat_lst, var_com, snp_lst_0=e2e_lst, p_cut=P_CUT,
-                                        out_file=out_file + ".f64")
-                            torch.cuda.synchronize()
-                            e2e_f64 = float(e2e_pairs) / (time.perf_counter() - t0)
-                    finally:
-                        del os.environ["GMAT_B200_EXACT_ENGINE"]
-                line["extra"] = extras(engine, torch, synth, store, model, lut, args, prefix, pymat, e2e_f64)
-            if not args.no_cpu:
-                cpu = CpuExact(prefix, pheno, ag)
-                cp, ct = cpu.sample(4)
-                line["cpu_baseline"] = {"value": cp / ct, "unit": "pairs/s", "cores": os.cpu_count(), "kind": "port",
-                                        "sample": "numpy restatement of remma_epiAA.py:72-77 on 4 evenly spread "
-                                                  "first-SNPs of the same data (%d pairs, %.1f s)" % (cp, ct)}
+            line["roofline"] = {"bound": "tensor", "achieved": achieved, "unit": "TFLOP/s", "peak": peak,
+                                "frac": achieved / peak, "frac_issued": issued / peak, "traffic": None,
+                                "kernel": "epi_exact_rb_kernel<%d,..,scan>" % bn,
+                                "flops_per_pair_algorithmic": f_exact(n), "issued_tflops": issued,
+                                "note": "achieved = pairs/s x (2n^2+5n), the reference formulation's flop; the kernel "
+                                        "exploits the symmetry of Z'PZ and issues ~51.5 % of them, so frac > 1 is "
+                                        "expected: read frac_issued as pipe utilisation", **peaks}
+        if world == 1 and not args.no_extra:
+            e2e_f64 = None
+            if i8 is not None:
+                # the same drop-in call on the FP64 DMMA engine (one timed call after one warm call)
+                os.environ["GMAT_B200_EXACT_ENGINE"] = "f64"
+                try:
+                    for it in range(2):
+                        torch.cuda.synchronize()
+                        t0 = time.perf_counter()
+                        remma_epiAA(pheno, prefix, gmat_lst, var_com, snp_lst_0=e2e_lst, p_cut=P_CUT,
+                                    out_file=out_file + ".f64")
+                        torch.cuda.synchronize()
+                        e2e_f64 = float(e2e_pairs) / (time.perf_counter() - t0)
+                finally:
+                    del os.environ["GMAT_B200_EXACT_ENGINE"]
+            extra.update(extras(engine, torch, synth, store, model, lut, args, prefix, pymat, i8_peak_burst, e2e_f64))
+        if extra:
+            line["extra"] = extra
+        if world == 1 and not args.no_cpu:
+            cp, loop_s, whole_s, _ = reference_sample(prefix, pheno)
+            line["cpu_baseline"] = {"value": cp / loop_s, "unit": "pairs/s", "cores": os.cpu_count(),
+                                    "kind": "reference",
+                                    "sample": REF_SAMPLE + "; %d pairs, loop %.2f s, whole call incl. preamble and file "
+                                                           "read %.2f s" % (cp, loop_s, whole_s)}
         print(json.dumps(line))
     if world > 1:
+        dist.barrier()
         dist.destroy_process_group()
     return 0
 
 
-def extras(engine, torch, synth, store, model, lut, args, prefix, pymat, e2e_f64=None):
+# ----------------------------------------------------------------------------------------------------------------
+# multi-GPU parity inside the run: sharded file == single-GPU file
+# ----------------------------------------------------------------------------------------------------------------
+def multi_gpu_parity(torch, dist, engine, synth, remma_epiAA, rank, world, workdir, barrier):
+    """The same remma_epiAA call (data WITH missing calls: the imputed genotypes must be the same on every rank)
+    sharded over all ranks and on rank 0 alone; the two output files must be equal byte for byte."""
+    from gmat_b200.gmatrix.gmatrix import grm_device
+    from gmat_b200.process_plink.process_plink import load_store
+    from gmat_b200.remma import parallel as par
+    n, m = 600, 3000
+    box = [None]
+    if rank == 0:
+        d = tempfile.mkdtemp(prefix="gmat_parity_")
+        pre = os.path.join(d, "par")
+        synth.write_dataset(pre, n, m, seed=SEED + 7, missing_rate=0.002, n_planted=6)
+        box[0] = pre
+    dist.broadcast_object_list(box, src=0)
+    pre = box[0]
+    barrier()
+    with par.single_rank():
+        np.random.seed(11)
+        st = engine.GenotypeStore(pre)
+        ag = grm_device(load_store(pre, warn=lambda *_: None), engine.ADD)[0].cpu().numpy()
+    vc = var_com_for(pre + ".pheno")
+    first = list(range(0, m - 1, 2))
+    np.random.seed(12)                                       # rank 0's draws decide the imputation of both runs
+    remma_epiAA(pre + ".pheno", pre, [ag, ag * ag], vc, snp_lst_0=first, p_cut=1e-3, out_file=pre + ".sharded")
+    barrier()
+    res = None
+    if rank == 0:
+        np.random.seed(12)
+        with par.single_rank():
+            remma_epiAA(pre + ".pheno", pre, [ag, ag * ag], vc, snp_lst_0=first, p_cut=1e-3, out_file=pre + ".single")
+        a, b = open(pre + ".sharded", "rb").read(), open(pre + ".single", "rb").read()
+        res = {"identical": a == b, "rows": a.count(b"\n") - 1, "bytes": len(a), "missing_calls": int(st.n_missing()),
+               "what": "remma_epiAA on synthetic n=%d x m=%d with %.1f %% missing calls, %d first-SNPs, p_cut=1e-3: "
+                       "output file of the %d-rank sharded run (rank 0 imputes and broadcasts the 2-bit store, hits "
+                       "gathered over NCCL) vs the same call on rank 0 alone" % (n, m, 0.2, len(first), world)}
+    barrier()
+    return res
+
+
+# ----------------------------------------------------------------------------------------------------------------
+# north-star shape through the drop-in API, verified by the oracle inside the run
+# ----------------------------------------------------------------------------------------------------------------
+def northstar(args, torch, dist, engine, _core, synth, rank, world, barrier, reduce, MAX):
+    import importlib
+    from scipy.stats import chi2
+    from gmat_b200.gmatrix.gmatrix import grm_device
+    from gmat_b200.uvlmm.design_matrix import design_matrix_wemai_multi_gmat
+    n, m = args.ns_n, args.ns_m
+    full = args.northstar_full or world >= 8
+    out = {"shape": "synthetic n=%d x m=%d, planted AA/AD/DD pairs, p_cut=%g" % (n, m, NS_P_CUT), "n_gpus": world}
+    t0 = time.perf_counter()
+    box = [None]
+    if rank == 0:
+        d = tempfile.mkdtemp(prefix="gmat_northstar_")
+        pre = os.path.join(d, "ns")
+        ds = synth.write_dataset(pre, n, m, seed=20201013 + 4, n_planted=12, planted_kind="mix", also_records=(3,))
+        box[0] = (pre, ds["planted"])
+        del ds
+    if world > 1:
+        dist.broadcast_object_list(box, src=0)
+    pre, planted = box[0]
+    barrier()
+    out["seconds_dataset"] = time.perf_counter() - t0
+    t0 = time.perf_counter()
+    store = engine.GenotypeStore(pre)
+    ag = grm_device(store, engine.ADD)[0].cpu().numpy()            # sharded over the ranks + all_reduce when N > 1
+    dg = grm_device(store, engine.DOM)[0].cpu().numpy()
+    del store
+    barrier()
+    out["seconds_grms"] = time.perf_counter() - t0
+    s2 = float(np.var([float(line.split()[-1]) for line in open(pre + ".pheno")]))
+    s2r = float(np.var([float(line.split()[-1]) for line in open(pre + ".rep3.pheno")]))
+    models = {
+        "AA": (pre + ".pheno", [ag, ag * ag], [0.35 * s2, 0.10 * s2, 0.55 * s2]),
+        "ADD": (pre + ".pheno", [ag, dg, ag * ag], [0.30 * s2, 0.05 * s2, 0.10 * s2, 0.55 * s2]),
+        "REP": (pre + ".rep3.pheno", [ag, ag * ag, np.eye(n)], [0.28 * s2r, 0.08 * s2r, 0.15 * s2r, 0.44 * s2r]),
+    }
+    oracle_models = {}
+
+    def run_block(name, kind, model_key, first, what):
+        pheno, gmat_lst, var_com = models[model_key]
+        mod = importlib.import_module("gmat_b200.remma.remma_epi" + kind)
+        scan = getattr(mod, "remma_epi" + kind)
+        out_file = pre + "." + name
+        tests = (len(first) * m if kind == "AD" else n_pairs(first, m)) if first is not None else \
+            (m * m if kind == "AD" else m * (m - 1) // 2)
+        barrier()
+        t0 = time.perf_counter()
+        scan(pheno, pre, gmat_lst, var_com, snp_lst_0=first, p_cut=NS_P_CUT, out_file=out_file)
+        barrier()
+        secs = reduce(time.perf_counter() - t0, MAX)
+        phases = dict(_core.PHASES)
+        blk = None
+        if world > 1:                                              # slowest rank per phase
+            keys = sorted(set(phases) | {"gather", "write", "design_matrix", "preamble", "bed_read_h2d", "engine_init",
+                                         "scan"})
+            t = torch.tensor([phases.get(k, 0.0) for k in keys], dtype=torch.float64, device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            phases = dict(zip(keys, t.tolist()))
+        if rank == 0:
+            blk = {"what": what, "kind": kind, "tests": int(tests), "seconds": secs, "pairs_per_s": tests / secs,
+                   "first_snps": len(first) if first is not None else (m if kind == "AD" else m - 1),
+                   "grms": len(gmat_lst), "records": sum(1 for _ in open(pheno)),
+                   "phases_max_over_ranks_s": {k: round(v, 3) for k, v in phases.items()}}
+            if not args.no_verify:
+                blk.update(verify_file(out_file, pre, pheno, kind, model_key, gmat_lst, var_com, first, planted, n, m,
+                                       oracle_models, design_matrix_wemai_multi_gmat, chi2))
+        barrier()
+        return blk
+
+    sub8 = list(range(0, m - 1, 8))
+    blocks = {}
+    blocks["strong_AA"] = run_block(
+        "strongAA", "AA", "AA", sub8,
+        "FIXED problem at every N (strong scaling): remma_epiAA exact, every 8th first SNP, all j>i (1/8 of the "
+        "exhaustive scan)")
+    if full:
+        blocks["AA"] = run_block("AA", "AA", "AA", None, "remma_epiAA exact, EXHAUSTIVE, GRMs [A, A*A]")
+        blocks["AD"] = run_block("AD", "AD", "ADD", None, "remma_epiAD exact, EXHAUSTIVE (every ordered pair incl. "
+                                                          "j=i), GRMs [A, D, A*A] (BASELINE configs[3])")
+        blocks["DD"] = run_block("DD", "DD", "ADD", None, "remma_epiDD exact, EXHAUSTIVE, GRMs [A, D, A*A] "
+                                                          "(BASELINE configs[3])")
+        blocks["AA_15000_records"] = run_block(
+            "REP", "AA", "REP", None, "remma_epiAA exact, EXHAUSTIVE, 3 records per individual (15,000 records), GRMs "
+                                      "[A, A*A, I] (BASELINE configs[4])")
+    else:
+        blocks["AD"] = run_block("AD", "AD", "ADD", list(range(0, m, 16)),
+                                 "remma_epiAD exact, every 16th first SNP x all m second SNPs, GRMs [A, D, A*A] "
+                                 "(BASELINE configs[3]; exhaustive at N=8)")
+        blocks["DD"] = run_block("DD", "DD", "ADD", sub8, "remma_epiDD exact, every 8th first SNP, GRMs [A, D, A*A] "
+                                                          "(BASELINE configs[3]; exhaustive at N=8)")
+        blocks["AA_15000_records"] = run_block(
+            "REP", "AA", "REP", sub8, "remma_epiAA exact, every 8th first SNP, 3 records per individual (15,000 "
+                                      "records), GRMs [A, A*A, I] (BASELINE configs[4]; exhaustive at N=8)")
+    out["exhaustive"] = bool(full)
+    out["blocks"] = blocks
+    if rank == 0:
+        out["verified"] = all(b.get("verified", args.no_verify) for b in blocks.values())
+    return out
+
+
+def verify_file(out_file, pre, pheno, kind, model_key, gmat_lst, var_com, first, planted, n, m, cache,
+                design_matrix, chi2):
+    """Re-derive the output file with the numpy oracle (host preamble on the same files): every reported row (eff, chi
+    within 1e-9, p < p_cut), every planted pair in scope (reported iff its oracle p < p_cut), and 2000 random
+    unreported pairs (oracle p >= p_cut)."""
+    from oracle import oracle
+    t0 = time.perf_counter()
+    rows = [line.split() for line in open(out_file).read().splitlines()[1:]]
+    got = {(int(r[0]), int(r[1])): (float(r[2]), float(r[3]), float(r[4])) for r in rows}
+    if model_key not in cache:
+        y, xmat, zmat = design_matrix(pheno, pre)
+        cache[model_key] = oracle.preamble(y, xmat, zmat, gmat_lst, var_com)
+    pymat, pvpmat = cache[model_key]
+    raw = np.fromfile(pre + ".bed", dtype=np.uint8)[3:].reshape(m, (n + 3) // 4)
+
+    def cols(snps, coding):
+        r = raw[np.asarray(snps)]
+        c = np.stack([(r >> (2 * q)) & 3 for q in range(4)], axis=2).reshape(len(snps), -1)[:, :n]
+        g = np.array([0.0, np.nan, 1.0, 2.0])[c]
+        f = g.sum(axis=1, keepdims=True) / (2 * n)
+        x = g - 2 * f if coding == "A" else np.where(g > 1.5, 0.0, g) - 2 * f * (1 - f)
+        return x.T
+
+    def stats(pairs):
+        pairs = np.asarray(pairs, dtype=np.int64).reshape(-1, 2)
+        if len(pairs) == 0:
+            return np.zeros(0), np.zeros(0), np.zeros(0)
+        su, sv = sorted(set(pairs[:, 0].tolist())), sorted(set(pairs[:, 1].tolist()))
+        U, V = cols(su, kind[0]), cols(sv, kind[1])
+        iu, iv = {s: k for k, s in enumerate(su)}, {s: k for k, s in enumerate(sv)}
+        W = U[:, [iu[a] for a in pairs[:, 0].tolist()]] * V[:, [iv[b] for b in pairs[:, 1].tolist()]]
+        eff = (W.T @ pymat).ravel()
+        var = np.sum(W * (pvpmat @ W), axis=0)
+        chi = eff * eff / var
+        return eff, chi, chi2.sf(chi, 1)
+
+    ok, msgs, max_rel = True, [], 0.0
+    keys = sorted(got)
+    for k0 in range(0, len(keys), 512):
+        part = keys[k0:k0 + 512]
+        eff, chi, p = stats(part)
+        for q, k in enumerate(part):
+            ge, gc, gp = got[k]
+            rel = max(abs(ge - eff[q]) / abs(eff[q]), abs(gc - chi[q]) / abs(chi[q]))
+            max_rel = max(max_rel, rel)
+            if rel > 1e-9 or not (p[q] < NS_P_CUT):
+                ok = False
+                msgs.append("row %s: rel %.2e, oracle p %.3e" % (k, rel, p[q]))
+    in_first = set(first) if first is not None else None
+    scope = []
+    for a, b in planted:
+        cands = [(a, b), (b, a)] if kind == "AD" else [(a, b)]
+        scope += [c for c in cands if in_first is None or c[0] in in_first]
+    _, _, pl_p = stats(scope)
+    planted_sig = 0
+    for pr, pv in zip(scope, pl_p):
+        planted_sig += int(pv < NS_P_CUT)
+        if (tuple(pr) in got) != bool(pv < NS_P_CUT):
+            ok = False
+            msgs.append("planted %s: oracle p %.3e, in file: %s" % (pr, pv, tuple(pr) in got))
+    rng = np.random.Generator(np.random.PCG64(1))
+    firsts = np.asarray(first if first is not None else np.arange(m if kind == "AD" else m - 1))
+    rnd = []
+    while len(rnd) < 2000:
+        a, b = int(firsts[rng.integers(0, len(firsts))]), int(rng.integers(0, m))
+        if kind != "AD" and b <= a:
+            continue
+        if (a, b) not in got:
+            rnd.append((a, b))
+    _, _, rp = stats(rnd)
+    if not np.all(rp >= NS_P_CUT):
+        ok = False
+        msgs.append("unreported random pairs below p_cut: %d" % int(np.sum(rp < NS_P_CUT)))
+    res = {"verified": ok, "rows_in_file": len(got), "max_rel_err_vs_oracle": max_rel,
+           "planted_in_scope": len(scope), "planted_significant_and_reported": planted_sig,
+           "random_unreported_checked": len(rnd), "seconds_verify": time.perf_counter() - t0}
+    if msgs:
+        res["messages"] = msgs[:10]
+    return res
+
+
+def extras(engine, torch, synth, store, model, lut, args, prefix, pymat, i8_peak, e2e_f64=None):
     """Secondary numbers of BASELINE.json's metric, same process, N=1: approximate screen pairs/s on the same
-    data, agmat TFLOP/s on configs[1] (n=10,000 x m=500,000, generated in HBM), decode GB/s."""
+    data, agmat TFLOP/s on configs[1] (n=10,000 x m=500,000, generated in HBM), decode GB/s.  Every int8 fraction
+    divides by the same ``i8_peak`` as the headline's."""
     out = {}
 
     def timed(fn, reps=3):
@@ -469,15 +740,14 @@ def extras(engine, torch, synth, store, model, lut, args, prefix, pymat, e2e_f64
         return best * 1e-3
 
     # the FP64 DMMA engine on a 256-first-SNP batch of the same data: the mechanism north_star names for the
-    # quadratic forms (and what the exact scan runs when genotypes are missing, GMAT_B200_EXACT_ENGINE=f64), with its
-    # own roofline against the measured FP64 peak, and its own end-to-end drop-in call
+    # quadratic forms (GMAT_B200_EXACT_ENGINE=f64), with its own roofline against the measured FP64 peak
     sub = np.asarray(batch_first_snps(N_SNP, 0, 1, 256), dtype=np.int64)
     t = timed(lambda: engine.epi_exact_scan(store, lut, lut, model.py, model.packed, sub, engine.PAIRS_UPPER, 19.5),
               reps=2)
     from gmat_b200._ffi import ffi
     cfg = ffi.new("int[3]")
     engine.lib.gmat_b200_exact_config(cfg, cfg + 1, cfg + 2)
-    peaks = measure_fp64_peaks(engine, torch)
+    peaks = measure_fp64_peaks(torch)
     peak = max(peaks["dmma_tflops"], peaks["cublas_dgemm_tflops"])
     issued = n_pairs(sub, N_SNP) * exact_issued_flop_per_pair(N_ID, int(cfg[0])) / t / 1e12
     out["exact_f64_engine"] = {"pairs_per_s": n_pairs(sub, N_SNP) / t, "seconds": t,
@@ -487,10 +757,10 @@ def extras(engine, torch, synth, store, model, lut, args, prefix, pymat, e2e_f64
                                **peaks}
     if e2e_f64 is not None:
         out["exact_f64_engine"]["e2e_pairs_per_s"] = e2e_f64
-    # approximate screen: full scan of the C3 data (1.9999e8 pairs).  Default engine (no missing call): int8
-    # tensor-core prefilter (2 planes x 2n int8 ops per pair) + FP64 re-test of the survivors (screen_i8.cu); the
-    # FP64 DMMA kernel (F_approx = 2n flop per pair, eff.cu) beside it.  The cut is a real one (p_cut = 1e-5 on a
-    # variance of the size random pairs show), so the survivors, the re-test and the hit records are in the time.
+    # approximate screen: full scan of the C3 data (1.9999e8 pairs).  Default engine: int8 tensor-core prefilter
+    # (2 planes x 2n int8 ops per pair) + FP64 re-test of the survivors (screen_i8.cu); the FP64 DMMA kernel
+    # (F_approx = 2n flop per pair, eff.cu) beside it.  The cut is a real one (p_cut = 1e-5 on a variance of the size
+    # random pairs show), so the survivors, the re-test and the hit records are in the time.
     la = store.lut(engine.ADD, engine.FREQ_CLOOP)
     full = np.arange(N_SNP - 1, dtype=np.int64)
     pairs = N_SNP * (N_SNP - 1) // 2
@@ -506,10 +776,14 @@ def extras(engine, torch, synth, store, model, lut, args, prefix, pymat, e2e_f64
     n_hits = len(box["hits"])
     out["approx_screen"] = {"engine": which, "pairs_per_s": pairs / t, "seconds": t, "pairs": pairs, "hits": n_hits,
                             "eff_cut": cut,
-                            "int8_tops_algorithmic": pairs * 4.0 * N_ID / t / 1e12 if which == "i8" else None,
                             "fp64_equivalent_tflops": pairs * 2.0 * N_ID / t / 1e12,
                             "workload": "remma_epiAA_eff_cpu formulation, full scan n=%d x m=%d, whole call "
                                         "(operand build, prefilter, FP64 re-test, hit records)" % (N_ID, N_SNP)}
+    if which == "i8":
+        tops = pairs * 4.0 * N_ID / t / 1e12
+        out["approx_screen"]["roofline"] = {"bound": "tensor", "unit": "TOP/s", "achieved": tops, "peak": i8_peak,
+                                            "frac": tops / i8_peak,
+                                            "note": "4n int8 ops per pair (two digit planes of Z'Py) / the whole call"}
     t64 = timed(lambda: run_screen(None))
     out["approx_screen"]["f64_engine"] = {"pairs_per_s": pairs / t64, "seconds": t64, "hits": len(box["hits"]),
                                           "same_hit_count": len(box["hits"]) == n_hits,
@@ -535,7 +809,16 @@ def extras(engine, torch, synth, store, model, lut, args, prefix, pymat, e2e_f64
     dec = torch.empty((m3, n3), dtype=torch.float64, device=store.device)
     t = timed(lambda: engine.decode_into(st3, None, dec))
     nbytes = m3 * ((n3 + 3) // 4) + 8.0 * m3 * n3
+    mp = {}
+    try:
+        mp = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    hbm = mp.get("hbm_gbs")
     out["decode"] = {"gb_per_s": nbytes / t / 1e9, "seconds": t, "bytes": nbytes,
+                     "roofline": {"bound": "hbm", "unit": "GB/s", "achieved": nbytes / t / 1e9, "peak": hbm,
+                                  "frac": nbytes / t / 1e9 / hbm if hbm else None,
+                                  "peak_source": "MEASURED_PEAKS.json hbm_gbs (copy bandwidth)"},
                      "workload": "gmat_b200_decode n=%d x m=%d (0.25 B in + 8 B out per genotype)" % (n3, m3)}
     del dec, st3
     if not args.no_grm:
@@ -555,13 +838,11 @@ def extras(engine, torch, synth, store, model, lut, args, prefix, pymat, e2e_f64
                         "seconds": t, "workload": "agmat GRM, synthetic n=%d x m=%d generated in HBM "
                                                   "(BASELINE configs[1])" % (n2, m2)}
         if which == "i8":
-            import probe
-            i8_peak = probe.i8_peak(20000)
             out["agmat"]["roofline"] = {
                 "bound": "tensor", "unit": "TOP/s", "achieved": float(n2) * (n2 + 1) * m2 / t / 1e12,
                 "peak": i8_peak, "frac": float(n2) * (n2 + 1) * m2 / t / 1e12 / i8_peak,
                 "note": "n(n+1)m int8 ops (lower triangle of G G', 2 ops per MAC) / the whole call (2-bit -> int8 "
-                        "transpose, i8_gram_pair_kernel, FP64 corrections); peak = int8 MMA issue rate measured live"}
+                        "transpose, i8_gram_pair_kernel, FP64 corrections); same denominator as the headline"}
             t64 = timed(lambda: engine.grm(st2, engine.ADD, 1.0, 0.001, out=kin, which="f64"), reps=1)
             out["agmat"]["f64_engine"] = {"seconds": t64,
                                           "tflops_algorithmic_n(n+1)m": float(n2) * (n2 + 1) * m2 / t64 / 1e12,
@@ -602,6 +883,12 @@ def main():
     ap.add_argument("--no-extra", action="store_true", help="skip the approx/GRM/decode secondary numbers")
     ap.add_argument("--no-grm", action="store_true")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-northstar", action="store_true", help="skip the n=5000 x m=50000 blocks")
+    ap.add_argument("--northstar-full", action="store_true", help="exhaustive north-star scans at any N (default: N>=8)")
+    ap.add_argument("--no-verify", action="store_true", help="skip the oracle re-derivation of the north-star files")
+    ap.add_argument("--no-parity", action="store_true", help="skip the sharded-vs-single-GPU file comparison (N>=2)")
+    ap.add_argument("--ns-n", type=int, default=NS_N)
+    ap.add_argument("--ns-m", type=int, default=NS_M)
     ap.add_argument("--agmat-e2e", action="store_true", help="also time agmat(bed_file) on files (writes ~4 GB)")
     ap.add_argument("--grm-n", type=int, default=10000)
     ap.add_argument("--grm-m", type=int, default=500000)

@@ -44,12 +44,28 @@ def impute_geno(snp_mat):
 def load_store(bed_file, warn=logging.warning):
     """Device genotype store for the numpy-flavoured paths: if the file has missing calls they are
     imputed exactly like the reference does before any statistic is formed (remma_epiAA.py:56-58),
-    then re-packed to 2 bits on the device."""
+    then re-packed to 2 bits on the device.  One process per GPU: the reference imputes ONCE per call, so rank 0
+    draws the genotypes and broadcasts the re-packed 2-bit store -- every rank then tests against the same matrix
+    (per-rank draws from the unseeded global RNG would give every shard its own genotypes)."""
+    from ..remma import parallel as par
     store = GenotypeStore(bed_file)
     if store.n_missing() > 0:
         warn('Missing genotypes are imputed with random genotypes.')
-        dense = store.decode(None).t().contiguous().cpu().numpy()
-        dense[np.abs(dense - 1.0 / 3) < 0.0001] = np.nan
-        dense = impute_geno(dense)
-        store = GenotypeStore.from_dense(np.ascontiguousarray(dense.T), device=store.device)
+        rank, world = par.rank_world()
+        if rank == 0:
+            dense = store.decode(None).t().contiguous().cpu().numpy()
+            dense[np.abs(dense - 1.0 / 3) < 0.0001] = np.nan
+            dense = impute_geno(dense)
+            store = GenotypeStore.from_dense(np.ascontiguousarray(dense.T), device=store.device)
+        if world > 1:
+            import torch.distributed as dist
+            bed = store.bed if rank == 0 else torch.empty_like(store.bed)
+            if dist.get_backend() == "nccl":
+                dist.broadcast(bed, src=0)
+            else:
+                host = bed.cpu()
+                dist.broadcast(host, src=0)
+                bed = host.to(store.device)
+            if rank != 0:
+                store = GenotypeStore.from_device_payload(bed, store.n)
     return store

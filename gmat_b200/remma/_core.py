@@ -136,13 +136,42 @@ class DeviceModel(object):
         self.packed = engine.pack_pvp(self.pvp)
         return self
 
+    @classmethod
+    def build_shared(cls, y, xmat, zmat, gmat_lst, var_com, device, scipy_inv=True):
+        """One process per GPU: the preamble is the same on every rank, so rank 0 computes it and broadcasts Z'Py and
+        Z'PZ (NCCL over NVLink: 200 MB at n = 5000) instead of every rank uploading the GRMs and inverting V
+        (N = 15000 records in BASELINE configs[4]); the other ranks only re-tile Z'PZ for the FP64 pair kernel.
+        All ranks then hold bit-identical model matrices.  One rank (or a gloo group): plain build."""
+        import torch.distributed as dist
+        rank, world = par.rank_world()
+        if world == 1 or dist.get_backend() != "nccl":
+            return cls.build(y, xmat, zmat, gmat_lst, var_com, device, scipy_inv=scipy_inv)
+        n = zmat.shape[1]
+        if rank == 0:
+            self = cls.build(y, xmat, zmat, gmat_lst, var_com, device, scipy_inv=scipy_inv)
+        else:
+            self = cls.__new__(cls)
+            self.py = torch.empty((n,), dtype=torch.float64, device=device)
+            self.pvp = torch.empty((n, n), dtype=torch.float64, device=device)
+            self.h2d_bytes = 0
+        dist.broadcast(self.py, src=0)
+        dist.broadcast(self.pvp, src=0)
+        if rank != 0:
+            self.packed = engine.pack_pvp(self.pvp)
+        return self
+
+    engine_note = ""
+
     def scanner(self, store, lut_u, lut_v, coding_v):
         """The exact-scan engine for this model and genotype store: ``scan(ilist, pair_space, chi_cut)``.
         GMAT_B200_EXACT_ENGINE = auto (default: the INT8 tensor-core engine) | i8 | f64 (the FP64 DMMA kernel)."""
         which = engine.exact_engine(store)
         if which == "i8":
             eng = engine.I8Exact(store, lut_u, lut_v, coding_v, self.py, self.pvp, packed=self.packed)
+            self.engine_note = ("int8 tensor cores (tcgen05 kind::i8), %d base-256 digit planes = %d bits, weak pairs "
+                                "re-checked by the FP64 pair kernel" % (eng.n_planes, 8 * eng.n_planes - 1))
             return eng.scan
+        self.engine_note = "FP64 DMMA kernel (GMAT_B200_EXACT_ENGINE=f64)"
         return lambda ilist, pair_space, chi_cut: engine.epi_exact_scan(store, lut_u, lut_v, self.py, self.packed,
                                                                         ilist, pair_space, chi_cut)
 
@@ -173,26 +202,52 @@ def _write_rows(out_file, cols):
     res.to_csv(out_file, sep=' ', header=False, index=False, mode='a')
 
 
+PHASES = {}     # wall seconds of the phases of the last exact_scan call on this rank (bench.py prints them)
+
+
+class _Phase(object):
+    """with _Phase('name'): ... -- adds the wall time of the block (device work included) to PHASES[name]."""
+
+    def __init__(self, name):
+        self.name = name
+
+    def __enter__(self):
+        self.t0 = time.perf_counter()
+
+    def __exit__(self, *exc):
+        if torch.cuda.is_available():
+            torch.cuda.synchronize()
+        PHASES[self.name] = PHASES.get(self.name, 0.0) + time.perf_counter() - self.t0
+        return False
+
+
 def exact_scan(kind, y, xmat, zmat, gmat_lst, var_com, bed_file, snp_lst_0=None, p_cut=1.0e-5,
                out_file='epi'):
+    design_s = PHASES.get("design_matrix")
+    PHASES.clear()
+    if design_s is not None:
+        PHASES["design_matrix"] = design_s
     logging.info("Calculate the phenotypic covariance matrix and inversion")
     device = engine.current_device()
-    model = DeviceModel.build(y, xmat, zmat, gmat_lst, var_com, device, scipy_inv=True)
-    logging.info("Read the SNP")
     rank, world = par.rank_world()
+    with _Phase("preamble"):
+        model = DeviceModel.build_shared(y, xmat, zmat, gmat_lst, var_com, device, scipy_inv=True)
+    logging.info("Read the SNP")
     if rank == 0:
         np.savetxt(out_file, ['snp_0 snp_1 eff chi p_val'], fmt='%s')     # header first (remma_epiAA.py:53)
-    store = load_store(bed_file)
+    with _Phase("bed_read_h2d"):
+        store = load_store(bed_file)
     num_snp = store.m
     logging.info('Test')
     if snp_lst_0 is None:
         snp_lst_0 = kind.default_snp_lst_0(num_snp)
     else:
         kind.check_snp_lst_0(snp_lst_0, num_snp)
-    snp_lst_0 = [int(i) for i in snp_lst_0]
-    order = {}
-    for pos, i in enumerate(snp_lst_0):
-        order.setdefault(i, pos)
+    snp_lst_0 = np.fromiter((int(i) for i in snp_lst_0), dtype=np.int64)
+    # position of every first SNP in the caller's list (first occurrence): the reference's row order
+    order = np.full(num_snp, -1, dtype=np.int64)
+    uniq, first_pos = np.unique(snp_lst_0, return_index=True)
+    order[uniq] = first_pos
     lut_u, lut_v = store.lut(kind.coding_u), store.lut(kind.coding_v)
     # p < p_cut  <=>  chi > isf(p_cut); the device keeps a slightly larger set, the host re-applies the
     # reference's own comparison on scipy p-values (remma_epiAA.py:77,81)
@@ -201,30 +256,36 @@ def exact_scan(kind, y, xmat, zmat, gmat_lst, var_com, bed_file, snp_lst_0=None,
     my_list = par.shard_first_snps(snp_lst_0, num_snp, kind.all_pairs, rank, world)
     clock_t0 = time.perf_counter()
     cpu_t0 = time.process_time()
+
     def emit(hits):
         if len(hits) == 0:
             return
-        pos = np.array([order[i] for i in hits['snp_0']], dtype=np.int64)
-        hits = hits[np.lexsort((hits['snp_1'], pos))]          # (i in list order, j ascending)
+        hits = hits[np.lexsort((hits['snp_1'], order[hits['snp_0']]))]     # (i in list order, j ascending)
         p_vec = chi2.sf(hits['chi'], 1)
         keep = p_vec < p_cut                                   # the reference's comparison (remma_epiAA.py:81)
         _write_rows(out_file, {0: hits['snp_0'][keep].astype(np.int64), 1: hits['snp_1'][keep].astype(np.int64),
                                2: hits['eff'][keep], 3: hits['chi'][keep], 4: p_vec[keep]})
 
     mine = []
-    scan = model.scanner(store, lut_u, lut_v, kind.coding_v)
+    with _Phase("engine_init"):
+        scan = model.scanner(store, lut_u, lut_v, kind.coding_v)
+        logging.info("Exact-scan engine: %s", model.engine_note)
     for chunk in _chunks(kind, my_list, num_snp):
-        hits = scan(np.asarray(chunk, dtype=np.int64), pair_space, chi_cut)
+        with _Phase("scan"):
+            hits = scan(np.asarray(chunk, dtype=np.int64), pair_space, chi_cut)
         if world == 1:
-            emit(hits)                                         # appended launch by launch (resume granularity)
+            with _Phase("write"):
+                emit(hits)                                     # appended launch by launch (resume granularity)
         else:
             mine.append(hits)
     if world > 1:
         # the only collective of the scan: variable-length gather of hit records to rank 0
-        local = np.concatenate(mine) if mine else np.zeros((0,), dtype=engine.HIT_DTYPE)
-        hits = par.gather_hits(local, store.device)
+        with _Phase("gather"):
+            local = np.concatenate(mine) if mine else np.zeros((0,), dtype=engine.HIT_DTYPE)
+            hits = par.gather_hits(local, store.device)
         if rank == 0:
-            emit(hits)
+            with _Phase("write"):
+                emit(hits)
     torch.cuda.synchronize()
     clock_t1 = time.perf_counter()
     cpu_t1 = time.process_time()

@@ -13,7 +13,10 @@ def build(kind, ns):
         return _core.exact_scan(kind, y, xmat, zmat, gmat_lst, var_com, bed_file, snp_lst_0, p_cut, out_file)
 
     def scan(pheno_file, bed_file, gmat_lst, var_com, snp_lst_0=None, p_cut=1.0e-5, out_file='epi' + K):
+        import time
+        t0 = time.perf_counter()
         y, xmat, zmat = design_matrix_wemai_multi_gmat(pheno_file, bed_file)
+        _core.PHASES["design_matrix"] = time.perf_counter() - t0
         return _scan(y, xmat, zmat, gmat_lst, var_com, bed_file, snp_lst_0=snp_lst_0, p_cut=p_cut, out_file=out_file)
 
     def _scan_parallel(y, xmat, zmat, gmat_lst, var_com, bed_file, parallel, p_cut=1.0e-5 if K == 'AA' else 1.0e-4,

@@ -4,7 +4,7 @@ Two layers, as in SURVEY section 8e:
  * ``parallel_lists``: the reference's manual ``parallel=[P, k]`` partition, arithmetic reproduced verbatim
    (remma_epiAA.py:125-137; AD variant remma_epiAD.py:130-139) -- file-level drop-in (``out_file.k``).
  * ``shard_first_snps`` / ``gather_hits``: one process per GPU (torch.distributed).  First-SNP blocks are dealt
-   round-robin in a boustrophedon order so the triangular work is balanced; the scan itself has no
+   to the least-loaded rank by pair count so the triangular work is balanced; the scan itself has no
    collective; hit records (32 bytes each) are gathered to rank 0 once at the end (NCCL on GPUs, gloo in
    CPU tests).
 """
@@ -15,8 +15,24 @@ import torch.distributed as dist
 HIT_BYTES = 32
 
 
+_SINGLE = [False]
+
+
+class single_rank(object):
+    """Context manager: inside it the front-ends behave as a one-process job even though a process group exists
+    (bench.py uses it on rank 0 to compare a sharded scan with the same scan on one GPU)."""
+
+    def __enter__(self):
+        _SINGLE[0] = True
+        return self
+
+    def __exit__(self, *exc):
+        _SINGLE[0] = False
+        return False
+
+
 def rank_world():
-    if dist.is_available() and dist.is_initialized():
+    if not _SINGLE[0] and dist.is_available() and dist.is_initialized():
         return dist.get_rank(), dist.get_world_size()
     return 0, 1
 
@@ -34,24 +50,26 @@ def parallel_lists(num_snp, parallel, all_pairs=False):
     return snp_list_0, [snp_pos_0, snp_pos_1, snp_pos_2, snp_pos_3]
 
 
-SHARD_BLOCK = 64        # first-SNPs per dealt block (multiple of the kernel's 8-SNP I-block)
+SHARD_BLOCK = 32        # first-SNPs per dealt block
 
 
 def shard_first_snps(snp_lst_0, num_snp, all_pairs, rank, world):
-    """This rank's share of the first-SNP list.  Blocks of SHARD_BLOCK consecutive list entries are dealt
-    0,1,..,R-1,R-1,..,1,0,0,1,.. so that for the triangular (j > i) workload every rank gets the same
-    number of pairs to within one block row."""
-    snp_lst_0 = list(snp_lst_0)
+    """This rank's share of the first-SNP list.  Blocks of SHARD_BLOCK consecutive list entries are dealt, in list
+    order, to the rank that has the fewest PAIRS so far (a first SNP i has num_snp - 1 - i of them in the triangular
+    scans, num_snp in the AD scan; ties go to the lowest rank), so the ranks' pair counts differ by less than one
+    block whatever the list looks like.  Every rank computes the same deal; list order is kept within a rank."""
+    snp_lst_0 = np.asarray(list(snp_lst_0), dtype=np.int64)
     if world == 1:
-        return snp_lst_0
-    out = []
-    nblk = (len(snp_lst_0) + SHARD_BLOCK - 1) // SHARD_BLOCK
-    for b in range(nblk):
-        r = b % (2 * world)
-        owner = r if r < world else 2 * world - 1 - r
+        return snp_lst_0.tolist()
+    weight = np.full(len(snp_lst_0), num_snp, dtype=np.int64) if all_pairs else np.maximum(num_snp - 1 - snp_lst_0, 0)
+    load = [0] * world
+    mine = []
+    for b0 in range(0, len(snp_lst_0), SHARD_BLOCK):
+        owner = min(range(world), key=lambda r: (load[r], r))
+        load[owner] += int(weight[b0:b0 + SHARD_BLOCK].sum())
         if owner == rank:
-            out.extend(snp_lst_0[b * SHARD_BLOCK:(b + 1) * SHARD_BLOCK])
-    return out
+            mine.append(snp_lst_0[b0:b0 + SHARD_BLOCK])
+    return np.concatenate(mine).tolist() if mine else []
 
 
 def gather_hits(local, device):

@@ -9,7 +9,8 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 
 def main():
     import torch
-    from gmat_b200 import engine, synth
+    from gmat_b200 import engine
+    import synth
     n, m = int(sys.argv[1]), int(sys.argv[2])
     dev = engine.current_device()
     store = engine.GenotypeStore.from_device_payload(synth.device_payload(n, m, 13, dev, engine.row_stride(n)), n)

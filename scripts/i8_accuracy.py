@@ -26,7 +26,8 @@ def main():
     ap.add_argument("--min-maf", type=float, default=0.002, help="lowest MAF of the synthetic data")
     args = ap.parse_args()
     import torch
-    from gmat_b200 import engine, synth
+    from gmat_b200 import engine
+    import synth
     from gmat_b200.gmatrix.gmatrix import grm_device
     dev = engine.current_device()
     n, m = args.n, args.m

@@ -13,7 +13,8 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 def main():
     import torch
     import torch.distributed as dist
-    from gmat_b200 import engine, synth
+    from gmat_b200 import engine
+    import synth
     from gmat_b200.gmatrix.gmatrix import grm_device
     rank, local = int(os.environ["RANK"]), int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(local)

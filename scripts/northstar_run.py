@@ -47,7 +47,8 @@ def main():
     import torch
     import torch.distributed as dist
     from scipy.stats import chi2
-    from gmat_b200 import engine, synth
+    from gmat_b200 import engine
+    import synth
     from gmat_b200.gmatrix.gmatrix import grm_device
     from gmat_b200 import remma
     import importlib

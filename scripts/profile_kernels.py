@@ -30,7 +30,8 @@ def main():
     args = ap.parse_args()
     only = set(args.only.split(","))
     import torch
-    from gmat_b200 import engine, synth
+    from gmat_b200 import engine
+    import synth
     dev = engine.current_device()
     out = {}
 

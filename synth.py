@@ -41,8 +41,10 @@ def random_genotypes(n, m, seed, missing_rate=0.0):
 
 
 def write_dataset(prefix, n, m, seed=20201013, missing_rate=0.0, records_per_id=1, n_planted=10,
-                  planted_kind="AA", geno=None):
-    """Write prefix.bed/.bim/.fam and prefix.pheno; returns dict(geno=[m][n] int8, planted=[(i,j)], pheno=path)."""
+                  planted_kind="AA", geno=None, also_records=()):
+    """Write prefix.bed/.bim/.fam and prefix.pheno; returns dict(geno=[m][n] int8, planted=[(i,j)], pheno=path).
+    planted_kind "mix" cycles AA, AD, DD over the planted pairs; also_records=(R, ...) writes prefix.rep<R>.pheno
+    with R records per individual (same genetic values plus a permanent-environment effect) beside prefix.pheno."""
     rng = np.random.Generator(np.random.PCG64(seed + 1))
     g = random_genotypes(n, m, seed, missing_rate) if geno is None else np.asarray(geno, dtype=np.int8)
     os.makedirs(os.path.dirname(os.path.abspath(prefix)), exist_ok=True)
@@ -63,10 +65,11 @@ def write_dataset(prefix, n, m, seed=20201013, missing_rate=0.0, records_per_id=
     sel = rng.choice(m, size=min(100, m), replace=False)
     gv = (xa[sel] * rng.normal(0, 0.05, size=(len(sel), 1))).sum(axis=0)
     planted = []
-    for _ in range(n_planted if m >= 4 else 0):
+    for q in range(n_planted if m >= 4 else 0):
         i, j = sorted(rng.choice(m, size=2, replace=False).tolist())
-        u = xa[i] if planted_kind in ("AA", "AD") else xd[i]
-        v = xa[j] if planted_kind == "AA" else xd[j]
+        kind_q = ("AA", "AD", "DD")[q % 3] if planted_kind == "mix" else planted_kind
+        u = xa[i] if kind_q in ("AA", "AD") else xd[i]
+        v = xa[j] if kind_q == "AA" else xd[j]
         w = u * v
         gv = gv + w * (rng.uniform(0.25, 0.4) / max(w.std(), 1e-9)) * rng.choice([-1.0, 1.0])
         planted.append((int(i), int(j)))
@@ -77,7 +80,16 @@ def write_dataset(prefix, n, m, seed=20201013, missing_rate=0.0, records_per_id=
             for _ in range(records_per_id):
                 yv = 1.0 + 0.3 * cov[k] + gv[k] + perm[k] + rng.normal()
                 f.write("fam%d id%d 1 %d %.6f\n" % (k, k, cov[k], yv))
-    return {"geno": g, "planted": planted, "pheno": prefix + ".pheno"}
+    out = {"geno": g, "planted": planted, "pheno": prefix + ".pheno"}
+    for reps in also_records:
+        pe = rng.normal(0, np.sqrt(0.3), size=n)
+        path = prefix + ".rep%d.pheno" % reps
+        with open(path, "w") as f:
+            for k in range(n):
+                for _ in range(reps):
+                    f.write("fam%d id%d 1 %d %.6f\n" % (k, k, cov[k], 1.0 + 0.3 * cov[k] + gv[k] + pe[k] + rng.normal()))
+        out["pheno_rep%d" % reps] = path
+    return out
 
 
 def device_payload(n, m, seed, device, row_bytes, chunk=8192):

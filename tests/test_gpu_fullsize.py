@@ -68,7 +68,7 @@ def _oracle_pairs(payload_host, n, pairs, cu, cv, py, pvp):
                                       (5000, 50000, "AD")])
 def test_exact_scan_full_shape_sampled_against_oracle(eng, n, m, kind):
     import torch
-    from gmat_b200 import synth
+    import synth
     dev = eng.current_device()
     payload = synth.device_payload(n, m, 20201013 + n, dev, eng.row_stride(n))
     store = eng.GenotypeStore.from_device_payload(payload, n)
@@ -119,7 +119,7 @@ def test_i8_scan_full_shape_sampled_against_oracle(eng, n, m, kind):
     """The int8 tensor-core engine at BASELINE's shapes: same hit set as the DMMA kernel on the same first SNPs, and
     a sample of its rows (plus unreported pairs) recomputed by the numpy oracle to 1e-9."""
     import torch
-    from gmat_b200 import synth
+    import synth
     dev = eng.current_device()
     payload = synth.device_payload(n, m, 20201013 + n, dev, eng.row_stride(n))
     store = eng.GenotypeStore.from_device_payload(payload, n)
@@ -152,7 +152,7 @@ def test_i8_scan_full_shape_sampled_against_oracle(eng, n, m, kind):
 
 def test_screen_full_c3_shape_subset_equals_oracle(eng):
     import torch
-    from gmat_b200 import synth
+    import synth
     n, m = 2000, 20000
     dev = eng.current_device()
     payload = synth.device_payload(n, m, 77, dev, eng.row_stride(n))
@@ -188,7 +188,7 @@ def test_screen_full_c3_shape_subset_equals_oracle(eng):
 
 def test_grm_c3_shape_sampled_entries(eng):
     import torch
-    from gmat_b200 import synth
+    import synth
     from gmat_b200.gmatrix.gmatrix import grm_device
     n, m = 2000, 20000
     dev = eng.current_device()

@@ -20,7 +20,7 @@ def eng():
 
 
 def _dataset(tmp_path, n, m, seed, missing=0.0, geno=None):
-    from gmat_b200 import synth
+    import synth
     prefix = str(tmp_path / ("syn_%d_%d" % (n, m)))
     return prefix, synth.write_dataset(prefix, n, m, seed=seed, missing_rate=missing, geno=geno)
 
@@ -167,7 +167,7 @@ def test_i8_monomorphic_snps_and_small_batches(eng, tmp_path, monkeypatch):
     reference (0/0), never a hit; a first SNP of that kind too.  Also: plane buffer budget of one first SNP per
     launch gives the same result as one launch."""
     import torch
-    from gmat_b200 import synth
+    import synth
     n, m = 140, 60
     g = synth.random_genotypes(n, m, 77, 0.0)
     g[5, :] = 0
@@ -222,7 +222,7 @@ def test_i8_missing_calls_are_nan_like_the_reference(eng, tmp_path, kind):
     involves such a SNP is NaN (never reported); all other pairs are untouched.  Same NaN pattern and same numbers
     as the DMMA kernel and the oracle."""
     import torch
-    from gmat_b200 import synth
+    import synth
     n, m = 150, 70
     g = synth.random_genotypes(n, m, 9, 0.0)
     for snp, ids in ((3, [0, 7]), (20, [149]), (41, [5, 6, 77]), (69, [10])):
@@ -308,7 +308,7 @@ def test_i8_weak_pairs_are_rechecked_in_fp64(eng, tmp_path, planes):
     number of planes, and every pair is still reported exactly once.  Rare first / second SNPs (3 carriers) make
     var tiny against max|u|^2 max|A|."""
     import torch
-    from gmat_b200 import synth
+    import synth
     n, m = 400, 120
     g = synth.random_genotypes(n, m, 5, 0.0)
     for snp in (2, 9, 50, 51, 100):                                     # singletons / rare variants

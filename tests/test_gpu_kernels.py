@@ -22,7 +22,7 @@ def eng():
 
 
 def _dataset(tmp_path, n, m, seed, missing=0.0):
-    from gmat_b200 import synth
+    import synth
     prefix = str(tmp_path / ("syn_%d_%d" % (n, m)))
     return prefix, synth.write_dataset(prefix, n, m, seed=seed, missing_rate=missing)
 
@@ -312,7 +312,7 @@ def test_grm_i8_wave_schedule_and_chunked_corrections(eng, monkeypatch, n, m):
     FP64 corrections over more than one 4096-SNP chunk (m=9000), against numpy on genotypes generated in HBM, and
     against the FP64 DMMA kernel; bit-identical run to run."""
     import torch
-    from gmat_b200 import synth
+    import synth
     from gmat_b200.gmatrix.gmatrix import grm_device
     payload = synth.device_payload(n, m, 4242 + n, "cuda", eng.row_stride(n))
     store = eng.GenotypeStore.from_device_payload(payload, n)

@@ -41,7 +41,7 @@ def _mid_gap_cut(abs_eff, quantile):
 @pytest.mark.parametrize("n,m", [(131, 77), (300, 600), (520, 300), (64, 1000), (1100, 260)])
 def test_i8_screen_equals_f64_engine_and_oracle(eng, tmp_path, kind, n, m):
     import torch
-    from gmat_b200 import synth
+    import synth
     prefix = str(tmp_path / "scr")
     synth.write_dataset(prefix, n, m, seed=3 * n + m)
     store = eng.GenotypeStore(prefix)
@@ -76,7 +76,7 @@ def test_i8_screen_equals_f64_engine_and_oracle(eng, tmp_path, kind, n, m):
 
 def test_i8_screen_maf_table_small_cuts_and_forced_engines(eng, tmp_path, monkeypatch):
     import torch
-    from gmat_b200 import synth
+    import synth
     n, m = 260, 700
     prefix = str(tmp_path / "maf")
     ds = synth.write_dataset(prefix, n, m, seed=5)
