@@ -344,13 +344,12 @@ i8_scan_pair_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_cons
 // ------------------------------------------------------------------------------------------ operand builders
 // integer code of the second SNP: additive dosage {0,miss->0,1,2}; dominance indicator {0,miss->0,1,0}
 __global__ void i8_dosage_kernel(const unsigned char *__restrict__ bed, int n, long long m, long long row_bytes,
-                                 int coding, signed char *__restrict__ g8, unsigned char *__restrict__ g2, int ld) {
+                                 unsigned tab, signed char *__restrict__ g8, unsigned char *__restrict__ g2, int ld) {
     const long long groups = ld / 16;
     const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= m * groups) return;
     const long long snp = t / groups;
     const int k0 = (int)(t % groups) * 16;
-    const unsigned tab = coding == GMAT_B200_CODING_DOM ? 0x00010000u : 0x02010000u;   // byte[code]
     unsigned w = 0;
     if (k0 / 4 + 3 < row_bytes) w = *reinterpret_cast<const unsigned *>(bed + snp * row_bytes + k0 / 4);
     unsigned out[4], packed = 0;
@@ -630,6 +629,14 @@ i8_split_kernel(const double *__restrict__ A, int n, const double *__restrict__ 
     }
 }
 
+int launch_i8_dosage(const unsigned char *bed_dev, int n, long long m, long long row_bytes, unsigned tab,
+                     signed char *g8_dev, unsigned char *g2_dev, int ld, cudaStream_t st) {
+    const long long work = m * (ld / 16);
+    i8_dosage_kernel<<<(unsigned)((work + 255) / 256), 256, 0, st>>>(bed_dev, n, m, row_bytes, tab, g8_dev, g2_dev, ld);
+    GB_LAUNCH_CHECK();
+    return GMAT_B200_OK;
+}
+
 }  // namespace gb
 
 using namespace gb;
@@ -641,11 +648,9 @@ extern "C" int gmat_b200_i8_dosage(const unsigned char *bed_dev, long long n, lo
     GB_CHECK_ARG(bed_dev && g8_dev && n > 0 && m > 0, "null buffer or empty shape");
     GB_CHECK_ARG(ld >= n && ld % 16 == 0 && row_bytes % 4 == 0, "ld must be a multiple of 16 not below n");
     GB_CHECK_ARG(coding == GMAT_B200_CODING_ADD || coding == GMAT_B200_CODING_DOM, "coding");
-    const long long work = m * (ld / 16);
-    i8_dosage_kernel<<<(unsigned)((work + 255) / 256), 256, 0, (cudaStream_t)stream>>>(bed_dev, (int)n, m, row_bytes,
-                                                                                      coding, g8_dev, g2_dev, (int)ld);
-    GB_LAUNCH_CHECK();
-    return GMAT_B200_OK;
+    // byte[code]: additive dosage {0, miss -> 0, 1, 2}; dominance indicator {0, miss -> 0, 1, 0}
+    return launch_i8_dosage(bed_dev, (int)n, m, row_bytes, coding == GMAT_B200_CODING_DOM ? 0x00010000u : 0x02010000u,
+                            g8_dev, g2_dev, (int)ld, (cudaStream_t)stream);
 }
 
 extern "C" int gmat_b200_i8_offs(const int *counts_dev, const double *lutV_dev, long long m, int coding,

@@ -18,22 +18,45 @@
 // 2 S n int8 ops per pair at ~3 POP/s against 2 n FP64 flop per pair at 35 TFLOP/s.
 //
 // Tiles: M = 256 second SNPs (two CTAs x 128 TMEM lanes) x N = 128 first SNPs x K = all ids in slabs of 128; the S
-// plane accumulators of a tile sit side by side in TMEM (S x 128 columns), double-buffered (2 x 256 columns).
+// plane accumulators of a tile sit side by side in TMEM (S x 128 columns), double-buffered when they fit twice.
+//
+// Missing calls.  The reference C screen does not impute: code 01 is the value 1/3 (_remma_epi_eff_cpu.c:42), so
+// a in {0, 1/3, 1, 2} (dominance: {0, 1/3, 1, 0}).  Both operands then carry 3a in {0, 1, 3, 6} -- still small
+// integers -- and Q = Q'/9.  (3 a_ik)(d_sk) must stay an int8, so py is cut into S = 3 signed base-32 digits
+// (|d| <= 16, 15 bits) instead of 2 base-128 digits (14 bits): 1.5 x the MMAs of the clean case, same margin formula
+// (2 n scale B^-S), same FP64 re-test.  Real PLINK files almost always have missing calls; before this the screen
+// dropped to the 14-42 x slower FP64 DMMA kernel for them.
+//
+// No host synchronisation: the scale of py, the margin, the FP32 cuts and the "is the int8 path worth it" decision
+// are formed ON THE DEVICE (sc_setup_kernel) and read by the kernels from a small scalar block; stage 2 is a
+// grid-stride kernel over the device-side candidate count.  The caller reads one status word with the hit count.
 #include "tc5.cuh"
 #include <cstdlib>
 #include <vector>
 
 namespace gb {
 
-constexpr int SC_S = 2;                                           // digit planes of py
+constexpr int SC_SMAX = 3;                                        // digit planes of py: 2 (base 128) or 3 (base 32)
 constexpr int SC_TI = 128;                                        // first SNPs per tile (UMMA N)
-constexpr int SC_NS = 6;                                          // smem ring stages
+constexpr int SC_NS_MAX = 6;                                      // smem ring stages (6 for S = 2, 5 for S = 3)
 constexpr int SC_THREADS = 192;                                   // producer, issuer, 4 epilogue warps
 constexpr int SC_B_BYTES = (SC_TI / 2) * I8_SLAB;                 // 8 KB: this CTA's half of one plane tile
-constexpr int SC_STAGE_BYTES = I8_A_BYTES + SC_S * SC_B_BYTES;    // 32 KB per CTA
+template <int S> struct ScreenCfg {
+    static constexpr int NS = S == 2 ? 6 : 5;
+    static constexpr int STAGE_BYTES = I8_A_BYTES + S * SC_B_BYTES;   // 32 / 40 KB per CTA
+    static constexpr int NBUF = 2 * S * SC_TI <= 512 ? 2 : 1;         // accumulator buffers that fit the 512 TMEM columns
+};
+
+struct ScreenScalars {                                            // written by sc_setup_kernel, read by every kernel
+    float cut;                                                    // eff_cut - margin, rounded down
+    float qscale;                                                 // scale * B^-S (/ 9 with tripled codes)
+    float base;                                                   // digit base B
+    int fallback;                                                 // 1: margin not small against the cut -> nothing runs
+    double margin;
+};
 
 struct ScreenBars {
-    uint64_t full[SC_NS], empty[SC_NS], tfull[2], tempty[2];
+    uint64_t full[SC_NS_MAX], empty[SC_NS_MAX], tfull[2], tempty[2];
     uint32_t tmem_base;
     int col_snp[2][SC_TI];                                        // per accumulator buffer: first SNP of a column (-1: none)
     float col_t[2][SC_TI], col_o[2][SC_TI];
@@ -51,8 +74,7 @@ struct ScreenParams {
     const float *oV, *cV;                                         // [m]    o_j,  t_j - o_j P
     const int *binI, *binJ;                                       // [m] each or NULL
     const float *cut_table;                                       // 111 floats (cut - margin, rounded down) or NULL
-    float cut;                                                    // eff_cut - margin, rounded down
-    float qscale;                                                 // scale * 128^-S
+    const ScreenScalars *scal;
     int2 *cand; long long cand_cap; unsigned long long *cand_count;
 };
 
@@ -65,9 +87,12 @@ __device__ __forceinline__ int sc_find(const int *prefix, int n, int item) {
     return lo;
 }
 
+template <int S>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(SC_THREADS, 1)
 i8_screen_pair_kernel(const __grid_constant__ CUtensorMap map_v, const __grid_constant__ CUtensorMap map_p,
                       const ScreenParams p) {
+    constexpr int SC_S = S, SC_NS = ScreenCfg<S>::NS, SC_STAGE_BYTES = ScreenCfg<S>::STAGE_BYTES;
+    constexpr int NBUF = ScreenCfg<S>::NBUF;
     extern __shared__ unsigned char smem_raw[];
     unsigned char *smem = reinterpret_cast<unsigned char *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                                            ~static_cast<uintptr_t>(1023));
@@ -76,7 +101,7 @@ i8_screen_pair_kernel(const __grid_constant__ CUtensorMap map_v, const __grid_co
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int rank = (int)cluster_ctarank();
     const int cluster_id = blockIdx.x >> 1, n_clusters = gridDim.x >> 1;
-    const int total_items = p.item_prefix[p.n_ib];
+    const int total_items = p.scal->fallback ? 0 : p.item_prefix[p.n_ib];
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < SC_NS; ++s) { mbar_init(&bars->full[s], 1); mbar_init(&bars->empty[s], 1); }
@@ -147,17 +172,19 @@ i8_screen_pair_kernel(const __grid_constant__ CUtensorMap map_v, const __grid_co
                     }
                     if (++stage == SC_NS) { stage = 0; phase ^= 1u; }
                 }
-                if (++abuf == 2) { abuf = 0; aphase ^= 1u; }
+                if (++abuf == NBUF) { abuf = 0; aphase ^= 1u; }
             }
         }
     } else {
         // ================================ epilogue (both CTAs): TMEM lane = second SNP =============
         const int q = warp & 3;
         const int e = (warp - 2) * 32 + lane;                     // the column whose constants this thread stages
+        const float qscale = p.scal->qscale, cut0 = p.scal->cut, base = p.scal->base;
         int abuf = 0; unsigned aphase = 0;
         for (int item = cluster_id; item < total_items; item += n_clusters) {
             const int ib = sc_find(p.item_prefix, p.n_ib, item);
             const int jb = p.jb0[ib] + (item - p.item_prefix[ib]);
+            if (NBUF == 1) named_bar_sync(2, 128);                // single buffer: nobody still reads the last item's constants
             {
                 const int ii = ib * SC_TI + e;
                 const bool has = ii < p.n_i;
@@ -177,18 +204,20 @@ i8_screen_pair_kernel(const __grid_constant__ CUtensorMap map_v, const __grid_co
             const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(abuf * SC_S * SC_TI);
 #pragma unroll 1
             for (int ch = 0; ch < SC_TI / 32; ++ch) {
-                int v0[32], v1[32];
-                tmem_ld32(taddr + ch * 32, v0);
-                tmem_ld32(taddr + SC_TI + ch * 32, v1);
+                int v[SC_S][32];
+#pragma unroll
+                for (int sp = 0; sp < SC_S; ++sp) tmem_ld32(taddr + sp * SC_TI + ch * 32, v[sp]);
                 tmem_ld_wait();
                 unsigned mask = 0;
 #pragma unroll
                 for (int c = 0; c < 32; ++c) {
                     const int col = ch * 32 + c;
-                    const float t32 = fmaf((float)v0[c], 128.f, (float)v1[c]);
+                    float t32 = (float)v[0][c];                   // Horner over the planes, most significant first
+#pragma unroll
+                    for (int sp = 1; sp < SC_S; ++sp) t32 = fmaf(t32, base, (float)v[sp][c]);
                     const float r = fmaf(-oj, bars->col_t[abuf][col], -bars->col_o[abuf][col] * cj);
-                    const float eff = fmaf(t32, p.qscale, r);
-                    const float cut = p.cut_table != nullptr ? bars->table[bars->col_bin[abuf][col] + bj] : p.cut;
+                    const float eff = fmaf(t32, qscale, r);
+                    const float cut = p.cut_table != nullptr ? bars->table[bars->col_bin[abuf][col] + bj] : cut0;
                     const int snp = bars->col_snp[abuf][col];
                     const bool ok = jok && snp >= 0 && (p.pair_space == GMAT_B200_PAIRS_ALL || j > snp);
                     if (ok && fabsf(eff) >= cut) mask |= 1u << c;
@@ -206,7 +235,7 @@ i8_screen_pair_kernel(const __grid_constant__ CUtensorMap map_v, const __grid_co
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive_leader(&bars->tempty[abuf]);
-            if (++abuf == 2) { abuf = 0; aphase ^= 1u; }
+            if (++abuf == NBUF) { abuf = 0; aphase ^= 1u; }
         }
     }
     tc_fence_before();
@@ -236,23 +265,62 @@ __global__ void __launch_bounds__(1024) sc_py_stats_kernel(const double *__restr
         out[0] = a; out[1] = b;
     }
 }
-// balanced base-128 digits of py[k] / scale, |py / scale| <= 0.49: dig[s][k] in [-64, 63], zero for k >= n
-__global__ void sc_digits_kernel(const double *__restrict__ py, int n, int ld, double inv_scale,
-                                 signed char *__restrict__ dig) {
+// balanced base-2^bits digits of py[k] / scale, scale = max|py| / 0.49 read from stats[0] on the device:
+// dig[s][k] in [-B/2, B/2 - 1] (most significant plane first), zero for k >= n
+__global__ void sc_digits_kernel(const double *__restrict__ py, int n, int ld, const double *__restrict__ stats,
+                                 int n_planes, int bits, signed char *__restrict__ dig) {
     const int k = blockIdx.x * blockDim.x + threadIdx.x;
     if (k >= ld) return;
-    long long t = k < n ? __double2ll_rn(py[k] * inv_scale * 16384.0) : 0;    // 128^SC_S
-#pragma unroll
-    for (int s = SC_S - 1; s >= 1; --s) {
-        const long long d = ((t + 64) & 127) - 64;
-        t = (t - d) >> 7;
+    const double maxabs = stats[0];
+    const double inv_scale = maxabs > 0.0 ? 0.49 / maxabs : 0.0;
+    const long long B = 1LL << bits, half = B >> 1;
+    long long t = k < n ? __double2ll_rn(py[k] * inv_scale * (double)(1LL << (bits * n_planes))) : 0;
+    for (int s = n_planes - 1; s >= 1; --s) {
+        const long long d = ((t + half) & (B - 1)) - half;
+        t = (t - d) >> bits;
         dig[(size_t)s * ld + k] = (signed char)d;
     }
     dig[k] = (signed char)t;
 }
+// Everything the kernels need that depends on the cut: scale, margin, FP32 cut(s), and whether the int8 path is worth
+// it at all.  One block.  status[0] = 1 when it is not (the caller runs the FP64 kernel instead).
+__global__ void sc_setup_kernel(const double *__restrict__ stats, int n, double eff_cut, const double *__restrict__ table,
+                                int n_planes, int bits, int tripled, ScreenScalars *__restrict__ scal,
+                                float *__restrict__ tab32, int *__restrict__ status) {
+    __shared__ double smin[128];
+    const double maxabs = stats[0];
+    const double scale = maxabs / 0.49;
+    const double bpow = 1.0 / (double)(1LL << (bits * n_planes));                  // B^-S
+    // everything stage 1 drops: digit truncation scale B^-S 2n, FP32 rounding of Q~ and of the rank-one terms
+    const double margin = scale * (double)n * (2.0 * bpow + 4.0e-6);
+    double mn = 1e300;
+    if (table != nullptr) {
+        if (threadIdx.x < 111) { mn = table[threadIdx.x]; tab32[threadIdx.x] = __double2float_rd(table[threadIdx.x] - margin); }
+        if (mn != mn) mn = -1.0;                                                   // a NaN cut: never the int8 path
+    } else {
+        mn = eff_cut == eff_cut ? eff_cut : -1.0;
+    }
+    smin[threadIdx.x] = mn;
+    __syncthreads();
+    for (int d = 64; d >= 1; d >>= 1) {
+        if (threadIdx.x < d) smin[threadIdx.x] = fmin(smin[threadIdx.x], smin[threadIdx.x + d]);
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        const double cut_min = smin[0];
+        const bool ok = maxabs > 0.0 && maxabs < 1e300 && margin < 0.25 * cut_min;  // a cut near zero keeps every pair
+        scal->cut = __double2float_rd(eff_cut - margin);
+        scal->qscale = (float)(scale * bpow * (tripled ? 1.0 / 9.0 : 1.0));
+        scal->base = (float)(1 << bits);
+        scal->fallback = ok ? 0 : 1;
+        scal->margin = margin;
+        if (!ok) status[0] = 1;
+    }
+}
 // t[snp] = sum_k a_k py_k over the int8 codes of one SNP row (one warp per SNP, fixed order)
 __global__ void __launch_bounds__(256) sc_dot_kernel(const signed char *__restrict__ g8, int ld, int n, long long m,
-                                                     const double *__restrict__ py, double *__restrict__ t) {
+                                                     const double *__restrict__ py, double mult,
+                                                     double *__restrict__ t) {
     const long long snp = (long long)blockIdx.x * 8 + (threadIdx.x >> 5);
     if (snp >= m) return;
     const int lane = threadIdx.x & 31;
@@ -268,13 +336,15 @@ __global__ void __launch_bounds__(256) sc_dot_kernel(const signed char *__restri
     }
 #pragma unroll
     for (int d = 16; d >= 1; d >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, d);
-    if (lane == 0) t[snp] = acc;
+    if (lane == 0) t[snp] = acc * mult;
 }
 // per second SNP: o_j = -lutV[j][0], c_j = t_j - o_j P  (FP32 copies for stage 1)
-__global__ void sc_second_kernel(const double *__restrict__ lutV, const double *__restrict__ tV, double P, long long m,
-                                 float *__restrict__ oV, float *__restrict__ cV) {
+__global__ void sc_second_kernel(const double *__restrict__ lutV, const double *__restrict__ tV,
+                                 const double *__restrict__ stats, long long m, float *__restrict__ oV,
+                                 float *__restrict__ cV) {
     const long long j = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (j >= m) return;
+    const double P = stats[1];
     const double o = -lutV[j * 4];
     oV[j] = (float)o;
     cV[j] = (float)(tV[j] - o * P);
@@ -283,7 +353,7 @@ __global__ void sc_second_kernel(const double *__restrict__ lutV, const double *
 // plus the FP32 per-first-SNP constants
 __global__ void __launch_bounds__(256) sc_planes_kernel(const signed char *__restrict__ g8U, int ld,
                                                         const long long *__restrict__ ilist, int n_i, int plane_rows,
-                                                        const signed char *__restrict__ dig,
+                                                        int n_planes, const signed char *__restrict__ dig,
                                                         const double *__restrict__ lutU, const double *__restrict__ tUall,
                                                         signed char *__restrict__ pu, float *__restrict__ tU,
                                                         float *__restrict__ oU) {
@@ -294,8 +364,7 @@ __global__ void __launch_bounds__(256) sc_planes_kernel(const signed char *__res
         uint4 a = make_uint4(0u, 0u, 0u, 0u);
         if (snp >= 0) a = *reinterpret_cast<const uint4 *>(g8U + (size_t)snp * ld + k0);
         const unsigned aw[4] = {a.x, a.y, a.z, a.w};
-#pragma unroll
-        for (int s = 0; s < SC_S; ++s) {
+        for (int s = 0; s < n_planes; ++s) {
             const uint4 d = *reinterpret_cast<const uint4 *>(dig + (size_t)s * ld + k0);
             const unsigned dw[4] = {d.x, d.y, d.z, d.w};
             unsigned o[4];
@@ -334,10 +403,6 @@ __global__ void sc_tiles_kernel(const long long *__restrict__ ilist, int n_i, in
         for (int ib = 0; ib < n_ib; ++ib) prefix[ib + 1] += prefix[ib];
     }
 }
-__global__ void sc_table_kernel(const double *__restrict__ table, double margin, float *__restrict__ out) {
-    if (threadIdx.x < 111) out[threadIdx.x] = __double2float_rd(table[threadIdx.x] - margin);
-}
-
 // Stage 2: eff of the candidates in FP64 from the LUT values (the arithmetic of the FP64 engine and of the
 // reference: lutU[i][c_ik] * lutV[j][c_jk] * py[k]), the reference's threshold, the hit record.  One warp per
 // candidate, lanes stride over the bytes of the two .bed rows, fixed reduction order.
@@ -346,9 +411,13 @@ __global__ void __launch_bounds__(256) screen_exact_kernel(
     const double *__restrict__ lutV, const double *__restrict__ py, const int2 *__restrict__ cand,
     const unsigned long long *__restrict__ n_cand, int flags, double eff_cut, const double *__restrict__ cut_table,
     const int *__restrict__ binI, const int *__restrict__ binJ, gmat_b200_hit *__restrict__ hits, long long cap,
-    unsigned long long *__restrict__ count) {
+    unsigned long long *__restrict__ count, long long cand_cap, int *__restrict__ status) {
     const int lane = threadIdx.x & 31;
-    const long long total = (long long)*n_cand;
+    long long total = (long long)*n_cand;
+    if (total > cand_cap) {                                       // more survivors than the buffer holds: the caller must
+        if (blockIdx.x == 0 && threadIdx.x == 0) status[0] = 2;   // fall back (or retry with a larger buffer)
+        return;
+    }
     const bool ge = (flags & GMAT_B200_EFF_GE) != 0, swap = (flags & GMAT_B200_EFF_SWAP) != 0;
     for (long long c = (long long)blockIdx.x * 8 + (threadIdx.x >> 5); c < total; c += (long long)gridDim.x * 8) {
         const int i = cand[c].x, j = cand[c].y;
@@ -385,13 +454,6 @@ __global__ void __launch_bounds__(256) screen_exact_kernel(
 
 using namespace gb;
 
-extern "C" int gmat_b200_epi_eff(const unsigned char *bed_dev, long long n, long long m, long long row_bytes,
-                                 const double *lutU_dev, const double *lutV_dev, const double *py_dev,
-                                 const long long *ilist_dev, long long n_i, int flags, double eff_cut,
-                                 const double *cut_table_dev, const int *binI_dev, const int *binJ_dev,
-                                 gmat_b200_hit *hits_dev, long long cap, unsigned long long *count_dev,
-                                 void *stream);
-
 namespace {
 struct Scratch {                                                  // stream-ordered scratch, freed on scope exit
     cudaStream_t st;
@@ -405,93 +467,97 @@ struct Scratch {                                                  // stream-orde
         return reinterpret_cast<T *>(q);
     }
 };
+inline int sc_planes_of(int tripled) { return tripled ? 3 : 2; }
+inline int sc_bits_of(int tripled) { return tripled ? 5 : 7; }
 }  // namespace
 
-extern "C" int gmat_b200_epi_eff_i8(const unsigned char *bed_dev, long long n, long long m, long long row_bytes,
-                                    const double *lutU_dev, const double *lutV_dev, int codingU, int codingV,
-                                    const double *py_dev, const long long *ilist_dev, long long n_i, int flags,
-                                    double eff_cut, const double *cut_table_dev, const int *binI_dev,
-                                    const int *binJ_dev, gmat_b200_hit *hits_dev, long long cap,
-                                    unsigned long long *count_dev, int *engine_used, void *stream) {
-    GB_CHECK_ARG(bed_dev && lutU_dev && lutV_dev && py_dev && ilist_dev && count_dev, "NULL pointer");
-    GB_CHECK_ARG(n > 0 && m > 0 && n_i >= 0, "sizes");
+extern "C" long long gmat_b200_screen_ld(long long n) { return round_up(n, I8_TK); }
+
+extern "C" int gmat_b200_screen_operand(const unsigned char *bed_dev, long long n, long long m, long long row_bytes,
+                                        int coding, int tripled, const double *py_dev, signed char *g8_dev,
+                                        double *t_dev, void *stream) {
+    GB_CHECK_ARG(bed_dev && py_dev && g8_dev && t_dev && n > 0 && m > 0, "null buffer or empty shape");
+    GB_CHECK_ARG(coding == GMAT_B200_CODING_ADD || coding == GMAT_B200_CODING_DOM, "coding");
     GB_CHECK_ARG(row_bytes >= (n + 3) / 4 && row_bytes % 16 == 0, "row_bytes");
-    GB_CHECK_ARG((codingU == GMAT_B200_CODING_ADD || codingU == GMAT_B200_CODING_DOM) &&
-                 (codingV == GMAT_B200_CODING_ADD || codingV == GMAT_B200_CODING_DOM), "coding");
+    cudaStream_t st = (cudaStream_t)stream;
+    const int ld = (int)round_up(n, I8_TK);
+    // byte[code]: plain {0, 0, 1, 2} / {0, 0, 1, 0}; tripled (code 01 = 1/3, x 3): {0, 1, 3, 6} / {0, 1, 3, 0}
+    const unsigned tab = tripled ? (coding == GMAT_B200_CODING_DOM ? 0x00030100u : 0x06030100u)
+                                 : (coding == GMAT_B200_CODING_DOM ? 0x00010000u : 0x02010000u);
+    int rc = launch_i8_dosage(bed_dev, (int)n, m, row_bytes, tab, g8_dev, nullptr, ld, st);
+    if (rc != GMAT_B200_OK) return rc;
+    sc_dot_kernel<<<(unsigned)((m + 7) / 8), 256, 0, st>>>(g8_dev, ld, (int)n, m, py_dev, tripled ? 1.0 / 3.0 : 1.0,
+                                                          t_dev);
+    GB_LAUNCH_CHECK();
+    return GMAT_B200_OK;
+}
+
+extern "C" int gmat_b200_screen_py(const double *py_dev, long long n, int tripled, signed char *dig_dev,
+                                   double *stats_dev, void *stream) {
+    GB_CHECK_ARG(py_dev && dig_dev && stats_dev && n > 0, "null buffer or empty shape");
+    cudaStream_t st = (cudaStream_t)stream;
+    const int ld = (int)round_up(n, I8_TK);
+    sc_py_stats_kernel<<<1, 1024, 0, st>>>(py_dev, (int)n, stats_dev);
+    GB_LAUNCH_CHECK();
+    sc_digits_kernel<<<(unsigned)((ld + 255) / 256), 256, 0, st>>>(py_dev, (int)n, ld, stats_dev, sc_planes_of(tripled),
+                                                                   sc_bits_of(tripled), dig_dev);
+    GB_LAUNCH_CHECK();
+    return GMAT_B200_OK;
+}
+
+template <int S>
+static int sc_launch_stage1(const CUtensorMap &map_v, const CUtensorMap &map_p, const ScreenParams &p, int n_ib, int n_jb,
+                            cudaStream_t st) {
+    const int smem_bytes = ScreenCfg<S>::NS * ScreenCfg<S>::STAGE_BYTES + 1024 + (int)sizeof(ScreenBars);
+    GB_CUDA(cudaFuncSetAttribute(i8_screen_pair_kernel<S>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
+    long long pairs_of_sms = sm_count() / 2;
+    const long long max_items = (long long)n_ib * n_jb;
+    if (pairs_of_sms > max_items) pairs_of_sms = max_items;
+    i8_screen_pair_kernel<S><<<(unsigned)(2 * pairs_of_sms), SC_THREADS, smem_bytes, st>>>(map_v, map_p, p);
+    GB_LAUNCH_CHECK();
+    return GMAT_B200_OK;
+}
+
+extern "C" int gmat_b200_epi_eff_i8p(const unsigned char *bed_dev, long long n, long long m, long long row_bytes,
+                                     const double *lutU_dev, const double *lutV_dev, const signed char *g8U_dev,
+                                     const signed char *g8V_dev, const double *tU_dev, const double *tV_dev,
+                                     const signed char *dig_dev, const double *stats_dev, int tripled,
+                                     const double *py_dev, const long long *ilist_dev, long long n_i, int flags,
+                                     double eff_cut, const double *cut_table_dev, const int *binI_dev,
+                                     const int *binJ_dev, gmat_b200_hit *hits_dev, long long cap,
+                                     unsigned long long *count_dev, int *cand_dev, long long cand_cap,
+                                     unsigned long long *cand_count_dev, int *status_dev, void *stream) {
+    GB_CHECK_ARG(bed_dev && lutU_dev && lutV_dev && g8U_dev && g8V_dev && tU_dev && tV_dev && dig_dev && stats_dev &&
+                 py_dev && ilist_dev && count_dev && cand_dev && cand_count_dev && status_dev, "NULL pointer");
+    GB_CHECK_ARG(n > 0 && m > 0 && n_i >= 0 && cand_cap > 0, "sizes");
+    GB_CHECK_ARG(row_bytes >= (n + 3) / 4 && row_bytes % 16 == 0, "row_bytes");
     GB_CHECK_ARG(cap == 0 || hits_dev != nullptr, "hits_dev is NULL");
     GB_CHECK_ARG(cut_table_dev == nullptr || (binI_dev && binJ_dev), "bins required with cut table");
-    if (engine_used) *engine_used = 0;
-    if (n_i == 0) return GMAT_B200_OK;
+    // int32 plane sums must convert to FP32 without losing the margin's assumptions (|Y| <= 576 n < 2^24) and SNP
+    // indices are ints in the kernels
+    GB_CHECK_ARG(n < (tripled ? 29000 : 60000) && m < (1LL << 31) && n_i < (1LL << 31),
+                 "shape outside the int8 screen's integer ranges (use gmat_b200_epi_eff)");
     cudaStream_t st = (cudaStream_t)stream;
+    GB_CUDA(cudaMemsetAsync(status_dev, 0, sizeof(int), st));
+    GB_CUDA(cudaMemsetAsync(cand_count_dev, 0, sizeof(unsigned long long), st));
+    if (n_i == 0) return GMAT_B200_OK;
     keep_scratch_pool();
-#define SC_FALLBACK()                                                                                            \
-    return gmat_b200_epi_eff(bed_dev, n, m, row_bytes, lutU_dev, lutV_dev, py_dev, ilist_dev, n_i, flags, eff_cut,   \
-                             cut_table_dev, binI_dev, binJ_dev, hits_dev, cap, count_dev, stream)
-    // int32 plane sums must convert to FP32 exactly (|Y| <= 256 n < 2^24) and SNP indices are ints in the kernels
-    if (n >= 60000 || m >= (1LL << 31) || n_i >= (1LL << 31)) SC_FALLBACK();
-    Scratch sc(st);
-    // ---- scale of py, margin of stage 1, is the int8 path worth it? ----
-    double *stats = sc.get<double>(2);
-    GB_CHECK_ARG(stats != nullptr, "out of device memory");
-    sc_py_stats_kernel<<<1, 1024, 0, st>>>(py_dev, (int)n, stats);
-    GB_LAUNCH_CHECK();
-    double hstats[2];
-    double htable[111];
-    GB_CUDA(cudaMemcpyAsync(hstats, stats, sizeof(hstats), cudaMemcpyDeviceToHost, st));
-    if (cut_table_dev) GB_CUDA(cudaMemcpyAsync(htable, cut_table_dev, sizeof(htable), cudaMemcpyDeviceToHost, st));
-    GB_CUDA(cudaStreamSynchronize(st));
-    const double maxabs = hstats[0], P = hstats[1];
-    double cut_min = eff_cut;
-    if (cut_table_dev) { cut_min = htable[0]; for (int q = 1; q < 111; ++q) cut_min = htable[q] < cut_min ? htable[q] : cut_min; }
-    if (!(maxabs > 0.0) || !(maxabs < 1e300) || !(cut_min == cut_min)) SC_FALLBACK();
-    const double scale = maxabs / 0.49;
-    // everything stage 1 drops: digit truncation scale 128^-S 2n, FP32 rounding of Q~ and of the rank-one terms
-    const double margin = scale * (double)n * (2.0 / 16384.0 + 4.0e-6);
-    if (!(margin < 0.25 * cut_min)) SC_FALLBACK();            // a cut near zero keeps (almost) every pair: FP64 kernel
+    const int S = sc_planes_of(tripled), bits = sc_bits_of(tripled);
     const int ld = (int)round_up(n, I8_TK);
     const int n_slab = (int)((n + I8_SLAB - 1) / I8_SLAB);
     const int n_jb = (int)((m + 2 * I8_TJ - 1) / (2 * I8_TJ));
-
-    // ---- operands that do not depend on the first-SNP list ----
-    signed char *g8V = sc.get<signed char>((size_t)m * ld), *g8U = g8V;
-    signed char *dig = sc.get<signed char>((size_t)SC_S * ld);
-    double *tV = sc.get<double>((size_t)m), *tUall = tV;
+    Scratch sc(st);
+    ScreenScalars *scal = sc.get<ScreenScalars>(1);
     float *oV = sc.get<float>((size_t)m), *cV = sc.get<float>((size_t)m), *tab32 = sc.get<float>(112);
-    GB_CHECK_ARG(g8V && dig && tV && oV && cV && tab32, "out of device memory");
-    int rc = gmat_b200_i8_dosage(bed_dev, n, m, row_bytes, codingV, g8V, nullptr, ld, stream);
-    if (rc != GMAT_B200_OK) return rc;
-    sc_dot_kernel<<<(unsigned)((m + 7) / 8), 256, 0, st>>>(g8V, ld, (int)n, m, py_dev, tV);
+    GB_CHECK_ARG(scal && oV && cV && tab32, "out of device memory");
+    sc_setup_kernel<<<1, 128, 0, st>>>(stats_dev, (int)n, eff_cut, cut_table_dev, S, bits, tripled, scal, tab32,
+                                       status_dev);
     GB_LAUNCH_CHECK();
-    if (codingU != codingV) {
-        g8U = sc.get<signed char>((size_t)m * ld);
-        tUall = sc.get<double>((size_t)m);
-        GB_CHECK_ARG(g8U && tUall, "out of device memory");
-        rc = gmat_b200_i8_dosage(bed_dev, n, m, row_bytes, codingU, g8U, nullptr, ld, stream);
-        if (rc != GMAT_B200_OK) return rc;
-        sc_dot_kernel<<<(unsigned)((m + 7) / 8), 256, 0, st>>>(g8U, ld, (int)n, m, py_dev, tUall);
-        GB_LAUNCH_CHECK();
-    }
-    sc_digits_kernel<<<(unsigned)((ld + 255) / 256), 256, 0, st>>>(py_dev, (int)n, ld, 1.0 / scale, dig);
+    sc_second_kernel<<<(unsigned)((m + 255) / 256), 256, 0, st>>>(lutV_dev, tV_dev, stats_dev, m, oV, cV);
     GB_LAUNCH_CHECK();
-    sc_second_kernel<<<(unsigned)((m + 255) / 256), 256, 0, st>>>(lutV_dev, tV, P, m, oV, cV);
-    GB_LAUNCH_CHECK();
-    if (cut_table_dev) {
-        sc_table_kernel<<<1, 128, 0, st>>>(cut_table_dev, margin, tab32);
-        GB_LAUNCH_CHECK();
-    }
-
-    // ---- candidates of the whole call (stage 2 runs once, after the last chunk) ----
-    const long long cand_cap = 1LL << 22;
-    int2 *cand = sc.get<int2>((size_t)cand_cap);
-    unsigned long long *cand_count = sc.get<unsigned long long>(1);
-    GB_CHECK_ARG(cand && cand_count, "out of device memory");
-    GB_CUDA(cudaMemsetAsync(cand_count, 0, sizeof(unsigned long long), st));
-
     CUtensorMap map_v;
-    rc = make_map(&map_v, g8V, ld, m, ld, I8_TJ);
+    int rc = make_map(&map_v, g8V_dev, ld, m, ld, I8_TJ);
     if (rc != GMAT_B200_OK) return rc;
-    const int smem_bytes = SC_NS * SC_STAGE_BYTES + 1024 + (int)sizeof(ScreenBars);
-    GB_CUDA(cudaFuncSetAttribute(i8_screen_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
 
     // ---- first SNPs in chunks (plane buffer <= 1 GiB) ----
     long long budget = 1LL << 30;
@@ -499,19 +565,19 @@ extern "C" int gmat_b200_epi_eff_i8(const unsigned char *bed_dev, long long n, l
         const long long v = atoll(e);
         if (v > 0) budget = v;
     }
-    long long chunk = budget / ((long long)SC_S * ld);
+    long long chunk = budget / ((long long)S * ld);
     chunk = chunk / SC_TI * SC_TI;
     if (chunk < SC_TI) chunk = SC_TI;
     for (long long c0 = 0; c0 < n_i; c0 += chunk) {
         const int ni = (int)((n_i - c0 < chunk) ? n_i - c0 : chunk);
         const int n_ib = (ni + SC_TI - 1) / SC_TI, plane_rows = n_ib * SC_TI;
         Scratch csc(st);                                          // this chunk's buffers: freed (stream-ordered) per chunk
-        signed char *pu = csc.get<signed char>((size_t)SC_S * plane_rows * ld);
+        signed char *pu = csc.get<signed char>((size_t)S * plane_rows * ld);
         float *tU = csc.get<float>((size_t)plane_rows), *oU = csc.get<float>((size_t)plane_rows);
         int *tiles = csc.get<int>((size_t)2 * n_ib + 2);
         GB_CHECK_ARG(pu && tU && oU && tiles, "out of device memory");
-        sc_planes_kernel<<<(unsigned)plane_rows, 256, 0, st>>>(g8U, ld, ilist_dev + c0, ni, plane_rows, dig, lutU_dev,
-                                                               tUall, pu, tU, oU);
+        sc_planes_kernel<<<(unsigned)plane_rows, 256, 0, st>>>(g8U_dev, ld, ilist_dev + c0, ni, plane_rows, S, dig_dev,
+                                                               lutU_dev, tU_dev, pu, tU, oU);
         GB_LAUNCH_CHECK();
         const int pair_space = GMAT_B200_PAIRS_UPPER;            // the screen only ever tests j > i (:69-77, :233-247)
         sc_tiles_kernel<<<1, 1024, 0, st>>>(ilist_dev + c0, ni, n_ib, n_jb, pair_space, tiles, tiles + n_ib + 1);
@@ -521,31 +587,76 @@ extern "C" int gmat_b200_epi_eff_i8(const unsigned char *bed_dev, long long n, l
         p.plane_rows = plane_rows; p.item_prefix = tiles; p.jb0 = tiles + n_ib + 1; p.ilist = ilist_dev + c0;
         p.tU = tU; p.oU = oU; p.oV = oV; p.cV = cV; p.binI = binI_dev; p.binJ = binJ_dev;
         p.cut_table = cut_table_dev ? tab32 : nullptr;
-        p.cut = __builtin_nextafterf((float)(eff_cut - margin), -1.0e38f);
-        p.qscale = (float)(scale / 16384.0);
-        p.cand = cand; p.cand_cap = cand_cap; p.cand_count = cand_count;
+        p.scal = scal;
+        p.cand = reinterpret_cast<int2 *>(cand_dev); p.cand_cap = cand_cap; p.cand_count = cand_count_dev;
         CUtensorMap map_p;
-        rc = make_map(&map_p, pu, ld, (long long)SC_S * plane_rows, ld, SC_TI / 2);
+        rc = make_map(&map_p, pu, ld, (long long)S * plane_rows, ld, SC_TI / 2);
         if (rc != GMAT_B200_OK) return rc;
-        long long pairs_of_sms = sm_count() / 2;
-        const long long max_items = (long long)n_ib * n_jb;
-        if (pairs_of_sms > max_items) pairs_of_sms = max_items;
-        i8_screen_pair_kernel<<<(unsigned)(2 * pairs_of_sms), SC_THREADS, smem_bytes, st>>>(map_v, map_p, p);
-        GB_LAUNCH_CHECK();
+        rc = S == 2 ? sc_launch_stage1<2>(map_v, map_p, p, n_ib, n_jb, st) : sc_launch_stage1<3>(map_v, map_p, p, n_ib, n_jb, st);
+        if (rc != GMAT_B200_OK) return rc;
     }
-    unsigned long long hcount = 0;
-    GB_CUDA(cudaMemcpyAsync(&hcount, cand_count, sizeof(hcount), cudaMemcpyDeviceToHost, st));
+    // stage 2 over the device-side candidate count (a grid-stride kernel: no host read of the count)
+    screen_exact_kernel<<<(unsigned)(4 * sm_count()), 256, 0, st>>>(
+        bed_dev, (int)n, row_bytes, lutU_dev, lutV_dev, py_dev, reinterpret_cast<const int2 *>(cand_dev), cand_count_dev,
+        flags, eff_cut, cut_table_dev, binI_dev, binJ_dev, hits_dev, cap, count_dev, cand_cap, status_dev);
+    GB_LAUNCH_CHECK();
+    return GMAT_B200_OK;
+}
+
+// One-shot form: builds the operands, runs the prepared screen, reads the status back (one synchronisation) and runs
+// the FP64 kernel itself when the int8 path declined.  Callers that screen more than once with the same Z'Py (the two
+// directions of AD, the stages of the _approx pipelines, repeated calls) keep the operands and use the prepared form.
+extern "C" int gmat_b200_epi_eff_i8(const unsigned char *bed_dev, long long n, long long m, long long row_bytes,
+                                    const double *lutU_dev, const double *lutV_dev, int codingU, int codingV,
+                                    int tripled, const double *py_dev, const long long *ilist_dev, long long n_i,
+                                    int flags, double eff_cut, const double *cut_table_dev, const int *binI_dev,
+                                    const int *binJ_dev, gmat_b200_hit *hits_dev, long long cap,
+                                    unsigned long long *count_dev, int *engine_used, void *stream) {
+    GB_CHECK_ARG(bed_dev && lutU_dev && lutV_dev && py_dev && ilist_dev && count_dev, "NULL pointer");
+    GB_CHECK_ARG(n > 0 && m > 0 && n_i >= 0, "sizes");
+    GB_CHECK_ARG((codingU == GMAT_B200_CODING_ADD || codingU == GMAT_B200_CODING_DOM) &&
+                 (codingV == GMAT_B200_CODING_ADD || codingV == GMAT_B200_CODING_DOM), "coding");
+    if (engine_used) *engine_used = 0;
+    if (n_i == 0) return GMAT_B200_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    keep_scratch_pool();
+#define SC_FALLBACK()                                                                                            \
+    return gmat_b200_epi_eff(bed_dev, n, m, row_bytes, lutU_dev, lutV_dev, py_dev, ilist_dev, n_i, flags, eff_cut,   \
+                             cut_table_dev, binI_dev, binJ_dev, hits_dev, cap, count_dev, stream)
+    if (n >= (tripled ? 29000 : 60000) || m >= (1LL << 31) || n_i >= (1LL << 31)) SC_FALLBACK();
+    const int ld = (int)round_up(n, I8_TK);
+    const long long cand_cap = 1LL << 22;
+    Scratch sc(st);
+    signed char *g8V = sc.get<signed char>((size_t)m * ld), *g8U = g8V;
+    double *tV = sc.get<double>((size_t)m), *tU = tV;
+    signed char *dig = sc.get<signed char>((size_t)SC_SMAX * ld);
+    double *stats = sc.get<double>(4);
+    int *cand = sc.get<int>((size_t)2 * cand_cap), *status = sc.get<int>(2);
+    unsigned long long *cand_count = sc.get<unsigned long long>(1);
+    GB_CHECK_ARG(g8V && tV && dig && stats && cand && status && cand_count, "out of device memory");
+    int rc = gmat_b200_screen_operand(bed_dev, n, m, row_bytes, codingV, tripled, py_dev, g8V, tV, stream);
+    if (rc != GMAT_B200_OK) return rc;
+    if (codingU != codingV) {
+        g8U = sc.get<signed char>((size_t)m * ld);
+        tU = sc.get<double>((size_t)m);
+        GB_CHECK_ARG(g8U && tU, "out of device memory");
+        rc = gmat_b200_screen_operand(bed_dev, n, m, row_bytes, codingU, tripled, py_dev, g8U, tU, stream);
+        if (rc != GMAT_B200_OK) return rc;
+    }
+    rc = gmat_b200_screen_py(py_dev, n, tripled, dig, stats, stream);
+    if (rc != GMAT_B200_OK) return rc;
+    rc = gmat_b200_epi_eff_i8p(bed_dev, n, m, row_bytes, lutU_dev, lutV_dev, g8U, g8V, tU, tV, dig, stats, tripled, py_dev,
+                               ilist_dev, n_i, flags, eff_cut, cut_table_dev, binI_dev, binJ_dev, hits_dev, cap, count_dev,
+                               cand, cand_cap, cand_count, status, stream);
+    if (rc != GMAT_B200_OK) return rc;
+    int hstatus = 0;
+    GB_CUDA(cudaMemcpyAsync(&hstatus, status, sizeof(int), cudaMemcpyDeviceToHost, st));
     GB_CUDA(cudaStreamSynchronize(st));
-    if ((long long)hcount > cand_cap) SC_FALLBACK();              // too many survivors for the buffer: FP64 kernel
-#undef SC_FALLBACK
-    if (hcount > 0) {
-        long long blocks = ((long long)hcount + 7) / 8;
-        if (blocks > 8LL * sm_count()) blocks = 8LL * sm_count();
-        screen_exact_kernel<<<(unsigned)blocks, 256, 0, st>>>(bed_dev, (int)n, row_bytes, lutU_dev, lutV_dev, py_dev,
-                                                              cand, cand_count, flags, eff_cut, cut_table_dev, binI_dev,
-                                                              binJ_dev, hits_dev, cap, count_dev);
-        GB_LAUNCH_CHECK();
+    if (hstatus != 0) {                                           // margin not small against the cut, or too many survivors
+        GB_CUDA(cudaMemsetAsync(count_dev, 0, sizeof(unsigned long long), st));
+        SC_FALLBACK();
     }
+#undef SC_FALLBACK
     if (engine_used) *engine_used = 1;
     return GMAT_B200_OK;
 }

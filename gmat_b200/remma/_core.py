@@ -424,11 +424,24 @@ def eff_screen(kind, y, xmat, zmat, gmat_lst, var_com, bed_file, snp_lst_0=None,
 def eff_screen_parallel(kind, y, xmat, zmat, gmat_lst, var_com, bed_file, parallel, var_app, p_cut, out_file):
     logging.info("Parallel: " + str(parallel[0]) + ', ' + str(parallel[1]))
     num_snp = engine.count_lines(bed_file + '.bim')
-    # every _eff_parallel copy uses the AA cut points (num_snp - 1), also AD (remma_epiAD_eff.py:120-153)
-    snp_list_0, pos = par.parallel_lists(num_snp, parallel, False)
+    # last cut of part 1: num_snp - 1 in the AA / DD copies (remma_epiAA_eff.py:148), num_snp in the AD copy
+    # (remma_epiAD_eff.py:147) -- the extra first SNP has no j > i, so only the logged cut points differ
+    snp_list_0, pos = par.parallel_lists(num_snp, parallel, kind.all_pairs)
     logging.info('SNP position point: ' + ','.join(str(v) for v in pos))
     return eff_screen(kind, y, xmat, zmat, gmat_lst, var_com, bed_file, snp_lst_0=snp_list_0, var_app=var_app,
                       p_cut=p_cut, out_file=out_file + '.' + str(parallel[1]))
+
+
+def maf_eff_screen_parallel(kind, y, xmat, zmat, gmat_lst, var_com, bed_file, parallel, freq, freq2, freq_deno,
+                            p_cut, out_file):
+    """remma_epiAA_maf_eff.py:129-161 and the AD / DD copies: part k of P of the MAF-binned screen, output
+    ``out_file.k``.  All three copies cut part 1 at num_snp - 1 (remma_epiAD_maf_eff.py:158 too)."""
+    logging.info("Parallel: " + str(parallel[0]) + ', ' + str(parallel[1]))
+    num_snp = engine.count_lines(bed_file + '.bim')
+    snp_list_0, pos = par.parallel_lists(num_snp, parallel, False)
+    logging.info('SNP position point: ' + ','.join(str(v) for v in pos))
+    return maf_eff_screen(kind, y, xmat, zmat, gmat_lst, var_com, bed_file, snp_lst_0=snp_list_0, freq=freq,
+                          freq2=freq2, freq_deno=freq_deno, p_cut=p_cut, out_file=out_file + '.' + str(parallel[1]))
 
 
 def maf_eff_screen(kind, y, xmat, zmat, gmat_lst, var_com, bed_file, snp_lst_0=None, freq=None, freq2=None,

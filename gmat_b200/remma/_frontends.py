@@ -71,8 +71,9 @@ def build(kind, ns):
             return _maf_eff(y, xmat, zmat, gmat_lst, var_com, bed_file, snp_lst_0=snp_lst_0, freqA=freqA,
                             freqD=freqD, freq_deno=freq_deno, p_cut=p_cut, out_file=out_file)
     else:
+        # (the AA underscore form keeps the _eff default name: remma_epiAA_maf_eff.py:20)
         def _maf_eff(y, xmat, zmat, gmat_lst, var_com, bed_file, snp_lst_0=None, freq=None, freq_deno=None,
-                     p_cut=1.0e-5, out_file='epi%s_maf_eff' % K):
+                     p_cut=1.0e-5, out_file='epiAA_eff' if K == 'AA' else 'epi%s_maf_eff' % K):
             return _core.maf_eff_screen(kind, y, xmat, zmat, gmat_lst, var_com, bed_file, snp_lst_0, freq, None,
                                         freq_deno, p_cut, out_file)
 
@@ -81,6 +82,30 @@ def build(kind, ns):
             y, xmat, zmat = design_matrix_wemai_multi_gmat(pheno_file, bed_file)
             return _maf_eff(y, xmat, zmat, gmat_lst, var_com, bed_file, snp_lst_0=snp_lst_0, freq=freq,
                             freq_deno=freq_deno, p_cut=p_cut, out_file=out_file)
+
+    if K == 'AD':
+        # (the AD copy keeps the AA default name: remma_epiAD_maf_eff.py:131-132,167-168)
+        def _maf_eff_parallel(y, xmat, zmat, gmat_lst, var_com, bed_file, parallel, freqA=None, freqD=None,
+                              freq_deno=None, p_cut=1.0e-5, out_file='epiAA_maf_eff_parallel'):
+            return _core.maf_eff_screen_parallel(kind, y, xmat, zmat, gmat_lst, var_com, bed_file, parallel, freqA,
+                                                 freqD, freq_deno, p_cut, out_file)
+
+        def maf_eff_parallel(pheno_file, bed_file, gmat_lst, var_com, parallel, freqA=None, freqD=None,
+                             freq_deno=None, p_cut=1.0e-5, out_file='epiAA_maf_eff_parallel'):
+            y, xmat, zmat = design_matrix_wemai_multi_gmat(pheno_file, bed_file)
+            return _maf_eff_parallel(y, xmat, zmat, gmat_lst, var_com, bed_file, parallel, freqA=freqA, freqD=freqD,
+                                     freq_deno=freq_deno, p_cut=p_cut, out_file=out_file)
+    else:
+        def _maf_eff_parallel(y, xmat, zmat, gmat_lst, var_com, bed_file, parallel, freq=None, freq_deno=None,
+                              p_cut=1.0e-5, out_file='epi%s_maf_eff_parallel' % K):
+            return _core.maf_eff_screen_parallel(kind, y, xmat, zmat, gmat_lst, var_com, bed_file, parallel, freq,
+                                                 None, freq_deno, p_cut, out_file)
+
+        def maf_eff_parallel(pheno_file, bed_file, gmat_lst, var_com, parallel, freq=None, freq_deno=None,
+                             p_cut=1.0e-5, out_file='epi%s_maf_eff_parallel' % K):
+            y, xmat, zmat = design_matrix_wemai_multi_gmat(pheno_file, bed_file)
+            return _maf_eff_parallel(y, xmat, zmat, gmat_lst, var_com, bed_file, parallel, freq=freq,
+                                     freq_deno=freq_deno, p_cut=p_cut, out_file=out_file)
 
     def approx(pheno_file, bed_file, gmat_lst, var_com, p_cut=1.0e-5, num_random_pair=100000,
                out_file='epi%s_approx' % K):
@@ -107,6 +132,7 @@ def build(kind, ns):
         'remma_epi%s_eff': eff, '_remma_epi%s_eff': _eff,
         'remma_epi%s_eff_parallel': eff_parallel, '_remma_epi%s_eff_parallel': _eff_parallel,
         'remma_epi%s_maf_eff': maf_eff, '_remma_epi%s_maf_eff': _maf_eff,
+        'remma_epi%s_maf_eff_parallel': maf_eff_parallel, '_remma_epi%s_maf_eff_parallel': _maf_eff_parallel,
         'remma_epi%s_approx': approx, 'remma_epi%s_approx_parallel': approx_parallel,
         'remma_epi%s_maf_approx': maf_approx, 'remma_epi%s_maf_approx_parallel': maf_approx_parallel,
     }

@@ -339,3 +339,21 @@ def test_bench_reference_arm_contract():
     assert d["config"] == json.loads(json.dumps(bench.CONFIG))            # byte-identical config in both arms
     tail = json.loads(out.stderr.strip().splitlines()[-1])
     assert tail["mods"] == [] and tail["so"] is False, tail
+
+
+def test_every_reference_front_end_exists_with_the_same_signature():
+    """Every public function of the reference's remma_epi{AA,AD,DD} packages (fixture written from the unmodified
+    reference by oracle/make_golden_signatures.py) exists in gmat_b200.remma.remma_epiXX with the same parameter names,
+    order and defaults."""
+    import importlib
+    import inspect
+    import json
+    want = json.load(open(os.path.join(GOLD, "frontend_signatures.json")))
+    for kind, table in want.items():
+        mod = importlib.import_module("gmat_b200.remma.remma_epi" + kind)
+        assert len(table) >= 18
+        for name, params in table.items():
+            assert hasattr(mod, name), name
+            got = [[p.name, None if p.default is inspect.Parameter.empty else repr(p.default)]
+                   for p in inspect.signature(getattr(mod, name)).parameters.values()]
+            assert got == params, (name, got, params)
