@@ -768,27 +768,34 @@ def extras(engine, torch, synth, store, model, lut, args, prefix, pymat, i8_peak
     from scipy.stats import chi2
     cut = float(np.sqrt(chi2.isf(P_CUT, 1) * np.median(sample["eff"] ** 2) / chi2.ppf(0.5, 1)))
     box = {}
+    ops = engine.ScreenOperands(store, model.py)        # int8 codes, a.Z'Py, digits of Z'Py: built once, kept
 
-    def run_screen(codings):
-        box["hits"] = engine.epi_eff(store, la, la, model.py, full, 0, cut, codings=codings)
+    def run_screen(codings, prepared=True):
+        box["hits"] = engine.epi_eff(store, la, la, model.py, full, 0, cut, codings=codings,
+                                     ops=ops if (prepared and codings is not None) else None)
     t = timed(lambda: run_screen((engine.ADD, engine.ADD)))
     which = engine.LAST_SCREEN_ENGINE
     n_hits = len(box["hits"])
     out["approx_screen"] = {"engine": which, "pairs_per_s": pairs / t, "seconds": t, "pairs": pairs, "hits": n_hits,
                             "eff_cut": cut,
                             "fp64_equivalent_tflops": pairs * 2.0 * N_ID / t / 1e12,
-                            "workload": "remma_epiAA_eff_cpu formulation, full scan n=%d x m=%d, whole call "
-                                        "(operand build, prefilter, FP64 re-test, hit records)" % (N_ID, N_SNP)}
+                            "workload": "remma_epiAA_eff_cpu formulation, full scan n=%d x m=%d, whole call on "
+                                        "prepared operands (first-SNP upload, planes of the first SNPs, prefilter, "
+                                        "FP64 re-test, hit records to the host; the int8 codes of the store and the "
+                                        "digits of Z'Py are kept across calls)" % (N_ID, N_SNP)}
     if which == "i8":
         tops = pairs * 4.0 * N_ID / t / 1e12
         out["approx_screen"]["roofline"] = {"bound": "tensor", "unit": "TOP/s", "achieved": tops, "peak": i8_peak,
                                             "frac": tops / i8_peak,
                                             "note": "4n int8 ops per pair (two digit planes of Z'Py) / the whole call"}
+        t1 = timed(lambda: run_screen((engine.ADD, engine.ADD), prepared=False))
+        out["approx_screen"]["one_shot_call_seconds"] = t1
     t64 = timed(lambda: run_screen(None))
     out["approx_screen"]["f64_engine"] = {"pairs_per_s": pairs / t64, "seconds": t64, "hits": len(box["hits"]),
                                           "same_hit_count": len(box["hits"]) == n_hits,
                                           "tflops_algorithmic": pairs * 2.0 * N_ID / t64 / 1e12,
                                           "kernel": "epi_eff_kernel (FP64 DMMA)"}
+    del ops
     if not args.no_cpu:
         # the reference's own C screen (oracle/_ref, compiled from gmat/remma/_remma_epi_eff_cpu.c) on the same
         # files with all host threads; bounded sample of first-SNPs.  It re-reads and re-codes the whole .bed into
@@ -820,7 +827,46 @@ def extras(engine, torch, synth, store, model, lut, args, prefix, pymat, i8_peak
                                   "frac": nbytes / t / 1e9 / hbm if hbm else None,
                                   "peak_source": "MEASURED_PEAKS.json hbm_gbs (copy bandwidth)"},
                      "workload": "gmat_b200_decode n=%d x m=%d (0.25 B in + 8 B out per genotype)" % (n3, m3)}
-    del dec, st3
+    del dec
+    # approximate screen at the north-star shape (1.25e9 pairs), clean store and the same store with 0.5 % missing
+    # calls (the C path's code 01 = 1/3: tripled integer coding, three base-32 planes)
+    gen = torch.Generator(device=store.device)
+    gen.manual_seed(5)
+    py3 = torch.randn((n3,), dtype=torch.float64, device=store.device, generator=gen)
+    py3 = (py3 - py3.mean()).contiguous()
+    full3 = np.arange(m3 - 1, dtype=np.int64)
+    pairs3 = m3 * (m3 - 1) // 2
+    out["approx_screen_northstar"] = {}
+    for tag, st in (("clean", st3), ("missing_0.5pct", None)):
+        if st is None:
+            bed = st3.bed.clone()
+            hole = torch.rand(bed.shape, generator=gen, device=store.device) < 0.005 * 4
+            slot = torch.randint(0, 4, bed.shape, generator=gen, device=store.device, dtype=torch.uint8)
+            clear = (~(torch.tensor(3, dtype=torch.uint8, device=store.device) << (2 * slot))) & 0xFF
+            setb = torch.tensor(1, dtype=torch.uint8, device=store.device) << (2 * slot)
+            bed = torch.where(hole, (bed & clear) | setb, bed)             # code 01 in one slot of ~2 % of the bytes
+            st = engine.GenotypeStore.from_device_payload(bed, n3)
+        l3 = st.lut(engine.ADD, engine.FREQ_CLOOP)
+        smp = engine.epi_eff(st, l3, l3, py3, np.arange(0, m3 - 1, 997, dtype=np.int64), 0, 0.0)
+        cut3 = float(np.sqrt(chi2.isf(1e-7, 1) * np.median(smp["eff"] ** 2) / chi2.ppf(0.5, 1)))
+        ops3 = engine.ScreenOperands(st, py3)
+        hbox = {}
+
+        def go():
+            hbox["h"] = engine.epi_eff(st, l3, l3, py3, full3, 0, cut3, codings=(engine.ADD, engine.ADD), ops=ops3)
+        t3 = timed(go, reps=2)
+        planes3 = 3 if ops3.tripled else 2
+        tops3 = pairs3 * 2.0 * planes3 * n3 / t3 / 1e12
+        out["approx_screen_northstar"][tag] = {
+            "engine": engine.LAST_SCREEN_ENGINE, "note": engine.LAST_SCREEN_NOTE, "missing_calls": int(st.n_missing()),
+            "pairs": pairs3, "seconds": t3, "pairs_per_s": pairs3 / t3, "hits": len(hbox["h"]), "eff_cut": cut3,
+            "digit_planes": planes3,
+            "roofline": {"bound": "tensor", "unit": "TOP/s", "achieved": tops3, "peak": i8_peak, "frac": tops3 / i8_peak,
+                         "note": "2 n int8 ops per pair and digit plane / the whole call"},
+            "workload": "full AA screen n=%d x m=%d on prepared operands, cut at p = 1e-7 on the median null variance"
+                        % (n3, m3)}
+        del ops3
+    del st3
     if not args.no_grm:
         n2, m2 = args.grm_n, args.grm_m
         rb = engine.row_stride(n2)

@@ -96,16 +96,41 @@ int run_screen(char *bed_file, long long num_id, long long num_snp, long long *s
         GB_CUDA(cudaMemcpy(table.p, cut_table, sizeof(double) * 111, cudaMemcpyHostToDevice));
     }
 
-    // engine of the screen: int8 tensor cores when no genotype is missing (GMAT_B200_SCREEN_ENGINE=f64 forces DMMA)
+    // engine of the screen: int8 tensor-core prefilter + FP64 re-test (screen_i8.cu; GMAT_B200_SCREEN_ENGINE=f64 forces
+    // the DMMA kernel).  Missing calls (code 01 = 1/3 in the C path) select the tripled integer coding.
     const char *f64_only = getenv("GMAT_B200_SCREEN_ENGINE");
     if (f64_only != nullptr && strcmp(f64_only, "f64") != 0) f64_only = nullptr;
-    bool clean = false;
+    int tripled = 0;
     {
         std::vector<int> hc((size_t)(4 * num_snp));
         GB_CUDA(cudaMemcpy(hc.data(), st.counts.p, sizeof(int) * hc.size(), cudaMemcpyDeviceToHost));
         long long missing = 0;
         for (long long s = 0; s < num_snp; ++s) missing += hc[(size_t)(4 * s + 1)];
-        clean = missing == 0;
+        tripled = missing != 0;
+    }
+    bool i8 = f64_only == nullptr && num_id < (tripled ? 29000 : 60000) && len_snp_lst_0 > 0;
+    // operands of the int8 screen, built ONCE for all passes of the call (the two directions of AD share them)
+    DevBuf g8A, g8D, tA, tD, dig, stats, cand, scr;
+    const long long cand_cap = 1LL << 22;
+    if (i8) {
+        const long long ld = gmat_b200_screen_ld(num_id);
+        if (needA) {
+            GB_TRY(g8A.alloc((size_t)num_snp * ld));
+            GB_TRY(tA.alloc(sizeof(double) * (size_t)num_snp));
+            GB_TRY(gmat_b200_screen_operand(st.bed.as<unsigned char>(), st.n, st.m, st.row_bytes, GMAT_B200_CODING_ADD,
+                                            tripled, py.as<double>(), g8A.as<signed char>(), tA.as<double>(), nullptr));
+        }
+        if (needD) {
+            GB_TRY(g8D.alloc((size_t)num_snp * ld));
+            GB_TRY(tD.alloc(sizeof(double) * (size_t)num_snp));
+            GB_TRY(gmat_b200_screen_operand(st.bed.as<unsigned char>(), st.n, st.m, st.row_bytes, GMAT_B200_CODING_DOM,
+                                            tripled, py.as<double>(), g8D.as<signed char>(), tD.as<double>(), nullptr));
+        }
+        GB_TRY(dig.alloc((size_t)3 * ld));
+        GB_TRY(stats.alloc(sizeof(double) * 4));
+        GB_TRY(gmat_b200_screen_py(py.as<double>(), st.n, tripled, dig.as<signed char>(), stats.as<double>(), nullptr));
+        GB_TRY(cand.alloc(sizeof(int) * 2 * (size_t)cand_cap));
+        GB_TRY(scr.alloc(64));                                    // [0] candidate count (u64), [8] status (int)
     }
 
     std::vector<gmat_b200_hit> all;
@@ -127,26 +152,36 @@ int run_screen(char *bed_file, long long num_id, long long num_snp, long long *s
             GB_CUDA(cudaMemcpy(bI.p, hI.data(), sizeof(int) * (size_t)num_snp, cudaMemcpyHostToDevice));
             GB_CUDA(cudaMemcpy(bJ.p, hJ.data(), sizeof(int) * (size_t)num_snp, cudaMemcpyHostToDevice));
         }
-        const double *lu = ps.codingU == GMAT_B200_CODING_ADD ? lutA.as<double>() : lutD.as<double>();
-        const double *lv = ps.codingV == GMAT_B200_CODING_ADD ? lutA.as<double>() : lutD.as<double>();
+        const bool uA = ps.codingU == GMAT_B200_CODING_ADD, vA = ps.codingV == GMAT_B200_CODING_ADD;
+        const double *lu = uA ? lutA.as<double>() : lutD.as<double>();
+        const double *lv = vA ? lutA.as<double>() : lutD.as<double>();
         long long cap = 1 << 20;
-        for (int attempt = 0; attempt < 2; ++attempt) {
+        bool use_i8 = i8;
+        for (int attempt = 0; attempt < 4; ++attempt) {
             DevBuf h;
             GB_TRY(h.alloc(sizeof(gmat_b200_hit) * (size_t)cap));
             GB_CUDA(cudaMemset(count.p, 0, sizeof(unsigned long long)));
-            if (clean && f64_only == nullptr)              // no missing call: int8 prefilter + FP64 re-test (screen_i8.cu)
-                GB_TRY(gmat_b200_epi_eff_i8(st.bed.as<unsigned char>(), st.n, st.m, st.row_bytes, lu, lv, ps.codingU,
-                                            ps.codingV, py.as<double>(), ilist.as<long long>(), len_snp_lst_0,
-                                            ps.flags, eff_cut, cut_table ? table.as<double>() : nullptr, bI.as<int>(),
-                                            bJ.as<int>(), h.as<gmat_b200_hit>(), cap,
-                                            count.as<unsigned long long>(), nullptr, nullptr));
+            if (use_i8)
+                GB_TRY(gmat_b200_epi_eff_i8p(
+                    st.bed.as<unsigned char>(), st.n, st.m, st.row_bytes, lu, lv,
+                    uA ? g8A.as<signed char>() : g8D.as<signed char>(), vA ? g8A.as<signed char>() : g8D.as<signed char>(),
+                    uA ? tA.as<double>() : tD.as<double>(), vA ? tA.as<double>() : tD.as<double>(),
+                    dig.as<signed char>(), stats.as<double>(), tripled, py.as<double>(), ilist.as<long long>(),
+                    len_snp_lst_0, ps.flags, eff_cut, cut_table ? table.as<double>() : nullptr, bI.as<int>(), bJ.as<int>(),
+                    h.as<gmat_b200_hit>(), cap, count.as<unsigned long long>(), cand.as<int>(), cand_cap,
+                    scr.as<unsigned long long>(), scr.as<int>() + 2, nullptr));
             else
                 GB_TRY(gmat_b200_epi_eff(st.bed.as<unsigned char>(), st.n, st.m, st.row_bytes, lu, lv,
                                          py.as<double>(), ilist.as<long long>(), len_snp_lst_0, ps.flags, eff_cut,
                                          cut_table ? table.as<double>() : nullptr, bI.as<int>(), bJ.as<int>(),
                                          h.as<gmat_b200_hit>(), cap, count.as<unsigned long long>(), nullptr));
             unsigned long long cnt = 0;
-            GB_CUDA(cudaMemcpy(&cnt, count.p, sizeof(cnt), cudaMemcpyDeviceToHost));
+            GB_CUDA(cudaMemcpy(&cnt, count.p, sizeof(cnt), cudaMemcpyDeviceToHost));   // the one synchronisation
+            if (use_i8) {
+                int status = 0;
+                GB_CUDA(cudaMemcpy(&status, scr.as<int>() + 2, sizeof(int), cudaMemcpyDeviceToHost));
+                if (status != 0) { use_i8 = false; continue; }   // the int8 path declined: FP64 DMMA kernel
+            }
             if ((long long)cnt > cap) { cap = (long long)cnt; continue; }   // exact count known: retry once
             const size_t old = all.size();
             all.resize(old + (size_t)cnt);

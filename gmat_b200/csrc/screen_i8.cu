@@ -509,7 +509,13 @@ template <int S>
 static int sc_launch_stage1(const CUtensorMap &map_v, const CUtensorMap &map_p, const ScreenParams &p, int n_ib, int n_jb,
                             cudaStream_t st) {
     const int smem_bytes = ScreenCfg<S>::NS * ScreenCfg<S>::STAGE_BYTES + 1024 + (int)sizeof(ScreenBars);
-    GB_CUDA(cudaFuncSetAttribute(i8_screen_pair_kernel<S>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
+    static bool attr_set[64];                                     // per device: one driver call, not one per launch
+    int dev = 0;
+    GB_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64 || !attr_set[dev]) {
+        GB_CUDA(cudaFuncSetAttribute(i8_screen_pair_kernel<S>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
+        if (dev >= 0 && dev < 64) attr_set[dev] = true;
+    }
     long long pairs_of_sms = sm_count() / 2;
     const long long max_items = (long long)n_ib * n_jb;
     if (pairs_of_sms > max_items) pairs_of_sms = max_items;
@@ -547,9 +553,12 @@ extern "C" int gmat_b200_epi_eff_i8p(const unsigned char *bed_dev, long long n, 
     const int n_slab = (int)((n + I8_SLAB - 1) / I8_SLAB);
     const int n_jb = (int)((m + 2 * I8_TJ - 1) / (2 * I8_TJ));
     Scratch sc(st);
-    ScreenScalars *scal = sc.get<ScreenScalars>(1);
-    float *oV = sc.get<float>((size_t)m), *cV = sc.get<float>((size_t)m), *tab32 = sc.get<float>(112);
-    GB_CHECK_ARG(scal && oV && cV && tab32, "out of device memory");
+    // one stream-ordered allocation for the call's small buffers: [scalars | tab32 (112) | oV (m) | cV (m)]
+    unsigned char *blob = sc.get<unsigned char>(256 + 512 + 8 * (size_t)m);
+    GB_CHECK_ARG(blob != nullptr, "out of device memory");
+    ScreenScalars *scal = reinterpret_cast<ScreenScalars *>(blob);
+    float *tab32 = reinterpret_cast<float *>(blob + 256);
+    float *oV = reinterpret_cast<float *>(blob + 768), *cV = oV + m;
     sc_setup_kernel<<<1, 128, 0, st>>>(stats_dev, (int)n, eff_cut, cut_table_dev, S, bits, tripled, scal, tab32,
                                        status_dev);
     GB_LAUNCH_CHECK();
@@ -572,10 +581,12 @@ extern "C" int gmat_b200_epi_eff_i8p(const unsigned char *bed_dev, long long n, 
         const int ni = (int)((n_i - c0 < chunk) ? n_i - c0 : chunk);
         const int n_ib = (ni + SC_TI - 1) / SC_TI, plane_rows = n_ib * SC_TI;
         Scratch csc(st);                                          // this chunk's buffers: freed (stream-ordered) per chunk
-        signed char *pu = csc.get<signed char>((size_t)S * plane_rows * ld);
-        float *tU = csc.get<float>((size_t)plane_rows), *oU = csc.get<float>((size_t)plane_rows);
-        int *tiles = csc.get<int>((size_t)2 * n_ib + 2);
-        GB_CHECK_ARG(pu && tU && oU && tiles, "out of device memory");
+        // one allocation per chunk: [planes | tU | oU | tiles]
+        const size_t plane_bytes = (size_t)S * plane_rows * ld;
+        signed char *pu = csc.get<signed char>(plane_bytes + 8 * (size_t)plane_rows + 4 * ((size_t)2 * n_ib + 2));
+        GB_CHECK_ARG(pu != nullptr, "out of device memory");
+        float *tU = reinterpret_cast<float *>(pu + plane_bytes), *oU = tU + plane_rows;
+        int *tiles = reinterpret_cast<int *>(oU + plane_rows);
         sc_planes_kernel<<<(unsigned)plane_rows, 256, 0, st>>>(g8U_dev, ld, ilist_dev + c0, ni, plane_rows, S, dig_dev,
                                                                lutU_dev, tU_dev, pu, tU, oU);
         GB_LAUNCH_CHECK();

@@ -97,7 +97,9 @@ class GenotypeStore(object):
 
     # -- statistics ------------------------------------------------------------------------------
     def n_missing(self):
-        return int(self.counts[:, 1].sum().item())
+        if getattr(self, "_n_missing", None) is None:
+            self._n_missing = int(self.counts[:, 1].sum().item())
+        return self._n_missing
 
     def lut(self, coding, freq_mode=FREQ_NUMPY):
         key = (coding, freq_mode)
@@ -173,9 +175,23 @@ def pack_pvp(pvp_dev):
     return packed
 
 
+_PINNED = {}
+
+
 def hits_to_numpy(hits_dev, count):
-    raw = hits_dev[:count].cpu().numpy()
-    return raw.view(HIT_DTYPE).reshape(-1)
+    """Device hit records -> host structured array.  Larger results go through a cached pinned staging buffer (a
+    pageable D2H of a few MB costs more than a whole screen call)."""
+    if count * 32 < (1 << 16):
+        raw = hits_dev[:count].cpu().numpy()
+        return raw.view(HIT_DTYPE).reshape(-1)
+    key = hits_dev.device.index
+    buf = _PINNED.get(key)
+    if buf is None or buf.shape[0] < count:
+        buf = torch.empty((max(int(count), 1 << 17), 32), dtype=torch.uint8, pin_memory=True)
+        _PINNED[key] = buf
+    buf[:count].copy_(hits_dev[:count], non_blocking=True)
+    torch.cuda.current_stream().synchronize()
+    return buf[:count].numpy().copy().view(HIT_DTYPE).reshape(-1)
 
 
 def alloc_hits(cap, device):
@@ -404,49 +420,108 @@ def epi_exact_pairs(store, lutU, lutV, py_dev, packed, pairs):
 
 def screen_engine(store):
     """Which engine runs the approximate screen: "i8" (int8 tensor-core prefilter + FP64 re-test of the survivors;
-    needs a store without missing calls) or "f64" (DMMA).  GMAT_B200_SCREEN_ENGINE = auto (default) | i8 | f64."""
+    stores with missing calls use the tripled integer coding, see ScreenOperands) or "f64" (DMMA).
+    GMAT_B200_SCREEN_ENGINE = auto (default) | i8 | f64."""
     want = os.environ.get("GMAT_B200_SCREEN_ENGINE", "auto").lower()
     if want not in ("auto", "i8", "f64"):
         raise ValueError("GMAT_B200_SCREEN_ENGINE must be auto, i8 or f64")
     if want == "f64":
         return "f64"
-    clean = store.n_missing() == 0
-    if want == "i8" and not clean:
-        raise ValueError("the int8 screen needs genotypes without missing calls")
-    return "i8" if clean else "f64"
+    fits = store.n < (29000 if store.n_missing() > 0 else 60000)   # int32 plane sums must stay FP32-exact
+    if want == "i8" and not fits:
+        raise ValueError("the int8 screen needs n < 60000 (29000 with missing calls)")
+    return "i8" if fits else "f64"
 
 
 LAST_SCREEN_ENGINE = None      # "i8" / "f64": what the last epi_eff call actually ran (tests, bench)
+LAST_SCREEN_NOTE = ""          # why, when the int8 path was asked for and declined
+
+
+class ScreenOperands(object):
+    """Operands of the int8 screen that depend only on (genotype store, Z'Py): the integer codes of every SNP per
+    coding ([m][ld] int8) with t = a . Z'Py, the digits of Z'Py and its statistics, and the candidate buffer.  Built
+    once and kept across screen calls -- the two directions of the AD screen, the stages of an _approx pipeline,
+    repeated calls -- instead of re-coding the whole store on every call.  ``tripled``: the store has missing calls;
+    the reference C screen does not impute (code 01 is the value 1/3, _remma_epi_eff_cpu.c:42), so the codes are 3a
+    in {0,1,3,6} / {0,1,3,0} and Z'Py is cut into three base-32 digits instead of two base-128 ones."""
+
+    CAND_CAP = 1 << 22
+
+    def __init__(self, store, py_dev):
+        self.store, self.py = store, py_dev.reshape(-1).contiguous()
+        self.tripled = 1 if store.n_missing() > 0 else 0
+        dev = store.device
+        self.ld = int(lib.gmat_b200_screen_ld(store.n))
+        self._ops = {}
+        self.dig = torch.empty((3, self.ld), dtype=torch.int8, device=dev)
+        self.stats = torch.empty((4,), dtype=torch.float64, device=dev)
+        check(lib.gmat_b200_screen_py(_p(self.py, "double *"), store.n, self.tripled, _p(self.dig, "signed char *"),
+                                      _p(self.stats, "double *"), _stream()), "gmat_b200_screen_py")
+        self.cand = torch.empty((self.CAND_CAP, 2), dtype=torch.int32, device=dev)
+
+    def operand(self, coding):
+        if coding not in self._ops:
+            st = self.store
+            g8 = torch.empty((st.m, self.ld), dtype=torch.int8, device=st.device)
+            t = torch.empty((st.m,), dtype=torch.float64, device=st.device)
+            check(lib.gmat_b200_screen_operand(_p(st.bed, "unsigned char *"), st.n, st.m, st.row_bytes, int(coding),
+                                               self.tripled, _p(self.py, "double *"), _p(g8, "signed char *"),
+                                               _p(t, "double *"), _stream()), "gmat_b200_screen_operand")
+            self._ops[coding] = (g8, t)
+        return self._ops[coding]
 
 
 def epi_eff(store, lutU, lutV, py_dev, ilist, flags, eff_cut, cut_table=None, binI=None, binJ=None,
-            cap=1 << 20, codings=None):
+            cap=1 << 20, codings=None, ops=None):
     """Approximate screen on device buffers; returns HIT_DTYPE array (unordered).  ``codings`` = (coding of lutU,
-    coding of lutV): with it (and a store without missing calls) the int8 tensor-core engine runs, see
-    screen_engine; without it the FP64 DMMA kernel."""
-    global LAST_SCREEN_ENGINE
+    coding of lutV): with it the int8 tensor-core engine runs (see screen_engine); without it the FP64 DMMA kernel.
+    ``ops``: a ScreenOperands of (store, py_dev) to reuse across calls (else the operands are built for this call)."""
+    global LAST_SCREEN_ENGINE, LAST_SCREEN_NOTE
     dev = store.device
     il = torch.as_tensor(np.ascontiguousarray(ilist, dtype=np.int64)).to(dev)
-    count = torch.zeros((1,), dtype=torch.int64, device=dev)
+    count = torch.zeros((3,), dtype=torch.int64, device=dev)       # [hits, stage-1 survivors, status]
     tab = bI = bJ = None
     if cut_table is not None:
         tab = torch.as_tensor(np.ascontiguousarray(cut_table, dtype=np.float64)).to(dev)
         bI = torch.as_tensor(np.ascontiguousarray(binI, dtype=np.int32)).to(dev)
         bJ = torch.as_tensor(np.ascontiguousarray(binJ, dtype=np.int32)).to(dev)
     which = screen_engine(store) if codings is not None else "f64"
+    LAST_SCREEN_NOTE = ""
     used = ffi.new("int *")
     while True:
         hits = alloc_hits(cap, dev)
         count.zero_()
-        if which == "i8":
+        if which == "i8" and ops is not None:
+            g8U, tU = ops.operand(codings[0])
+            g8V, tV = ops.operand(codings[1])
+            check(lib.gmat_b200_epi_eff_i8p(
+                _p(store.bed, "unsigned char *"), store.n, store.m, store.row_bytes,
+                _p(lutU, "double *"), _p(lutV, "double *"), _p(g8U, "signed char *"), _p(g8V, "signed char *"),
+                _p(tU, "double *"), _p(tV, "double *"), _p(ops.dig, "signed char *"), _p(ops.stats, "double *"),
+                ops.tripled, _p(py_dev, "double *"), _p(il, "long long *"), il.numel(), flags, float(eff_cut),
+                _p(tab, "double *"), _p(bI, "int *"), _p(bJ, "int *"),
+                ffi.cast("gmat_b200_hit *", hits.data_ptr()), cap,
+                ffi.cast("unsigned long long *", count.data_ptr()), _p(ops.cand, "int *"), ops.CAND_CAP,
+                ffi.cast("unsigned long long *", count.data_ptr() + 8), ffi.cast("int *", count.data_ptr() + 16),
+                _stream()), "gmat_b200_epi_eff_i8p")
+            cnt, _, status = (int(v) for v in count.tolist())       # the one synchronisation of the call
+            if status != 0:
+                LAST_SCREEN_NOTE = ("margin not small against the cut" if status == 1 else
+                                    "more survivors than the candidate buffer") + ": FP64 DMMA kernel"
+                which = "f64"
+                continue
+            LAST_SCREEN_ENGINE = "i8"
+        elif which == "i8":
             check(lib.gmat_b200_epi_eff_i8(
                 _p(store.bed, "unsigned char *"), store.n, store.m, store.row_bytes,
-                _p(lutU, "double *"), _p(lutV, "double *"), int(codings[0]), int(codings[1]), _p(py_dev, "double *"),
+                _p(lutU, "double *"), _p(lutV, "double *"), int(codings[0]), int(codings[1]),
+                1 if store.n_missing() > 0 else 0, _p(py_dev, "double *"),
                 _p(il, "long long *"), il.numel(), flags, float(eff_cut),
                 _p(tab, "double *"), _p(bI, "int *"), _p(bJ, "int *"),
                 ffi.cast("gmat_b200_hit *", hits.data_ptr()), cap,
                 ffi.cast("unsigned long long *", count.data_ptr()), used, _stream()), "gmat_b200_epi_eff_i8")
             LAST_SCREEN_ENGINE = "i8" if used[0] == 1 else "f64"
+            cnt = int(count[0].item())
         else:
             check(lib.gmat_b200_epi_eff(
                 _p(store.bed, "unsigned char *"), store.n, store.m, store.row_bytes,
@@ -456,7 +531,7 @@ def epi_eff(store, lutU, lutV, py_dev, ilist, flags, eff_cut, cut_table=None, bi
                 ffi.cast("gmat_b200_hit *", hits.data_ptr()), cap,
                 ffi.cast("unsigned long long *", count.data_ptr()), _stream()), "gmat_b200_epi_eff")
             LAST_SCREEN_ENGINE = "f64"
-        cnt = int(count.item())
+            cnt = int(count[0].item())
         if cnt <= cap:
             return hits_to_numpy(hits, cnt)
         cap = cnt

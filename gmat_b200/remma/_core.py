@@ -505,6 +505,7 @@ class Prepared(object):
             self.store = load_store(bed_file)                 # what the numpy paths see (imputed)
         self.model = DeviceModel.build(y, xmat, zmat, gmat_lst, var_com, self.store.device, scipy_inv=False)
         self.num_snp, self.num_id = self.store.m, self.store.n
+        self._screen_ops = None                               # int8 screen operands, shared by every screen call
 
     def pair_stats(self, pairs):
         k = self.kind
@@ -525,9 +526,12 @@ class Prepared(object):
         else:
             passes = [(ld, ld, 0, (D, D))]
         rows = []
+        if self._screen_ops is None and engine.screen_engine(st) == "i8":
+            self._screen_ops = engine.ScreenOperands(st, self.model.py)
         for d, (lu, lv, flags, codings) in enumerate(passes):
             h = engine.epi_eff(st, lu, lv, self.model.py, ilist, flags, eff_cut, cut_table, bin_i, bin_j,
-                               codings=codings)
+                               codings=codings, ops=self._screen_ops)
+            logging.info("Screen engine: %s %s", engine.LAST_SCREEN_ENGINE, engine.LAST_SCREEN_NOTE)
             swap = bool(flags & engine.EFF_SWAP)
             for s0, s1, e in zip(h['snp_0'].tolist(), h['snp_1'].tolist(), h['eff'].tolist()):
                 rows.append(((s1, s0, d) if swap else (s0, s1, d), s0, s1, e))

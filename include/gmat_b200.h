@@ -131,16 +131,45 @@ int gmat_b200_epi_eff(const unsigned char *bed_dev, long long n, long long m, lo
 
 /* The same screen with the INT8 tensor cores deciding which pairs are worth the FP64 arithmetic
  * (gmat_b200/csrc/screen_i8.cu).  Stage 1: eff = Q - o_j t_i - o_i (t_j - o_j P) with Q_ij = sum_k a_ik a_jk py_k
- * evaluated for every pair from two exact int8 GEMMs (py cut into two base-128 digits, tcgen05.mma cta_group::2
- * kind::i8) in FP32; pairs with |eff~| >= cut - margin survive, margin a rigorous bound of everything stage 1 drops.
+ * evaluated for every pair from S exact int8 GEMMs (py cut into S signed digits, tcgen05.mma cta_group::2 kind::i8)
+ * in FP32; pairs with |eff~| >= cut - margin survive, margin a rigorous bound of everything stage 1 drops.
  * Stage 2: eff of the survivors in FP64 from the LUT values (the arithmetic of gmat_b200_epi_eff) and the reference's
- * threshold -- so the reported set and the reported values are FP64 results.  codingU / codingV: the codings the two
- * LUTs were built for (GMAT_B200_CODING_ADD / _DOM); the store must not contain a missing call (callers use
- * gmat_b200_epi_eff then).  Falls back to gmat_b200_epi_eff by itself when the margin is not small against the cut
- * (e.g. eff_cut = 0) or the survivors do not fit its candidate buffer; *engine_used (optional) = 1 when the int8
- * path produced the result, 0 after a fallback.  Synchronises the stream (it reads two scalars back).            */
+ * threshold -- so the reported set and the reported values are FP64 results.
+ * `tripled` selects the integer coding: 0 = the store has no missing call (a in {0,1,2} / {0,1,0}, S = 2 base-128
+ * digits); 1 = missing calls present: the C screen does not impute, code 01 is the value 1/3
+ * (_remma_epi_eff_cpu.c:42), so both operands carry 3a in {0,1,3,6} / {0,1,3,0} and py is cut into S = 3 base-32
+ * digits (the products must stay int8).
+ *
+ * Prepared form (no host synchronisation inside; operands are caller-owned and can be kept across calls, the two
+ * directions of the AD screen and the stages of the _approx pipelines):
+ *   gmat_b200_screen_operand  g8[m][ld] integer codes of one coding (ld = gmat_b200_screen_ld(n)), t[m] = sum_k a_k py_k
+ *   gmat_b200_screen_py       dig[3][ld] digits of Z'Py, stats[4] = {max|py|, sum py, ..}
+ *   gmat_b200_epi_eff_i8p     the screen; cand_dev [cand_cap][2] ints + cand_count_dev: the survivor list of stage 1;
+ *                             status_dev[0] after the call: 0 = done on the int8 path (hits/count as in
+ *                             gmat_b200_epi_eff), 1 = the margin is not small against the cut (e.g. eff_cut = 0),
+ *                             2 = more survivors than cand_cap -- in both cases nothing was emitted and the caller
+ *                             runs gmat_b200_epi_eff (or retries with a larger candidate buffer).  The caller reads
+ *                             status together with the hit count: one synchronisation per call, made by the caller. */
+long long gmat_b200_screen_ld(long long n);
+int gmat_b200_screen_operand(const unsigned char *bed_dev, long long n, long long m, long long row_bytes,
+                             int coding, int tripled, const double *py_dev, signed char *g8_dev /* [m][ld] */,
+                             double *t_dev /* [m] */, void *stream);
+int gmat_b200_screen_py(const double *py_dev, long long n, int tripled, signed char *dig_dev /* [3][ld] */,
+                        double *stats_dev /* [4] */, void *stream);
+int gmat_b200_epi_eff_i8p(const unsigned char *bed_dev, long long n, long long m, long long row_bytes,
+                          const double *lutU_dev, const double *lutV_dev, const signed char *g8U_dev,
+                          const signed char *g8V_dev, const double *tU_dev, const double *tV_dev,
+                          const signed char *dig_dev, const double *stats_dev, int tripled,
+                          const double *py_dev, const long long *ilist_dev, long long n_i, int flags,
+                          double eff_cut, const double *cut_table_dev, const int *binI_dev,
+                          const int *binJ_dev, gmat_b200_hit *hits_dev, long long cap,
+                          unsigned long long *count_dev, int *cand_dev, long long cand_cap,
+                          unsigned long long *cand_count_dev, int *status_dev, void *stream);
+/* One-shot form: builds the operands in stream-ordered scratch, runs the prepared screen, reads the status back (it
+ * synchronises the stream once) and runs gmat_b200_epi_eff by itself when the int8 path declined; *engine_used
+ * (optional) = 1 when the int8 path produced the result, 0 after a fallback.                                    */
 int gmat_b200_epi_eff_i8(const unsigned char *bed_dev, long long n, long long m, long long row_bytes,
-                         const double *lutU_dev, const double *lutV_dev, int codingU, int codingV,
+                         const double *lutU_dev, const double *lutV_dev, int codingU, int codingV, int tripled,
                          const double *py_dev, const long long *ilist_dev, long long n_i, int flags, double eff_cut,
                          const double *cut_table_dev, const int *binI_dev, const int *binJ_dev,
                          gmat_b200_hit *hits_dev, long long cap, unsigned long long *count_dev,

@@ -21,7 +21,9 @@ def main():
     ap.add_argument("--only", default="i8,exact,eff,grm,decode,stats")
     ap.add_argument("--n", type=int, default=2000)
     ap.add_argument("--m", type=int, default=20000)
-    ap.add_argument("--first", type=int, default=64, help="first-SNPs of the exact-scan launch")
+    ap.add_argument("--first", type=int, default=64, help="first-SNPs of the FP64 exact-scan launch")
+    ap.add_argument("--i8-first", type=int, default=144, help="first-SNPs of the int8 scan (16 + 128: two launches)")
+    ap.add_argument("--missing", type=float, default=0.005, help="missing-call rate of the second screen store")
     ap.add_argument("--grm-n", type=int, default=4096)
     ap.add_argument("--grm-m", type=int, default=65536)
     ap.add_argument("--dec-n", type=int, default=5000)
@@ -77,10 +79,12 @@ def main():
         lut = store.lut(engine.ADD)
         pvp = pvp.contiguous()
         sc = engine.I8Exact(store, lut, lut, engine.ADD, py, pvp)
-        il = np.unique((np.linspace(0, m - 10, 8).astype(np.int64)[:, None] + np.arange(8)[None, :]).ravel())
+        nblk = max(1, args.i8_first // 8)
+        il = np.unique((np.linspace(0, m - 10, nblk).astype(np.int64)[:, None] + np.arange(8)[None, :]).ravel())
         pairs = int(np.sum(m - 1 - il))
         t = timed(lambda: sc.scan(il, engine.PAIRS_UPPER, 30.0))
         out["i8"] = {"seconds": t, "pairs": pairs, "pairs_per_s": pairs / t, "planes": sc.n_planes,
+                     "first_snps": len(il), "rechecked": sc.last_rechecked,
                      "int8_tops_algorithmic": pairs * sc.n_planes * float(n) * (n + 1) / t / 1e12}
         del sc
     if "eff" in only:
@@ -90,12 +94,31 @@ def main():
         t = timed(lambda: engine.epi_eff(store, la, la, py, full, 0, 1e30))
         out["eff"] = {"seconds": t, "pairs": pairs, "pairs_per_s": pairs / t,
                       "tflops_algorithmic": pairs * 2.0 * n / t / 1e12}
-        # the int8 tensor-core screen (prefilter + FP64 re-test) at a cut that keeps ~1e-5 of the pairs
+        # the int8 tensor-core screen (prefilter + FP64 re-test) at a cut that keeps ~1e-5 of the pairs, on prepared
+        # operands; then the same store with missing calls (tripled coding, three base-32 planes)
         smp = engine.epi_eff(store, la, la, py, np.arange(0, m - 1, 97, dtype=np.int64), 0, 0.0)
         cut = float(np.quantile(np.abs(smp["eff"]), 1.0 - 1e-5))
-        t = timed(lambda: engine.epi_eff(store, la, la, py, full, 0, cut, codings=(engine.ADD, engine.ADD)))
+        ops = engine.ScreenOperands(store, py)
+        t = timed(lambda: engine.epi_eff(store, la, la, py, full, 0, cut, codings=(engine.ADD, engine.ADD), ops=ops))
         out["eff_i8"] = {"seconds": t, "pairs": pairs, "pairs_per_s": pairs / t, "engine": engine.LAST_SCREEN_ENGINE,
                          "int8_tops_algorithmic": pairs * 4.0 * n / t / 1e12}
+        del ops
+        if args.missing > 0:
+            bed = store.bed.clone()
+            gen2 = torch.Generator(device=dev)
+            gen2.manual_seed(9)
+            hole = torch.rand(bed.shape, generator=gen2, device=dev) < args.missing * 4
+            slot = torch.randint(0, 4, bed.shape, generator=gen2, device=dev, dtype=torch.uint8)
+            clear = (~(torch.tensor(3, dtype=torch.uint8, device=dev) << (2 * slot))) & 0xFF
+            bed = torch.where(hole, (bed & clear) | (torch.tensor(1, dtype=torch.uint8, device=dev) << (2 * slot)), bed)
+            stm = engine.GenotypeStore.from_device_payload(bed, n)
+            lm = stm.lut(engine.ADD, engine.FREQ_CLOOP)
+            opm = engine.ScreenOperands(stm, py)
+            t = timed(lambda: engine.epi_eff(stm, lm, lm, py, full, 0, cut, codings=(engine.ADD, engine.ADD), ops=opm))
+            out["eff_i8_missing"] = {"seconds": t, "pairs": pairs, "pairs_per_s": pairs / t,
+                                     "engine": engine.LAST_SCREEN_ENGINE, "missing_calls": stm.n_missing(),
+                                     "int8_tops_algorithmic": pairs * 6.0 * n / t / 1e12}
+            del opm, stm
     if "decode" in only:
         n2, m2 = args.dec_n, args.dec_m
         st2 = engine.GenotypeStore.from_device_payload(synth.device_payload(n2, m2, 12, dev, engine.row_stride(n2)), n2)

@@ -114,13 +114,56 @@ def test_i8_screen_maf_table_small_cuts_and_forced_engines(eng, tmp_path, monkey
     monkeypatch.setenv("GMAT_B200_SCREEN_ENGINE", "f64")
     eng.epi_eff(store, la, la, pyd, lst, 0, base, codings=(eng.ADD, eng.ADD))
     assert eng.LAST_SCREEN_ENGINE == "f64"
-    # missing calls: auto uses the FP64 kernel, forcing i8 is refused
+    # missing calls: the int8 engine runs them too (tripled integer coding, three base-32 digit planes)
     monkeypatch.delenv("GMAT_B200_SCREEN_ENGINE")
     synth.write_dataset(prefix + "m", n, 90, seed=6, missing_rate=0.02)
     st2 = eng.GenotypeStore(prefix + "m")
     l2 = st2.lut(eng.ADD, eng.FREQ_CLOOP)
-    eng.epi_eff(st2, l2, l2, pyd, np.arange(89), 0, base, codings=(eng.ADD, eng.ADD))
-    assert eng.LAST_SCREEN_ENGINE == "f64"
-    monkeypatch.setenv("GMAT_B200_SCREEN_ENGINE", "i8")
-    with pytest.raises(ValueError):
-        eng.epi_eff(st2, l2, l2, pyd, np.arange(89), 0, base, codings=(eng.ADD, eng.ADD))
+    r64 = eng.epi_eff(st2, l2, l2, pyd, np.arange(89), 0, base)
+    r8 = eng.epi_eff(st2, l2, l2, pyd, np.arange(89), 0, base, codings=(eng.ADD, eng.ADD))
+    assert eng.LAST_SCREEN_ENGINE == "i8" and key(r64) == key(r8)
+
+
+@pytest.mark.parametrize("kind", ["AA", "DD", "AD"])
+@pytest.mark.parametrize("n,m,rate", [(131, 77, 0.05), (300, 600, 0.01), (520, 300, 0.002), (1100, 260, 0.02)])
+def test_i8_screen_with_missing_calls(eng, tmp_path, kind, n, m, rate):
+    """Stores WITH missing calls (what real PLINK files look like): the reference C screen does not impute, code 01 is
+    the value 1/3 (_remma_epi_eff_cpu.c:42).  The int8 engine carries 3a in {0,1,3,6} and three base-32 digit planes of
+    Z'Py: same hit set as the FP64 DMMA engine and as the reference's own C (oracle/_ref), FP64 effects; one-shot and
+    prepared (ScreenOperands, reused across the passes) forms agree."""
+    import torch
+    import synth
+    from oracle import ref_harness
+    prefix = str(tmp_path / "miss")
+    synth.write_dataset(prefix, n, m, seed=5 * n + m, missing_rate=rate)
+    store = eng.GenotypeStore(prefix)
+    assert store.n_missing() > 0
+    rng = np.random.Generator(np.random.PCG64(n + 3 * m))
+    py = rng.normal(size=n) * rng.choice([1.0, 10.0], size=n)
+    py -= py.mean()
+    pyd = torch.as_tensor(py).cuda()
+    lst = np.array([i for i in range(m - 1) if i % 5 != 2], dtype=np.int64)
+    ops = eng.ScreenOperands(store, pyd)
+    assert ops.tripled == 1
+    key = lambda h: h["snp_0"].astype(np.int64) * m + h["snp_1"]
+    rows = {}
+    for lu, lv, flags, codings in _passes(eng, store, kind):
+        every = eng.epi_eff(store, lu, lv, pyd, lst, flags, 0.0)
+        cut = _mid_gap_cut(np.abs(every["eff"]), 0.98)
+        ref = eng.epi_eff(store, lu, lv, pyd, lst, flags, cut)
+        one = eng.epi_eff(store, lu, lv, pyd, lst, flags, cut, codings=codings)
+        assert eng.LAST_SCREEN_ENGINE == "i8"
+        pre = eng.epi_eff(store, lu, lv, pyd, lst, flags, cut, codings=codings, ops=ops)
+        assert eng.LAST_SCREEN_ENGINE == "i8"
+        ref, one, pre = ref[np.argsort(key(ref))], one[np.argsort(key(one))], pre[np.argsort(key(pre))]
+        assert len(ref) > 0 and np.array_equal(key(ref), key(one)) and np.array_equal(key(ref), key(pre))
+        np.testing.assert_allclose(one["eff"], ref["eff"], rtol=1e-12, atol=1e-13 * np.abs(ref["eff"]).max())
+        assert np.array_equal(one["eff"], pre["eff"])
+        rows[flags] = (cut, ref)
+    if kind != "AD" and ref_harness.ref_so_available():
+        # the reference's own C on the same files
+        cut, ref = rows[0]
+        out = str(tmp_path / "ref_screen.txt")
+        oracle.ref_screen_file(prefix, kind, lst, py.reshape(-1, 1), cut, out)
+        want = {(int(r[0]), int(r[1])) for r in (line.split() for line in open(out).read().splitlines()[1:])}
+        assert want == set(zip(ref["snp_0"].tolist(), ref["snp_1"].tolist()))
