@@ -878,22 +878,32 @@ def extras(engine, torch, synth, store, model, lut, args, prefix, pymat, i8_peak
         # rank-one corrections, gram_i8.cu), then the FP64 DMMA kernel (grm.cu) north_star names, same output buffer
         which = engine.grm_engine(st2)
         t = timed(lambda: engine.grm(st2, engine.ADD, 1.0, 0.001, out=kin, which=which), reps=2)
+        ops_n = float(n2) * (n2 + 1) * m2
         out["agmat"] = {"engine": which,
                         "tflops_full_gemm_convention_2n2m": 2.0 * n2 * n2 * m2 / t / 1e12,
-                        "tflops_algorithmic_n(n+1)m": float(n2) * (n2 + 1) * m2 / t / 1e12,
+                        "tflops_algorithmic_n(n+1)m": ops_n / t / 1e12,
                         "seconds": t, "workload": "agmat GRM, synthetic n=%d x m=%d generated in HBM "
                                                   "(BASELINE configs[1])" % (n2, m2)}
-        if which == "i8":
+        if which in ("f4", "i8"):
+            # FP4 (tcgen05 kind::mxf4) issues at twice the int8 rate: its roofline denominator is 2 x the int8 issue
+            # rate measured at the start of the run (the probe library has no FP4 microbenchmark)
+            pk = i8_peak * (2.0 if which == "f4" else 1.0)
             out["agmat"]["roofline"] = {
-                "bound": "tensor", "unit": "TOP/s", "achieved": float(n2) * (n2 + 1) * m2 / t / 1e12,
-                "peak": i8_peak, "frac": float(n2) * (n2 + 1) * m2 / t / 1e12 / i8_peak,
-                "note": "n(n+1)m int8 ops (lower triangle of G G', 2 ops per MAC) / the whole call (2-bit -> int8 "
-                        "transpose, i8_gram_pair_kernel, FP64 corrections); same denominator as the headline"}
+                "bound": "tensor", "unit": "TOP/s", "achieved": ops_n / t / 1e12, "peak": pk, "frac": ops_n / t / 1e12 / pk,
+                "frac_of_int8_peak": ops_n / t / 1e12 / i8_peak,
+                "note": "n(n+1)m ops (lower triangle of G G', 2 ops per MAC) / the whole call (2-bit -> packed operand "
+                        "transpose, the GEMM kernel, corrections); peak = the int8 issue rate of the headline"
+                        + (" x 2 (E2M1 operands, kind::mxf4)" if which == "f4" else "")}
+            if which == "f4":
+                t8 = timed(lambda: engine.grm(st2, engine.ADD, 1.0, 0.001, out=kin, which="i8"), reps=1)
+                out["agmat"]["i8_engine"] = {"seconds": t8, "tflops_algorithmic_n(n+1)m": ops_n / t8 / 1e12,
+                                             "frac_of_int8_peak": ops_n / t8 / 1e12 / i8_peak,
+                                             "kernel": "i8_gram_pair_kernel (tcgen05 kind::i8)"}
             t64 = timed(lambda: engine.grm(st2, engine.ADD, 1.0, 0.001, out=kin, which="f64"), reps=1)
             out["agmat"]["f64_engine"] = {"seconds": t64,
-                                          "tflops_algorithmic_n(n+1)m": float(n2) * (n2 + 1) * m2 / t64 / 1e12,
+                                          "tflops_algorithmic_n(n+1)m": ops_n / t64 / 1e12,
                                           "fp64_peak_tflops": peak,
-                                          "frac": float(n2) * (n2 + 1) * m2 / t64 / 1e12 / peak,
+                                          "frac": ops_n / t64 / 1e12 / peak,
                                           "kernel": "grm_kernel (FP64 DMMA, 2-bit codes staged by TMA)"}
         if args.agmat_e2e:
             # the public call on files: agmat(bed_file) = .bed/.bim/.fam read + H2D + counts + GRM kernel + D2H +

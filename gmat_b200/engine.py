@@ -538,18 +538,24 @@ def epi_eff(store, lutU, lutV, py_dev, ilist, flags, eff_cut, cut_table=None, bi
 
 
 def grm_engine(store, snp_begin=0, snp_end=None):
-    """Which kernel builds the GRM: "i8" (one exact int8 tensor-core GEMM; needs a SNP range without missing
-    genotypes) or "f64" (DMMA).  GMAT_B200_GRM_ENGINE = auto (default) | i8 | f64."""
+    """Which kernel builds the GRM: "f4" (one exact FP4 tensor-core GEMM, tcgen05 kind::mxf4; needs a SNP range
+    without missing genotypes, shorter than 2^21 SNPs), "i8" (the same as an int8 GEMM) or "f64" (DMMA).
+    GMAT_B200_GRM_ENGINE = auto (default) | f4 | i8 | f64."""
     want = os.environ.get("GMAT_B200_GRM_ENGINE", "auto").lower()
-    if want not in ("auto", "i8", "f64"):
-        raise ValueError("GMAT_B200_GRM_ENGINE must be auto, i8 or f64")
+    if want not in ("auto", "f4", "i8", "f64"):
+        raise ValueError("GMAT_B200_GRM_ENGINE must be auto, f4, i8 or f64")
     if want == "f64":
         return "f64"
     snp_end = store.m if snp_end is None else snp_end
     clean = int(store.counts[snp_begin:snp_end, 1].sum().item()) == 0
-    if want == "i8" and not clean:
-        raise ValueError("the int8 GRM kernel needs genotypes without missing calls")
-    return "i8" if clean else "f64"
+    if want in ("i8", "f4") and not clean:
+        raise ValueError("the tensor-core GRM kernels need genotypes without missing calls")
+    if not clean:
+        return "f64"
+    short = snp_end - snp_begin < (1 << 21)
+    if want == "f4" and not short:
+        raise ValueError("the FP4 GRM kernel needs a SNP range shorter than 2^21")
+    return "i8" if (want == "i8" or not short) else "f4"
 
 
 def grm(store, coding, scale, small_val, snp_begin=0, snp_end=None, out=None, accumulate=False, which=None):
@@ -560,10 +566,11 @@ def grm(store, coding, scale, small_val, snp_begin=0, snp_end=None, out=None, ac
         out = torch.zeros((store.n, store.n), dtype=torch.float64, device=store.device) if accumulate \
             else torch.empty((store.n, store.n), dtype=torch.float64, device=store.device)
     which = grm_engine(store, snp_begin, snp_end) if which is None else which
-    if which == "i8":
-        check(lib.gmat_b200_grm_i8(_p(store.bed, "unsigned char *"), store.n, store.m, store.row_bytes,
-                                   _p(lut, "double *"), coding, snp_begin, snp_end, float(scale), float(small_val),
-                                   1 if accumulate else 0, _p(out, "double *"), _stream()), "gmat_b200_grm_i8")
+    if which in ("i8", "f4"):
+        fn = lib.gmat_b200_grm_i8 if which == "i8" else lib.gmat_b200_grm_f4
+        check(fn(_p(store.bed, "unsigned char *"), store.n, store.m, store.row_bytes,
+                 _p(lut, "double *"), coding, snp_begin, snp_end, float(scale), float(small_val),
+                 1 if accumulate else 0, _p(out, "double *"), _stream()), "gmat_b200_grm_" + which)
         return out
     check(lib.gmat_b200_grm(_p(store.bed, "unsigned char *"), store.n, store.m, store.row_bytes,
                             _p(lut, "double *"), snp_begin, snp_end, float(scale), float(small_val),

@@ -275,6 +275,16 @@ int gmat_b200_grm_i8(const unsigned char *bed_dev, long long n, long long m, lon
                      const double *lut_dev, int coding, long long snp_begin, long long snp_end,
                      double scale, double small_val, int accumulate, double *K_dev, void *stream);
 
+/* The same GRM with FP4 operands (gmat_b200/csrc/gram_i8.cu, f4_gram_pair_kernel): the entries of G are {0, 1, 2},
+ * all exactly representable in E2M1, so G G' is one exact tcgen05.mma kind::mxf4 GEMM (unit block scales, FP32
+ * accumulation exact below 2^24) at twice the int8 MMA rate on half the operand bytes; c_k = sum_s o_s a_ks comes out
+ * of the same GEMM from 18 extra rows holding the base-8 digits of o_s.  Same arguments and semantics as
+ * gmat_b200_grm_i8; the SNP range must not contain a missing genotype and must be shorter than 2^21 SNPs (callers use
+ * gmat_b200_grm_i8 / gmat_b200_grm beyond that).                                                                 */
+int gmat_b200_grm_f4(const unsigned char *bed_dev, long long n, long long m, long long row_bytes,
+                     const double *lut_dev, int coding, long long snp_begin, long long snp_end,
+                     double scale, double small_val, int accumulate, double *K_dev, void *stream);
+
 /* Host text writer, byte-identical to np.savetxt(path, mat) as used by output_mat (gmat/gmatrix/gmatrix.py:10-14:
  * '%.18e', ' ' delimiter, '\n'): rows formatted in parallel by `threads` host threads (<= 0: all).  No GPU work. */
 int gmat_b200_savetxt_host(const char *path, const double *mat /* HOST [rows][cols] */, long long rows,

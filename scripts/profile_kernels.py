@@ -134,7 +134,7 @@ def main():
         st2 = engine.GenotypeStore.from_device_payload(synth.device_payload(n2, m2, 13, dev, engine.row_stride(n2)), n2)
         st2.lut(engine.ADD)
         kin = torch.empty((n2, n2), dtype=torch.float64, device=dev)
-        for which in ("i8", "f64"):                      # int8 tensor-core GEMM (default engine), FP64 DMMA kernel
+        for which in ("f4", "i8", "f64"):                # FP4 (default) and int8 tensor-core GEMMs, FP64 DMMA kernel
             t = timed(lambda: engine.grm(st2, engine.ADD, 1.0, 0.001, out=kin, which=which))
             out["grm_" + which] = {"seconds": t, "tflops_algorithmic_n(n+1)m": float(n2) * (n2 + 1) * m2 / t / 1e12}
     print(json.dumps(out))

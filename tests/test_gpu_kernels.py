@@ -259,10 +259,12 @@ def test_exact_scan_hit_buffer_overflow_retry(eng, tmp_path):
 
 
 # ------------------------------------------------------------------------------------------ GRM
-@pytest.mark.parametrize("which", ["i8", "f64"])
-@pytest.mark.parametrize("n,m", [(131, 300), (128, 16), (260, 1000), (5, 3), (513, 130)])
+@pytest.mark.parametrize("which", ["f4", "i8", "f64"])
+@pytest.mark.parametrize("n,m", [(131, 300), (128, 16), (260, 1000), (5, 3), (513, 130), (250, 513), (495, 257)])
 def test_grm_vs_oracle_synthetic(eng, tmp_path, monkeypatch, n, m, which):
-    """Both GRM kernels (int8 tensor cores: gram_i8.cu; FP64 DMMA: grm.cu) against the numpy oracle."""
+    """The three GRM kernels (FP4 and int8 tensor cores: gram_i8.cu; FP64 DMMA: grm.cu) against the numpy oracle;
+    n = 250 / 495: the 18 digit rows of the FP4 kernel cross / open a 256-row tile, m = 513 / 257: ragged last
+    256-SNP slab."""
     from gmat_b200.gmatrix.gmatrix import grm_device
     monkeypatch.setenv("GMAT_B200_GRM_ENGINE", which)
     prefix, _ = _dataset(tmp_path, n, m, seed=n + 3 * m)
@@ -284,7 +286,7 @@ def test_grm_vs_oracle_synthetic(eng, tmp_path, monkeypatch, n, m, which):
     assert np.abs(acc.cpu().numpy() / scale - want).max() <= RTOL * np.abs(want).max()
 
 
-@pytest.mark.parametrize("which", ["i8", "f64"])
+@pytest.mark.parametrize("which", ["f4", "i8", "f64"])
 def test_grm_streamk_many_tiles_reproducible(eng, tmp_path, monkeypatch, which):
     """n large enough for more tiles than SMs (the equal-range stream-K split with atomically added partial tiles):
     parity with the oracle and bit-identical results run to run (FP64: a tile never has more than two parts;
@@ -323,22 +325,27 @@ def test_grm_i8_wave_schedule_and_chunked_corrections(eng, monkeypatch, n, m):
     scale = np.sum(2.0 * freq * (1.0 - freq))
     want = x @ x.T / scale
     want[np.diag_indices(n)] *= 1.001
-    monkeypatch.setenv("GMAT_B200_GRM_ENGINE", "i8")
-    kin, s = grm_device(store, eng.ADD)
-    got = kin.cpu().numpy()
-    assert abs(s - scale) <= 1e-12 * scale
-    assert np.abs(got - want).max() <= RTOL * np.abs(want).max()
-    assert np.array_equal(got, got.T)
-    again, _ = grm_device(store, eng.ADD)
-    assert np.array_equal(again.cpu().numpy(), got)
+    results = {}
+    for which in ("i8", "f4"):
+        monkeypatch.setenv("GMAT_B200_GRM_ENGINE", which)
+        kin, s = grm_device(store, eng.ADD)
+        got = kin.cpu().numpy()
+        assert abs(s - scale) <= 1e-12 * scale
+        assert np.abs(got - want).max() <= RTOL * np.abs(want).max(), which
+        assert np.array_equal(got, got.T)
+        again, _ = grm_device(store, eng.ADD)
+        assert np.array_equal(again.cpu().numpy(), got)
+        results[which] = got
+    # both tensor-core kernels form the same exact integer sums; they differ only in how c_k is rounded
+    assert np.abs(results["f4"] - results["i8"]).max() <= 1e-13 * np.abs(want).max()
     monkeypatch.setenv("GMAT_B200_GRM_ENGINE", "f64")
     ref, _ = grm_device(store, eng.ADD)
     assert np.abs(ref.cpu().numpy() - got).max() <= 1e-12 * np.abs(want).max()
 
 
 def test_grm_engine_selection_and_missing_calls(eng, tmp_path, monkeypatch):
-    """auto = int8 kernel for SNP ranges without a missing call, DMMA kernel otherwise (same result as forcing f64);
-    forcing i8 on data with missing calls is refused."""
+    """auto = FP4 tensor-core kernel for SNP ranges without a missing call, DMMA kernel otherwise (same result as
+    forcing f64); forcing a tensor-core kernel on data with missing calls is refused."""
     from gmat_b200.gmatrix.gmatrix import grm_device
     prefix, _ = _dataset(tmp_path, 90, 150, seed=4, missing=0.02)
     store = eng.GenotypeStore(prefix)
@@ -346,7 +353,7 @@ def test_grm_engine_selection_and_missing_calls(eng, tmp_path, monkeypatch):
     assert eng.grm_engine(store) == "f64"
     clean = [s for s in range(150) if int(store.counts[s, 1]) == 0]
     if clean:
-        assert eng.grm_engine(store, clean[0], clean[0] + 1) == "i8"
+        assert eng.grm_engine(store, clean[0], clean[0] + 1) == "f4"
     a, _ = grm_device(store, eng.ADD)
     monkeypatch.setenv("GMAT_B200_GRM_ENGINE", "f64")
     b, _ = grm_device(store, eng.ADD)
