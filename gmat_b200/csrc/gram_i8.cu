@@ -287,25 +287,50 @@ __global__ void i8_rowsum_kernel(const double *__restrict__ part, int chunks, in
     c_out[k] = t;
 }
 
-__global__ void i8_gram_finish_kernel(const int *__restrict__ S, int np, const double *__restrict__ c, int n,
-                                      double scale, double small_val, int accumulate, double *__restrict__ K) {
-    const long long total = (long long)n * n;
+// K = ((S - c 1' - 1 c') + d) / scale with the diagonal inflation, from the lower triangle of S, written symmetrically.
+// One block per 32 x 32 tile of the lower block triangle: S is read coalesced ONCE (the first version read S[l][k] for
+// the upper half: a column walk, 8 x the sectors), both K[k][l] and its mirror K[l][k] leave as full rows through a
+// shared-memory transpose; the same expression, (S_hl - c_h) - c_l + d with h >= l, gives both entries of a pair.
+__global__ void __launch_bounds__(256)
+i8_gram_finish_kernel(const int *__restrict__ S, int np, const double *__restrict__ c, int n,
+                      double scale, double small_val, int accumulate, double *__restrict__ K) {
+    __shared__ double t[32][33];
+    int bk = 0, rem = blockIdx.x;                                   // blockIdx.x -> (bk, bl), bl <= bk
+    {
+        bk = (int)((sqrtf(8.0f * (float)rem + 1.0f) - 1.0f) * 0.5f);
+        while ((long long)(bk + 1) * (bk + 2) / 2 <= rem) ++bk;
+        while ((long long)bk * (bk + 1) / 2 > rem) --bk;
+        rem -= bk * (bk + 1) / 2;
+    }
+    const int bl = rem, k0 = bk * 32, l0 = bl * 32;
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
     const double d = c[n];
-    for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
-         idx += (long long)gridDim.x * blockDim.x) {
-        const int k = (int)(idx / n), l = (int)(idx % n);
-        const int hi = k > l ? k : l, lo = k > l ? l : k;
-        double v = ((double)S[(size_t)hi * np + lo] - c[hi]) - c[lo] + d;     // same expression for (k,l) and (l,k)
-        if (accumulate) {
-            K[idx] += v;
-        } else {
-            v /= scale;
-            if (k == l) v += v * small_val;
-            K[idx] = v;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const int k = k0 + ty + 8 * i, l = l0 + tx;
+        double v = 0.0;
+        if (k < n && l <= k) {
+            v = ((double)S[(size_t)k * np + l] - c[k]) - c[l] + d;
+            if (!accumulate) {
+                v /= scale;
+                if (k == l) v += v * small_val;
+            }
+            const size_t idx = (size_t)k * n + l;
+            if (accumulate) K[idx] += v; else K[idx] = v;
+        }
+        t[ty + 8 * i][tx] = v;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {                                   // the mirror: row l0 + .., column k0 + ..
+        const int l = l0 + ty + 8 * i, k = k0 + tx;
+        if (k < n && l < k) {
+            const size_t idx = (size_t)l * n + k;
+            const double v = t[tx][ty + 8 * i];
+            if (accumulate) K[idx] += v; else K[idx] = v;
         }
     }
 }
-
 
 // =====================================================================================================================
 // The same GRM with FP4 operands: tcgen05.mma kind::mxf4 (block-scaled E2M1, unit scales), twice the int8 MMA rate.
@@ -493,10 +518,32 @@ f4_gram_pair_kernel(const __grid_constant__ CUtensorMap map_gt, const GramParams
 // kernel's 32-byte pieces made DRAM fetch 4.9 GB for a 1.25 GB store); then, for each of the four 128-id quarters,
 // thread (sg = lane, ig = warp) turns the code words of 8 SNPs x 16 ids into 16 words "8 SNPs of one id" and stores
 // them conflict-free (row stride 33 words), and full 128-byte lines of Gt4 are written, 8 lanes per id row.
-// `table`: nibble[code] (E2M1: 0 -> 0x0, 1 -> 0x2, 2 -> 0x4).
+// The 8 x 16 block is transposed WORD-PARALLEL: each code word is widened to nibble fields (three shift-or-mask
+// steps), the E2M1 nibble of every code is formed by bit logic on all eight fields at once (code 10 -> 0x2 = 1.0,
+// code 11 -> 0x4 = 2.0 additive / 0 dominance, codes 00 and 01 -> 0), and the 8 x 8 nibble matrix is transposed by a
+// three-stage butterfly -- ~3 instructions per genotype instead of the ~7 of a per-nibble extract / look-up / insert.
+__device__ __forceinline__ unsigned f4_expand8(unsigned x16, bool dominance) {
+    unsigned x = x16 & 0xFFFFu;                                     // eight 2-bit codes
+    x = (x | (x << 8)) & 0x00FF00FFu;
+    x = (x | (x << 4)) & 0x0F0F0F0Fu;
+    x = (x | (x << 2)) & 0x33333333u;                              // each code in the low 2 bits of its nibble
+    const unsigned h = (x >> 1) & 0x11111111u, l = x & 0x11111111u;
+    const unsigned one = (h & ~l) << 1;                             // code 10 -> nibble 0x2
+    return dominance ? one : (one | ((h & l) << 2));                // code 11 -> nibble 0x4
+}
+__device__ __forceinline__ void f4_transpose8(unsigned (&a)[8]) {   // 8 x 8 nibble transpose, rows = words
+#pragma unroll
+    for (int i = 0; i < 4; ++i) { const unsigned t = ((a[i] >> 16) ^ a[i + 4]) & 0x0000FFFFu; a[i + 4] ^= t; a[i] ^= t << 16; }
+#pragma unroll
+    for (int i = 0; i < 8; i += 4)
+#pragma unroll
+        for (int j = 0; j < 2; ++j) { const unsigned t = ((a[i + j] >> 8) ^ a[i + j + 2]) & 0x00FF00FFu; a[i + j + 2] ^= t; a[i + j] ^= t << 8; }
+#pragma unroll
+    for (int i = 0; i < 8; i += 2) { const unsigned t = ((a[i] >> 4) ^ a[i + 1]) & 0x0F0F0F0Fu; a[i + 1] ^= t; a[i] ^= t << 4; }
+}
 __global__ void __launch_bounds__(256)
 f4_dosage_t_kernel(const unsigned char *__restrict__ bed, int n, long long row_bytes, long long s0, long long s1,
-                   unsigned table, unsigned char *__restrict__ gt, long long mld) {
+                   int dominance, unsigned char *__restrict__ gt, long long mld) {
     extern __shared__ unsigned f4_smem[];
     // raw: the code words of SNP row r live at [r & 7][r >> 3][0..31] with plane stride 1060 and row stride 33 words:
     // both the row-wise writes of pass 1 and the "8 rows of one word column" reads of pass 2 are bank-conflict free
@@ -521,15 +568,19 @@ f4_dosage_t_kernel(const unsigned char *__restrict__ bed, int n, long long row_b
     const int sg = threadIdx.x & 31, ig = threadIdx.x >> 5;       // SNPs 8 sg .. 8 sg + 7, ids 16 ig .. 16 ig + 15 of a quarter
     for (int quarter = 0; quarter < 4; ++quarter) {
         const int k0 = kblk + quarter * 128;
-        unsigned w[8];
+        unsigned lo[8], hi[8];                                     // rows = SNPs, nibble columns = ids 0..7 / 8..15
 #pragma unroll
-        for (int q = 0; q < 8; ++q) w[q] = raw[q * RAWQ + sg * 33 + quarter * 8 + ig];
+        for (int q = 0; q < 8; ++q) {
+            const unsigned w = raw[q * RAWQ + sg * 33 + quarter * 8 + ig];
+            lo[q] = f4_expand8(w, dominance != 0);
+            hi[q] = f4_expand8(w >> 16, dominance != 0);
+        }
+        f4_transpose8(lo);                                         // rows = ids, nibble columns = SNPs
+        f4_transpose8(hi);
 #pragma unroll
-        for (int e = 0; e < 16; ++e) {
-            unsigned o = 0;
-#pragma unroll
-            for (int q = 0; q < 8; ++q) o |= ((table >> (4 * ((w[q] >> (2 * e)) & 3u))) & 0xfu) << (4 * q);
-            tile[16 * ig + e][sg] = (k0 + 16 * ig + e < n) ? o : 0u;
+        for (int e = 0; e < 8; ++e) {
+            tile[16 * ig + e][sg] = (k0 + 16 * ig + e < n) ? lo[e] : 0u;
+            tile[16 * ig + 8 + e][sg] = (k0 + 16 * ig + 8 + e < n) ? hi[e] : 0u;
         }
         __syncthreads();
 #pragma unroll
@@ -652,7 +703,11 @@ extern "C" int gmat_b200_grm_i8(const unsigned char *bed_dev, long long n, long 
         count_launch();
         i8_rowsum_kernel<<<(unsigned)((n + 256) / 256), 256, 0, st>>>(part, chunks, (int)n, c);
         count_launch();
-        i8_gram_finish_kernel<<<sm_count() * 8, 256, 0, st>>>(S, np, c, (int)n, scale, small_val, accumulate, K_dev);
+        {
+            const long long nb32 = (n + 31) / 32;
+            i8_gram_finish_kernel<<<(unsigned)(nb32 * (nb32 + 1) / 2), 256, 0, st>>>(S, np, c, (int)n, scale, small_val,
+                                                                                    accumulate, K_dev);
+        }
         count_launch();
         cudaError_t e = cudaGetLastError();
         if (e != cudaSuccess) { set_error("kernel launch failed: %s", cudaGetErrorString(e)); rc = GMAT_B200_ERR_CUDA; }
@@ -687,7 +742,6 @@ extern "C" int gmat_b200_grm_f4(const unsigned char *bed_dev, long long n, long 
     GB_CUDA(cudaMemsetAsync(S, 0, (size_t)np * np * sizeof(int), st));
     int rc = GMAT_B200_OK;
     if (ms > 0) {
-        const unsigned table = coding == GMAT_B200_CODING_DOM ? 0x0200u : 0x4200u;   // nibble[code]: E2M1 of {0,0,1,2} / {0,0,1,0}
         const int smem_t = (8 * 1060 + 128 * 33) * 4;
         cudaError_t e = cudaFuncSetAttribute(f4_dosage_t_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_t);
         if (e != cudaSuccess) { set_error("cudaFuncSetAttribute: %s", cudaGetErrorString(e)); rc = GMAT_B200_ERR_CUDA; }
@@ -699,7 +753,8 @@ extern "C" int gmat_b200_grm_f4(const unsigned char *bed_dev, long long n, long 
                 cudaFreeAsync(gt, st);
                 GB_CUDA(cudaMallocAsync((void **)&gt, (size_t)round_up(np, 512) * mld, st));
             }
-            f4_dosage_t_kernel<<<tg, 256, smem_t, st>>>(bed_dev, (int)n, row_bytes, snp_begin, snp_end, table, gt, mld);
+            f4_dosage_t_kernel<<<tg, 256, smem_t, st>>>(bed_dev, (int)n, row_bytes, snp_begin, snp_end,
+                                                         coding == GMAT_B200_CODING_DOM ? 1 : 0, gt, mld);
             count_launch();
             f4_offs_rows_kernel<<<(unsigned)((ms / 8 + 256) / 256), 256, 0, st>>>(lut_dev, snp_begin, ms, (int)n, mld, gt);
             count_launch();
@@ -728,7 +783,11 @@ extern "C" int gmat_b200_grm_f4(const unsigned char *bed_dev, long long n, long 
         } else {
             GB_CUDA(cudaMemsetAsync(c, 0, (size_t)(n + 1) * sizeof(double), st));
         }
-        i8_gram_finish_kernel<<<sm_count() * 8, 256, 0, st>>>(S, np, c, (int)n, scale, small_val, accumulate, K_dev);
+        {
+            const long long nb32 = (n + 31) / 32;
+            i8_gram_finish_kernel<<<(unsigned)(nb32 * (nb32 + 1) / 2), 256, 0, st>>>(S, np, c, (int)n, scale, small_val,
+                                                                                    accumulate, K_dev);
+        }
         count_launch();
         cudaError_t e = cudaGetLastError();
         if (e != cudaSuccess) { set_error("kernel launch failed: %s", cudaGetErrorString(e)); rc = GMAT_B200_ERR_CUDA; }

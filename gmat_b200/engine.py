@@ -175,23 +175,9 @@ def pack_pvp(pvp_dev):
     return packed
 
 
-_PINNED = {}
-
-
 def hits_to_numpy(hits_dev, count):
-    """Device hit records -> host structured array.  Larger results go through a cached pinned staging buffer (a
-    pageable D2H of a few MB costs more than a whole screen call)."""
-    if count * 32 < (1 << 16):
-        raw = hits_dev[:count].cpu().numpy()
-        return raw.view(HIT_DTYPE).reshape(-1)
-    key = hits_dev.device.index
-    buf = _PINNED.get(key)
-    if buf is None or buf.shape[0] < count:
-        buf = torch.empty((max(int(count), 1 << 17), 32), dtype=torch.uint8, pin_memory=True)
-        _PINNED[key] = buf
-    buf[:count].copy_(hits_dev[:count], non_blocking=True)
-    torch.cuda.current_stream().synchronize()
-    return buf[:count].numpy().copy().view(HIT_DTYPE).reshape(-1)
+    raw = hits_dev[:count].cpu().numpy()
+    return raw.view(HIT_DTYPE).reshape(-1)
 
 
 def alloc_hits(cap, device):
