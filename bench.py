@@ -48,8 +48,9 @@ REF_FIRST = 4                           # first-SNPs per step of the reference a
 NS_N, NS_M, NS_P_CUT = 5000, 50000, 1.0e-7     # the north-star shape (BASELINE configs[3]/[4])
 METRIC = "snp_pairs_per_sec_remma_epiAA_exact"
 # dram__bytes_read.sum + dram__bytes_write.sum of one i8_scan_pair_kernel launch (128 first SNPs of this shape), from the
-# committed ncu --set full capture (profiles/r02_kernels.md); filled in once that capture exists
-I8_TRAFFIC_BYTES = None
+# committed ncu --set full capture (profiles/r02_kernels.md: 2.515 GB read + 4.4 MB written; the compulsory bytes are
+# the digit planes once -- 1.58 GB written by i8_split_kernel just before -- and the int8 / 2-bit codes, 51 MB)
+I8_TRAFFIC_BYTES = 2.52e9
 CONFIG = {"workload": "remma_epiAA exact test, synthetic n=%d x m=%d, GRMs [A, A*A] (BASELINE configs[2])"
                       % (N_ID, N_SNP),
           "step": "one batch of %d first-SNPs (evenly spread blocks of 8), all j>i (~1.0e7 pairs) per rank" % BATCH,

@@ -412,39 +412,57 @@ __global__ void __launch_bounds__(256) screen_exact_kernel(
     const unsigned long long *__restrict__ n_cand, int flags, double eff_cut, const double *__restrict__ cut_table,
     const int *__restrict__ binI, const int *__restrict__ binJ, gmat_b200_hit *__restrict__ hits, long long cap,
     unsigned long long *__restrict__ count, long long cand_cap, int *__restrict__ status) {
-    const int lane = threadIdx.x & 31;
-    long long total = (long long)*n_cand;
+    __shared__ double prod[8][16];                                // per warp: lutU[i][cu] * lutV[j][cv]
+    __shared__ int s_flag[8], s_off[8];
+    __shared__ unsigned long long s_base;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const long long total = (long long)*n_cand;
     if (total > cand_cap) {                                       // more survivors than the buffer holds: the caller must
         if (blockIdx.x == 0 && threadIdx.x == 0) status[0] = 2;   // fall back (or retry with a larger buffer)
         return;
     }
     const bool ge = (flags & GMAT_B200_EFF_GE) != 0, swap = (flags & GMAT_B200_EFF_SWAP) != 0;
-    for (long long c = (long long)blockIdx.x * 8 + (threadIdx.x >> 5); c < total; c += (long long)gridDim.x * 8) {
-        const int i = cand[c].x, j = cand[c].y;
-        const double lu[4] = {lutU[(size_t)i * 4], lutU[(size_t)i * 4 + 1], lutU[(size_t)i * 4 + 2], lutU[(size_t)i * 4 + 3]};
-        const double lv[4] = {lutV[(size_t)j * 4], lutV[(size_t)j * 4 + 1], lutV[(size_t)j * 4 + 2], lutV[(size_t)j * 4 + 3]};
-        const unsigned char *ri = bed + (size_t)i * row_bytes, *rj = bed + (size_t)j * row_bytes;
+    // every warp of the block runs the same number of iterations (the hit records of an iteration are appended with
+    // ONE atomic per block: a per-hit atomic on the single counter serialised 1e5 hits into ~0.4 ms)
+    for (long long base = (long long)blockIdx.x * 8; base < total; base += (long long)gridDim.x * 8) {
+        const long long c = base + warp;
+        const bool active = c < total;
+        int i = 0, j = 0;
         double acc = 0.0;
-        for (int b = lane; b * 4 < n; b += 32) {
-            const unsigned ci = ri[b], cj = rj[b];
-#pragma unroll
-            for (int r = 0; r < 4; ++r) {
-                const int k = b * 4 + r;
-                if (k < n) acc += lu[(ci >> (2 * r)) & 3u] * lv[(cj >> (2 * r)) & 3u] * py[k];
+        bool hit = false;
+        if (active) {
+            i = cand[c].x; j = cand[c].y;
+            if (lane < 16) prod[warp][lane] = lutU[(size_t)i * 4 + (lane >> 2)] * lutV[(size_t)j * 4 + (lane & 3)];
+            __syncwarp();
+            const unsigned *ri = reinterpret_cast<const unsigned *>(bed + (size_t)i * row_bytes);
+            const unsigned *rj = reinterpret_cast<const unsigned *>(bed + (size_t)j * row_bytes);
+            // lane <-> individual: py is read in full lines, the two code words of a step are warp broadcasts
+            for (int k = lane; k < n; k += 32) {
+                const unsigned ci = __ldg(ri + (k >> 4)), cj = __ldg(rj + (k >> 4));
+                const int sh = 2 * (k & 15);
+                acc += prod[warp][(((ci >> sh) & 3u) << 2) | ((cj >> sh) & 3u)] * py[k];
             }
-        }
 #pragma unroll
-        for (int d = 16; d >= 1; d >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, d);
-        if (lane == 0) {
+            for (int d = 16; d >= 1; d >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, d);
             const double cut = cut_table != nullptr ? cut_table[binI[i] * 10 + binJ[j]] : eff_cut;
             const double a = fabs(acc);
-            if (ge ? a >= cut : a > cut) {
-                const unsigned long long pos = atomicAdd(count, 1ULL);
-                if ((long long)pos < cap) {
-                    gmat_b200_hit h;
-                    h.snp_0 = swap ? j : i; h.snp_1 = swap ? i : j; h.eff = acc; h.var = 0.0; h.chi = 0.0;
-                    hits[pos] = h;
-                }
+            hit = ge ? a >= cut : a > cut;
+        }
+        if (lane == 0) s_flag[warp] = hit ? 1 : 0;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            int tot = 0;
+#pragma unroll
+            for (int w = 0; w < 8; ++w) { s_off[w] = tot; tot += s_flag[w]; }
+            s_base = tot ? atomicAdd(count, (unsigned long long)tot) : 0ULL;
+        }
+        __syncthreads();
+        if (lane == 0 && hit) {
+            const unsigned long long pos = s_base + (unsigned long long)s_off[warp];
+            if ((long long)pos < cap) {
+                gmat_b200_hit h;
+                h.snp_0 = swap ? j : i; h.snp_1 = swap ? i : j; h.eff = acc; h.var = 0.0; h.chi = 0.0;
+                hits[pos] = h;
             }
         }
     }
