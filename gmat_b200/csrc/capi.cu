@@ -21,6 +21,14 @@ void set_error(const char *fmt, ...) {
     va_end(ap);
 }
 
+static thread_local char g_note[256] = "";
+void set_engine_note(const char *fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_note, sizeof(g_note), fmt, ap);
+    va_end(ap);
+}
+
 int sm_count() {
     static int cached[64];
     int dev = 0;
@@ -54,6 +62,7 @@ using namespace gb;
 
 extern "C" int gmat_b200_version(void) { return 100; }
 extern "C" const char *gmat_b200_last_error(void) { return g_err; }
+extern "C" const char *gmat_b200_last_engine_note(void) { return g_note; }
 extern "C" long long gmat_b200_kernel_launches(void) { return g_launches.load(); }
 
 extern "C" int gmat_b200_device_count(void) {

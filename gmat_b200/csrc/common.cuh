@@ -15,6 +15,7 @@ namespace gb {
 
 // ---------------------------------------------------------------- host: errors, launch count
 void set_error(const char *fmt, ...);
+void set_engine_note(const char *fmt, ...);   // which engine a drop-in symbol ran (gmat_b200_last_engine_note)
 extern std::atomic<long long> g_launches;
 inline void count_launch(int n = 1) { g_launches.fetch_add(n, std::memory_order_relaxed); }
 

@@ -135,6 +135,11 @@ int run_screen(char *bed_file, long long num_id, long long num_snp, long long *s
 
     std::vector<gmat_b200_hit> all;
     std::vector<int> dir;
+    if (i8) set_engine_note("int8 tensor-core prefilter + FP64 re-test (%s)",
+                            tripled ? "3 base-32 planes: the store has missing calls" : "2 base-128 planes");
+    else set_engine_note("FP64 DMMA kernel (%s)", f64_only ? "GMAT_B200_SCREEN_ENGINE=f64"
+                                                            : (len_snp_lst_0 == 0 ? "empty first-SNP list"
+                                                                                  : "n beyond the int8 screen's range"));
     for (int q = 0; q < n_pass; ++q) {
         const Pass &ps = passes[q];
         DevBuf bI, bJ;
@@ -180,7 +185,12 @@ int run_screen(char *bed_file, long long num_id, long long num_snp, long long *s
             if (use_i8) {
                 int status = 0;
                 GB_CUDA(cudaMemcpy(&status, scr.as<int>() + 2, sizeof(int), cudaMemcpyDeviceToHost));
-                if (status != 0) { use_i8 = false; continue; }   // the int8 path declined: FP64 DMMA kernel
+                if (status != 0) {                                // the int8 path declined: FP64 DMMA kernel
+                    set_engine_note("FP64 DMMA kernel (%s)", status == 1 ? "margin of the int8 prefilter not small "
+                                    "against the cut" : "more stage-1 survivors than the candidate buffer");
+                    use_i8 = false;
+                    continue;
+                }
             }
             if ((long long)cnt > cap) { cap = (long long)cnt; continue; }   // exact count known: retry once
             const size_t old = all.size();

@@ -412,6 +412,7 @@ def eff_screen(kind, y, xmat, zmat, gmat_lst, var_com, bed_file, snp_lst_0=None,
     fn = getattr(lib, 'remma_epi%s_eff_cpu' % kind.name)
     check(fn(pbed_file, num_id, num_snp, psnp_lst_0, len(snp_lst_0), ppymat, float(eff_cut), pout_file),
           'remma_epi%s_eff_cpu' % kind.name)
+    logging.info("Screen engine: %s", ffi.string(lib.gmat_b200_last_engine_note()).decode())
     clock_t1 = time.perf_counter()
     cpu_t1 = time.process_time()
     logging.info("Running time: Clock time, {:.5f} sec; CPU time, {:.5f} sec.".format(clock_t1 - clock_t0,
@@ -481,6 +482,7 @@ def maf_eff_screen(kind, y, xmat, zmat, gmat_lst, var_com, bed_file, snp_lst_0=N
     else:
         rc = fn(pbed_file, num_id, num_snp, psnp_lst_0, len(snp_lst_0), ppymat, pf, peff_cut, pout_file)
     check(rc, 'remma_epi%s_maf_eff_cpu' % kind.name)
+    logging.info("Screen engine: %s", ffi.string(lib.gmat_b200_last_engine_note()).decode())
     logging.info('Add the approximate P values')
     freq_deno = np.asarray(freq_deno, dtype=np.float64)
     _append_p_app(temp_file, out_file,

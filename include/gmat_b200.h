@@ -65,6 +65,10 @@ typedef struct gmat_b200_hit {
 /* ------------------------------------------------------------------ runtime / errors ------- */
 int         gmat_b200_version(void);
 const char *gmat_b200_last_error(void);            /* thread-local, valid until the next call   */
+/* which engine the last drop-in screen symbol (group 1) ran on this thread, and why when the int8 path was not
+ * taken: e.g. "int8 tensor-core prefilter + FP64 re-test (3 base-32 planes: missing calls)" or "FP64 DMMA kernel
+ * (margin not small against the cut)".  The fast paths never narrow silently.                                   */
+const char *gmat_b200_last_engine_note(void);
 int         gmat_b200_device_count(void);          /* >= 0, or negative error                   */
 int         gmat_b200_set_device(int device);
 int         gmat_b200_device_info(int *sm_count, int *cc_major, int *cc_minor, long long *hbm_bytes);

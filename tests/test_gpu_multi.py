@@ -40,3 +40,14 @@ def test_sharded_exact_scan_file_equals_oracle():
                     "--workdir", "/tmp/gmat_northstar_test", port=29578)
     assert out["verified"] and out["n_gpus"] == 2 and out["rows_in_file"] > 0
     assert out["max_rel_err_vs_oracle"] <= 1e-9
+
+
+def test_one_imputation_for_all_ranks():
+    """Missing calls under torchrun: rank 0 imputes and broadcasts the 2-bit store (the reference imputes once per
+    call); every rank then holds the same genotypes and the same GRM although their numpy RNG states differ."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    out = _torchrun(2, "multi_gpu_impute_check.py", "300", "900", port=29579)
+    assert out["world"] == 2 and out["missing_in_file"] > 0 and out["missing_after_impute"] == 0
+    assert out["store_identical_on_all_ranks"] and out["grm_identical_on_all_ranks"] and out["scale_identical"]
