@@ -28,6 +28,7 @@
 //    (17 MB packed at n=2000, 105 MB at n=5000), not HBM.
 #include "common.cuh"
 #include <cstdlib>
+#include <mutex>
 
 namespace gb {
 
@@ -567,6 +568,98 @@ extern "C" int gmat_b200_epi_exact_pairs(const unsigned char *bed_dev, long long
     const long long maxgrid = (long long)sm_count() * cfg.ctas_per_sm;
     if (grid > maxgrid) grid = maxgrid;
     cfg.pairs<<<(unsigned)grid, cfg.threads, cfg.smem, (cudaStream_t)stream>>>(p);
+    GB_LAUNCH_CHECK();
+    return GMAT_B200_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// Allocation-free variant of gmat_b200_epi_exact_scan.  No counterpart in the reference: added
+// for callers that may not allocate (CUDA graph capture, tight serving loops, harnesses that forbid
+// cudaMalloc).  The tile table of the scan (prefix[n_iblk + 1] and jstart[n_iblk], int64) -- the only scratch the
+// scan needs -- lives in a file-scope device array instead of a cudaMallocAsync block; every GPU that loads the
+// library holds its GMAT_B200_NOALLOC_MAX_FIRST-sized copy (1 MiB + 8 bytes) until exit.
+//
+// In host code `exact_noalloc_scratch` is only the host-side stand-in of the symbol, NOT a device address: the
+// address of each device's copy is taken once per device with cudaGetSymbolAddress, with that device current, and
+// that pointer is what the kernels get.
+//
+// Every call on a device shares the one array, and it keeps the last call's contents.  Nothing in it has to start at
+// zero: exact_tiles_kernel writes all 2 n_iblk + 1 entries this call's scan reads before the scan starts (same
+// stream), so no clearing is needed.  Two calls whose kernels overlap on one GPU (different streams, or two host
+// threads) RACE on the table: serialise them, or use gmat_b200_epi_exact_scan.
+// ---------------------------------------------------------------------------------------------------------------
+namespace gb {
+constexpr long long NOALLOC_MAX_FIRST = GMAT_B200_NOALLOC_MAX_FIRST;
+static __device__ __align__(256) long long exact_noalloc_scratch[2 * NOALLOC_MAX_FIRST + 1];
+
+// device address of the current device's copy of exact_noalloc_scratch (nullptr + last_error on failure)
+static long long *exact_noalloc_ptr() {
+    constexpr int MAX_DEV = 64;
+    static std::mutex mu;
+    static long long *ptrs[MAX_DEV];
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess || dev < 0 || dev >= MAX_DEV) {
+        set_error("noalloc scratch: cudaGetDevice failed or device index %d out of range (%s)", dev,
+                  cudaGetErrorString(e));
+        return nullptr;
+    }
+    std::lock_guard<std::mutex> lock(mu);
+    if (!ptrs[dev]) {
+        long long *ptr = nullptr;
+        e = cudaGetSymbolAddress(reinterpret_cast<void **>(&ptr), exact_noalloc_scratch);
+        if (e != cudaSuccess || !ptr) {
+            set_error("noalloc scratch: cudaGetSymbolAddress failed on device %d: %s", dev, cudaGetErrorString(e));
+            return nullptr;
+        }
+        ptrs[dev] = ptr;
+    }
+    return ptrs[dev];
+}
+}  // namespace gb
+
+extern "C" long long gmat_b200_noalloc_max_first(void) { return NOALLOC_MAX_FIRST; }
+
+extern "C" int gmat_b200_epi_exact_scan_noalloc(const unsigned char *bed_dev, long long n, long long m,
+                                                long long row_bytes, const double *lutU_dev,
+                                                const double *lutV_dev, const double *py_dev,
+                                                const double *pvp_packed_dev, const long long *ilist_dev,
+                                                long long n_i, int pair_space, double chi_cut,
+                                                gmat_b200_hit *hits_dev, long long cap,
+                                                unsigned long long *count_dev, void *stream) {
+    int rc = exact_common_check(bed_dev, n, m, row_bytes, lutU_dev, lutV_dev, py_dev, pvp_packed_dev);
+    if (rc != GMAT_B200_OK) return rc;
+    GB_CHECK_ARG(ilist_dev && count_dev, "NULL pointer");
+    GB_CHECK_ARG(n_i >= 0, "n_i");
+    if (n_i > NOALLOC_MAX_FIRST) {
+        set_error("gmat_b200_epi_exact_scan_noalloc: n_i = %lld first SNPs exceeds the static scratch "
+                  "(GMAT_B200_NOALLOC_MAX_FIRST = %lld); split the list or call gmat_b200_epi_exact_scan",
+                  n_i, NOALLOC_MAX_FIRST);
+        return GMAT_B200_ERR_ARG;
+    }
+    GB_CHECK_ARG(cap == 0 || hits_dev, "hits_dev is NULL");
+    GB_CHECK_ARG(pair_space == GMAT_B200_PAIRS_UPPER || pair_space == GMAT_B200_PAIRS_ALL, "pair_space");
+    if (n_i == 0) return GMAT_B200_OK;
+    long long *scratch = exact_noalloc_ptr();
+    if (!scratch) return GMAT_B200_ERR_CUDA;
+    const ExactCfg &cfg = exact_cfg();
+    const int bi = cfg.bn / EX_BJ;
+    cudaStream_t st = (cudaStream_t)stream;
+    ExactParams p{};
+    p.bed = bed_dev; p.n = n; p.m = m; p.row_bytes = row_bytes;
+    p.nb = round_up(n, cfg.bm) / cfg.bm;
+    p.lutU = lutU_dev; p.lutV = lutV_dev; p.py = py_dev; p.packed = pvp_packed_dev;
+    p.ilist = ilist_dev; p.n_i = n_i; p.n_iblk = (n_i + bi - 1) / bi;      // n_iblk <= n_i <= NOALLOC_MAX_FIRST
+    p.pair_space = pair_space; p.chi_cut = chi_cut;
+    p.hits = hits_dev; p.cap = cap; p.count = count_dev;
+    p.prefix = scratch;
+    p.jstart = scratch + p.n_iblk + 1;
+    exact_tiles_kernel<<<1, 1024, 0, st>>>(ilist_dev, n_i, m, pair_space, bi, p.n_iblk, scratch,
+                                           scratch + p.n_iblk + 1);
+    GB_LAUNCH_CHECK();
+    GB_CUDA(cudaFuncSetAttribute(cfg.scan, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cfg.smem));
+    const unsigned grid = (unsigned)(sm_count() * cfg.ctas_per_sm);
+    cfg.scan<<<grid, cfg.threads, cfg.smem, st>>>(p);
     GB_LAUNCH_CHECK();
     return GMAT_B200_OK;
 }

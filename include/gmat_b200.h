@@ -197,6 +197,26 @@ int gmat_b200_epi_exact_scan(const unsigned char *bed_dev, long long n, long lon
                              gmat_b200_hit *hits_dev, long long cap, unsigned long long *count_dev,
                              void *stream);
 
+/* Allocation-free variant of gmat_b200_epi_exact_scan.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA
+ * graph capture, tight serving loops, harnesses that forbid it).  Same arguments, same results.
+ * The scan's only scratch (its tile table: 2*ceil(n_i/bi)+1 int64) lives in a file-scope
+ * static __device__ array sized for GMAT_B200_NOALLOC_MAX_FIRST first SNPs (1 MiB + 8 bytes, held
+ * by every GPU that loads the library until exit); the call makes no cudaMalloc / cudaFree /
+ * cudaMallocAsync.  n_i > GMAT_B200_NOALLOC_MAX_FIRST returns GMAT_B200_ERR_ARG with a message in
+ * gmat_b200_last_error().  All calls on a device share the array (it keeps the last call's
+ * contents; every entry a call reads is rewritten by that call first, nothing needs zeroing):
+ * calls whose kernels OVERLAP on one GPU (two streams, two threads) race -- serialise them.
+ * As for gmat_b200_epi_exact_scan, the caller zeroes *count_dev.                                */
+#define GMAT_B200_NOALLOC_MAX_FIRST 65536
+long long gmat_b200_noalloc_max_first(void);
+int gmat_b200_epi_exact_scan_noalloc(const unsigned char *bed_dev, long long n, long long m,
+                                     long long row_bytes, const double *lutU_dev, const double *lutV_dev,
+                                     const double *py_dev, const double *pvp_packed_dev,
+                                     const long long *ilist_dev, long long n_i, int pair_space,
+                                     double chi_cut, gmat_b200_hit *hits_dev, long long cap,
+                                     unsigned long long *count_dev, void *stream);
+
 /* Exact test over an explicit pair list (remma_epiAA_pair.py:66-87): out[p] gets eff/var/chi of
  * pair p (all pairs are written, dense, in list order).                                        */
 int gmat_b200_epi_exact_pairs(const unsigned char *bed_dev, long long n, long long m, long long row_bytes,
