@@ -302,6 +302,7 @@ def run_gpu(args):
     # unthrottled part, measured before anything else (the sustained, power-capped rate is measured after the timed
     # steps and reported beside it)
     i8_peak_burst = probe.i8_peak(20000) if rank == 0 else None
+    f4_peak_burst = probe.f4_peak(20000) if rank == 0 else None     # same microbenchmark with the GRM's FP4 MMA
 
     workdir = tempfile.mkdtemp(prefix="gmat_bench_r%d_" % rank)
     prefix, pheno = make_dataset(workdir)            # every rank writes its own identical copy (seeded)
@@ -481,7 +482,8 @@ def run_gpu(args):
                         e2e_f64 = float(e2e_pairs) / (time.perf_counter() - t0)
                 finally:
                     del os.environ["GMAT_B200_EXACT_ENGINE"]
-            extra.update(extras(engine, torch, synth, store, model, lut, args, prefix, pymat, i8_peak_burst, e2e_f64))
+            extra.update(extras(engine, torch, synth, store, model, lut, args, prefix, pymat, i8_peak_burst, e2e_f64,
+                                f4_peak=f4_peak_burst))
         if extra:
             line["extra"] = extra
         if world == 1 and not args.no_cpu:
@@ -722,7 +724,7 @@ def verify_file(out_file, pre, pheno, kind, model_key, gmat_lst, var_com, first,
     return res
 
 
-def extras(engine, torch, synth, store, model, lut, args, prefix, pymat, i8_peak, e2e_f64=None):
+def extras(engine, torch, synth, store, model, lut, args, prefix, pymat, i8_peak, e2e_f64=None, f4_peak=None):
     """Secondary numbers of BASELINE.json's metric, same process, N=1: approximate screen pairs/s on the same
     data, agmat TFLOP/s on configs[1] (n=10,000 x m=500,000, generated in HBM), decode GB/s.  Every int8 fraction
     divides by the same ``i8_peak`` as the headline's."""
@@ -886,15 +888,19 @@ def extras(engine, torch, synth, store, model, lut, args, prefix, pymat, i8_peak
                         "seconds": t, "workload": "agmat GRM, synthetic n=%d x m=%d generated in HBM "
                                                   "(BASELINE configs[1])" % (n2, m2)}
         if which in ("f4", "i8"):
-            # FP4 (tcgen05 kind::mxf4) issues at twice the int8 rate: its roofline denominator is 2 x the int8 issue
-            # rate measured at the start of the run (the probe library has no FP4 microbenchmark)
-            pk = i8_peak * (2.0 if which == "f4" else 1.0)
+            # the FP4 GRM's denominator is the issue rate of ITS MMA (tcgen05 kind::mxf4.block_scale 128x256x64, unit
+            # scale factors), measured by the same microbenchmark as the int8 one at the start of the run on the cold
+            # part (probe/: f4_peak); 2 x the int8 rate, the nominal ratio, is listed beside it
+            pk = (f4_peak if f4_peak else 2.0 * i8_peak) if which == "f4" else i8_peak
             out["agmat"]["roofline"] = {
                 "bound": "tensor", "unit": "TOP/s", "achieved": ops_n / t / 1e12, "peak": pk, "frac": ops_n / t / 1e12 / pk,
                 "frac_of_int8_peak": ops_n / t / 1e12 / i8_peak,
+                "f4_mma_issue_tops": f4_peak, "i8_mma_issue_tops_x2": 2.0 * i8_peak,
                 "note": "n(n+1)m ops (lower triangle of G G', 2 ops per MAC) / the whole call (2-bit -> packed operand "
-                        "transpose, the GEMM kernel, corrections); peak = the int8 issue rate of the headline"
-                        + (" x 2 (E2M1 operands, kind::mxf4)" if which == "f4" else "")}
+                        "transpose, the GEMM kernel, corrections); peak = "
+                        + ("the measured issue rate of tcgen05.mma kind::mxf4.block_scale (E2M1 operands) on "
+                           "resident tiles, all SMs, cold part" if which == "f4" else
+                           "the int8 issue rate of the headline")}
             if which == "f4":
                 t8 = timed(lambda: engine.grm(st2, engine.ADD, 1.0, 0.001, out=kin, which="i8"), reps=1)
                 out["agmat"]["i8_engine"] = {"seconds": t8, "tflops_algorithmic_n(n+1)m": ops_n / t8 / 1e12,

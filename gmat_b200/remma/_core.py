@@ -629,6 +629,12 @@ def approx(kind, pheno_file, bed_file, gmat_lst, var_com, p_cut=1.0e-5, num_rand
         hits = ctx.screen(snp_lst_0, eff_cut=float(np.sqrt(chi_cut * var_median)))
         deno = lambda s0, s1: var_median                                    # noqa: E731
     else:
+        # the _maf_ pipelines of the reference leave the random pairs' exact statistics on disk: they never remove
+        # out_file.random[.k] (remma_epiAA_maf_approx.py:29-31,114-116; the plain _approx variants do, :33)
+        with open(out_file + '.random' + sfx, 'w') as fout:
+            fout.write('snp_0 snp_1 eff var chi p\n')
+            for arr in rand_rows:
+                fout.write(' '.join(arr) + '\n')
         bin_i, bin_j, saved = _maf_bins(kind, ctx.store)
         for ext, arr in saved.items():
             np.savetxt(out_file + ext + sfx, arr)
@@ -657,6 +663,8 @@ def approx(kind, pheno_file, bed_file, gmat_lst, var_com, p_cut=1.0e-5, num_rand
                     fout.write(kv + ' ' + str(sums[kv]) + '\n')
                     freq_deno[key1 * 10 + key2] = sums[kv]
         bi, bj = np.asarray(bin_i, dtype=np.int64), np.asarray(bin_j, dtype=np.int64)
+        if not ad:
+            np.savetxt('eff_cut', np.sqrt(chi_cut * freq_deno))   # written by the nested _maf_eff call (remma_epiAA_maf_eff.py:79)
         hits = ctx.screen(snp_lst_0, cut_table=np.sqrt(chi_cut * freq_deno), bin_i=bi, bin_j=bj)
         deno = lambda s0, s1: freq_deno[bi[s0] * 10 + bj[s1]]              # noqa: E731
     # approximate p from the %g-truncated effect, exactly like the text round trip of the reference

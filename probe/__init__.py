@@ -30,6 +30,11 @@ def i8_peak(iters=20000):
     return _call(lib.gmat_b200_i8_peak, iters)
 
 
+def f4_peak(iters=20000):
+    """Measured issue rate of the FP4 (E2M1, block-scaled) tensor-core MMA on this GPU, TOPS (2 ops per MAC)."""
+    return _call(lib.gmat_b200_f4_peak, iters)
+
+
 def fp64_peak(kind=0, iters=20000):
     """kind 0: DMMA (mma.sync m8n8k4 f64), kind 1: DFMA; TFLOP/s."""
     return _call(lib.gmat_b200_fp64_peak, kind, iters)

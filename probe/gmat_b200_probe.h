@@ -9,6 +9,8 @@ const char *gmat_b200_last_error(void);
 int         gmat_b200_set_device(int device);
 /* int8 tensor-core issue-rate microbenchmark (tcgen05.mma kind::i8 128x256x32 on resident tiles, all SMs): TOPS  */
 int gmat_b200_i8_peak(int iters, double *tops);
+/* the same for the FP4 MMA of the GRM (kind::mxf4.block_scale 128x256x64, unit scale factors): TOPS                */
+int gmat_b200_f4_peak(int iters, double *tops);
 /* FP64 issue-rate microbenchmarks (used by bench.py for the roofline denominator).
  * kind 0: DMMA (mma.sync m8n8k4 f64) ; kind 1: DFMA.  Writes TFLOP/s.  */
 int gmat_b200_fp64_peak(int kind, int iters, double *tflops);

@@ -47,6 +47,76 @@ __global__ void __launch_bounds__(128, 1) i8_peak_kernel(int iters) {
 }
 
 
+// The same for the FP4 MMA of the GRM (gram_i8.cu: tcgen05.mma kind::mxf4.block_scale.block32, E2M1 operands, unit
+// UE8M0 scale factors in TMEM columns [256, 320)): back-to-back 128x256x64 MMAs on a resident tile pair into one
+// 256-column accumulator, the way the GRM kernel's K loop issues them.  Every nibble pattern is a finite E2M1 value.
+constexpr uint32_t F4_PROBE_IDESC = (1u << 7) | (1u << 10) | ((uint32_t)(I8_TK >> 3) << 17) | (1u << 23) |
+                                    ((uint32_t)(I8_TJ >> 4) << 24);
+__device__ __forceinline__ void umma_f4(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
+                                        uint32_t tsfa, uint32_t tsfb, uint32_t accumulate) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "setp.ne.b32 p, %4, 0;\n"
+        "tcgen05.mma.cta_group::1.kind::mxf4.block_scale.block32 [%0], %1, %2, %3, [%5], [%6], p;\n"
+        "}\n" ::"r"(tmem_d),
+        "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate), "r"(tsfa), "r"(tsfb)
+        : "memory");
+}
+__global__ void __launch_bounds__(128, 1) f4_peak_kernel(int iters) {
+    extern __shared__ unsigned char smem_raw[];
+    unsigned char *smem = reinterpret_cast<unsigned char *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                                           ~static_cast<uintptr_t>(1023));
+    __shared__ uint64_t bar;
+    __shared__ uint32_t tbase_slot;
+    for (int k = threadIdx.x; k < I8_STAGE_BYTES / 4; k += blockDim.x)
+        reinterpret_cast<unsigned *>(smem)[k] = (unsigned)(k * 2654435761u) ^ (blockIdx.x * 40503u);
+    if (threadIdx.x == 0) { mbar_init(&bar, 1); mbar_fence_init(); }
+    if (threadIdx.x < 32) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;\n" ::"r"(smem_u32(&tbase_slot)),
+                     "r"(512)
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;\n" ::: "memory");
+    }
+    fence_proxy_async();
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tbase = tbase_slot;
+    {   // unit scale factors (UE8M0 2^0 = 0x7F) in columns [256, 320) of this warp's 32 lanes
+        const uint32_t tq = tbase + ((uint32_t)((threadIdx.x >> 5) * 32) << 16) + (uint32_t)I8_TK;
+        asm volatile(
+            "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
+            "{%1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, "
+            "%1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1};\n" ::"r"(tq), "r"(0x7F7F7F7Fu) : "memory");
+        asm volatile(
+            "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
+            "{%1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, "
+            "%1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1};\n" ::"r"(tq + 32u), "r"(0x7F7F7F7Fu) : "memory");
+        asm volatile("tcgen05.wait::st.sync.aligned;\n" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    if (threadIdx.x == 0) {
+        const uint32_t sa = smem_u32(smem);
+        const uint64_t da = umma_desc_sw128(sa), db = umma_desc_sw128(sa + I8_A_BYTES);
+        const uint32_t tsf = tbase + (uint32_t)I8_TK;
+        for (int it = 0; it < iters; ++it) {
+#pragma unroll
+            for (int k = 0; k < 4; ++k)                                // K = 64 nibbles = 32 bytes per MMA
+                umma_f4(tbase, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), F4_PROBE_IDESC, tsf, tsf + 32u,
+                        (uint32_t)(it > 0));
+        }
+        tc_commit(&bar);
+        mbar_wait(&bar, 0);
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (threadIdx.x < 32)
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;\n" ::"r"(tbase), "r"(512) : "memory");
+}
+
 // ---- FP64 issue-rate microbenchmarks ---------------------------------------------------------
 __global__ void __launch_bounds__(512) peak_dmma_kernel(double *out, int iters) {
     double c[8][2];
@@ -213,6 +283,28 @@ extern "C" int gmat_b200_i8_peak(int iters, double *tops) {
     return GMAT_B200_OK;
 }
 
+
+extern "C" int gmat_b200_f4_peak(int iters, double *tops) {
+    GB_CHECK_ARG(iters > 0 && tops, "iters/tops");
+    const int smem_bytes = I8_STAGE_BYTES + 1024;
+    GB_CUDA(cudaFuncSetAttribute(f4_peak_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
+    cudaEvent_t e0, e1;
+    GB_CUDA(cudaEventCreate(&e0));
+    GB_CUDA(cudaEventCreate(&e1));
+    const int grid = sm_count();
+    f4_peak_kernel<<<grid, 128, smem_bytes>>>(iters / 8 + 1);          // warm-up
+    GB_CUDA(cudaEventRecord(e0));
+    f4_peak_kernel<<<grid, 128, smem_bytes>>>(iters);
+    GB_CUDA(cudaEventRecord(e1));
+    GB_CUDA(cudaEventSynchronize(e1));
+    GB_LAUNCH_CHECK();
+    float ms = 0.f;
+    GB_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    *tops = 2.0 * grid * (double)iters * 4.0 * I8_TJ * I8_TK * 64.0 / (ms * 1e-3) / 1e12;
+    return GMAT_B200_OK;
+}
 
 extern "C" int gmat_b200_dmma_dmul_probe(int warps, int nmul, int mode, int iters, double *tflops) {
     GB_CHECK_ARG(tflops != nullptr && iters > 0 && warps >= 1 && warps <= 8, "args");

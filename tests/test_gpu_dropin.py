@@ -191,8 +191,22 @@ def test_approx_pipelines(grms, golden, kind, maf, tmp_path, monkeypatch):
     gl, vc = ([ag, ag * ag], golden["var_com_ag_agag"]) if kind == "AA" else \
         ([ag, dg, ag * ag], golden["var_com_ag_dg_agag"])
     out = str(tmp_path / stem)
+    monkeypatch.chdir(tmp_path)                  # the _maf_ pipelines write ./eff_cut, like the reference
     fn = getattr(mod, "remma_epi%s_%sapprox" % (kind, "maf_" if maf else ""))
     assert fn(grms["pheno"], grms["bed"], gl, vc, p_cut=1e-4, num_random_pair=20000, out_file=out) == 0
+    # what is left on disk is what the reference leaves (remma_epiAA_maf_approx.py:29-31,88-89 / remma_epiAA_approx.py:32-33,51-52)
+    for ext in (".random_pair", ".random_pairAD", ".approx_p", ".exact_p"):
+        assert not os.path.exists(out + ext)
+    assert os.path.exists(out + ".random") == maf
+    if maf:
+        # out_file.random = the reference's own _pair call on the random pairs with p_cut = 1
+        getattr(mod, "remma_epi%s_pair" % kind)(grms["pheno"], grms["bed"], gl, vc,
+                                                snp_pair_file=gold_path(stem + ".random_pair"), p_cut=1,
+                                                out_file=out + ".random_by_pair")
+        assert open(out + ".random").read() == open(out + ".random_by_pair").read()
+        assert os.path.exists(str(tmp_path / "eff_cut")) == (kind != "AD")
+        if kind != "AD":
+            assert np.loadtxt(str(tmp_path / "eff_cut")).shape == (111,)
     # columns: snp_0 snp_1 eff var chi p_app p ; p_app derives from the %g-truncated effect
     n = _cmp_set(out, gold_path(stem + ".txt"), (2, 3, 4), RTOL)
     _cmp_set(out, gold_path(stem + ".txt"), (6,), 1e-7)
