@@ -612,6 +612,45 @@ def northstar(args, torch, dist, engine, _core, synth, rank, world, barrier, red
         barrier()
         return blk
 
+    def run_approx(exact_name, exact_scope):
+        """The three-stage approximate pipeline (remma_epiAA_approx.py:10-53: 100,000 random pairs -> median null
+        variance -> screen of ALL pairs -> exact re-test of the survivors) through the public call, files in, file
+        out, on rank 0's GPU alone (the call has no sharded form: the reference's _approx_parallel parts draw their
+        own random pairs and cuts)."""
+        from gmat_b200.remma.remma_epiAA import remma_epiAA_approx
+        pheno, gmat_lst, var_com = models["AA"]
+        out_file = pre + ".AAapprox"
+        blk = None
+        barrier()
+        if rank == 0:
+            np.random.seed(20201013)
+            with _core.par.single_rank():
+                torch.cuda.synchronize()
+                t0 = time.perf_counter()
+                remma_epiAA_approx(pheno, pre, gmat_lst, var_com, p_cut=NS_P_CUT, num_random_pair=100000,
+                                   out_file=out_file)
+                torch.cuda.synchronize()
+                secs = time.perf_counter() - t0
+            tests = m * (m - 1) // 2
+            blk = {"what": "remma_epiAA_approx, ALL pairs screened (approximate test at p_cut on the median null "
+                           "variance of 100,000 random pairs), survivors re-tested exactly; public call on files, one GPU",
+                   "kind": "AA", "tests": int(tests), "seconds": secs, "pairs_per_s": tests / secs, "n_gpus_used": 1,
+                   "screen_engine": engine.LAST_SCREEN_ENGINE,
+                   "phases_s": {k: round(v, 3) for k, v in _core.PHASES.items()}}
+            if not args.no_verify:
+                if "AA" not in oracle_models:
+                    y, xmat, zmat = design_matrix_wemai_multi_gmat(pheno, pre)
+                    from oracle import oracle
+                    oracle_models["AA"] = oracle.preamble(y, xmat, zmat, gmat_lst, var_com)
+                exact_rows = None
+                if os.path.exists(pre + "." + exact_name):
+                    exact_rows = {(int(r.split()[0]), int(r.split()[1]))
+                                  for r in open(pre + "." + exact_name).read().splitlines()[1:]}
+                blk.update(verify_approx_file(out_file, pre, n, m, oracle_models["AA"][0], oracle_models["AA"][1],
+                                              exact_rows, exact_scope, chi2))
+        barrier()
+        return blk
+
     sub8 = list(range(0, m - 1, 8))
     blocks = {}
     blocks["strong_AA"] = run_block(
@@ -636,11 +675,87 @@ def northstar(args, torch, dist, engine, _core, synth, rank, world, barrier, red
         blocks["AA_15000_records"] = run_block(
             "REP", "AA", "REP", sub8, "remma_epiAA exact, every 8th first SNP, 3 records per individual (15,000 "
                                       "records), GRMs [A, A*A, I] (BASELINE configs[4]; exhaustive at N=8)")
+    blocks["AA_approx"] = run_approx("AA" if full else "strongAA", None if full else set(sub8))
     out["exhaustive"] = bool(full)
     out["blocks"] = blocks
     if rank == 0:
         out["verified"] = all(b.get("verified", args.no_verify) for b in blocks.values())
     return out
+
+
+def oracle_pair_stats(pre, n, m, kind, pymat, pvpmat, pairs, chi2):
+    """eff, var, chi, p of explicit pairs by the numpy oracle expressions (remma_epiAA.py:59-61,72-77) on the files."""
+    raw = np.fromfile(pre + ".bed", dtype=np.uint8)[3:].reshape(m, (n + 3) // 4)
+
+    def cols(snps, coding):
+        r = raw[np.asarray(snps)]
+        c = np.stack([(r >> (2 * q)) & 3 for q in range(4)], axis=2).reshape(len(snps), -1)[:, :n]
+        g = np.array([0.0, np.nan, 1.0, 2.0])[c]
+        f = g.sum(axis=1, keepdims=True) / (2 * n)
+        x = g - 2 * f if coding == "A" else np.where(g > 1.5, 0.0, g) - 2 * f * (1 - f)
+        return x.T
+
+    pairs = np.asarray(pairs, dtype=np.int64).reshape(-1, 2)
+    effs, vars_ = [], []
+    for k0 in range(0, len(pairs), 512):
+        part = pairs[k0:k0 + 512]
+        su, sv = sorted(set(part[:, 0].tolist())), sorted(set(part[:, 1].tolist()))
+        U, V = cols(su, kind[0]), cols(sv, kind[1])
+        iu, iv = {s_: k for k, s_ in enumerate(su)}, {s_: k for k, s_ in enumerate(sv)}
+        W = U[:, [iu[a] for a in part[:, 0].tolist()]] * V[:, [iv[b] for b in part[:, 1].tolist()]]
+        effs.append((W.T @ pymat).ravel())
+        vars_.append(np.sum(W * (pvpmat @ W), axis=0))
+    eff = np.concatenate(effs) if effs else np.zeros(0)
+    var = np.concatenate(vars_) if vars_ else np.zeros(0)
+    chi = eff * eff / var
+    return eff, var, chi, chi2.sf(chi, 1)
+
+
+def verify_approx_file(out_file, pre, n, m, pymat, pvpmat, exact_rows, exact_scope, chi2):
+    """The final file of remma_epiAA_approx (snp_0 snp_1 eff var chi p_app p) against the numpy oracle: every row with
+    p < 1e-5 and 2000 random other rows re-derived (eff, var, chi within 1e-9, p within 1e-7); p_app consistent with
+    the %g-truncated effect (one null variance for the whole file); and against the EXACT scan of the same run: every
+    approx row with p < p_cut whose first SNP the exact scan covered must be in the exact file (the FP64 pair kernel
+    and the int8 scan kernel decide the same pairs), recall = the share of the exact scan's rows the screen kept."""
+    t0 = time.perf_counter()
+    lines = open(out_file).read().splitlines()
+    ok, msgs = lines[0] == "snp_0 snp_1 eff var chi p_app p", []
+    rows = [ln.split() for ln in lines[1:]]
+    key = np.array([[int(r[0]), int(r[1])] for r in rows], dtype=np.int64).reshape(-1, 2)
+    val = np.array([[float(v) for v in r[2:]] for r in rows], dtype=np.float64).reshape(-1, 5)
+    rng = np.random.Generator(np.random.PCG64(2))
+    strong = np.flatnonzero(val[:, 4] < 1e-5)
+    rest = np.setdiff1d(np.arange(len(rows)), strong)
+    pick = np.concatenate([strong, rng.choice(rest, size=min(2000, len(rest)), replace=False)]).astype(np.int64)
+    eff, var, chi, pv = oracle_pair_stats(pre, n, m, "AA", pymat, pvpmat, key[pick], chi2)
+    rel = np.max(np.abs(np.stack([val[pick, 0] / eff, val[pick, 1] / var, val[pick, 2] / chi]) - 1.0)) if len(pick) else 0.0
+    relp = np.max(np.abs(val[pick, 4] / pv - 1.0)) if len(pick) else 0.0
+    if rel > 1e-9 or relp > 1e-7:
+        ok = False
+        msgs.append("rows vs oracle: rel %.2e, p rel %.2e" % (rel, relp))
+    # p_app = chi2.sf(float('%g' % eff)^2 / var_median): one denominator must explain every row
+    e_tr = np.array([float("%g" % e) for e in val[:, 0]])
+    den = e_tr * e_tr / chi2.isf(val[:, 3], 1)
+    spread = float(np.max(np.abs(den / np.median(den) - 1.0))) if len(den) else 0.0
+    if spread > 1e-6:
+        ok = False
+        msgs.append("p_app not consistent with one null variance: spread %.2e" % spread)
+    sig = {(int(a), int(b)) for (a, b), q in zip(key.tolist(), val[:, 4].tolist()) if q < NS_P_CUT}
+    res = {"rows_in_file": len(rows), "rows_exact_p_below_cut": len(sig), "rows_checked_by_oracle": int(len(pick)),
+           "max_rel_err_vs_oracle": float(rel), "null_variance": float(np.median(den)) if len(den) else None}
+    if exact_rows is not None:
+        in_scope = {k for k in sig if exact_scope is None or k[0] in exact_scope}
+        missing = sorted(in_scope - exact_rows)
+        if missing:
+            ok = False
+            msgs.append("significant in the approx file but not in the exact scan: %s" % missing[:5])
+        res["exact_scan_rows"] = len(exact_rows)
+        res["recall_of_exact_scan_rows"] = len(in_scope & exact_rows) / len(exact_rows) if exact_rows else None
+    res["verified"] = ok
+    res["seconds_verify"] = time.perf_counter() - t0
+    if msgs:
+        res["messages"] = msgs[:10]
+    return res
 
 
 def verify_file(out_file, pre, pheno, kind, model_key, gmat_lst, var_com, first, planted, n, m, cache,

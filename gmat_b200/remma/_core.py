@@ -555,14 +555,18 @@ def random_pair(num_snp, out_file='random_pair', num_pair=100000, num_each_pair=
     while True:
         arr = np.random.randint(num_snp, size=(num_each_pair, 2))
         arr = arr[arr[:, 0] < arr[:, 1], :] if ordered else arr[arr[:, 0] != arr[:, 1], :]
-        arr = np.array(arr, dtype=str)
-        lst = map(lambda x, y: x + ' ' + y, arr[:, 0], arr[:, 1])
-        res_lst.update(set(lst))
+        # the same strings as str(a) + ' ' + str(b), entered through a temporary set like the reference does: the
+        # iteration order of res_lst (hence WHICH pairs survive the truncation) depends on the insertion history
+        res_lst.update(set(['%d %d' % (a, b) for a, b in arr.tolist()]))
         if len(res_lst) >= num_pair:
             break
     res_lst = list(res_lst)[:num_pair]
-    np.savetxt(out_file, np.array(res_lst), fmt="%s", header='snp_0 snp_1', comments='')
-    return np.loadtxt(out_file, dtype=int, skiprows=1)
+    # the bytes np.savetxt(out_file, np.array(res_lst), fmt="%s", header='snp_0 snp_1', comments='') writes, and the
+    # array np.loadtxt(out_file, dtype=int, skiprows=1) reads back (random_pair.py:33-36 + the next stage's read),
+    # without numpy's per-line text machinery (0.2 s of a 0.7 s pipeline at 100,000 pairs)
+    with open(out_file, 'w') as fout:
+        fout.write('snp_0 snp_1\n' + '\n'.join(res_lst) + '\n')
+    return np.array(' '.join(res_lst).split(), dtype=int).reshape(-1, 2)
 
 
 def random_pairAD(num_snp, out_file='random_pair', num_pair=100000, num_each_pair=5000):
@@ -613,11 +617,19 @@ def approx(kind, pheno_file, bed_file, gmat_lst, var_com, p_cut=1.0e-5, num_rand
     num_snp = engine.count_lines(bed_file + '.bim')
     ad = kind.name == 'AD'
     rp_name = out_file + ('.random_pairAD' if (ad and maf) else '.random_pair') + sfx
-    pairs = (random_pairAD if ad else random_pair)(num_snp, out_file=rp_name, num_pair=num_random_pair)
-    os.remove(rp_name)
-    pairs = np.asarray(pairs, dtype=np.int64).reshape(-1, 2)
-    ctx = Prepared(kind, pheno_file, bed_file, gmat_lst, var_com)
-    rand_rows, rand_var = _exact_rows_text(pairs, ctx.pair_stats(pairs))
+    PHASES.clear()
+    with _Phase("random_pairs"):
+        pairs = (random_pairAD if ad else random_pair)(num_snp, out_file=rp_name, num_pair=num_random_pair)
+        os.remove(rp_name)
+        pairs = np.asarray(pairs, dtype=np.int64).reshape(-1, 2)
+    with _Phase("model_and_store"):
+        ctx = Prepared(kind, pheno_file, bed_file, gmat_lst, var_com)
+    with _Phase("random_pairs_exact_test"):
+        res = ctx.pair_stats(pairs)
+        if maf:                                # rows as text: the per-bin table and out_file.random need them
+            rand_rows, rand_var = _exact_rows_text(pairs, res)
+        else:                                  # only the variances of the rows _pair(p_cut=1) keeps (p < 1)
+            rand_rows, rand_var = None, res['var'][chi2.sf(res['chi'], 1) < 1]
     if parallel is None:
         snp_lst_0 = range(num_snp) if (ad and not maf) else range(num_snp - 1)
     else:
@@ -626,7 +638,8 @@ def approx(kind, pheno_file, bed_file, gmat_lst, var_com, p_cut=1.0e-5, num_rand
     logging.info("\n\n#####Screen the epistatic effects and select top SNP pairs based on approximate test#####")
     if not maf:
         var_median = np.median(rand_var)                                   # remma_epiAA_approx.py:30-31
-        hits = ctx.screen(snp_lst_0, eff_cut=float(np.sqrt(chi_cut * var_median)))
+        with _Phase("screen"):
+            hits = ctx.screen(snp_lst_0, eff_cut=float(np.sqrt(chi_cut * var_median)))
         deno = lambda s0, s1: var_median                                    # noqa: E731
     else:
         # the _maf_ pipelines of the reference leave the random pairs' exact statistics on disk: they never remove
@@ -665,20 +678,22 @@ def approx(kind, pheno_file, bed_file, gmat_lst, var_com, p_cut=1.0e-5, num_rand
         bi, bj = np.asarray(bin_i, dtype=np.int64), np.asarray(bin_j, dtype=np.int64)
         if not ad:
             np.savetxt('eff_cut', np.sqrt(chi_cut * freq_deno))   # written by the nested _maf_eff call (remma_epiAA_maf_eff.py:79)
-        hits = ctx.screen(snp_lst_0, cut_table=np.sqrt(chi_cut * freq_deno), bin_i=bi, bin_j=bj)
+        with _Phase("screen"):
+            hits = ctx.screen(snp_lst_0, cut_table=np.sqrt(chi_cut * freq_deno), bin_i=bi, bin_j=bj)
         deno = lambda s0, s1: freq_deno[bi[s0] * 10 + bj[s1]]              # noqa: E731
     # approximate p from the %g-truncated effect, exactly like the text round trip of the reference
     # (as arrays: the same IEEE operations and the same str() of the same doubles as a per-row loop, without scipy's
     # 70 us scalar call per row)
     surv = [(s0, s1) for s0, s1, _ in hits]
     p_dct = {}
-    if hits:
-        e_trunc = np.array([float('%g' % e) for _, _, e in hits], dtype=np.float64)
-        den = np.array([deno(s0, s1) for s0, s1 in surv], dtype=np.float64)
-        p_app = chi2.sf(e_trunc * e_trunc / den, 1)
-        p_dct = {'%d %d' % k: str(q) for k, q in zip(surv, p_app)}
+    with _Phase("p_app"):
+        if hits:
+            e_trunc = np.array([float('%g' % e) for _, _, e in hits], dtype=np.float64)
+            den = np.array([deno(s0, s1) for s0, s1 in surv], dtype=np.float64)
+            p_app = chi2.sf(e_trunc * e_trunc / den, 1)
+            p_dct = {'%d %d' % k: str(q) for k, q in zip(surv, p_app)}
     logging.info("\n\n#####Calculate exact p values for top SNP pairs#####")
-    with open(out_file + sfx, 'w') as fout:
+    with _Phase("survivors_exact_test_and_write"), open(out_file + sfx, 'w') as fout:
         # header of .exact_p with the token p_app spliced in (remma_epiAA_approx.py:41-50)
         fout.write('snp_0 snp_1 eff var chi p_app p\n')
         if surv:

@@ -286,6 +286,21 @@ def parallel_lists(num_snp, parallel, all_pairs=False):
     return list(range(p0, p1)) + list(range(p2, p3)), [p0, p1, p2, p3]
 
 
+def random_pairs(num_snp, out_file, num_pair=100000, num_each_pair=5000, ordered=True):
+    """gmat/remma/random_pair.py:21-34 (ordered: i < j, the AA / DD sampler) and :52-65 (not ordered: i != j, the AD
+    sampler), step by step: draws from the global numpy RNG, a set of 'i j' strings filled through a temporary set
+    per draw, truncation of the set's iteration order, np.savetxt, np.loadtxt of the file just written."""
+    seen = set()
+    while len(seen) < num_pair:
+        draw = np.random.randint(num_snp, size=(num_each_pair, 2))
+        draw = draw[draw[:, 0] < draw[:, 1]] if ordered else draw[draw[:, 0] != draw[:, 1]]
+        text = np.array(draw, dtype=str)
+        seen.update(set(map(lambda a, b: a + ' ' + b, text[:, 0], text[:, 1])))
+    kept = list(seen)[:num_pair]
+    np.savetxt(out_file, np.array(kept), fmt="%s", header='snp_0 snp_1', comments='')
+    return np.loadtxt(out_file, dtype=int, skiprows=1)
+
+
 # ---------------------------------------------------------------- REML (row f3), numpy restatement
 def wemai_multi_gmat(y, xmat, zmat, gmat_lst, init=None, maxiter=200, cc_par=1.0e-8, cc_gra=1.0e-6):
     """gmat/uvlmm/uvlmm_varcom.py:8-104 restated: weighted EM + AI REML.  Pinned by tests/test_oracle.py against

@@ -138,8 +138,23 @@ def test_random_pair_restatement(tmp_path):
     a = random_pair(500, out_file=str(tmp_path / "rp"), num_pair=6000)
     assert a.shape == (6000, 2) and (a[:, 0] < a[:, 1]).all() and len({tuple(r) for r in a}) == 6000
     assert open(str(tmp_path / "rp")).readline() == "snp_0 snp_1\n"
+    assert np.array_equal(a, np.loadtxt(str(tmp_path / "rp"), dtype=int, skiprows=1))   # what the reference reads back
     b = random_pairAD(500, out_file=str(tmp_path / "rq"), num_pair=6000)
     assert (b[:, 0] != b[:, 1]).all() and (b[:, 0] > b[:, 1]).any()
+    # same RNG state, same process (same string hashes): the same pairs in the same order and the same file bytes as
+    # the step-by-step restatement of random_pair.py (the product builds the strings and the file without numpy's
+    # text machinery)
+    from oracle import oracle
+    for fn, ordered, shape in ((random_pair, True, (1407, 20000)), (random_pairAD, False, (1407, 20000)),
+                               (random_pair, True, (50000, 100000))):
+        np.random.seed(11)
+        got = fn(shape[0], out_file=str(tmp_path / "g"), num_pair=shape[1])
+        state = np.random.get_state()[1].copy()
+        np.random.seed(11)
+        want = oracle.random_pairs(shape[0], str(tmp_path / "w"), num_pair=shape[1], ordered=ordered)
+        assert np.array_equal(got, want) and got.dtype == want.dtype
+        assert open(str(tmp_path / "g"), "rb").read() == open(str(tmp_path / "w"), "rb").read()
+        assert np.array_equal(state, np.random.get_state()[1])        # and the RNG is left where the reference leaves it
 
 
 def test_synth_bed_roundtrip(tmp_path):
@@ -357,3 +372,56 @@ def test_every_reference_front_end_exists_with_the_same_signature():
             got = [[p.name, None if p.default is inspect.Parameter.empty else repr(p.default)]
                    for p in inspect.signature(getattr(mod, name)).parameters.values()]
             assert got == params, (name, got, params)
+
+
+def test_bench_approx_verifier_accepts_a_correct_file_and_rejects_a_wrong_one(tmp_path):
+    """bench.py's checker of the approximate pipeline's file (extra.northstar.blocks.AA_approx): a file built from the
+    oracle's own numbers passes, one corrupted value / one significant row the exact scan does not hold fails."""
+    import importlib.util
+    from scipy.stats import chi2
+    from oracle import oracle
+    import synth
+    spec = importlib.util.spec_from_file_location("bench_mod", os.path.join(ROOT, "bench.py"))
+    bench = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(bench)
+    n, m = 90, 50
+    pre = str(tmp_path / "d")
+    synth.write_dataset(pre, n, m, seed=5, n_planted=3)
+    from gmat_b200.uvlmm.design_matrix import design_matrix_wemai_multi_gmat
+    y, xmat, zmat = design_matrix_wemai_multi_gmat(pre + ".pheno", pre)
+    snp = oracle.read_plink(pre)
+    x = snp - 2 * snp.mean(axis=0) / 2
+    ag = x @ x.T / m
+    pymat, pvpmat = oracle.preamble(y, xmat, zmat, [ag, ag * ag], [0.3, 0.1, 0.6])
+    pairs = np.array([(i, j) for i in range(m - 1) for j in range(i + 1, m)][::7])
+    eff, var, chi, p = bench.oracle_pair_stats(pre, n, m, "AA", pymat, pvpmat, pairs, chi2)
+    # the same numbers by the oracle's own routine
+    U, V = oracle.coded_pair("AA", snp)
+    w = U[:, pairs[:, 0]] * V[:, pairs[:, 1]]
+    np.testing.assert_allclose(eff, (w.T @ pymat).ravel(), rtol=1e-12, atol=1e-14)
+    np.testing.assert_allclose(var, np.sum(w * (pvpmat @ w), axis=0), rtol=1e-12)
+    var_med = float(np.median(var))
+
+    def write(path, eff_rows):
+        with open(path, "w") as f:
+            f.write("snp_0 snp_1 eff var chi p_app p\n")
+            for (a, b), e, v, c, q in zip(pairs.tolist(), eff_rows, var, chi, p):
+                e_tr = float("%g" % e)
+                f.write(" ".join([str(a), str(b), repr(float(e)), repr(float(v)), repr(float(c)),
+                                  str(chi2.sf(e_tr * e_tr / var_med, 1)), repr(float(q))]) + "\n")
+    bench.NS_P_CUT = cut = 0.05              # the tiny data set has nothing at the north-star cut
+    exact = {(int(a), int(b)) for (a, b), q in zip(pairs.tolist(), p) if q < cut}
+    good = str(tmp_path / "good")
+    write(good, eff)
+    res = bench.verify_approx_file(good, pre, n, m, pymat, pvpmat, exact, None, chi2)
+    assert res["verified"], res
+    assert res["rows_in_file"] == len(pairs) and abs(res["null_variance"] / var_med - 1) < 1e-6
+    assert res["recall_of_exact_scan_rows"] == 1.0
+    bad_eff = eff.copy()
+    bad_eff[np.argmin(p)] *= 1 + 1e-6
+    bad = str(tmp_path / "bad")
+    write(bad, bad_eff)
+    assert not bench.verify_approx_file(bad, pre, n, m, pymat, pvpmat, exact, None, chi2)["verified"]
+    assert len(exact) > 3
+    fewer = set(sorted(exact)[1:])
+    assert not bench.verify_approx_file(good, pre, n, m, pymat, pvpmat, fewer, None, chi2)["verified"]
