@@ -228,7 +228,8 @@ class I8Exact(object):
     four extra plane rows.  Every step is a kernel of libgmat_b200.so; torch owns the buffers, streams and events.
     Built once per scan (operands of the second SNPs stay resident: integer codes [m][ld] int8, o_j, sum a_j^2)."""
 
-    PLANE_BYTES = 4 << 30          # budget of ONE digit-plane buffer (first SNPs per launch follow from it); two exist
+    # budget of ONE digit-plane buffer in bytes (first SNPs per launch follow from it); two exist.  GMAT_B200_I8_PLANE_GIB
+    PLANE_BYTES = int(os.environ.get("GMAT_B200_I8_PLANE_GIB", "4")) << 30
     MAX_BATCH = 128                # first SNPs per launch at most
     RECHECK_TOL = 2.5e-10          # a pair is re-evaluated in FP64 when 10 sigma of the split error > this x |var|
     RECHECK_CAP = 1 << 20
