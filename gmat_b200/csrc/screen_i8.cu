@@ -502,7 +502,7 @@ extern "C" int gmat_b200_screen_operand(const unsigned char *bed_dev, long long 
     // byte[code]: plain {0, 0, 1, 2} / {0, 0, 1, 0}; tripled (code 01 = 1/3, x 3): {0, 1, 3, 6} / {0, 1, 3, 0}
     const unsigned tab = tripled ? (coding == GMAT_B200_CODING_DOM ? 0x00030100u : 0x06030100u)
                                  : (coding == GMAT_B200_CODING_DOM ? 0x00010000u : 0x02010000u);
-    int rc = launch_i8_dosage(bed_dev, (int)n, m, row_bytes, tab, g8_dev, nullptr, ld, st);
+    int rc = launch_i8_dosage(bed_dev, (int)n, m, row_bytes, tab, nullptr, g8_dev, nullptr, ld, st);
     if (rc != GMAT_B200_OK) return rc;
     sc_dot_kernel<<<(unsigned)((m + 7) / 8), 256, 0, st>>>(g8_dev, ld, (int)n, m, py_dev, tripled ? 1.0 / 3.0 : 1.0,
                                                           t_dev);

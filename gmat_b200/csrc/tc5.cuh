@@ -140,6 +140,7 @@ __device__ __forceinline__ void mbar_arrive_leader(uint64_t *bar) {
 // 2-bit store -> int8 codes g8[snp][k] = byte code_of(c) of `tab` (byte c = the value of 2-bit code c), 0 for k >= n;
 // g2 (optional): the same values 2 bits each.  Defined in ozaki.cu.
 int launch_i8_dosage(const unsigned char *bed_dev, int n, long long m, long long row_bytes, unsigned tab,
+                     const int *counts_dev /* nullable: per-SNP minor-allele coding of the additive table */,
                      signed char *g8_dev, unsigned char *g2_dev, int ld, cudaStream_t st);
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,

@@ -234,6 +234,7 @@ class I8Exact(object):
     RECHECK_TOL = 2.5e-10          # a pair is re-evaluated in FP64 when 10 sigma of the split error > this x |var|
     RECHECK_CAP = 1 << 20
     FIRST_BATCH = 16               # the first launch of a scan is small: its operands cannot be built behind a scan
+    MINOR_ALLELE = True            # code additive second SNPs by their minor allele (False: A/B runs of scripts/i8_accuracy.py)
 
     def __init__(self, store, lutU, lutV, coding_v, py_dev, pvp_dev, n_planes=None, packed=None):
         self.store, self.lutU, self.lutV, self.py = store, lutU, lutV, py_dev.reshape(-1).contiguous()
@@ -246,12 +247,16 @@ class I8Exact(object):
         self.ld = int(lib.gmat_b200_i8_ld(n))
         self.g8 = torch.empty((m, self.ld), dtype=torch.int8, device=dev)
         self.g2 = torch.empty((m, self.ld // 4), dtype=torch.uint8, device=dev)
+        # with the counts: additive SNPs are coded by their MINOR allele (a' = 2 - a where 11 outnumbers 00): same
+        # var, eff sign restored by the scan, and the split error -- proportional to sum a^2 -- up to 35x smaller
         check(lib.gmat_b200_i8_dosage(_p(store.bed, "unsigned char *"), n, m, store.row_bytes, coding_v,
+                                      _p(store.counts, "int *") if self.MINOR_ALLELE else ffi.NULL,
                                       _p(self.g8, "signed char *"), _p(self.g2, "unsigned char *"), self.ld,
                                       _stream()), "gmat_b200_i8_dosage")
         self.offs = torch.empty((m,), dtype=torch.float64, device=dev)
         self.asq = torch.empty((m,), dtype=torch.float64, device=dev)
         check(lib.gmat_b200_i8_offs(_p(store.counts, "int *"), _p(lutV, "double *"), m, coding_v,
+                                    1 if self.MINOR_ALLELE else 0,
                                     _p(self.offs, "double *"), _p(self.asq, "double *"), _stream()),
               "gmat_b200_i8_offs")
         self.amax = torch.empty((1,), dtype=torch.float64, device=dev)

@@ -248,13 +248,20 @@ long long gmat_b200_i8_ld(long long n);      /* bytes per row AND rows per plane
                                               * to 4, plus the 4 extra rows, rounded up to 256                   */
 /* integer code of every SNP: g8[snp][k] = dosage {0,1,2} (ADD) or heterozygote indicator (DOM), 0 for a missing
  * call and for k >= n; ld a multiple of 16, >= n.  g2_dev (optional, [m][ld/4]): the same values packed 2 bits each,
- * low bits first (what the scan kernel's epilogue reads)                                                       */
+ * low bits first (what the scan kernel's epilogue reads).
+ * counts_dev (optional, [m][4] genotype counts; what the exact engine passes): an additive SNP with more 11 than 00
+ * homozygotes is coded by the OTHER allele, a' = 2 - a.  v'_j = a'_j - (2 - o_j) = -v_j, so var_ij is unchanged and
+ * eff_ij changes sign (gmat_b200_i8_offs marks the SNP, the scan restores the sign); sum_k a'^2 -- which the error of
+ * the digit-plane split scales with -- is up to 35x smaller.  NULL: the plain dosage for every SNP.              */
 int gmat_b200_i8_dosage(const unsigned char *bed_dev, long long n, long long m, long long row_bytes, int coding,
-                        signed char *g8_dev /* [m][ld] */, unsigned char *g2_dev /* [m][ld/4] or NULL */,
-                        long long ld, void *stream);
-/* per second SNP: offs[j] = o_j = -lutV[j][0] with the two flags above, asq[j] = sum_k a_jk^2 (from the counts)   */
+                        const int *counts_dev /* [m][4] or NULL */, signed char *g8_dev /* [m][ld] */,
+                        unsigned char *g2_dev /* [m][ld/4] or NULL */, long long ld, void *stream);
+/* per second SNP: offs[j] = o_j = -lutV[j][0] with the two flags above, |asq[j]| = sum_k a_jk^2 (from the counts);
+ * for an additive SNP coded by the other allele (see gmat_b200_i8_dosage with counts) offs[j] = 2 - o_j, the sums are
+ * those of a' = 2 - a, and asq[j] carries a NEGATIVE sign as the mark the scan kernel reads                       */
 int gmat_b200_i8_offs(const int *counts_dev /* [m][4] */, const double *lutV_dev /* [m][4] */, long long m,
-                      int coding, double *offs_dev /* [m] */, double *asq_dev /* [m] */, void *stream);
+                      int coding, int minor_allele /* 1 when gmat_b200_i8_dosage was given the counts, else 0 */,
+                      double *offs_dev /* [m] */, double *asq_dev /* [m] */, void *stream);
 /* *out_dev = max |x[k]| (NaN if any x is NaN)                                                                    */
 int gmat_b200_absmax(const double *x_dev, long long len, double *out_dev, void *stream);
 /* Per batch of n_i first SNPs (ilist_dev): u[ii][k] = lutU[i][code] (coded first SNPs), r = u o (Z'PZ u)

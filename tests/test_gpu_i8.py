@@ -84,11 +84,23 @@ def test_i8_operands_exact(eng, tmp_path):
     raw = oracle.read_bed_raw(prefix)                                     # [m][n] 0/1/2
     pyd = torch.as_tensor(pymat.ravel().copy()).cuda()
     pvd = torch.as_tensor(pvp).cuda().contiguous()
-    for coding, want in ((eng.ADD, raw), (eng.DOM, np.where(raw > 1.5, 0.0, raw))):
+    # additive SNPs with more 11 than 00 homozygotes are coded by the other allele (2 - dosage) and marked by the sign
+    # of asq; the dominance indicator is never flipped
+    major = (raw == 2).sum(axis=1) > (raw == 0).sum(axis=1)
+    assert 10 < major.sum() < m - 10
+    for coding, want, flipped in ((eng.ADD, np.where(major[:, None], 2.0 - raw, raw), major),
+                                  (eng.DOM, np.where(raw > 1.5, 0.0, raw), np.zeros(m, dtype=bool))):
         sc = eng.I8Exact(store, store.lut(coding), store.lut(coding), coding, pyd, pvd)
         g8 = sc.g8.cpu().numpy()
         assert np.array_equal(g8[:, :n].astype(np.float64), want) and not g8[:, n:].any()
-        assert np.array_equal(sc.asq.cpu().numpy(), (want ** 2).sum(axis=1))
+        g2 = sc.g2.cpu().numpy()
+        unpacked = np.stack([(g2 >> (2 * q)) & 3 for q in range(4)], axis=2).reshape(m, -1)
+        assert np.array_equal(unpacked[:, :sc.ld], g8)
+        asq = sc.asq.cpu().numpy()
+        assert np.array_equal(np.abs(asq), (want ** 2).sum(axis=1)) and np.array_equal(np.signbit(asq), flipped)
+        offs = sc.offs.cpu().numpy()
+        o_ref = -store.lut(coding).cpu().numpy()[:, 0]
+        assert np.array_equal(offs, np.where(flipped, 2.0 - o_ref, o_ref))
     U, _ = oracle.coded_pair("AA", oracle.read_plink(prefix))            # [n][m] coded columns
     for planes in (3, 6, 7):
         sc = eng.I8Exact(store, store.lut(eng.ADD), store.lut(eng.ADD), eng.ADD, pyd, pvd, n_planes=planes)
@@ -314,6 +326,10 @@ def test_i8_weak_pairs_are_rechecked_in_fp64(eng, tmp_path, planes):
     for snp in (2, 9, 50, 51, 100):                                     # singletons / rare variants
         g[snp, :] = 0
         g[snp, [snp, snp + 7, 2 * snp + 1]] = 1
+    for snp in (30, 31, 77):                                            # the same with the COUNTED allele the common
+        g[snp, :] = 2                                                   # one: coded by the other allele in the engine
+        g[snp, [snp, snp + 5, 3 * snp + 1]] = 1
+        g[snp, snp + 11] = 0
     prefix, _ = _dataset(tmp_path, n, m, seed=1, geno=g)
     pymat, pvp = _random_model(n, 12)
     store = eng.GenotypeStore(prefix)
