@@ -18,8 +18,10 @@ print('reference %.4g ratio e2e %.0f same_config %s' % (ref['value'], d['e2e']['
 x=d['extra']
 print('northstar verified', x['northstar'].get('verified'), {k:(round(b['seconds'],2), b['verified']) for k,b in x['northstar']['blocks'].items()})
 print('screen C3 %.3f ms frac %.2f; northstar clean %.2f ms frac %.2f; missing %.2f ms frac %.2f' % (x['approx_screen']['seconds']*1e3, x['approx_screen']['roofline']['frac'], x['approx_screen_northstar']['clean']['seconds']*1e3, x['approx_screen_northstar']['clean']['roofline']['frac'], x['approx_screen_northstar']['missing_0.5pct']['seconds']*1e3, x['approx_screen_northstar']['missing_0.5pct']['roofline']['frac']))
-print('agmat %s %.2f ms frac %.2f (of 2x int8) i8 %.2f ms' % (x['agmat']['engine'], x['agmat']['seconds']*1e3, x['agmat']['roofline']['frac'], x['agmat']['i8_engine']['seconds']*1e3))
+print('agmat %s %.2f ms frac %.2f (of the measured FP4 issue rate) i8 %.2f ms' % (x['agmat']['engine'], x['agmat']['seconds']*1e3, x['agmat']['roofline']['frac'], x['agmat']['i8_engine']['seconds']*1e3))
 print('decode %.0f GB/s' % x['decode']['gb_per_s'])
+b=x['northstar']['blocks']['AA_approx']
+print('AA_approx %.3f s %.3g pairs/s verified %s recall %s phases %s' % (b['seconds'], b['pairs_per_s'], b['verified'], b.get('recall_of_exact_scan_rows'), b['phases_s']))
 PY
 BN="python bench.py --steps 2 --warmup 1 --no-cpu --no-extra --no-northstar"
 timeout 1500 ncu --metrics gpu__time_duration.sum --clock-control none --csv \
