@@ -221,6 +221,32 @@ def i8_planes():
     return int(os.environ.get("GMAT_B200_I8_PLANES", "6"))
 
 
+# The two digit-plane buffers of an I8Exact (4 GiB each by default) are kept for the next engine of the process: a
+# fresh cudaMalloc of that size costs 20 - 400 ms (measured on the multi-GPU boxes, where every rank allocates at the
+# same moment), which a scan of a second or two cannot hide; the front-ends build one engine per call (AA, then AD,
+# then DD ...).  A buffer is zeroed when handed out (3 ms): the split kernel never writes the blocks right of the
+# diagonal or the padding, and the geometry of the previous user may have been another.
+_PLANE_FREE = {}
+
+
+def _acquire_plane_buffer(dev, nbytes):
+    key = (dev.index if dev.index is not None else torch.cuda.current_device(), int(nbytes))
+    for other in [k for k in _PLANE_FREE if k[0] == key[0] and k != key]:
+        del _PLANE_FREE[other]                         # another size is wanted now: give the old ones back to torch
+    free = _PLANE_FREE.get(key)
+    if free:
+        return free.pop().zero_()
+    return torch.zeros((int(nbytes),), dtype=torch.int8, device=dev)
+
+
+def _release_plane_buffers(dev, bufs):
+    for b in bufs:
+        key = (dev.index if dev.index is not None else torch.cuda.current_device(), int(b.numel()))
+        lst = _PLANE_FREE.setdefault(key, [])
+        if len(lst) < 2:
+            lst.append(b)
+
+
 class I8Exact(object):
     """INT8 tensor-core engine of the exact scan (gmat_b200/csrc/ozaki.cu): same statistics as
     ``epi_exact_scan`` (remma_epiAA.py:72-82), the n^2-per-pair quadratic form evaluated with tcgen05 int8 MMAs on
@@ -266,7 +292,7 @@ class I8Exact(object):
         self.batch = int(max(1, min(self.MAX_BATCH, self.PLANE_BYTES // per_first)))
         # two plane buffers (and two sets of per-batch scratch): the operands of batch k+1 are built on a side
         # stream while the scan of batch k is running
-        self.planes = [torch.zeros((self.batch * per_first,), dtype=torch.int8, device=dev) for _ in range(2)]
+        self.planes = [_acquire_plane_buffer(dev, self.batch * per_first) for _ in range(2)]
         self.u = [torch.empty((self.batch, n), dtype=torch.float64, device=dev) for _ in range(2)]
         self.r = [torch.empty((self.batch, n), dtype=torch.float64, device=dev) for _ in range(2)]
         self.side = [torch.empty((self.batch, 8), dtype=torch.float64, device=dev) for _ in range(2)]
@@ -278,6 +304,15 @@ class I8Exact(object):
             raise ValueError("GMAT_B200_I8_VARIANT must be 2 or 3")
         self.kernel_events = None      # bench.py: list of (start, end) CUDA events around every i8_scan launch
         self.last_rechecked = 0        # pairs of the last scan that were re-evaluated in FP64
+
+    def __del__(self):
+        try:
+            planes, self.planes = self.planes, []
+            torch.cuda.current_stream(self.store.device).synchronize()      # nothing of this engine is still running
+            self._prep_stream.synchronize()
+            _release_plane_buffers(self.store.device, planes)
+        except Exception:                                                    # interpreter shutdown
+            pass
 
     def _work_items(self, ih, pair_space):
         """(item_prefix[n_i+1], jt0[n_i]) int32 host arrays: tiles of 256 second SNPs every first SNP needs."""
