@@ -527,16 +527,29 @@ def multi_gpu_parity(torch, dist, engine, synth, remma_epiAA, rank, world, workd
     np.random.seed(12)                                       # rank 0's draws decide the imputation of both runs
     remma_epiAA(pre + ".pheno", pre, [ag, ag * ag], vc, snp_lst_0=first, p_cut=1e-3, out_file=pre + ".sharded")
     barrier()
+    # once more with the speed-aware deal of long scans forced on this small one (calibration share, exchange of the
+    # measured rates, re-deal of the rest: _core.exact_scan)
+    from gmat_b200.remma import _core
+    keep_min, _core.REBALANCE_MIN_WORK = _core.REBALANCE_MIN_WORK, 0.0
+    np.random.seed(12)
+    remma_epiAA(pre + ".pheno", pre, [ag, ag * ag], vc, snp_lst_0=first, p_cut=1e-3, out_file=pre + ".sharded2")
+    _core.REBALANCE_MIN_WORK = keep_min
+    rates = list(_core.LAST_RATES)
+    barrier()
     res = None
     if rank == 0:
         np.random.seed(12)
         with par.single_rank():
             remma_epiAA(pre + ".pheno", pre, [ag, ag * ag], vc, snp_lst_0=first, p_cut=1e-3, out_file=pre + ".single")
         a, b = open(pre + ".sharded", "rb").read(), open(pre + ".single", "rb").read()
-        res = {"identical": a == b, "rows": a.count(b"\n") - 1, "bytes": len(a), "missing_calls": int(st.n_missing()),
+        a2 = open(pre + ".sharded2", "rb").read()
+        res = {"identical": a == b and a2 == b, "identical_static_deal": a == b, "identical_speed_aware_deal": a2 == b,
+               "speed_aware_deal_used": len(rates) == world,
+               "rows": a.count(b"\n") - 1, "bytes": len(a), "missing_calls": int(st.n_missing()),
                "what": "remma_epiAA on synthetic n=%d x m=%d with %.1f %% missing calls, %d first-SNPs, p_cut=1e-3: "
                        "output file of the %d-rank sharded run (rank 0 imputes and broadcasts the 2-bit store, hits "
-                       "gathered over NCCL) vs the same call on rank 0 alone" % (n, m, 0.2, len(first), world)}
+                       "gathered over NCCL), with the static deal and with the speed-aware deal forced, vs the same "
+                       "call on rank 0 alone" % (n, m, 0.2, len(first), world)}
     barrier()
     return res
 
@@ -606,6 +619,8 @@ def northstar(args, torch, dist, engine, _core, synth, rank, world, barrier, red
                    "first_snps": len(first) if first is not None else (m if kind == "AD" else m - 1),
                    "grms": len(gmat_lst), "records": sum(1 for _ in open(pheno)),
                    "phases_max_over_ranks_s": {k: round(v, 3) for k, v in phases.items()}}
+            if _core.LAST_RATES:           # the speed-aware deal was used: relative scan rates of the ranks it measured
+                blk["rank_rates_rel"] = list(_core.LAST_RATES)
             if not args.no_verify:
                 blk.update(verify_file(out_file, pre, pheno, kind, model_key, gmat_lst, var_com, first, planted, n, m,
                                        oracle_models, design_matrix_wemai_multi_gmat, chi2))

@@ -202,6 +202,8 @@ def _write_rows(out_file, cols):
     res.to_csv(out_file, sep=' ', header=False, index=False, mode='a')
 
 
+REBALANCE_MIN_WORK = 1.5e15     # pairs per rank x n^2 from which the speed-aware deal is used (~3 s of scan per rank)
+LAST_RATES = []                 # relative scan rates of the ranks measured by the last speed-aware deal (bench.py prints them)
 PHASES = {}     # wall seconds of the phases of the last exact_scan call on this rank (bench.py prints them)
 
 
@@ -253,7 +255,19 @@ def exact_scan(kind, y, xmat, zmat, gmat_lst, var_com, bed_file, snp_lst_0=None,
     # reference's own comparison on scipy p-values (remma_epiAA.py:77,81)
     chi_cut = -1.0 if p_cut >= 1.0 else float(chi2.isf(p_cut, 1)) * (1.0 - 1e-9)
     pair_space = engine.PAIRS_ALL if kind.all_pairs else engine.PAIRS_UPPER
-    my_list = par.shard_first_snps(snp_lst_0, num_snp, kind.all_pairs, rank, world)
+    # Sharding over the ranks: a static deal of first-SNP blocks by pair count; for a long scan (seconds per rank)
+    # the deal is speed-aware -- a first share is scanned and timed, the rest dealt by the measured rates, because
+    # the GPUs of one box run a few per cent apart under the power cap and everyone waits for the slowest
+    # (GMAT_B200_REBALANCE=0 keeps the static deal)
+    n_tests = float(num_snp) * len(snp_lst_0) if kind.all_pairs else float(np.maximum(num_snp - 1 - snp_lst_0, 0).sum())
+    rebalance = (world > 1 and os.environ.get("GMAT_B200_REBALANCE", "1") != "0"
+                 and n_tests / world * float(store.n) ** 2 >= REBALANCE_MIN_WORK and len(snp_lst_0) > 0)
+    rest = None
+    del LAST_RATES[:]
+    if rebalance:
+        my_list, head_pairs, rest = par.calibration_split(snp_lst_0, num_snp, kind.all_pairs, rank, world)
+    else:
+        my_list = par.shard_first_snps(snp_lst_0, num_snp, kind.all_pairs, rank, world)
     clock_t0 = time.perf_counter()
     cpu_t0 = time.process_time()
 
@@ -270,14 +284,27 @@ def exact_scan(kind, y, xmat, zmat, gmat_lst, var_com, bed_file, snp_lst_0=None,
     with _Phase("engine_init"):
         scan = model.scanner(store, lut_u, lut_v, kind.coding_v)
         logging.info("Exact-scan engine: %s", model.engine_note)
-    for chunk in _chunks(kind, my_list, num_snp):
-        with _Phase("scan"):
-            hits = scan(np.asarray(chunk, dtype=np.int64), pair_space, chi_cut)
-        if world == 1:
-            with _Phase("write"):
-                emit(hits)                                     # appended launch by launch (resume granularity)
-        else:
-            mine.append(hits)
+    while True:
+        t_scan0 = time.perf_counter()
+        for chunk in _chunks(kind, my_list, num_snp):
+            with _Phase("scan"):
+                hits = scan(np.asarray(chunk, dtype=np.int64), pair_space, chi_cut)
+            if world == 1:
+                with _Phase("write"):
+                    emit(hits)                                 # appended launch by launch (resume granularity)
+            else:
+                mine.append(hits)
+        if rest is None:
+            break
+        # the calibration share is done: exchange the measured rates (pairs/s; one float per rank, no data-path
+        # collective) and take this rank's part of what is left
+        torch.cuda.synchronize()
+        secs = max(time.perf_counter() - t_scan0, 1e-6)
+        rates = par.all_gather_floats(head_pairs / secs if head_pairs > 0 else 0.0, store.device)
+        good = [v for v in rates if v > 0]
+        rates = [v if v > 0 else (min(good) if good else 1.0) for v in rates]
+        LAST_RATES[:] = [round(v / max(rates), 4) for v in rates]
+        my_list, rest = par.redeal(rest, rates, rank), None
     if world > 1:
         # the only collective of the scan: variable-length gather of hit records to rank 0
         with _Phase("gather"):

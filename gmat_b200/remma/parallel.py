@@ -72,6 +72,73 @@ def shard_first_snps(snp_lst_0, num_snp, all_pairs, rank, world):
     return np.concatenate(mine).tolist() if mine else []
 
 
+def _blocks(snp_lst_0, num_snp, all_pairs):
+    snp_lst_0 = np.asarray(list(snp_lst_0), dtype=np.int64)
+    weight = np.full(len(snp_lst_0), num_snp, dtype=np.int64) if all_pairs else np.maximum(num_snp - 1 - snp_lst_0, 0)
+    starts = np.arange(0, len(snp_lst_0), SHARD_BLOCK)
+    wblk = np.add.reduceat(weight, starts) if len(starts) else np.zeros(0, dtype=np.int64)
+    return snp_lst_0, starts, wblk
+
+
+def deal_blocks(wblk, rates, load=None):
+    """Owner of every block: in order, to the rank that would FINISH it first, (load + w) / rate (ties: lowest rank).
+    With equal rates this is the deal of shard_first_snps."""
+    world = len(rates)
+    load = [0.0] * world if load is None else [float(v) for v in load]
+    owner = np.empty(len(wblk), dtype=np.int64)
+    for b, w in enumerate(wblk.tolist()):
+        r = min(range(world), key=lambda q: ((load[q] + w) / rates[q], q))
+        owner[b] = r
+        load[r] += w
+    return owner
+
+
+CALIBRATION_SHARE = 0.08
+
+
+def calibration_split(snp_lst_0, num_snp, all_pairs, rank, world, share=CALIBRATION_SHARE):
+    """Speed-aware sharding, step 1.  GPUs of one box do not run at the same clock under the power cap (a few per cent
+    apart), and a static deal by pair count makes every rank wait for the slowest one.  So: the static deal's first
+    blocks of every rank, ``share`` of its pairs, are scanned first and timed (``head``, this rank's first SNPs);
+    the rest of ALL ranks' blocks (``rest``: (snp_lst_0 array, block starts, block weights) in list order) is dealt again
+    by ``redeal`` once the ranks have exchanged their measured rates.  Every rank computes the same split."""
+    lst, starts, wblk = _blocks(snp_lst_0, num_snp, all_pairs)
+    owner = deal_blocks(wblk, [1.0] * world)
+    total = np.array([wblk[owner == r].sum() for r in range(world)], dtype=np.float64)
+    in_head = np.zeros(len(wblk), dtype=bool)
+    acc = [0.0] * world
+    for b in range(len(wblk)):
+        r = int(owner[b])
+        if acc[r] < share * total[r]:
+            in_head[b] = True
+            acc[r] += float(wblk[b])
+    head = [lst[starts[b]:starts[b] + SHARD_BLOCK] for b in range(len(wblk)) if in_head[b] and owner[b] == rank]
+    head = np.concatenate(head).tolist() if head else []
+    rest_blocks = np.flatnonzero(~in_head)
+    return head, float(acc[rank]), (lst, starts[rest_blocks], wblk[rest_blocks])
+
+
+def redeal(rest, rates, rank):
+    """Speed-aware sharding, step 2: this rank's first SNPs of the remaining blocks, dealt by the measured rates
+    (pairs per second of every rank's calibration scan)."""
+    lst, starts, wblk = rest
+    owner = deal_blocks(wblk, [float(v) for v in rates])
+    mine = [lst[s:s + SHARD_BLOCK] for s, o in zip(starts.tolist(), owner.tolist()) if o == rank]
+    return np.concatenate(mine).tolist() if mine else []
+
+
+def all_gather_floats(value, device):
+    """One float of every rank, as a list in rank order (all ranks get the same list)."""
+    rank, world = rank_world()
+    if world == 1:
+        return [float(value)]
+    dev = device if dist.get_backend() == "nccl" else torch.device("cpu")
+    t = torch.tensor([float(value)], dtype=torch.float64, device=dev)
+    out = [torch.zeros_like(t) for _ in range(world)]
+    dist.all_gather(out, t)
+    return [float(v.item()) for v in out]
+
+
 def gather_hits(local, device):
     """Gather variable-length hit arrays (engine.HIT_DTYPE) to rank 0.  Returns the concatenation on rank 0,
     None elsewhere.  One all_gather of counts + one padded all_gather of records."""

@@ -184,6 +184,14 @@ hits["snp_1"] = rank
 hits["eff"] = np.arange(len(hits)) + 0.5 * rank
 out = par.gather_hits(hits, torch.device("cpu"))
 empty = par.gather_hits(np.zeros(0, dtype=HIT_DTYPE), torch.device("cpu"))
+# the speed-aware deal's exchange of measured rates, and the deal itself on two ranks: every first SNP once
+assert par.all_gather_floats(rank + 0.5, torch.device("cpu")) == [0.5, 1.5]
+head, head_pairs, rest = par.calibration_split(list(range(m - 1)), m, False, rank, 2)
+rates = par.all_gather_floats([1.0, 0.8][rank], torch.device("cpu"))
+tail = par.redeal(rest, rates, rank)
+cover = par.gather_hits(np.array([(i, 0, 0.0, 0.0, 0.0) for i in head + tail], dtype=HIT_DTYPE), torch.device("cpu"))
+if rank == 0:
+    assert np.array_equal(np.sort(cover["snp_0"]), np.arange(m - 1))
 if rank == 0:
     n0 = len(par.shard_first_snps(list(range(m - 1)), m, False, 0, 2)) // 7
     n1 = len(par.shard_first_snps(list(range(m - 1)), m, False, 1, 2)) // 8
@@ -425,3 +433,37 @@ def test_bench_approx_verifier_accepts_a_correct_file_and_rejects_a_wrong_one(tm
     assert len(exact) > 3
     fewer = set(sorted(exact)[1:])
     assert not bench.verify_approx_file(good, pre, n, m, pymat, pvpmat, fewer, None, chi2)["verified"]
+
+
+def test_speed_aware_deal_covers_the_list_once_and_follows_the_rates():
+    """parallel.calibration_split + redeal (the speed-aware sharding of long multi-GPU scans): whatever the measured
+    rates, every first SNP is scanned by exactly one rank; with equal rates the pair counts are balanced like the
+    static deal; a rank measured 10 % slower gets ~10 % fewer pairs of the re-dealt part."""
+    from gmat_b200.remma import parallel as par
+    m = 50000
+    for all_pairs, lst in ((False, np.arange(m - 1)), (True, np.arange(m)), (False, np.arange(0, m - 1, 8))):
+        w = (lambda a: np.full(len(a), m) if all_pairs else m - 1 - np.asarray(a))
+        for world, rates in ((2, [1.0, 1.0]), (4, [1.0, 0.9, 1.0, 1.05]), (8, [1.0] * 7 + [0.9])):
+            heads, tails, head_pairs = [], [], []
+            for r in range(world):
+                head, hp, rest = par.calibration_split(lst, m, all_pairs, r, world)
+                heads.append(head)
+                head_pairs.append(hp)
+                tails.append(par.redeal(rest, rates, r))
+                assert hp == float(np.sum(w(head)))
+            everything = np.concatenate([np.asarray(h + t, dtype=np.int64) for h, t in zip(heads, tails)])
+            assert len(everything) == len(lst) and np.array_equal(np.sort(everything), lst)
+            total = float(np.sum(w(lst)))
+            blk = par.SHARD_BLOCK * m
+            for r in range(world):                  # the calibration share: 8 % of a rank's pairs, to within a block
+                assert 0.08 * (total / world - blk) <= head_pairs[r] <= 0.08 * (total / world + blk) + blk
+            tail_pairs = np.array([float(np.sum(w(t))) for t in tails])
+            want = np.asarray(rates) / np.sum(rates) * tail_pairs.sum()
+            assert np.max(np.abs(tail_pairs - want)) <= 2 * par.SHARD_BLOCK * m
+    # equal rates = the static deal
+    lst = np.arange(m - 1)
+    _, starts, wblk = par._blocks(lst, m, False)
+    owner = par.deal_blocks(wblk, [1.0] * 4)
+    for r in range(4):
+        mine = np.concatenate([lst[s:s + par.SHARD_BLOCK] for s, o in zip(starts, owner) if o == r])
+        assert np.array_equal(mine, par.shard_first_snps(lst, m, False, r, 4))
