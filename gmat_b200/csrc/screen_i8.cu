@@ -477,6 +477,16 @@ __global__ void __launch_bounds__(256) screen_exact_kernel(
 // beyond n: staged once per block), so a warp reads 32 consecutive doubles per step.  Same products, same threshold,
 // same hit records; the sum runs per lane over its words, then the same shuffle tree.
 constexpr int SC_ROWS_MAX_N = 20480;                              // 16 x (n/16 rounded up to 32) doubles of shared memory
+// append a warp's buffered hit records to the global list: one atomic, the records copied by the lanes
+__device__ __forceinline__ void sc_flush_hits(const gmat_b200_hit *buf, int nbuf, int lane, gmat_b200_hit *hits,
+                                              long long cap, unsigned long long *count) {
+    __syncwarp();
+    unsigned long long base = 0;
+    if (lane == 0) base = atomicAdd(count, (unsigned long long)nbuf);
+    base = __shfl_sync(0xffffffffu, base, 0);
+    if (lane < nbuf && (long long)(base + lane) < cap) hits[base + lane] = buf[lane];
+    __syncwarp();
+}
 __global__ void __launch_bounds__(256) screen_exact_rows_kernel(
     const unsigned char *__restrict__ bed, int n, long long row_bytes, const double *__restrict__ lutU,
     const double *__restrict__ lutV, const double *__restrict__ py, const int2 *__restrict__ cand,
@@ -485,8 +495,7 @@ __global__ void __launch_bounds__(256) screen_exact_rows_kernel(
     unsigned long long *__restrict__ count, long long cand_cap, int *__restrict__ status) {
     extern __shared__ double pyT[];                               // [16][wpad]
     __shared__ double prod[8][16];                                // per warp: lutU[i][cu] * lutV[j][cv]
-    __shared__ int s_flag[8], s_off[8];
-    __shared__ unsigned long long s_base;
+    __shared__ gmat_b200_hit hitbuf[8][32];                       // per warp: hit records waiting for their append
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const long long total = (long long)*n_cand;
     if (total > cand_cap) {
@@ -501,62 +510,55 @@ __global__ void __launch_bounds__(256) screen_exact_rows_kernel(
     }
     __syncthreads();
     const bool ge = (flags & GMAT_B200_EFF_GE) != 0, swap = (flags & GMAT_B200_EFF_SWAP) != 0;
-    for (long long base = (long long)blockIdx.x * 8; base < total; base += (long long)gridDim.x * 8) {
-        const long long c = base + warp;
-        const bool active = c < total;
-        int i = 0, j = 0;
+    // Every warp is on its own: it keeps its hit records in a private shared-memory buffer and appends them to the
+    // global list 32 at a time with ONE atomic (the per-iteration block-wide append of the kernel above put an atomic
+    // round trip and two block barriers on the path of every candidate).
+    gmat_b200_hit *mybuf = hitbuf[warp];
+    int nbuf = 0;                                                 // warp-uniform
+    for (long long c = (long long)blockIdx.x * 8 + warp; c < total; c += (long long)gridDim.x * 8) {
+        const int i = cand[c].x, j = cand[c].y;
+        if (lane < 16) prod[warp][lane] = lutU[(size_t)i * 4 + (lane >> 2)] * lutV[(size_t)j * 4 + (lane & 3)];
+        __syncwarp();
+        const unsigned *ri = reinterpret_cast<const unsigned *>(bed + (size_t)i * row_bytes);
+        const unsigned *rj = reinterpret_cast<const unsigned *>(bed + (size_t)j * row_bytes);
         double acc = 0.0;
-        bool hit = false;
-        if (active) {
-            i = cand[c].x; j = cand[c].y;
-            if (lane < 16) prod[warp][lane] = lutU[(size_t)i * 4 + (lane >> 2)] * lutV[(size_t)j * 4 + (lane & 3)];
-            __syncwarp();
-            const unsigned *ri = reinterpret_cast<const unsigned *>(bed + (size_t)i * row_bytes);
-            const unsigned *rj = reinterpret_cast<const unsigned *>(bed + (size_t)j * row_bytes);
-            for (int w0 = 0; w0 < wpad; w0 += 128) {              // passes of four words per row and lane
-                unsigned ci[4], cj[4];
+        for (int w0 = 0; w0 < wpad; w0 += 128) {                  // passes of four words per row and lane
+            unsigned ci[4], cj[4];
 #pragma unroll
-                for (int t = 0; t < 4; ++t) {
-                    const int w = w0 + 32 * t + lane;
-                    const bool in = w < nwords;
-                    ci[t] = in ? __ldg(ri + w) : 0u;
-                    cj[t] = in ? __ldg(rj + w) : 0u;
-                }
-#pragma unroll
-                for (int t = 0; t < 4; ++t) {
-                    const int w = w0 + 32 * t + lane;
-                    if (w0 + 32 * t < wpad) {                     // warp-uniform
-#pragma unroll
-                        for (int x = 0; x < 16; ++x)
-                            acc += prod[warp][(((ci[t] >> (2 * x)) & 3u) << 2) | ((cj[t] >> (2 * x)) & 3u)] *
-                                   pyT[x * wpad + w];
-                    }
-                }
+            for (int t = 0; t < 4; ++t) {
+                const int w = w0 + 32 * t + lane;
+                const bool in = w < nwords;
+                ci[t] = in ? __ldg(ri + w) : 0u;
+                cj[t] = in ? __ldg(rj + w) : 0u;
             }
 #pragma unroll
-            for (int d = 16; d >= 1; d >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, d);
-            const double cut = cut_table != nullptr ? cut_table[binI[i] * 10 + binJ[j]] : eff_cut;
-            const double a = fabs(acc);
-            hit = ge ? a >= cut : a > cut;
-        }
-        if (lane == 0) s_flag[warp] = hit ? 1 : 0;
-        __syncthreads();
-        if (threadIdx.x == 0) {
-            int tot = 0;
+            for (int t = 0; t < 4; ++t) {
+                const int w = w0 + 32 * t + lane;
+                if (w0 + 32 * t < wpad) {                         // warp-uniform
 #pragma unroll
-            for (int w = 0; w < 8; ++w) { s_off[w] = tot; tot += s_flag[w]; }
-            s_base = tot ? atomicAdd(count, (unsigned long long)tot) : 0ULL;
+                    for (int x = 0; x < 16; ++x)
+                        acc += prod[warp][(((ci[t] >> (2 * x)) & 3u) << 2) | ((cj[t] >> (2 * x)) & 3u)] *
+                               pyT[x * wpad + w];
+                }
+            }
         }
-        __syncthreads();
-        if (lane == 0 && hit) {
-            const unsigned long long pos = s_base + (unsigned long long)s_off[warp];
-            if ((long long)pos < cap) {
+#pragma unroll
+        for (int d = 16; d >= 1; d >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, d);
+        const double cut = cut_table != nullptr ? cut_table[binI[i] * 10 + binJ[j]] : eff_cut;
+        const double a = fabs(acc);
+        const bool hit = ge ? a >= cut : a > cut;                 // warp-uniform: acc is the same in every lane
+        __syncwarp();                                             // prod[warp] is rewritten by the next candidate
+        if (hit) {
+            if (lane == 0) {
                 gmat_b200_hit h;
                 h.snp_0 = swap ? j : i; h.snp_1 = swap ? i : j; h.eff = acc; h.var = 0.0; h.chi = 0.0;
-                hits[pos] = h;
+                mybuf[nbuf] = h;
             }
+            ++nbuf;
         }
+        if (nbuf == 32) { sc_flush_hits(mybuf, nbuf, lane, hits, cap, count); nbuf = 0; }
     }
+    if (nbuf > 0) sc_flush_hits(mybuf, nbuf, lane, hits, cap, count);
 }
 
 }  // namespace gb
@@ -733,7 +735,10 @@ extern "C" int gmat_b200_epi_eff_i8p(const unsigned char *bed_dev, long long n, 
                                          16 * ((SC_ROWS_MAX_N / 16 + 31) & ~31) * (int)sizeof(double)));
             attr_set[dev] = true;
         }
-        const int per_sm = smem_bytes <= 48 * 1024 ? 4 : (smem_bytes <= 100 * 1024 ? 2 : 1);
+        // as many blocks per SM as shared memory and the 64 warp slots allow: the kernel is a chain of dependent loads
+        // per candidate (pair -> tables -> rows), latency is hidden by warps
+        int per_sm = (200 * 1024) / (smem_bytes + 10 * 1024);
+        per_sm = per_sm < 1 ? 1 : (per_sm > 8 ? 8 : per_sm);
         screen_exact_rows_kernel<<<(unsigned)(per_sm * sm_count()), 256, smem_bytes, st>>>(
             bed_dev, (int)n, row_bytes, lutU_dev, lutV_dev, py_dev, reinterpret_cast<const int2 *>(cand_dev),
             cand_count_dev, flags, eff_cut, cut_table_dev, binI_dev, binJ_dev, hits_dev, cap, count_dev, cand_cap,
