@@ -239,6 +239,11 @@ def _acquire_plane_buffer(dev, nbytes):
     return torch.zeros((int(nbytes),), dtype=torch.int8, device=dev)
 
 
+def release_plane_buffers():
+    """Give the kept digit-plane buffers (8 GiB per device by default) back to torch's allocator."""
+    _PLANE_FREE.clear()
+
+
 def _release_plane_buffers(dev, bufs):
     for b in bufs:
         key = (dev.index if dev.index is not None else torch.cuda.current_device(), int(b.numel()))
