@@ -58,6 +58,7 @@ struct I8Params {
     long long recheck_cap;
     unsigned long long *recheck_count;
     double *q_debug;             // optional [n_i][m]: a_j' B_i a_j
+    double *e_debug;             // optional [n_i][m]: eff_ij (the rows form of the pair-list engine reads both)
     int trim;                    // issue only the plane rows that can be non-zero (i8p_shape)
 };
 
@@ -113,6 +114,55 @@ __device__ __forceinline__ void i8_load_dosage(const unsigned char *row, uint4 (
     for (int q = 0; q < I8_TK / 64; ++q) a[q] = __ldg(ap + q);
 }
 
+// The same for operand rows whose integer values do not fit two bits (the pair-list engine below: sums of two
+// genotype vectors, values 0..6): codes packed FOUR bits each, 32 registers per 256 ids.
+__device__ __forceinline__ int i8_dot_chunk4(const int (&v)[32], unsigned w0, unsigned w1, unsigned w2, unsigned w3) {
+    int c0 = 0, c1 = 0, c2 = 0, c3 = 0;
+    const unsigned w[4] = {w0, w1, w2, w3};
+#pragma unroll
+    for (int g = 0; g < 4; ++g) {
+#pragma unroll
+        for (int q = 0; q < 8; q += 4) {
+            c0 += (int)((w[g] >> (4 * q)) & 15u) * v[8 * g + q];
+            c1 += (int)((w[g] >> (4 * q + 4)) & 15u) * v[8 * g + q + 1];
+            c2 += (int)((w[g] >> (4 * q + 8)) & 15u) * v[8 * g + q + 2];
+            c3 += (int)((w[g] >> (4 * q + 12)) & 15u) * v[8 * g + q + 3];
+        }
+    }
+    return (c0 + c1) + (c2 + c3);                                 // |.| <= 32 * 15 * 2*128*n: int32 for n < 1.7e4
+}
+__device__ __forceinline__ long long i8_drain_tile4(uint32_t taddr, const uint4 (&a)[I8_TK / 32]) {
+    long long total = 0;
+    int v0[32], v1[32];
+    tmem_ld32(taddr, v0);
+#pragma unroll
+    for (int ch = 0; ch < I8_TK / 32; ch += 2) {
+        tmem_ld_wait();
+        tmem_ld32(taddr + (ch + 1) * 32, v1);
+        total += i8_dot_chunk4(v0, a[ch].x, a[ch].y, a[ch].z, a[ch].w);
+        tmem_ld_wait();
+        if (ch + 2 < I8_TK / 32) tmem_ld32(taddr + (ch + 2) * 32, v0);
+        total += i8_dot_chunk4(v1, a[ch + 1].x, a[ch + 1].y, a[ch + 1].z, a[ch + 1].w);
+    }
+    return total;
+}
+__device__ __forceinline__ void i8_load_dosage4(const unsigned char *row, uint4 (&a)[I8_TK / 32]) {
+    const uint4 *ap = reinterpret_cast<const uint4 *>(row);
+#pragma unroll
+    for (int q = 0; q < I8_TK / 32; ++q) a[q] = __ldg(ap + q);
+}
+template <int BITS> struct I8Codes;
+template <> struct I8Codes<2> {
+    uint4 a[I8_TK / 64];
+    __device__ __forceinline__ void load(const unsigned char *row) { i8_load_dosage(row, a); }
+    __device__ __forceinline__ long long drain(uint32_t taddr) const { return i8_drain_tile(taddr, a); }
+};
+template <> struct I8Codes<4> {
+    uint4 a[I8_TK / 32];
+    __device__ __forceinline__ void load(const unsigned char *row) { i8_load_dosage4(row, a); }
+    __device__ __forceinline__ long long drain(uint32_t taddr) const { return i8_drain_tile4(taddr, a); }
+};
+
 // Finish one pair (first SNP ii of the launch, second SNP j).  qacc = sum_s 256^-(s+1) sum_k a_jk Y_s[j][k];
 // t1acc / eacc = the digit sums of a_j.r_i and a_j.(u_i o py) in units of their scales.  The FP64 side terms, chi,
 // the a-posteriori guard, threshold, warp-ballot compaction, 32-byte hit record (remma_epiAA.py:75-82).  Called by all
@@ -134,6 +184,7 @@ __device__ __forceinline__ void i8_finish_pair(const I8Params &p, int ii, int j,
     else if (o > 1.0e300) { var = o - o; eff = var; plain = false; }   // missing genotype in the second SNP: NaN, as numpy
     const double chi = eff * eff / var;
     if (p.q_debug != nullptr && j < p.m) p.q_debug[(size_t)ii * p.m + jc] = quad;
+    if (p.e_debug != nullptr && j < p.m) p.e_debug[(size_t)ii * p.m + jc] = eff;
     // what the split may have dropped (ten standard deviations) against the variance itself; NaN compares false
     const bool weak = valid && plain && sd[5] * fabs(asq) > p.recheck_tol * fabs(var);
     gmat_b200_hit h;
@@ -207,10 +258,10 @@ __device__ __forceinline__ void i8p_shape(const I8Params &p, int kt, int l, int 
     if (l == 2 * kt + 1) { row_off = I8_TK / 2; nn -= I8_TK / 2; }
 }
 
-// (192 registers: 2 x 192 x 32 leave 4096 of a sub-partition's 16384 for a warp of an operand kernel of the next batch)
-__global__ void __cluster_dims__(2, 1, 1) __maxnreg__(192)
-i8_scan_pair_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_constant__ CUtensorMap map_ph,
-                    const I8Params p) {
+// BITS = width of the epilogue's packed copy of the operand rows (p.g2): 2 for genotype codes, 4 for the integer rows of
+// the pair-list engine.
+template <int BITS>
+__device__ __forceinline__ void i8_scan_pair_body(const CUtensorMap &map_g, const CUtensorMap &map_ph, const I8Params &p) {
     extern __shared__ unsigned char smem_raw[];
     unsigned char *smem = reinterpret_cast<unsigned char *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                                            ~static_cast<uintptr_t>(1023));
@@ -305,7 +356,7 @@ i8_scan_pair_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_cons
             const int ii = i8_find_first(p.item_prefix, p.n_i, item);
             const int jt = 2 * (p.jt0[ii] + (item - p.item_prefix[ii])) + rank;
             const int j = jt * I8_TJ + q * 32 + lane;
-            const unsigned char *arow = p.g2 + (size_t)(j < p.m ? j : p.m - 1) * (p.ld >> 2);
+            const unsigned char *arow = p.g2 + (size_t)(j < p.m ? j : p.m - 1) * (size_t)(p.ld * BITS / 8);
             double qacc = 0.0, wgt = 1.0;
             double rh = 0.0, rl = 0.0, eh = 0.0, el = 0.0;                  // digit sums of the four extra rows
             for (int s = 0; s < p.n_planes; ++s) {
@@ -313,12 +364,12 @@ i8_scan_pair_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_cons
                 long long plane_sum = 0;                                    // exact
                 int x[4] = {0, 0, 0, 0};
                 for (int kt = 0; kt < p.n_kt; ++kt) {
-                    uint4 abytes[I8_TK / 64];
-                    i8_load_dosage(arow + kt * (I8_TK / 4), abytes);
+                    I8Codes<BITS> codes;
+                    codes.load(arow + kt * (I8_TK * BITS / 8));
                     mbar_wait_warp(&bars->tfull[abuf], aphase);
                     tc_fence_after();
                     const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(abuf * I8_TK);
-                    plane_sum += i8_drain_tile(taddr, abytes);
+                    plane_sum += codes.drain(taddr);
                     if (kt == p.xkt) {                                      // a_j . digits of r_i and of u_i o py
                         tmem_ld4(taddr + (uint32_t)p.xcol, x);
                         tmem_ld_wait();
@@ -341,6 +392,19 @@ i8_scan_pair_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_cons
     if (warp == 1) {
         asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;\n" ::"r"(tmem_base), "r"(512) : "memory");
     }
+}
+
+// (192 registers: 2 x 192 x 32 leave 4096 of a sub-partition's 16384 for a warp of an operand kernel of the next batch)
+__global__ void __cluster_dims__(2, 1, 1) __maxnreg__(192)
+i8_scan_pair_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_constant__ CUtensorMap map_ph,
+                    const I8Params p) {
+    i8_scan_pair_body<2>(map_g, map_ph, p);
+}
+// the same kernel over integer operand rows with 4-bit epilogue codes (pair-list engine; no operand kernel runs beside it)
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(I8_THREADS, 1)
+i8_scan_rows_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_constant__ CUtensorMap map_ph,
+                    const I8Params p) {
+    i8_scan_pair_body<4>(map_g, map_ph, p);
 }
 
 // ------------------------------------------------------------------------------------------ operand builders
@@ -645,6 +709,110 @@ i8_split_kernel(const double *__restrict__ A, int n, const double *__restrict__ 
     }
 }
 
+// ------------------------------------------------------------------------------------------ pair lists
+// Exact test of an explicit pair list (remma_epiAA_pair.py:66-87) on the int8 tensor cores.  A list's pairs rarely
+// share a first SNP, so the planes cannot be those of diag(u_i) A diag(u_i); they are the planes of A itself (a "first
+// SNP" with u = 1, built once per model by the operand kernels above), and the operand rows are INTEGER vectors per
+// pair.  w_p = (a - o_i) o (b - o_j) is not one (a, b: the integer codes of the two SNPs), but
+//     w = q - o_j a - o_i b + o_i o_j 1,      q = a o b,
+// so w'Aw needs the bilinear forms of q, a, b, 1.  Those with 1 are dot products with t1 = A 1; the others follow from
+// QUADRATIC forms by polarisation, x'Ay = (Q(x + y) - Q(x) - Q(y)) / 2:  four rows per pair -- q, q + a, q + b, a + b
+// (values 0..6: int8 operand, 4-bit epilogue codes) -- plus one row per distinct first / second SNP of the chunk (a, b).
+// The scan kernel computes Q(x) = x'Ax (lower triangle, doubled) and x.py for every row; i8_pairs_combine_kernel puts
+// var, eff, chi together and applies the a-posteriori guard (the split error of every Q, weighted), weak pairs go to
+// the FP64 pair kernel like the scan's.  Cost: 4 rows x S n^2 / 2 int8 MACs per pair against n^2 issued FP64 FMAs.
+__global__ void i8_pair_rows_kernel(const unsigned char *__restrict__ bed, int n, long long row_bytes, unsigned tabU,
+                                    unsigned tabV, const int *__restrict__ pairs, int n_pairs,
+                                    const int *__restrict__ snpU, int nU, const int *__restrict__ snpV, int nV,
+                                    signed char *__restrict__ x8, unsigned char *__restrict__ x4, int ld) {
+    const long long groups = ld / 16;
+    const long long rows = 4LL * n_pairs + nU + nV;
+    const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= rows * groups) return;
+    const long long r = t / groups;
+    const int k0 = (int)(t % groups) * 16;
+    int i = -1, j = -1, mode;
+    if (r < 4LL * n_pairs) { mode = (int)(r & 3); i = pairs[2 * (r >> 2)]; j = pairs[2 * (r >> 2) + 1]; }
+    else if (r < 4LL * n_pairs + nU) { mode = 4; i = snpU[r - 4LL * n_pairs]; }
+    else { mode = 5; j = snpV[r - 4LL * n_pairs - nU]; }
+    unsigned wi = 0, wj = 0;
+    if (k0 / 4 + 3 < row_bytes) {
+        if (i >= 0) wi = *reinterpret_cast<const unsigned *>(bed + (size_t)i * row_bytes + k0 / 4);
+        if (j >= 0) wj = *reinterpret_cast<const unsigned *>(bed + (size_t)j * row_bytes + k0 / 4);
+    }
+    unsigned out8[4] = {0, 0, 0, 0}, out4[2] = {0, 0};
+#pragma unroll
+    for (int c = 0; c < 16; ++c) {
+        const unsigned a = (tabU >> (8 * ((wi >> (2 * c)) & 3u))) & 0xffu;
+        const unsigned b = (tabV >> (8 * ((wj >> (2 * c)) & 3u))) & 0xffu;
+        unsigned v = mode == 0 ? a * b : mode == 1 ? a * b + a : mode == 2 ? a * b + b : mode == 3 ? a + b
+                   : mode == 4 ? a : b;
+        if (k0 + c >= n) v = 0;
+        out8[c >> 2] |= v << (8 * (c & 3));
+        out4[c >> 3] |= v << (4 * (c & 7));
+    }
+    *reinterpret_cast<uint4 *>(x8 + r * ld + k0) = make_uint4(out8[0], out8[1], out8[2], out8[3]);
+    *reinterpret_cast<uint2 *>(x4 + r * (ld >> 1) + (k0 >> 1)) = make_uint2(out4[0], out4[1]);
+}
+
+// per operand row: sum x^2 (exact) and x . t1 (t1 = A 1; fixed order), one warp per row
+__global__ void __launch_bounds__(256) i8_rows_dots_kernel(const signed char *__restrict__ x8, int ld, int n, long long rows,
+                                                           const double *__restrict__ t1, double *__restrict__ asq,
+                                                           double *__restrict__ xt1) {
+    const long long r = (long long)blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (r >= rows) return;
+    const int lane = threadIdx.x & 31;
+    const unsigned *row = reinterpret_cast<const unsigned *>(x8 + r * ld);
+    double acc = 0.0;
+    int sq = 0;
+    for (int w = lane; w * 4 < n; w += 32) {
+        const unsigned x = __ldg(row + w);
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            const int v = (int)((x >> (8 * c)) & 0xffu), k = 4 * w + c;
+            sq += v * v;
+            if (k < n) acc += (double)v * t1[k];
+        }
+    }
+#pragma unroll
+    for (int d = 16; d >= 1; d >>= 1) {
+        acc += __shfl_xor_sync(0xffffffffu, acc, d);
+        sq += __shfl_xor_sync(0xffffffffu, sq, d);
+    }
+    if (lane == 0) { asq[r] = (double)sq; xt1[r] = acc; }
+}
+
+// var, eff, chi of every pair from the rows' Q(x) = x'Ax, E(x) = x.py, T(x) = x.t1 (see above); weak[p] = 1 when the
+// planes cannot resolve the variance (the caller re-evaluates the pair in FP64)
+__global__ void i8_pairs_combine_kernel(const int *__restrict__ pairs, int n_pairs, const int *__restrict__ invU, int nU,
+                                        const int *__restrict__ invV, const double *__restrict__ lutU,
+                                        const double *__restrict__ lutV, const double *__restrict__ Q,
+                                        const double *__restrict__ E, const double *__restrict__ T,
+                                        const double *__restrict__ asq, const double *__restrict__ side,
+                                        double recheck_tol, gmat_b200_hit *__restrict__ out,
+                                        unsigned char *__restrict__ weak) {
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= n_pairs) return;
+    const int i = pairs[2 * p], j = pairs[2 * p + 1];
+    const long long r0 = 4LL * p, ra = 4LL * n_pairs + invU[p], rb = 4LL * n_pairs + nU + invV[p];
+    const double oi = -lutU[4 * (size_t)i], oj = -lutV[4 * (size_t)j];
+    const double c2 = -oj, c3 = -oi, c4 = oi * oj;
+    const double Q0 = Q[r0], Q1 = Q[r0 + 1], Q2 = Q[r0 + 2], Q3 = Q[r0 + 3], Qa = Q[ra], Qb = Q[rb];
+    const double Bqa = 0.5 * ((Q1 - Q0) - Qa), Bqb = 0.5 * ((Q2 - Q0) - Qb), Bab = 0.5 * ((Q3 - Qa) - Qb);
+    const double s11 = side[1], sp = side[2];                     // 1'A1 and 1.py (side table of the u = 1 "first SNP")
+    const double var = Q0 + c2 * c2 * Qa + c3 * c3 * Qb + 2.0 * (c2 * Bqa + c3 * Bqb + c2 * c3 * Bab) +
+                       2.0 * c4 * (T[r0] + c2 * T[ra] + c3 * T[rb]) + c4 * c4 * s11;
+    const double eff = E[r0] + c2 * E[ra] + c3 * E[rb] + c4 * sp;
+    gmat_b200_hit h;
+    h.snp_0 = i; h.snp_1 = j; h.eff = eff; h.var = var; h.chi = eff * eff / var;
+    out[p] = h;
+    // what the split may have dropped: side[5] * sum x^2 per row, weighted by the row's coefficient in var
+    const double bound = side[5] * (fabs(1.0 - c2 - c3) * asq[r0] + fabs(c2) * asq[r0 + 1] + fabs(c3) * asq[r0 + 2] +
+                                    fabs(c2 * c3) * asq[r0 + 3] + fabs(c2 * c2 - c2 - c2 * c3) * asq[ra] +
+                                    fabs(c3 * c3 - c3 - c2 * c3) * asq[rb]);
+    weak[p] = !(bound <= recheck_tol * fabs(var)) ? 1 : 0;        // NaN-safe: anything odd is re-evaluated
+}
+
 int launch_i8_dosage(const unsigned char *bed_dev, int n, long long m, long long row_bytes, unsigned tab, const int *counts_dev,
                      signed char *g8_dev, unsigned char *g2_dev, int ld, cudaStream_t st) {
     const long long work = m * (ld / 16);
@@ -703,14 +871,16 @@ extern "C" int gmat_b200_i8_first(const unsigned char *bed_dev, long long n, lon
                                   const double *amax_dev, const long long *ilist_dev, long long n_i, int n_planes,
                                   double *u_dev, double *r_dev, double *side_dev, signed char *planes_dev,
                                   void *stream) {
-    GB_CHECK_ARG(bed_dev && lutU_dev && py_dev && pvp_dev && amax_dev && ilist_dev && u_dev && r_dev && side_dev &&
-                 planes_dev, "null buffer");
+    GB_CHECK_ARG(py_dev && pvp_dev && amax_dev && u_dev && r_dev && side_dev && planes_dev, "null buffer");
+    GB_CHECK_ARG(ilist_dev == nullptr || (bed_dev && lutU_dev), "null buffer");
     GB_CHECK_ARG(n > 0 && m > 0 && n_i > 0, "empty shape");
     GB_CHECK_ARG(n_planes >= 2 && n_planes <= I8_MAX_PLANES, "n_planes must be in [2, 7]");
     cudaStream_t st = (cudaStream_t)stream;
     const int ld = (int)i8_rows(n), np = ld, xrow = (int)i8_xrow(n);
-    i8_first_decode_kernel<<<(unsigned)n_i, 256, 0, st>>>(bed_dev, (int)n, row_bytes, lutU_dev, ilist_dev, u_dev);
-    GB_LAUNCH_CHECK();
+    if (ilist_dev != nullptr) {                  // NULL: u_dev already holds the n_i vectors (the pair-list engine: u = 1)
+        i8_first_decode_kernel<<<(unsigned)n_i, 256, 0, st>>>(bed_dev, (int)n, row_bytes, lutU_dev, ilist_dev, u_dev);
+        GB_LAUNCH_CHECK();
+    }
     dim3 grid((unsigned)((n + AU_BK - 1) / AU_BK), (unsigned)((n_i + AU_BI - 1) / AU_BI));
     i8_au_kernel<<<grid, 256, 0, st>>>(pvp_dev, (int)n, u_dev, (int)n_i, r_dev);
     GB_LAUNCH_CHECK();
@@ -776,6 +946,7 @@ extern "C" int gmat_b200_i8_scan(const signed char *g8_dev, const unsigned char 
     p.wlo = 2.0;
     for (int q = 0; q < n_planes; ++q) p.wlo *= 0.00390625;      // 2 * 256^-S: weight of the low digit rows
     p.q_debug = q_debug_dev;
+    p.e_debug = nullptr;
     p.trim = variant >= 3;
 
     CUtensorMap map_g, map_ph;                                    // plane map with 128-row boxes (one half per CTA)
@@ -792,6 +963,87 @@ extern "C" int gmat_b200_i8_scan(const signed char *g8_dev, const unsigned char 
     const int pairs_of_sms = sm_count() / 2;
     const int grid2 = 2 * (int)(total_items < pairs_of_sms ? total_items : pairs_of_sms);
     i8_scan_pair_kernel<<<grid2, I8_THREADS, smem_bytes, st>>>(map_g, map_ph, p);
+    GB_LAUNCH_CHECK();
+    return GMAT_B200_OK;
+}
+
+// ---- pair lists on the int8 tensor cores (see i8_pair_rows_kernel) ------------------------------------------------
+extern "C" int gmat_b200_i8_pair_rows(const unsigned char *bed_dev, long long n, long long row_bytes, int codingU,
+                                      int codingV, const int *pairs_dev, long long n_pairs, const int *snpU_dev,
+                                      long long nU, const int *snpV_dev, long long nV, const double *t1_dev,
+                                      signed char *x8_dev, unsigned char *x4_dev, double *asq_dev, double *xt1_dev,
+                                      void *stream) {
+    GB_CHECK_ARG(bed_dev && pairs_dev && snpU_dev && snpV_dev && t1_dev && x8_dev && x4_dev && asq_dev && xt1_dev,
+                 "null buffer");
+    GB_CHECK_ARG(n > 0 && n_pairs > 0 && nU > 0 && nV > 0 && row_bytes % 4 == 0, "shape");
+    GB_CHECK_ARG((codingU == GMAT_B200_CODING_ADD || codingU == GMAT_B200_CODING_DOM) &&
+                 (codingV == GMAT_B200_CODING_ADD || codingV == GMAT_B200_CODING_DOM), "coding");
+    const long long rows = 4 * n_pairs + nU + nV;
+    GB_CHECK_ARG(rows < (1LL << 31), "too many operand rows for one launch: split the list");
+    const int ld = (int)i8_rows(n);
+    cudaStream_t st = (cudaStream_t)stream;
+    const long long work = rows * (ld / 16);
+    i8_pair_rows_kernel<<<(unsigned)((work + 255) / 256), 256, 0, st>>>(
+        bed_dev, (int)n, row_bytes, codingU == GMAT_B200_CODING_DOM ? I8_TAB_DOM : I8_TAB_ADD,
+        codingV == GMAT_B200_CODING_DOM ? I8_TAB_DOM : I8_TAB_ADD, pairs_dev, (int)n_pairs, snpU_dev, (int)nU, snpV_dev,
+        (int)nV, x8_dev, x4_dev, ld);
+    GB_LAUNCH_CHECK();
+    i8_rows_dots_kernel<<<(unsigned)((rows + 7) / 8), 256, 0, st>>>(x8_dev, ld, (int)n, rows, t1_dev, asq_dev, xt1_dev);
+    GB_LAUNCH_CHECK();
+    return GMAT_B200_OK;
+}
+
+extern "C" int gmat_b200_i8_rows_scan(const signed char *x8_dev, const unsigned char *x4_dev, long long n,
+                                      long long rows, const signed char *planes_dev, int n_planes,
+                                      const double *side_dev, const double *zeros_dev, const double *asq_dev,
+                                      const long long *ilist_dev, const int *item_prefix_dev, const int *jt0_dev,
+                                      double *q_dev, double *e_dev, unsigned long long *count_dev,
+                                      unsigned long long *recheck_count_dev, void *stream) {
+    GB_CHECK_ARG(x8_dev && x4_dev && planes_dev && side_dev && zeros_dev && asq_dev && ilist_dev && item_prefix_dev &&
+                 jt0_dev && q_dev && e_dev && count_dev && recheck_count_dev, "null buffer");
+    GB_CHECK_ARG(n > 0 && rows > 0 && rows < (1LL << 31), "shape");
+    GB_CHECK_ARG(n_planes >= 2 && n_planes <= I8_MAX_PLANES, "n_planes must be in [2, 7]");
+    GB_CHECK_ARG(n < 17000, "4-bit epilogue sums fit int32 only for n < 17000");
+    cudaStream_t st = (cudaStream_t)stream;
+    I8Params p;
+    p.n = (int)n; p.m = (int)rows; p.ld = (int)i8_rows(n); p.np = p.ld;
+    p.n_planes = n_planes; p.n_kt = p.ld / I8_TK; p.n_slab = (int)((n + I8_SLAB - 1) / I8_SLAB);
+    p.n_i = 1; p.pair_space = GMAT_B200_PAIRS_ALL;
+    p.xkt = (int)(i8_xrow(n) / I8_TK); p.xcol = (int)(i8_xrow(n) % I8_TK);
+    p.total_items = (int)((rows + 2 * I8_TJ - 1) / (2 * I8_TJ)); p.item_prefix = item_prefix_dev; p.jt0 = jt0_dev;
+    p.ilist = ilist_dev; p.g8 = x8_dev; p.g2 = x4_dev; p.side = side_dev; p.offs = zeros_dev; p.asq = asq_dev;
+    p.chi_cut = (double)INFINITY;   // +inf: no hit records, only q / e
+    p.hits = nullptr; p.cap = 0; p.count = count_dev;
+    p.recheck = nullptr; p.recheck_cap = 0; p.recheck_count = recheck_count_dev;
+    p.recheck_tol = p.chi_cut;                                     // the guard is applied per PAIR by the combine kernel
+    p.wlo = 2.0;
+    for (int q = 0; q < n_planes; ++q) p.wlo *= 0.00390625;
+    p.q_debug = q_dev; p.e_debug = e_dev;
+    p.trim = 1;
+    CUtensorMap map_g, map_ph;
+    int rc = make_map(&map_g, x8_dev, p.ld, rows, p.ld, I8_TJ);
+    if (rc == GMAT_B200_OK) rc = make_map(&map_ph, planes_dev, p.ld, (long long)n_planes * p.np, p.ld, I8P_HALF);
+    if (rc != GMAT_B200_OK) return rc;
+    const int smem_bytes = I8P_NS * I8P_STAGE_BYTES + 1024 + (int)sizeof(I8PBars);
+    GB_CUDA(cudaFuncSetAttribute(i8_scan_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
+    const int pairs_of_sms = sm_count() / 2;
+    const int grid2 = 2 * (p.total_items < pairs_of_sms ? p.total_items : pairs_of_sms);
+    i8_scan_rows_kernel<<<grid2, I8_THREADS, smem_bytes, st>>>(map_g, map_ph, p);
+    GB_LAUNCH_CHECK();
+    return GMAT_B200_OK;
+}
+
+extern "C" int gmat_b200_i8_pairs_combine(const int *pairs_dev, long long n_pairs, const int *invU_dev, long long nU,
+                                          const int *invV_dev, const double *lutU_dev, const double *lutV_dev,
+                                          const double *q_dev, const double *e_dev, const double *xt1_dev,
+                                          const double *asq_dev, const double *side_dev, double recheck_tol,
+                                          gmat_b200_hit *out_dev, unsigned char *weak_dev, void *stream) {
+    GB_CHECK_ARG(pairs_dev && invU_dev && invV_dev && lutU_dev && lutV_dev && q_dev && e_dev && xt1_dev && asq_dev &&
+                 side_dev && out_dev && weak_dev, "null buffer");
+    GB_CHECK_ARG(n_pairs > 0 && nU > 0, "shape");
+    i8_pairs_combine_kernel<<<(unsigned)((n_pairs + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
+        pairs_dev, (int)n_pairs, invU_dev, (int)nU, invV_dev, lutU_dev, lutV_dev, q_dev, e_dev, xt1_dev, asq_dev,
+        side_dev, recheck_tol, out_dev, weak_dev);
     GB_LAUNCH_CHECK();
     return GMAT_B200_OK;
 }

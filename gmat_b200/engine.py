@@ -450,6 +450,119 @@ def epi_exact_pairs(store, lutU, lutV, py_dev, packed, pairs):
     return hits_to_numpy(out, k)
 
 
+def pair_engine(store, n_pairs):
+    """Which kernel tests an explicit pair list: "i8" (int8 tensor cores, I8Pairs) or "f64" (DMMA pair kernel).
+    GMAT_B200_PAIR_ENGINE = auto (default) | i8 | f64.  auto = i8 where it is measured faster: I8Pairs.MIN_IDS <= n <
+    17000, at least I8Pairs.MIN_PAIRS pairs, no missing calls (5.3 operand rows per pair at S n^2 / 2 int8 MACs each
+    against n^2 issued FP64 FMAs: 1.35x the DMMA kernel at n = 5000, 0.85x at n = 2000, scripts/pairs_speed.py)."""
+    want = os.environ.get("GMAT_B200_PAIR_ENGINE", "auto").lower()
+    if want not in ("auto", "i8", "f64"):
+        raise ValueError("GMAT_B200_PAIR_ENGINE must be auto, i8 or f64")
+    if want == "f64":
+        return "f64"
+    fits = store.n < 17000 and store.n_missing() == 0
+    if want == "i8":
+        if not fits:
+            raise ValueError("the int8 pair engine needs n < 17000 and genotypes without missing calls")
+        return "i8"
+    return "i8" if (fits and store.n >= I8Pairs.MIN_IDS and n_pairs >= I8Pairs.MIN_PAIRS) else "f64"
+
+
+class I8Pairs(object):
+    """Exact test of explicit pair lists on the int8 tensor cores (gmat_b200/csrc/ozaki.cu, "pair lists";
+    remma_epiAA_pair.py:66-87): digit planes of Z'PZ itself (built once per model), four integer operand rows per pair
+    (q = a o b, q + a, q + b, a + b) plus one per distinct SNP, var / eff by polarisation.  Pairs the planes cannot
+    resolve are re-evaluated by the FP64 pair kernel, like the scan's.  Same statistics as epi_exact_pairs."""
+
+    MIN_PAIRS = 16384             # auto: below this the fixed costs (planes of Z'PZ, one launch) are not worth it
+    MIN_IDS = 4096                # auto: below this n the FP64 DMMA pair kernel is as fast
+    CHUNK = 65536                 # pairs per launch (operand rows: <= 6 x CHUNK x ld bytes = 2 GB at n = 5000)
+    RECHECK_TOL = 2.5e-10
+
+    def __init__(self, store, coding_u, coding_v, lutU, lutV, py_dev, pvp_dev, packed=None, n_planes=None):
+        self.store, self.cu, self.cv, self.lutU, self.lutV = store, int(coding_u), int(coding_v), lutU, lutV
+        self.py = py_dev.reshape(-1).contiguous()
+        self.A, self._packed = pvp_dev, packed
+        self.n_planes = int(i8_planes() if n_planes is None else n_planes)
+        n, dev = store.n, store.device
+        self.ld = int(lib.gmat_b200_i8_ld(n))
+        amax = torch.empty((1,), dtype=torch.float64, device=dev)
+        check(lib.gmat_b200_absmax(_p(self.A, "double *"), self.A.numel(), _p(amax, "double *"), _stream()),
+              "gmat_b200_absmax")
+        ones = torch.ones((1, n), dtype=torch.float64, device=dev)
+        self.t1 = torch.empty((1, n), dtype=torch.float64, device=dev)           # Z'PZ 1
+        self.side = torch.empty((1, 8), dtype=torch.float64, device=dev)
+        self.planes = torch.zeros((self.n_planes * self.ld * self.ld,), dtype=torch.int8, device=dev)
+        check(lib.gmat_b200_i8_first(ffi.NULL, n, store.m, store.row_bytes, ffi.NULL, _p(self.py, "double *"),
+                                     _p(self.A, "double *"), _p(amax, "double *"), ffi.NULL, 1, self.n_planes,
+                                     _p(ones, "double *"), _p(self.t1, "double *"), _p(self.side, "double *"),
+                                     _p(self.planes, "signed char *"), _stream()), "gmat_b200_i8_first")
+        check(lib.gmat_b200_i8_split(_p(self.A, "double *"), n, _p(ones, "double *"), 1, _p(self.side, "double *"),
+                                     self.n_planes, _p(self.planes, "signed char *"), _stream()), "gmat_b200_i8_split")
+        self._ilist = torch.zeros((1,), dtype=torch.int64, device=dev)
+        self._jt0 = torch.zeros((1,), dtype=torch.int32, device=dev)
+        self._counters = torch.zeros((2,), dtype=torch.int64, device=dev)
+        self.last_rechecked = 0
+
+    def packed(self):
+        if self._packed is None:
+            self._packed = pack_pvp(self.A)
+        return self._packed
+
+    def stats(self, pairs):
+        """HIT_DTYPE array (snp_0, snp_1, eff, var, chi) in list order."""
+        pairs = np.ascontiguousarray(pairs, dtype=np.int32).reshape(-1, 2)
+        st, dev, n, ld = self.store, self.store.device, self.store.n, self.ld
+        outs, weak_all = [], []
+        for c0 in range(0, len(pairs), self.CHUNK):
+            ch = pairs[c0:c0 + self.CHUNK]
+            k = len(ch)
+            su, iu = np.unique(ch[:, 0], return_inverse=True)
+            sv, iv = np.unique(ch[:, 1], return_inverse=True)
+            rows = 4 * k + len(su) + len(sv)
+            up = lambda a: torch.as_tensor(np.ascontiguousarray(a, dtype=np.int32)).to(dev)
+            pr, su_d, sv_d, iu_d, iv_d = up(ch), up(su), up(sv), up(iu), up(iv)
+            x8 = torch.empty((rows, ld), dtype=torch.int8, device=dev)
+            x4 = torch.empty((rows, ld // 2), dtype=torch.uint8, device=dev)
+            asq = torch.empty((rows,), dtype=torch.float64, device=dev)
+            xt1 = torch.empty((rows,), dtype=torch.float64, device=dev)
+            q = torch.empty((rows,), dtype=torch.float64, device=dev)
+            e = torch.empty((rows,), dtype=torch.float64, device=dev)
+            zeros = torch.zeros((rows,), dtype=torch.float64, device=dev)
+            prefix = torch.tensor([0, (rows + 255) // 256], dtype=torch.int32, device=dev)
+            check(lib.gmat_b200_i8_pair_rows(
+                _p(st.bed, "unsigned char *"), n, st.row_bytes, self.cu, self.cv, _p(pr, "int *"), k,
+                _p(su_d, "int *"), len(su), _p(sv_d, "int *"), len(sv), _p(self.t1, "double *"),
+                _p(x8, "signed char *"), _p(x4, "unsigned char *"), _p(asq, "double *"), _p(xt1, "double *"),
+                _stream()), "gmat_b200_i8_pair_rows")
+            check(lib.gmat_b200_i8_rows_scan(
+                _p(x8, "signed char *"), _p(x4, "unsigned char *"), n, rows, _p(self.planes, "signed char *"),
+                self.n_planes, _p(self.side, "double *"), _p(zeros, "double *"), _p(asq, "double *"),
+                _p(self._ilist, "long long *"), _p(prefix, "int *"), _p(self._jt0, "int *"), _p(q, "double *"),
+                _p(e, "double *"), ffi.cast("unsigned long long *", self._counters.data_ptr()),
+                ffi.cast("unsigned long long *", self._counters.data_ptr() + 8), _stream()), "gmat_b200_i8_rows_scan")
+            out = alloc_hits(k, dev)
+            weak = torch.empty((k,), dtype=torch.uint8, device=dev)
+            check(lib.gmat_b200_i8_pairs_combine(
+                _p(pr, "int *"), k, _p(iu_d, "int *"), len(su), _p(iv_d, "int *"), _p(self.lutU, "double *"),
+                _p(self.lutV, "double *"), _p(q, "double *"), _p(e, "double *"), _p(xt1, "double *"),
+                _p(asq, "double *"), _p(self.side, "double *"), float(self.RECHECK_TOL),
+                ffi.cast("gmat_b200_hit *", out.data_ptr()), _p(weak, "unsigned char *"), _stream()),
+                "gmat_b200_i8_pairs_combine")
+            outs.append(out[:k])
+            weak_all.append(weak)
+        if not outs:
+            return np.zeros((0,), dtype=HIT_DTYPE)
+        res = torch.cat(outs).cpu().numpy().view(HIT_DTYPE).reshape(-1)
+        wk = np.flatnonzero(torch.cat(weak_all).cpu().numpy())
+        self.last_rechecked = int(len(wk))
+        if len(wk):                               # rare variants: the FP64 pair kernel decides these
+            fix = epi_exact_pairs(st, self.lutU, self.lutV, self.py, self.packed(), pairs[wk])
+            res = res.copy()
+            res[wk] = fix
+        return res
+
+
 def screen_engine(store):
     """Which engine runs the approximate screen: "i8" (int8 tensor-core prefilter + FP64 re-test of the survivors;
     stores with missing calls use the tripled integer coding, see ScreenOperands) or "f64" (DMMA).

@@ -347,6 +347,7 @@ def pair_test(kind, y, xmat, zmat, gmat_lst, var_com, bed_file, snp_pair_file, m
     clock_t0 = time.perf_counter()
     cpu_t0 = time.process_time()
     ipart = -1
+    i8_pairs = None
     while True:
         ipart += 1
         skiprows = 1 + ipart * max_test_pair          # first line is a header (remma_epiAA_pair.py:69)
@@ -360,7 +361,17 @@ def pair_test(kind, y, xmat, zmat, gmat_lst, var_com, bed_file, snp_pair_file, m
         if np.max(snp_pair) > num_snp - 1 or np.min(snp_pair) < 0:
             logging.error('snp_pair is out of range!')
             sys.exit()
-        res = engine.epi_exact_pairs(store, lut_u, lut_v, model.py, model.packed, snp_pair)
+        which = engine.pair_engine(store, len(snp_pair))
+        if ipart == 0:
+            logging.info("Pair-list engine: %s", "int8 tensor cores (tcgen05), FP64 re-check of weak pairs"
+                         if which == "i8" else "FP64 DMMA pair kernel")
+        if which == "i8":
+            if i8_pairs is None:
+                i8_pairs = engine.I8Pairs(store, kind.coding_u, kind.coding_v, lut_u, lut_v, model.py, model.pvp,
+                                          packed=model.packed)
+            res = i8_pairs.stats(snp_pair)
+        else:
+            res = engine.epi_exact_pairs(store, lut_u, lut_v, model.py, model.packed, snp_pair)
         p_vec = chi2.sf(res['chi'], 1)
         keep = p_vec < p_cut
         _write_rows(out_file, {0: snp_pair[keep, 0], 1: snp_pair[keep, 1], 2: res['eff'][keep],
@@ -535,11 +546,20 @@ class Prepared(object):
         self.model = DeviceModel.build(y, xmat, zmat, gmat_lst, var_com, self.store.device, scipy_inv=False)
         self.num_snp, self.num_id = self.store.m, self.store.n
         self._screen_ops = None                               # int8 screen operands, shared by every screen call
+        self._i8_pairs = None                                 # int8 pair-list engine (planes of Z'PZ), built on first use
 
     def pair_stats(self, pairs):
         k = self.kind
-        return engine.epi_exact_pairs(self.store, self.store.lut(k.coding_u), self.store.lut(k.coding_v),
-                                      self.model.py, self.model.packed, pairs)
+        lut_u, lut_v = self.store.lut(k.coding_u), self.store.lut(k.coding_v)
+        which = engine.pair_engine(self.store, len(pairs))
+        logging.info("Pair-list engine: %s", "int8 tensor cores (tcgen05), FP64 re-check of weak pairs"
+                     if which == "i8" else "FP64 DMMA pair kernel")
+        if which == "i8":
+            if self._i8_pairs is None:
+                self._i8_pairs = engine.I8Pairs(self.store, k.coding_u, k.coding_v, lut_u, lut_v, self.model.py,
+                                                self.model.pvp, packed=self.model.packed)
+            return self._i8_pairs.stats(pairs)
+        return engine.epi_exact_pairs(self.store, lut_u, lut_v, self.model.py, self.model.packed, pairs)
 
     def screen(self, snp_lst_0, eff_cut=0.0, cut_table=None, bin_i=None, bin_j=None):
         """Hits of the C screen in single-threaded C row order; returns list of (snp_0, snp_1, eff)."""

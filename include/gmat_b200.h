@@ -267,7 +267,9 @@ int gmat_b200_absmax(const double *x_dev, long long len, double *out_dev, void *
 /* Per batch of n_i first SNPs (ilist_dev): u[ii][k] = lutU[i][code] (coded first SNPs), r = u o (Z'PZ u)
  * (scratch, [n_i][n]), the side table side[ii][8] = {scale_i, s_i, u_i.Z'Py, scale_r, scale_e, guard unit, 0, 0}
  * and the four extra rows (n rounded up to 4, +0..3) of every plane of every first SNP.  amax_dev = max|Z'PZ|
- * (gmat_b200_absmax).  planes_dev: [n_i][n_planes][ld][ld] int8, ZERO-initialised by the caller once.           */
+ * (gmat_b200_absmax).  planes_dev: [n_i][n_planes][ld][ld] int8, ZERO-initialised by the caller once.
+ * ilist_dev == NULL: u_dev already holds the n_i vectors (bed_dev / lutU_dev unused) -- the pair-list engine below
+ * passes one vector of ones and gets the planes of Z'PZ itself, r = Z'PZ 1, side = {max|Z'PZ|/0.49, 1'Z'PZ 1, 1.Z'Py, ..}. */
 int gmat_b200_i8_first(const unsigned char *bed_dev, long long n, long long m, long long row_bytes,
                        const double *lutU_dev, const double *py_dev, const double *pvp_dev /* [n][n] */,
                        const double *amax_dev, const long long *ilist_dev, long long n_i, int n_planes,
@@ -295,6 +297,37 @@ int gmat_b200_i8_scan(const signed char *g8_dev, const unsigned char *g2_dev, lo
                       unsigned long long *count_dev, int *recheck_dev, long long recheck_cap,
                       unsigned long long *recheck_count_dev, double recheck_tol, double *q_debug_dev,
                       int variant, void *stream);
+
+/* ---- exact test of an explicit PAIR LIST on the int8 tensor cores (remma_epiAA_pair.py:66-87) -------------------
+ * A list's pairs rarely share a first SNP, so the digit planes are those of Z'PZ itself (gmat_b200_i8_first with
+ * ilist_dev == NULL and u = 1, then gmat_b200_i8_split with n_i = 1: once per model) and the operand rows are integer
+ * vectors per pair.  With a, b the integer codes of the two SNPs, q = a o b and o_i, o_j the offsets (-lut[.][0]):
+ *   w = (a - o_i) o (b - o_j) = q - o_j a - o_i b + o_i o_j 1,
+ * so w'Z'PZ w needs the bilinear forms of q, a, b and 1.  Those with 1 are dot products with t1 = Z'PZ 1; the others
+ * follow from quadratic forms by polarisation, x'Ay = (Q(x+y) - Q(x) - Q(y))/2.  Operand rows of a chunk of n_pairs
+ * pairs: 4p .. 4p+3 = q, q+a, q+b, a+b of pair p; then one row per DISTINCT first SNP (a, nU rows, snpU_dev) and per
+ * distinct second SNP (b, nV rows, snpV_dev).  gmat_b200_i8_pair_rows builds them as int8 (x8: the MMA operand,
+ * [rows][ld]) and packed 4 bits each (x4: [rows][ld/2], the epilogue's copy; values 0..6) together with
+ * asq[row] = sum x^2 and xt1[row] = x . t1.  gmat_b200_i8_rows_scan runs the scan kernel over the rows:
+ * q[row] = x'Z'PZ x, e[row] = x . Z'Py (zeros_dev: [rows] zeros; ilist_dev = {0}, item_prefix_dev = {0, ceil(rows/256)},
+ * jt0_dev = {0}; count_dev / recheck_count_dev stay 0).  gmat_b200_i8_pairs_combine writes eff, var, chi of every pair
+ * (invU/invV[p] = index of the pair's SNPs in snpU/snpV) and weak[p] = 1 where the split error of the Q's, weighted by
+ * their coefficients, exceeds recheck_tol * |var|: those pairs are for gmat_b200_epi_exact_pairs.  n < 17000.       */
+int gmat_b200_i8_pair_rows(const unsigned char *bed_dev, long long n, long long row_bytes, int codingU, int codingV,
+                           const int *pairs_dev /* [n_pairs][2] */, long long n_pairs, const int *snpU_dev,
+                           long long nU, const int *snpV_dev, long long nV, const double *t1_dev /* [n] */,
+                           signed char *x8_dev, unsigned char *x4_dev, double *asq_dev, double *xt1_dev,
+                           void *stream);
+int gmat_b200_i8_rows_scan(const signed char *x8_dev, const unsigned char *x4_dev, long long n, long long rows,
+                           const signed char *planes_dev, int n_planes, const double *side_dev,
+                           const double *zeros_dev, const double *asq_dev, const long long *ilist_dev,
+                           const int *item_prefix_dev, const int *jt0_dev, double *q_dev, double *e_dev,
+                           unsigned long long *count_dev, unsigned long long *recheck_count_dev, void *stream);
+int gmat_b200_i8_pairs_combine(const int *pairs_dev, long long n_pairs, const int *invU_dev, long long nU,
+                               const int *invV_dev, const double *lutU_dev, const double *lutV_dev,
+                               const double *q_dev, const double *e_dev, const double *xt1_dev,
+                               const double *asq_dev, const double *side_dev, double recheck_tol,
+                               gmat_b200_hit *out_dev, unsigned char *weak_dev, void *stream);
 
 /* The same GRM on the INT8 tensor cores (gmat_b200/csrc/gram_i8.cu): X X' = G G' - c 1' - 1 c' + d with G the
  * integer dosage / heterozygote indicator matrix, so the n^2 m term is ONE exact int8 x int8 -> int32 GEMM
