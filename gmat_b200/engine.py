@@ -454,7 +454,7 @@ def pair_engine(store, n_pairs):
     """Which kernel tests an explicit pair list: "i8" (int8 tensor cores, I8Pairs) or "f64" (DMMA pair kernel).
     GMAT_B200_PAIR_ENGINE = auto (default) | i8 | f64.  auto = i8 where it is measured faster: I8Pairs.MIN_IDS <= n <
     17000, at least I8Pairs.MIN_PAIRS pairs, no missing calls (5.3 operand rows per pair at S n^2 / 2 int8 MACs each
-    against n^2 issued FP64 FMAs: 1.35x the DMMA kernel at n = 5000, 0.85x at n = 2000, scripts/pairs_speed.py)."""
+    against n^2 issued FP64 FMAs: 2.3x the DMMA kernel at n = 5000, 1.26x at n = 2000, scripts/pairs_speed.py)."""
     want = os.environ.get("GMAT_B200_PAIR_ENGINE", "auto").lower()
     if want not in ("auto", "i8", "f64"):
         raise ValueError("GMAT_B200_PAIR_ENGINE must be auto, i8 or f64")
@@ -475,15 +475,20 @@ class I8Pairs(object):
     resolve are re-evaluated by the FP64 pair kernel, like the scan's.  Same statistics as epi_exact_pairs."""
 
     MIN_PAIRS = 16384             # auto: below this the fixed costs (planes of Z'PZ, one launch) are not worth it
-    MIN_IDS = 4096                # auto: below this n the FP64 DMMA pair kernel is as fast
+    MIN_IDS = 2000                # auto: below this n the FP64 DMMA pair kernel is as fast
     CHUNK = 65536                 # pairs per launch (operand rows: <= 6 x CHUNK x ld bytes = 2 GB at n = 5000)
     RECHECK_TOL = 2.5e-10
+    # Seven planes (55 bits), not the scan's six: the operand rows are dense sums of two genotype vectors (sum x^2 up
+    # to 36 n), and a re-check is dear here -- the FP64 pair kernel works in tiles of 128 pairs, so the 0.5 % of a
+    # random list that six planes leave weak (231 of 50 000 pairs at n = 5000) took 13.9 ms on two SMs, more than the
+    # whole tensor-core pass (11 ms).  With seven nothing but degenerate pairs is left: +17 % MMAs, -45 % time.
+    PLANES = 7
 
     def __init__(self, store, coding_u, coding_v, lutU, lutV, py_dev, pvp_dev, packed=None, n_planes=None):
         self.store, self.cu, self.cv, self.lutU, self.lutV = store, int(coding_u), int(coding_v), lutU, lutV
         self.py = py_dev.reshape(-1).contiguous()
         self.A, self._packed = pvp_dev, packed
-        self.n_planes = int(i8_planes() if n_planes is None else n_planes)
+        self.n_planes = int(self.PLANES if n_planes is None else n_planes)
         n, dev = store.n, store.device
         self.ld = int(lib.gmat_b200_i8_ld(n))
         amax = torch.empty((1,), dtype=torch.float64, device=dev)

@@ -112,7 +112,7 @@ def test_pair_engine_selection(eng, tmp_path, monkeypatch):
     store, *_ = _setup(eng, tmp_path, 140, 50, 9, "AA")
     monkeypatch.delenv("GMAT_B200_PAIR_ENGINE", raising=False)
     assert eng.pair_engine(store, 10) == "f64" and eng.pair_engine(store, 100000) == "f64"      # n = 140: DMMA
-    monkeypatch.setattr(eng.I8Pairs, "MIN_IDS", 100)
+    monkeypatch.setattr(eng.I8Pairs, "MIN_IDS", 100)                  # (2000 by default)
     assert eng.pair_engine(store, 10) == "f64" and eng.pair_engine(store, 100000) == "i8"
     monkeypatch.setenv("GMAT_B200_PAIR_ENGINE", "f64")
     assert eng.pair_engine(store, 100000) == "f64"
