@@ -732,21 +732,26 @@ def approx(kind, pheno_file, bed_file, gmat_lst, var_com, p_cut=1.0e-5, num_rand
     # (as arrays: the same IEEE operations and the same str() of the same doubles as a per-row loop, without scipy's
     # 70 us scalar call per row)
     surv = [(s0, s1) for s0, s1, _ in hits]
-    p_dct = {}
+    p_app_txt = None
     with _Phase("p_app"):
         if hits:
             e_trunc = np.array([float('%g' % e) for _, _, e in hits], dtype=np.float64)
             den = np.array([deno(s0, s1) for s0, s1 in surv], dtype=np.float64)
             p_app = chi2.sf(e_trunc * e_trunc / den, 1)
-            p_dct = {'%d %d' % k: str(q) for k, q in zip(surv, p_app)}
+            p_app_txt = np.array([str(q) for q in p_app], dtype=object)      # the text the .approx_p file would hold
     logging.info("\n\n#####Calculate exact p values for top SNP pairs#####")
     with _Phase("survivors_exact_test_and_write"), open(out_file + sfx, 'w') as fout:
-        # header of .exact_p with the token p_app spliced in (remma_epiAA_approx.py:41-50)
+        # header of .exact_p with the token p_app spliced in (remma_epiAA_approx.py:41-50); the rows are those
+        # remma_epiXX_pair(p_cut=1) keeps (p < 1) with the survivor's p_app inserted before p -- the reference looks it
+        # up by the 'snp_0 snp_1' key, here it is the same row of the same list; written as one table (pandas formats
+        # column by column: the same text per field as the row-by-row form)
         fout.write('snp_0 snp_1 eff var chi p_app p\n')
         if surv:
             sp = np.asarray(surv, dtype=np.int64)
-            rows, _ = _exact_rows_text(sp, ctx.pair_stats(sp))
-            for arr in rows:
-                arr.insert(-1, p_dct[' '.join(arr[:2])])
-                fout.write(' '.join(arr) + '\n')
+            res = ctx.pair_stats(sp)
+            p_vec = chi2.sf(res['chi'], 1)
+            keep = p_vec < 1
+            pd.DataFrame({0: sp[keep, 0], 1: sp[keep, 1], 2: res['eff'][keep], 3: res['var'][keep],
+                          4: res['chi'][keep], 5: p_app_txt[keep], 6: p_vec[keep]}).to_csv(
+                fout, sep=' ', header=False, index=False)
     return 0
