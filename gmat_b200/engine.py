@@ -453,17 +453,17 @@ def epi_exact_pairs(store, lutU, lutV, py_dev, packed, pairs):
 def pair_engine(store, n_pairs):
     """Which kernel tests an explicit pair list: "i8" (int8 tensor cores, I8Pairs) or "f64" (DMMA pair kernel).
     GMAT_B200_PAIR_ENGINE = auto (default) | i8 | f64.  auto = i8 where it is measured faster: I8Pairs.MIN_IDS <= n <
-    17000, at least I8Pairs.MIN_PAIRS pairs, no missing calls (5.3 operand rows per pair at S n^2 / 2 int8 MACs each
+    14000, at least I8Pairs.MIN_PAIRS pairs, no missing calls (5.3 operand rows per pair at S n^2 / 2 int8 MACs each
     against n^2 issued FP64 FMAs: 2.3x the DMMA kernel at n = 5000, 1.26x at n = 2000, scripts/pairs_speed.py)."""
     want = os.environ.get("GMAT_B200_PAIR_ENGINE", "auto").lower()
     if want not in ("auto", "i8", "f64"):
         raise ValueError("GMAT_B200_PAIR_ENGINE must be auto, i8 or f64")
     if want == "f64":
         return "f64"
-    fits = store.n < 17000 and store.n_missing() == 0
+    fits = store.n < 14000 and store.n_missing() == 0
     if want == "i8":
         if not fits:
-            raise ValueError("the int8 pair engine needs n < 17000 and genotypes without missing calls")
+            raise ValueError("the int8 pair engine needs n < 14000 and genotypes without missing calls")
         return "i8"
     return "i8" if (fits and store.n >= I8Pairs.MIN_IDS and n_pairs >= I8Pairs.MIN_PAIRS) else "f64"
 

@@ -312,7 +312,7 @@ int gmat_b200_i8_scan(const signed char *g8_dev, const unsigned char *g2_dev, lo
  * q[row] = x'Z'PZ x, e[row] = x . Z'Py (zeros_dev: [rows] zeros; ilist_dev = {0}, item_prefix_dev = {0, ceil(rows/256)},
  * jt0_dev = {0}; count_dev / recheck_count_dev stay 0).  gmat_b200_i8_pairs_combine writes eff, var, chi of every pair
  * (invU/invV[p] = index of the pair's SNPs in snpU/snpV) and weak[p] = 1 where the split error of the Q's, weighted by
- * their coefficients, exceeds recheck_tol * |var|: those pairs are for gmat_b200_epi_exact_pairs.  n < 17000.       */
+ * their coefficients, exceeds recheck_tol * |var|: those pairs are for gmat_b200_epi_exact_pairs.  n < 14000.       */
 int gmat_b200_i8_pair_rows(const unsigned char *bed_dev, long long n, long long row_bytes, int codingU, int codingV,
                            const int *pairs_dev /* [n_pairs][2] */, long long n_pairs, const int *snpU_dev,
                            long long nU, const int *snpV_dev, long long nV, const double *t1_dev /* [n] */,
