@@ -129,7 +129,7 @@ __device__ __forceinline__ int i8_dot_chunk4(const int (&v)[32], unsigned w0, un
             c3 += (int)((w[g] >> (4 * q + 12)) & 15u) * v[8 * g + q + 3];
         }
     }
-    return (c0 + c1) + (c2 + c3);                                 // |.| <= 32 * 15 * 2*128*n: int32 for n < 1.7e4
+    return (c0 + c1) + (c2 + c3);                // rows hold values <= 6: |.| <= 32 * 6 * (6*128*n), int32 for n < 1.45e4
 }
 __device__ __forceinline__ long long i8_drain_tile4(uint32_t taddr, const uint4 (&a)[I8_TK / 32]) {
     long long total = 0;
@@ -1003,7 +1003,7 @@ extern "C" int gmat_b200_i8_rows_scan(const signed char *x8_dev, const unsigned 
                  jt0_dev && q_dev && e_dev && count_dev && recheck_count_dev, "null buffer");
     GB_CHECK_ARG(n > 0 && rows > 0 && rows < (1LL << 31), "shape");
     GB_CHECK_ARG(n_planes >= 2 && n_planes <= I8_MAX_PLANES, "n_planes must be in [2, 7]");
-    GB_CHECK_ARG(n < 17000, "4-bit epilogue sums fit int32 only for n < 17000");
+    GB_CHECK_ARG(n < 14000, "4-bit epilogue sums fit int32 only for n < 14000");
     cudaStream_t st = (cudaStream_t)stream;
     I8Params p;
     p.n = (int)n; p.m = (int)rows; p.ld = (int)i8_rows(n); p.np = p.ld;
